@@ -1,0 +1,75 @@
+"""Seeded synthetic RefCOCO-shaped inputs.
+
+Shapes follow the reference's dataset (data_utils/refcoco.py:147-188, data_utils/utils.py:161-256):
+a 224x224 target crop with a pad-to-square mask band, a 224x224 context image whose target
+bbox is blanked and masked, a 5-d relative location vector ``[x1,y1,x2,y2,area]``, and (for
+training) BERT-wordpiece id rows ``[CLS] w.. [SEP] 0..`` of length 129 with their pad mask.
+Everything is generated on the host with ``torch.Generator().manual_seed(1234 + shard)``.
+"""
+import torch
+
+BOS, EOS, PAD = 101, 102, 0
+
+
+def make_batch(batch, shard=0, size=224, train=False, max_pos=128, vocab=30522):
+    g = torch.Generator().manual_seed(1234 + shard)
+
+    def image():
+        base = torch.randn(batch, 3, size, size, generator=g)
+        return base + 2.0 * torch.randn(batch, 3, 1, 1, generator=g)
+
+    t_img, g_img = image(), image()
+    t_mask = torch.zeros(batch, size, size, dtype=torch.bool)
+    g_mask = torch.zeros(batch, size, size, dtype=torch.bool)
+    aspect = 0.4 + 0.6 * torch.rand(batch, generator=g)
+    axis = torch.randint(0, 2, (batch,), generator=g)
+    box = torch.rand(batch, 4, generator=g)
+    loc = torch.zeros(batch, 5)
+    for b in range(batch):
+        band = int(round(size * (1.0 - float(aspect[b])) / 2.0))
+        if band:
+            if int(axis[b]) == 0:
+                t_mask[b, :band] = True; t_mask[b, size - band:] = True
+                t_img[b, :, :band] = 0; t_img[b, :, size - band:] = 0
+            else:
+                t_mask[b, :, :band] = True; t_mask[b, :, size - band:] = True
+                t_img[b, :, :, :band] = 0; t_img[b, :, :, size - band:] = 0
+        # context: pad band on the other axis + blanked target rectangle
+        cband = band // 2
+        if cband:
+            if int(axis[b]) == 0:
+                g_mask[b, :, :cband] = True; g_mask[b, :, size - cband:] = True
+            else:
+                g_mask[b, :cband] = True; g_mask[b, size - cband:] = True
+        x1, y1 = 0.1 + 0.4 * float(box[b, 0]), 0.1 + 0.4 * float(box[b, 1])
+        x2, y2 = x1 + 0.1 + 0.35 * float(box[b, 2]), y1 + 0.1 + 0.35 * float(box[b, 3])
+        px = [int(round(v * size)) for v in (x1, y1, x2, y2)]
+        g_mask[b, px[1]:px[3], px[0]:px[2]] = True
+        g_img[b, :, px[1]:px[3], px[0]:px[2]] = 0.0
+        loc[b] = torch.tensor([x1, y1, x2, y2, (x2 - x1) * (y2 - y1)])
+    out = dict(t_img=t_img, t_mask=t_mask, g_img=g_img, g_mask=g_mask, loc=loc)
+    if train:
+        caps = torch.zeros(batch, max_pos + 1, dtype=torch.long)
+        n = torch.randint(2, 11, (batch,), generator=g)
+        words = torch.randint(1000, vocab, (batch, 10), generator=g)
+        for b in range(batch):
+            k = int(n[b])
+            caps[b, 0] = BOS
+            caps[b, 1:1 + k] = words[b, :k]
+            caps[b, 1 + k] = EOS
+        out["caps"] = caps
+        out["cap_masks"] = caps == PAD
+    return out
+
+
+def pack(batch_dict, model_kind="CaptionGlobalLoc", loc7=False):
+    """-> the ``samples`` tuple the model classes take (engine.pack_encoder_inputs shapes)."""
+    from .models.utils import NestedTensor
+    t = NestedTensor(batch_dict["t_img"], batch_dict["t_mask"])
+    if model_kind == "Caption":
+        return (t,)
+    if model_kind == "CaptionLoc":
+        loc = batch_dict["loc"]
+        loc7_t = torch.cat([loc, loc[:, :2] * 0.5 + 0.25], 1)   # 7-d synthetic vector
+        return (t, loc7_t)
+    return (t, NestedTensor(batch_dict["g_img"], batch_dict["g_mask"]), batch_dict["loc"])
