@@ -1,0 +1,135 @@
+/* retr_b200 — C ABI of the Blackwell-native (sm_100a) RE⫶TR hot path.
+ *
+ * The reference (simeonjunker/retr) is pure Python/PyTorch and has no FFI layer; its
+ * boundary for this path is the Python API.  This header is the C ABI
+ * that sits directly beneath the re-implementation of those Python symbols; every entry
+ * point names the reference interface it replaces (paths relative to /root/reference).
+ *
+ * Conventions: plain pointers and sizes only (no torch types); device pointers unless a
+ * name ends in `_host`; `stream` is a cudaStream_t passed as void*; every call returns 0
+ * on success, non-zero on error with the message available from retr_last_error().
+ * A context is not thread-safe; distinct contexts are independent.
+ */
+#ifndef RETR_B200_H
+#define RETR_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct retr_ctx retr_ctx;
+
+enum { RETR_FP32 = 0, RETR_BF16 = 1 };
+
+/* Hyper-parameters of one model: the attributes build_model reads from Config
+ * (configuration_template.py:4-56, models/caption.py:177-212). */
+typedef struct retr_model_desc {
+  int32_t device;            /* CUDA ordinal */
+  int32_t precision;         /* RETR_FP32 (SIMT fp32 parity mode) | RETR_BF16 (tcgen05) */
+  int32_t blocks[4];         /* bottlenecks per ResNet stage, e.g. {3,4,23,3} */
+  int32_t dilation;          /* layer4 stride replaced by dilation (models/backbone.py:89-91) */
+  int32_t n_images;          /* backbone passes per sample: 1 Caption/CaptionLoc, 2 CaptionGlobalLoc */
+  int32_t loc_in_dim;        /* 0 none | 7 CaptionLoc (one token) | 1 CaptionGlobalLoc (token per scalar) */
+  int32_t n_loc;             /* location scalars per sample (5 for CaptionGlobalLoc, 7 for CaptionLoc) */
+  int32_t image_size;        /* H = W of the input crops (224) */
+  int32_t d_model, n_heads, d_ff, enc_layers, dec_layers;
+  int32_t max_pos;           /* max_position_embeddings == caption length T (128) */
+  int32_t vocab;
+  int32_t pre_norm;          /* final encoder LayerNorm present (models/ConcatTransformer.py:24) */
+  float   embed_ln_eps;      /* DecoderEmbeddings.LayerNorm eps (config.layer_norm_eps) */
+  int32_t max_batch;         /* largest number of samples per call; sizes the arena */
+} retr_model_desc;
+
+const char* retr_last_error(void);
+int         retr_abi_version(void);
+
+/* ---- context ------------------------------------------------------------------------- */
+/* replaces: models/caption.py:177-212 build_model (module construction). */
+int  retr_create(const retr_model_desc* desc, retr_ctx** out);
+void retr_destroy(retr_ctx* ctx);
+
+/* replaces: nn.Module.load_state_dict as used at eval_model.py:27-28.  `name` is the
+ * reference state_dict key; `data` is fp32, device or host. */
+int retr_load_weight(retr_ctx* ctx, const char* name, const float* data,
+                     const int64_t* shape, int32_t ndim, int32_t on_device);
+/* Repack everything loaded so far into kernel layouts (KRSC conv filters, bf16 copies,
+ * position-bias tables).  Must be called after the last retr_load_weight. */
+int retr_finalize_weights(retr_ctx* ctx);
+
+/* ---- hot path ------------------------------------------------------------------------ */
+/* replaces: Caption*.forward up to the encoder output (models/caption.py:112-149,
+ * models/backbone.py:68-77, models/ConcatTransformer.py:48-67) and the per-layer
+ * cross-attention K/V projections.  Images fp32 NCHW [B,3,H,W]; masks uint8 [B,H,W]
+ * (non-zero = padding); g_* may be NULL when n_images == 1; loc fp32 [B,n_loc] or NULL. */
+int retr_encode(retr_ctx* ctx, int32_t batch, const float* t_img, const uint8_t* t_mask,
+                const float* g_img, const uint8_t* g_mask, const float* loc, void* stream);
+
+/* replaces: the decoder + MLP half of Caption*.forward (models/ConcatTransformer.py:63-74,
+ * models/caption.py:153) for a full caption buffer.  ids int64 [B,T]; id_mask uint8 [B,T]
+ * (non-zero = padding key); logits fp32 [B,T,vocab].  Uses the encoder state of the last
+ * retr_encode.  att_* (optional, may be NULL): head-averaged attention stacks
+ * self [Ld,B,T,T], cross [Ld,B,T,S] (models/ConcatTransformer.py:72-74). */
+int retr_forward_teacher_forced(retr_ctx* ctx, const int64_t* ids, const uint8_t* id_mask,
+                                float* logits, float* att_self, float* att_cross, void* stream);
+/* return_attention=True support for the encoder half: while att_enc is non-NULL, retr_encode
+ * also writes the head-averaged encoder self-attention stack [Le,B,S,S] there. */
+int retr_set_encoder_attention_capture(retr_ctx* ctx, float* att_enc);
+
+/* replaces: eval_utils/decode.py:53-81 greedy (the loop after samples are on the device),
+ * as a KV-cached device-resident loop captured in a CUDA graph.  out_ids int64
+ * [B,max_len] (position 0 = bos, unwritten tail = 0, same early-return semantics);
+ * steps_run_host receives the number of decode steps executed. */
+int retr_decode_greedy(retr_ctx* ctx, int32_t bos, int32_t eos, int32_t max_len,
+                       int64_t* out_ids, int32_t* steps_run_host, void* stream);
+
+/* replaces: eval_utils/decode.py:53-81 greedy end to end with HOST buffers: H2D of the
+ * samples (decode.py:62), encode, decode, D2H of the ids. Pinned host memory recommended. */
+int retr_generate_host(retr_ctx* ctx, int32_t batch, const float* t_img_host,
+                       const uint8_t* t_mask_host, const float* g_img_host,
+                       const uint8_t* g_mask_host, const float* loc_host, int32_t bos,
+                       int32_t eos, int32_t max_len, int64_t* out_ids_host,
+                       int32_t* steps_run_host, void* stream);
+
+/* ---- introspection (tests, bench) ------------------------------------------------------ */
+int     retr_encoder_tokens(const retr_ctx* ctx);           /* S */
+/* Copies of intermediate state as fp32: "memory" [B,S,d], "mask" (uint8 [B,S]),
+ * "src" [B,S,d] (encoder input tokens), "feat_t"/"feat_g" [B,14,14,2048] NHWC. */
+int     retr_read_state(retr_ctx* ctx, const char* what, void* dst, int64_t dst_bytes, void* stream);
+int64_t retr_kernel_launches(const retr_ctx* ctx);          /* kernels launched so far */
+/* Per-phase device times (ms) of the last generate/encode/decode measured with CUDA events:
+ * out[0]=backbone, out[1]=encoder+crossKV, out[2]=decode loop. */
+int     retr_last_phase_ms(const retr_ctx* ctx, float* out3);
+
+/* ---- single-operator entry points (parity tests call kernels one at a time) ------------ */
+/* C[M,N] = epilogue(A[M,K] · W[N,K]^T).  dtype: RETR_FP32 -> fp32 SIMT kernel, A/W fp32;
+ * RETR_BF16 -> tcgen05 kernel, A/W bf16.  out_fp32 selects the C element type (else the
+ * A type).  Optional: scale[N], bias[N], rowbias[period,N] (row m uses m % period),
+ * residual[M,N] (res_fp32 selects its type), relu. */
+typedef struct retr_gemm_args {
+  const void* A; const void* W; void* C;
+  int64_t M; int32_t N, K; int64_t lda, ldc;
+  const float* scale; const float* bias; const float* rowbias; int32_t rowbias_period;
+  const void* residual; int64_t ldr; int32_t res_fp32; int32_t relu; int32_t out_fp32;
+  /* implicit-GEMM convolution view of A (NHWC input); kh == 0 -> plain matrix */
+  int32_t kh, kw, stride, pad, dil, H, W_in, C_in, OH, OW;
+  /* fused argmax over N (vocab head): packed (value,index) keys, uint64 [M]; C may be NULL */
+  unsigned long long* argmax_out;
+} retr_gemm_args;
+int retr_op_gemm(int32_t dtype, const retr_gemm_args* args, void* stream);
+
+/* LayerNorm over the last dim d of fp32 x[rows,d] -> y (fp32 or bf16 by out_bf16). */
+int retr_op_layernorm(const float* x, const float* gamma, const float* beta, void* y,
+                      int64_t rows, int32_t d, float eps, int32_t out_bf16, void* stream);
+
+/* Multi-head attention core on projected q/k/v (row-major, heads side by side, head dim 32):
+ * out[b,i,:] = softmax(q k^T / sqrt(dh) + masks) v.  key_pad uint8 [B,Lk] or NULL.
+ * probs (optional fp32 [B,Lq,Lk]) receives head-averaged probabilities. */
+int retr_op_attention(int32_t dtype, const void* q, const void* k, const void* v, void* out,
+                      int32_t B, int32_t Lq, int32_t Lk, int32_t n_heads, int64_t ldq,
+                      int64_t ldk, int64_t ldv, int64_t ldo, const uint8_t* key_pad,
+                      int32_t causal, float* probs, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,172 @@
+// extern "C" surface declared in include/retr_b200.h.  Every entry point converts C++ exceptions
+// into a non-zero status + retr_last_error(); there is no CPU fallback behind any of them.
+#include "engine.h"
+
+namespace retr {
+thread_local long long g_launches = 0;
+static thread_local std::string g_error;
+void set_error(const std::string& msg) { g_error = msg; }
+}  // namespace retr
+
+using namespace retr;
+
+struct retr_ctx {
+  std::unique_ptr<EngineBase> eng;
+};
+
+#define API_BEGIN try {
+#define API_END                                  \
+  return 0;                                      \
+  }                                              \
+  catch (const std::exception& e) {              \
+    retr::set_error(e.what());                   \
+    return 1;                                    \
+  }                                              \
+  catch (...) {                                  \
+    retr::set_error("unknown native exception"); \
+    return 1;                                    \
+  }
+
+extern "C" {
+
+const char* retr_last_error(void) { return g_error.c_str(); }
+int retr_abi_version(void) { return 1; }
+
+int retr_create(const retr_model_desc* desc, retr_ctx** out) {
+  API_BEGIN
+  RETR_CHECK(desc && out, "null argument");
+  int ndev = 0;
+  CUDA_OK(cudaGetDeviceCount(&ndev));
+  RETR_CHECK(desc->device >= 0 && desc->device < ndev, "no such CUDA device");
+  cudaDeviceProp prop;
+  CUDA_OK(cudaGetDeviceProperties(&prop, desc->device));
+  RETR_CHECK(prop.major == 10, std::string("retr_b200 is built for sm_100a only; device is sm_") +
+                                   std::to_string(prop.major) + std::to_string(prop.minor));
+  retr_ctx* c = new retr_ctx;
+  try {
+    c->eng = make_engine(*desc);
+  } catch (...) {
+    delete c;
+    throw;
+  }
+  *out = c;
+  API_END
+}
+
+void retr_destroy(retr_ctx* ctx) { delete ctx; }
+
+int retr_load_weight(retr_ctx* ctx, const char* name, const float* data, const int64_t* shape, int32_t ndim,
+                     int32_t on_device) {
+  API_BEGIN
+  RETR_CHECK(ctx && name && data && shape, "null argument");
+  CUDA_OK(cudaSetDevice(ctx->eng->desc.device));
+  ctx->eng->load_weight(name, data, shape, ndim, on_device != 0);
+  API_END
+}
+
+int retr_finalize_weights(retr_ctx* ctx) {
+  API_BEGIN
+  RETR_CHECK(ctx, "null context");
+  CUDA_OK(cudaSetDevice(ctx->eng->desc.device));
+  ctx->eng->finalize();
+  API_END
+}
+
+int retr_encode(retr_ctx* ctx, int32_t batch, const float* t_img, const uint8_t* t_mask, const float* g_img,
+                const uint8_t* g_mask, const float* loc, void* stream) {
+  API_BEGIN
+  RETR_CHECK(ctx, "null context");
+  ctx->eng->encode(batch, t_img, t_mask, g_img, g_mask, loc, static_cast<cudaStream_t>(stream));
+  API_END
+}
+
+int retr_forward_teacher_forced(retr_ctx* ctx, const int64_t* ids, const uint8_t* id_mask, float* logits,
+                                float* att_self, float* att_cross, void* stream) {
+  API_BEGIN
+  RETR_CHECK(ctx && ids && id_mask && logits, "null argument");
+  ctx->eng->teacher_forced(ids, id_mask, logits, att_self, att_cross, static_cast<cudaStream_t>(stream));
+  API_END
+}
+
+int retr_set_encoder_attention_capture(retr_ctx* ctx, float* att_enc) {
+  API_BEGIN
+  RETR_CHECK(ctx, "null context");
+  ctx->eng->att_enc_capture = att_enc;
+  API_END
+}
+
+int retr_decode_greedy(retr_ctx* ctx, int32_t bos, int32_t eos, int32_t max_len, int64_t* out_ids,
+                       int32_t* steps_run_host, void* stream) {
+  API_BEGIN
+  RETR_CHECK(ctx && out_ids, "null argument");
+  ctx->eng->decode_greedy(bos, eos, max_len, out_ids, steps_run_host, static_cast<cudaStream_t>(stream));
+  API_END
+}
+
+int retr_generate_host(retr_ctx* ctx, int32_t batch, const float* t_img_host, const uint8_t* t_mask_host,
+                       const float* g_img_host, const uint8_t* g_mask_host, const float* loc_host, int32_t bos,
+                       int32_t eos, int32_t max_len, int64_t* out_ids_host, int32_t* steps_run_host, void* stream) {
+  API_BEGIN
+  RETR_CHECK(ctx && t_img_host && t_mask_host && out_ids_host, "null argument");
+  ctx->eng->generate_host(batch, t_img_host, t_mask_host, g_img_host, g_mask_host, loc_host, bos, eos, max_len,
+                          out_ids_host, steps_run_host, static_cast<cudaStream_t>(stream));
+  API_END
+}
+
+int retr_encoder_tokens(const retr_ctx* ctx) { return ctx ? ctx->eng->S : -1; }
+
+int retr_read_state(retr_ctx* ctx, const char* what, void* dst, int64_t dst_bytes, void* stream) {
+  API_BEGIN
+  RETR_CHECK(ctx && what && dst, "null argument");
+  ctx->eng->read_state(what, dst, dst_bytes, static_cast<cudaStream_t>(stream));
+  API_END
+}
+
+int64_t retr_kernel_launches(const retr_ctx* ctx) { return ctx ? ctx->eng->launches : -1; }
+
+int retr_last_phase_ms(const retr_ctx* ctx, float* out3) {
+  API_BEGIN
+  RETR_CHECK(ctx && out3, "null argument");
+  for (int i = 0; i < 3; ++i) out3[i] = ctx->eng->phase_ms[i];
+  API_END
+}
+
+int retr_op_gemm(int32_t dtype, const retr_gemm_args* a, void* stream) {
+  API_BEGIN
+  RETR_CHECK(a, "null argument");
+  GemmParams p;
+  p.A = a->A; p.W = a->W; p.C = a->C; p.M = a->M; p.N = a->N; p.K = a->K; p.lda = a->lda; p.ldc = a->ldc;
+  p.scale = a->scale; p.bias = a->bias; p.rowbias = a->rowbias; p.rowbias_period = a->rowbias_period;
+  p.residual = a->residual; p.ldr = a->ldr; p.res_fp32 = a->res_fp32 != 0; p.relu = a->relu;
+  p.out_fp32 = a->out_fp32 != 0;
+  p.conv.kh = a->kh; p.conv.kw = a->kw; p.conv.stride = a->stride; p.conv.pad = a->pad; p.conv.dil = a->dil;
+  p.conv.H = a->H; p.conv.W = a->W_in; p.conv.C = a->C_in; p.conv.OH = a->OH; p.conv.OW = a->OW;
+  p.argmax_out = a->argmax_out;
+  if (dtype == RETR_FP32) gemm_fp32(p, static_cast<cudaStream_t>(stream));
+  else if (dtype == RETR_BF16) gemm_bf16(p, static_cast<cudaStream_t>(stream));
+  else throw Error("unknown dtype");
+  API_END
+}
+
+int retr_op_layernorm(const float* x, const float* gamma, const float* beta, void* y, int64_t rows, int32_t d,
+                      float eps, int32_t out_bf16, void* stream) {
+  API_BEGIN
+  if (out_bf16) layernorm<bf16>(x, gamma, beta, static_cast<bf16*>(y), rows, d, eps, static_cast<cudaStream_t>(stream));
+  else layernorm<float>(x, gamma, beta, static_cast<float*>(y), rows, d, eps, static_cast<cudaStream_t>(stream));
+  API_END
+}
+
+int retr_op_attention(int32_t dtype, const void* q, const void* k, const void* v, void* out, int32_t B, int32_t Lq,
+                      int32_t Lk, int32_t n_heads, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo,
+                      const uint8_t* key_pad, int32_t causal, float* probs, void* stream) {
+  API_BEGIN
+  AttnParams p{};
+  p.q = q; p.k = k; p.v = v; p.out = out; p.B = B; p.Lq = Lq; p.Lk = Lk; p.H = n_heads;
+  p.ldq = ldq; p.ldk = ldk; p.ldv = ldv; p.ldo = ldo; p.key_pad = key_pad; p.causal = causal; p.probs = probs;
+  if (dtype == RETR_FP32) attention<float>(p, static_cast<cudaStream_t>(stream));
+  else if (dtype == RETR_BF16) attention<bf16>(p, static_cast<cudaStream_t>(stream));
+  else throw Error("unknown dtype");
+  API_END
+}
+
+}  // extern "C"

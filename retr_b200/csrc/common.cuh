@@ -1,0 +1,80 @@
+// Shared host/device helpers for the retr_b200 native library (sm_100a only).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+
+typedef __nv_bfloat16 bf16;
+
+namespace retr {
+
+// ---- error plumbing -------------------------------------------------------------------
+void set_error(const std::string& msg);           // capi.cu
+extern thread_local long long g_launches;         // kernels launched by this thread's calls
+
+struct Error : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+
+#define RETR_CHECK(cond, msg)                                                              \
+  do {                                                                                     \
+    if (!(cond)) throw ::retr::Error(std::string(msg) + " [" #cond "] at " __FILE__ ":" +  \
+                                     std::to_string(__LINE__));                            \
+  } while (0)
+
+#define CUDA_OK(expr)                                                                      \
+  do {                                                                                     \
+    cudaError_t e_ = (expr);                                                               \
+    if (e_ != cudaSuccess)                                                                 \
+      throw ::retr::Error(std::string("CUDA error ") + cudaGetErrorString(e_) +            \
+                          " in " #expr " at " __FILE__ ":" + std::to_string(__LINE__));    \
+  } while (0)
+
+#define LAUNCH_OK()                                                                        \
+  do {                                                                                     \
+    ++::retr::g_launches;                                                                  \
+    CUDA_OK(cudaGetLastError());                                                           \
+  } while (0)
+
+static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+// ---- device helpers ---------------------------------------------------------------------
+__device__ __forceinline__ float to_f(float v) { return v; }
+__device__ __forceinline__ float to_f(bf16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ bf16 from_f<bf16>(float v) { return __float2bfloat16_rn(v); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// Monotone map float -> uint32 (larger float => larger key); NaN-free inputs assumed.
+__device__ __forceinline__ uint32_t float_order_key(float f) {
+  uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+// (value, index) packed so that atomicMax picks the largest value and, among equal values,
+// the smallest index — torch.argmax's tie rule.
+__device__ __forceinline__ unsigned long long pack_argmax(float v, uint32_t idx) {
+  return ((unsigned long long)float_order_key(v) << 32) | (unsigned long long)(0xffffffffu - idx);
+}
+__host__ __device__ __forceinline__ uint32_t unpack_argmax_index(unsigned long long key) {
+  return 0xffffffffu - (uint32_t)(key & 0xffffffffull);
+}
+
+}  // namespace retr

@@ -1,0 +1,646 @@
+// EngineT<T>: the schedule of the hot path.  T = float (fp32 parity mode, SIMT GEMMs) or bf16
+// (tcgen05 GEMMs; residual stream, LayerNorm statistics, softmax and accumulators stay fp32).
+//
+// Reference being replaced (paths relative to /root/reference):
+//   backbone     models/backbone.py:54-93 + torchvision ResNet Bottleneck (resnet.py:108-165)
+//   tokens       models/caption.py:112-147, models/ConcatTransformer.py:48-61
+//   encoder      models/ConcatTransformer.py:77-108,152-194 ; models/transformer_modules.py:22-46,77-97
+//   decoder      models/ConcatTransformer.py:111-149,197-257 ; transformer_modules.py:49-74,100-129
+//   head         models/caption.py:153,161-174
+//   greedy loop  eval_utils/decode.py:53-81
+//
+// "+pos" trick: every place the reference adds a position table to a projection INPUT
+// (q=k=LN(x)+pos, q=LN(y)+query_pos, k=memory+pos) is folded into a per-position bias table,
+// W(x+p)+b = Wx + (Wp+b), computed once in fp32 at weight-load time (rowbias epilogue).
+#include "engine.h"
+
+#include <tuple>
+#include <type_traits>
+
+namespace retr {
+namespace {
+
+template <typename T> void gemm(const GemmParams& p, cudaStream_t s);
+template <> void gemm<float>(const GemmParams& p, cudaStream_t s) { gemm_fp32(p, s); }
+template <> void gemm<bf16>(const GemmParams& p, cudaStream_t s) { gemm_bf16(p, s); }
+
+__global__ void fill_cols_kernel(float* dst, int rows, int ld, int col0, int ncols, const float* src) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx < rows * ncols) dst[(int64_t)(idx / ncols) * ld + col0 + idx % ncols] = src[idx % ncols];
+}
+template <typename T> __global__ void to_f32_kernel(const T* src, float* dst, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = to_f(src[i]);
+}
+template <typename T> __global__ void from_f32_kernel(const float* src, T* dst, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = from_f<T>(src[i]);
+}
+
+template <typename T> struct Conv {
+  int cin = 0, cout = 0, k = 1, stride = 1, pad = 0, dil = 1, kpad = 0;
+  T* w = nullptr;           // [cout, kpad], k index = (r*kw+s)*cin + c
+  float* scale = nullptr;   // folded FrozenBatchNorm2d: y = conv*scale + shift
+  float* shift = nullptr;
+};
+template <typename T> struct Block {
+  Conv<T> c1, c2, c3, ds;
+  bool has_ds = false;
+};
+template <typename T> struct Linear {
+  T* w = nullptr;           // [out, in]
+  float* b = nullptr;
+  int out = 0, in = 0;
+};
+template <typename T> struct EncLayer {
+  float *ln1_g, *ln1_b, *ln2_g, *ln2_b;
+  Linear<T> qkv, out, ff1, ff2;
+  float* rb_qkv;            // [S, 3d]: pos.Wqk^T + b_qk | b_v
+};
+template <typename T> struct DecLayer {
+  float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *ln3_g, *ln3_b;
+  Linear<T> s_qkv, s_out, c_q, c_kv, c_out, ff1, ff2;
+  float* rb_s_qkv;          // [T, 3d]: E_pos.Wqk^T + b_qk | b_v
+  float* rb_c_q;            // [T, d] : E_pos.Wq^T + b_q
+  float* rb_c_kv;           // [S, 2d]: pos.Wk^T + b_k | b_v
+};
+
+template <typename T>
+class EngineT final : public EngineBase {
+ public:
+  explicit EngineT(const retr_model_desc& d) : EngineBase(d) {}
+  ~EngineT() override {
+    for (auto& kv : graphs_) cudaGraphExecDestroy(kv.second);
+    if (done_host_) cudaFreeHost(done_host_);
+  }
+  void finalize() override;
+  void encode(int B, const float* t_img, const uint8_t* t_mask, const float* g_img, const uint8_t* g_mask,
+              const float* loc, cudaStream_t s) override;
+  void teacher_forced(const int64_t* ids, const uint8_t* id_mask, float* logits, float* att_self, float* att_cross,
+                      cudaStream_t s) override;
+  void decode_greedy(int bos, int eos, int max_len, int64_t* out_ids, int* steps_host, cudaStream_t s) override;
+  void read_state(const std::string& what, void* dst, int64_t bytes, cudaStream_t s) override;
+
+ private:
+  T* as_T(const RawWeight& w);                       // device copy of a weight in T
+  Linear<T> linear(const std::string& wname, const std::string& bname, int row0 = 0, int rows = -1);
+  Conv<T> conv(const std::string& wname, const std::string& bn, int stride, int pad, int dil);
+  float* pos_bias_table(const float* pos, int rows, const RawWeight& w, const RawWeight& b, int row0, int n_proj,
+                        int n_total);
+  void run_conv(const Conv<T>& c, const T* in, int64_t n, int H, int W, T* out, const T* residual, int relu,
+                int* OH, int* OW, cudaStream_t s);
+  void backbone(const float* img, int64_t n, T* feat, cudaStream_t s);
+  void decoder_layers_full(int B, const uint8_t* id_mask, float* att_self, float* att_cross, cudaStream_t s);
+  void decode_step(int B, int eos, int max_len, cudaStream_t s);
+  void alloc_buffers();
+  GemmParams lin(const Linear<T>& l, const void* A, int64_t M, void* C) {
+    GemmParams p;
+    p.A = A; p.W = l.w; p.C = C; p.M = M; p.N = l.out; p.K = l.in; p.lda = l.in; p.ldc = l.out; p.bias = l.b;
+    return p;
+  }
+
+  // weights
+  Conv<T> stem_;
+  std::vector<Block<T>> blocks_;
+  Linear<T> input_proj_;
+  float *loc_w_ = nullptr, *loc_b_ = nullptr;
+  std::vector<EncLayer<T>> enc_;
+  std::vector<DecLayer<T>> dec_;
+  float *enc_norm_g_ = nullptr, *enc_norm_b_ = nullptr, *dec_norm_g_ = nullptr, *dec_norm_b_ = nullptr;
+  float *e_word_ = nullptr, *e_pos_ = nullptr, *emb_g_ = nullptr, *emb_b_ = nullptr;
+  Linear<T> mlp_[3];
+  // activations
+  int chunk_ = 64;                                   // images per backbone pass
+  T *im2col_ = nullptr, *act_[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}, *feat_ = nullptr;
+  float *x_ = nullptr, *y_ = nullptr;                // fp32 residual streams (encoder, decoder)
+  T *n_ = nullptr, *qkv_ = nullptr, *att_ = nullptr, *h_ = nullptr, *memory_ = nullptr, *qc_ = nullptr;
+  T *hs_ = nullptr, *m1_ = nullptr, *m2_ = nullptr;
+  float* src_copy_ = nullptr;                        // encoder input tokens kept for read_state
+  std::vector<T*> ckv_, self_cache_;
+  uint8_t *tok_mask_ = nullptr, *finished_ = nullptr;
+  int64_t* caption_ = nullptr;
+  int *step_ = nullptr, *done_ = nullptr;
+  int* done_host_ = nullptr;                         // pinned [2]: done, step
+  unsigned long long* argmax_keys_ = nullptr;
+  std::map<std::tuple<int, int, int>, cudaGraphExec_t> graphs_;
+  long long step_kernels_ = 0;                       // kernels in one captured decode step
+};
+
+// ---- weight preparation -------------------------------------------------------------------------
+template <> float* EngineT<float>::as_T(const RawWeight& w) { return w.dev; }
+template <> bf16* EngineT<bf16>::as_T(const RawWeight& w) {
+  bf16* p = static_cast<bf16*>(dalloc(w.numel * 2));
+  f32_to_bf16(w.dev, p, w.numel, 0);
+  return p;
+}
+
+template <typename T>
+Linear<T> EngineT<T>::linear(const std::string& wname, const std::string& bname, int row0, int rows) {
+  const RawWeight& w = raw(wname);
+  RETR_CHECK(w.shape.size() >= 2, "linear weight rank");
+  Linear<T> l;
+  l.in = (int)(w.numel / w.shape[0]);
+  l.out = rows < 0 ? (int)w.shape[0] : rows;
+  T* full = as_T(w);
+  l.w = full + (int64_t)row0 * l.in;
+  l.b = bname.empty() ? nullptr : raw(bname).dev + row0;
+  return l;
+}
+
+template <typename T>
+Conv<T> EngineT<T>::conv(const std::string& wname, const std::string& bn, int stride, int pad, int dil) {
+  const RawWeight& w = raw(wname);
+  RETR_CHECK(w.shape.size() == 4, "conv weight must be OIHW");
+  Conv<T> c;
+  c.cout = (int)w.shape[0]; c.cin = (int)w.shape[1]; c.k = (int)w.shape[2];
+  c.stride = stride; c.pad = pad; c.dil = dil;
+  const int kk = c.k * c.k * c.cin;
+  c.kpad = (int)cdiv(kk, 16) * 16;
+  c.w = static_cast<T*>(dalloc((size_t)c.cout * c.kpad * sizeof(T)));
+  repack_filter<T>(w.dev, c.w, c.cout, c.cin, c.k, c.k, c.kpad, 0);
+  // FrozenBatchNorm2d fold (models/backbone.py:41-51), evaluated in fp32 like the reference
+  const int n = c.cout;
+  std::vector<float> bw(n), bb(n), rm(n), rv(n), sc(n), sh(n);
+  CUDA_OK(cudaMemcpy(bw.data(), raw(bn + ".weight").dev, n * 4, cudaMemcpyDeviceToHost));
+  CUDA_OK(cudaMemcpy(bb.data(), raw(bn + ".bias").dev, n * 4, cudaMemcpyDeviceToHost));
+  CUDA_OK(cudaMemcpy(rm.data(), raw(bn + ".running_mean").dev, n * 4, cudaMemcpyDeviceToHost));
+  CUDA_OK(cudaMemcpy(rv.data(), raw(bn + ".running_var").dev, n * 4, cudaMemcpyDeviceToHost));
+  for (int i = 0; i < n; ++i) {
+    sc[i] = bw[i] * (1.0f / sqrtf(rv[i] + 1e-5f));
+    sh[i] = bb[i] - rm[i] * sc[i];
+  }
+  c.scale = static_cast<float*>(dalloc(n * 4));
+  c.shift = static_cast<float*>(dalloc(n * 4));
+  CUDA_OK(cudaMemcpy(c.scale, sc.data(), n * 4, cudaMemcpyHostToDevice));
+  CUDA_OK(cudaMemcpy(c.shift, sh.data(), n * 4, cudaMemcpyHostToDevice));
+  return c;
+}
+
+// table[r, 0:n_proj] = pos[r,:] . W[row0:row0+n_proj,:]^T + b[row0:...]; table[r, n_proj:n_total] = b[row0+n_proj:...]
+template <typename T>
+float* EngineT<T>::pos_bias_table(const float* pos, int rows, const RawWeight& w, const RawWeight& b, int row0,
+                                  int n_proj, int n_total) {
+  const int d = desc.d_model;
+  float* t = static_cast<float*>(dalloc((size_t)rows * n_total * 4));
+  GemmParams p;
+  p.A = pos; p.W = w.dev + (int64_t)row0 * d; p.C = t; p.M = rows; p.N = n_proj; p.K = d; p.lda = d; p.ldc = n_total;
+  p.bias = b.dev + row0; p.out_fp32 = true;
+  gemm_fp32(p, 0);
+  if (n_total > n_proj) {
+    const int n = rows * (n_total - n_proj);
+    fill_cols_kernel<<<(unsigned)cdiv(n, 256), 256>>>(t, rows, n_total, n_proj, n_total - n_proj, b.dev + row0 + n_proj);
+    LAUNCH_OK();
+  }
+  return t;
+}
+
+template <typename T>
+void EngineT<T>::finalize() {
+  RETR_CHECK(!finalized_, "finalize called twice");
+  const int d = desc.d_model;
+  const std::string bb = "backbone.body.";
+  stem_ = conv(bb + "conv1.weight", bb + "bn1", 2, 3, 1);
+  RETR_CHECK(stem_.cin == 3 && stem_.k == 7, "unexpected stem");
+  int dil = 1;
+  for (int st = 0; st < 4; ++st) {
+    int stride = st == 0 ? 1 : 2;
+    const int first_dil = dil;
+    if (st == 3 && desc.dilation) { dil *= stride; stride = 1; }
+    for (int bi = 0; bi < desc.blocks[st]; ++bi) {
+      const std::string p = bb + "layer" + std::to_string(st + 1) + "." + std::to_string(bi) + ".";
+      const int s_ = bi == 0 ? stride : 1, dl = bi == 0 ? first_dil : dil;
+      Block<T> b;
+      b.c1 = conv(p + "conv1.weight", p + "bn1", 1, 0, 1);
+      b.c2 = conv(p + "conv2.weight", p + "bn2", s_, dl, dl);
+      b.c3 = conv(p + "conv3.weight", p + "bn3", 1, 0, 1);
+      b.has_ds = raw_.count(p + "downsample.0.weight") > 0;
+      if (b.has_ds) b.ds = conv(p + "downsample.0.weight", p + "downsample.1", s_, 0, 1);
+      blocks_.push_back(b);
+    }
+  }
+  input_proj_ = linear("input_proj.weight", "input_proj.bias");
+  RETR_CHECK(input_proj_.out == d, "input_proj width");
+  if (desc.loc_in_dim) { loc_w_ = raw("loc_proj.weight").dev; loc_b_ = raw("loc_proj.bias").dev; }
+
+  const float* pe = raw("transformer.positional_encoding.pe").dev;     // [1024,1,d]
+  RETR_CHECK(raw("transformer.positional_encoding.pe").shape[0] >= S, "sequence longer than the sine table");
+  e_word_ = raw("transformer.embeddings.word_embeddings.weight").dev;
+  e_pos_ = raw("transformer.embeddings.position_embeddings.weight").dev;
+  emb_g_ = raw("transformer.embeddings.LayerNorm.weight").dev;
+  emb_b_ = raw("transformer.embeddings.LayerNorm.bias").dev;
+  const int Tn = desc.max_pos;
+  for (int l = 0; l < desc.enc_layers; ++l) {
+    const std::string p = "transformer.encoder.layers." + std::to_string(l) + ".";
+    EncLayer<T> e;
+    e.ln1_g = raw(p + "self_attn.norm.weight").dev; e.ln1_b = raw(p + "self_attn.norm.bias").dev;
+    e.ln2_g = raw(p + "ff.norm.weight").dev; e.ln2_b = raw(p + "ff.norm.bias").dev;
+    e.qkv = linear(p + "self_attn.sublayer.in_proj_weight", "");
+    e.out = linear(p + "self_attn.sublayer.out_proj.weight", p + "self_attn.sublayer.out_proj.bias");
+    e.ff1 = linear(p + "ff.sublayer.0.weight", p + "ff.sublayer.0.bias");
+    e.ff2 = linear(p + "ff.sublayer.2.weight", p + "ff.sublayer.2.bias");
+    e.rb_qkv = pos_bias_table(pe, S, raw(p + "self_attn.sublayer.in_proj_weight"),
+                              raw(p + "self_attn.sublayer.in_proj_bias"), 0, 2 * d, 3 * d);
+    enc_.push_back(e);
+  }
+  if (desc.pre_norm) { enc_norm_g_ = raw("transformer.encoder.norm.weight").dev; enc_norm_b_ = raw("transformer.encoder.norm.bias").dev; }
+  for (int l = 0; l < desc.dec_layers; ++l) {
+    const std::string p = "transformer.decoder.layers." + std::to_string(l) + ".";
+    const std::string sa = p + "tgt_self_attn.sublayer.", ca = p + "tgt_src_cross_attn.sublayer.";
+    DecLayer<T> e;
+    e.ln1_g = raw(p + "tgt_self_attn.norm.weight").dev; e.ln1_b = raw(p + "tgt_self_attn.norm.bias").dev;
+    e.ln2_g = raw(p + "tgt_src_cross_attn.norm.weight").dev; e.ln2_b = raw(p + "tgt_src_cross_attn.norm.bias").dev;
+    e.ln3_g = raw(p + "ff.norm.weight").dev; e.ln3_b = raw(p + "ff.norm.bias").dev;
+    e.s_qkv = linear(sa + "in_proj_weight", "");
+    e.s_out = linear(sa + "out_proj.weight", sa + "out_proj.bias");
+    e.c_q = linear(ca + "in_proj_weight", "", 0, d);
+    e.c_kv = e.c_q; e.c_kv.w = e.c_q.w + (int64_t)d * d; e.c_kv.out = 2 * d;
+    e.c_out = linear(ca + "out_proj.weight", ca + "out_proj.bias");
+    e.ff1 = linear(p + "ff.sublayer.0.weight", p + "ff.sublayer.0.bias");
+    e.ff2 = linear(p + "ff.sublayer.2.weight", p + "ff.sublayer.2.bias");
+    e.rb_s_qkv = pos_bias_table(e_pos_, Tn, raw(sa + "in_proj_weight"), raw(sa + "in_proj_bias"), 0, 2 * d, 3 * d);
+    e.rb_c_q = pos_bias_table(e_pos_, Tn, raw(ca + "in_proj_weight"), raw(ca + "in_proj_bias"), 0, d, d);
+    e.rb_c_kv = pos_bias_table(pe, S, raw(ca + "in_proj_weight"), raw(ca + "in_proj_bias"), d, d, 2 * d);
+    dec_.push_back(e);
+  }
+  dec_norm_g_ = raw("transformer.decoder.norm.weight").dev; dec_norm_b_ = raw("transformer.decoder.norm.bias").dev;
+  for (int i = 0; i < 3; ++i)
+    mlp_[i] = linear("mlp.layers." + std::to_string(i) + ".weight", "mlp.layers." + std::to_string(i) + ".bias");
+  RETR_CHECK(mlp_[2].out == desc.vocab, "vocab size mismatch");
+  alloc_buffers();
+  CUDA_OK(cudaDeviceSynchronize());
+  finalized_ = true;
+}
+
+
+// ---- buffers ---------------------------------------------------------------------------------------
+template <typename T>
+void EngineT<T>::alloc_buffers() {
+  const int64_t B = desc.max_batch, d = desc.d_model, Tn = desc.max_pos, ff = desc.d_ff;
+  const int64_t nimg = B * desc.n_images;
+  if (const char* e = getenv("RETR_BACKBONE_CHUNK")) chunk_ = std::max(1, atoi(e));
+  chunk_ = (int)std::min<int64_t>(chunk_, nimg);
+  const int64_t h1 = (desc.image_size + 6 - 7) / 2 + 1;           // stem output side
+  const int64_t act = (int64_t)chunk_ * h1 * h1 * 64;              // largest activation of a chunk
+  im2col_ = static_cast<T*>(dalloc(chunk_ * h1 * h1 * stem_.kpad * sizeof(T)));
+  for (auto& a : act_) a = static_cast<T*>(dalloc(act * sizeof(T)));
+  const int64_t g2 = (int64_t)grid_hw * grid_hw, cfeat = blocks_.back().c3.cout;
+  feat_ = static_cast<T*>(dalloc(nimg * g2 * cfeat * sizeof(T)));
+  const int64_t Me = B * S, Md = B * Tn, Mx = std::max(Me, Md);
+  x_ = static_cast<float*>(dalloc(Me * d * 4));
+  src_copy_ = static_cast<float*>(dalloc(Me * d * 4));
+  y_ = static_cast<float*>(dalloc(Md * d * 4));
+  n_ = static_cast<T*>(dalloc(Mx * d * sizeof(T)));
+  qkv_ = static_cast<T*>(dalloc(Mx * 3 * d * sizeof(T)));
+  att_ = static_cast<T*>(dalloc(Mx * d * sizeof(T)));
+  h_ = static_cast<T*>(dalloc(Mx * ff * sizeof(T)));
+  memory_ = static_cast<T*>(dalloc(Me * d * sizeof(T)));
+  qc_ = static_cast<T*>(dalloc(Md * d * sizeof(T)));
+  hs_ = static_cast<T*>(dalloc(Md * d * sizeof(T)));
+  m1_ = static_cast<T*>(dalloc(Md * mlp_[0].out * sizeof(T)));
+  m2_ = static_cast<T*>(dalloc(Md * mlp_[1].out * sizeof(T)));
+  for (int l = 0; l < desc.dec_layers; ++l) {
+    ckv_.push_back(static_cast<T*>(dalloc(Me * 2 * d * sizeof(T))));
+    self_cache_.push_back(static_cast<T*>(dalloc(Md * 2 * d * sizeof(T))));
+  }
+  tok_mask_ = static_cast<uint8_t*>(dalloc(Me));
+  finished_ = static_cast<uint8_t*>(dalloc(B));
+  caption_ = static_cast<int64_t*>(dalloc(Md * 8));
+  step_ = static_cast<int*>(dalloc(16));
+  done_ = step_ + 1;
+  argmax_keys_ = static_cast<unsigned long long*>(dalloc(Md * 8));
+  CUDA_OK(cudaMemset(argmax_keys_, 0, Md * 8));
+  CUDA_OK(cudaMallocHost(&done_host_, 16));
+}
+
+// ---- backbone --------------------------------------------------------------------------------------
+template <typename T>
+void EngineT<T>::run_conv(const Conv<T>& c, const T* in, int64_t n, int H, int W, T* out, const T* residual,
+                          int relu, int* OH, int* OW, cudaStream_t s) {
+  const int oh = (H + 2 * c.pad - c.dil * (c.k - 1) - 1) / c.stride + 1;
+  const int ow = (W + 2 * c.pad - c.dil * (c.k - 1) - 1) / c.stride + 1;
+  GemmParams p;
+  p.A = in; p.W = c.w; p.C = out;
+  p.M = n * oh * ow; p.N = c.cout; p.K = c.kpad; p.lda = c.cin; p.ldc = c.cout;
+  p.scale = c.scale; p.bias = c.shift; p.relu = relu;
+  p.residual = residual; p.ldr = c.cout; p.res_fp32 = std::is_same<T, float>::value;
+  if (c.k != 1 || c.stride != 1) {
+    p.conv.kh = p.conv.kw = c.k; p.conv.stride = c.stride; p.conv.pad = c.pad; p.conv.dil = c.dil;
+    p.conv.H = H; p.conv.W = W; p.conv.C = c.cin; p.conv.OH = oh; p.conv.OW = ow;
+  }
+  gemm<T>(p, s);
+  *OH = oh; *OW = ow;
+}
+
+// img: fp32 NCHW [n,3,Hi,Wi] (n <= chunk_) -> feat NHWC [n, g, g, C4]
+template <typename T>
+void EngineT<T>::backbone(const float* img, int64_t n, T* feat, cudaStream_t s) {
+  const int Hi = desc.image_size;
+  int H = (Hi + 6 - 7) / 2 + 1, W = H;
+  stem_im2col<T>(img, im2col_, n, Hi, Hi, H, W, stem_.kpad, s);
+  {
+    GemmParams p;
+    p.A = im2col_; p.W = stem_.w; p.C = act_[0];
+    p.M = n * H * W; p.N = stem_.cout; p.K = stem_.kpad; p.lda = stem_.kpad; p.ldc = stem_.cout;
+    p.scale = stem_.scale; p.bias = stem_.shift; p.relu = 1;
+    gemm<T>(p, s);
+  }
+  const int PH = (H + 2 - 3) / 2 + 1;
+  maxpool_3x3s2<T>(act_[0], act_[1], n, H, W, stem_.cout, PH, PH, s);
+  H = W = PH;
+  T* x = act_[1];
+  T* other = act_[0];
+  for (size_t bi = 0; bi < blocks_.size(); ++bi) {
+    const Block<T>& b = blocks_[bi];
+    int h1, w1, h2, w2, h3, w3;
+    run_conv(b.c1, x, n, H, W, act_[2], nullptr, 1, &h1, &w1, s);
+    run_conv(b.c2, act_[2], n, h1, w1, act_[3], nullptr, 1, &h2, &w2, s);
+    const T* identity = x;
+    if (b.has_ds) {
+      int hd, wd;
+      run_conv(b.ds, x, n, H, W, act_[4], nullptr, 0, &hd, &wd, s);
+      identity = act_[4];
+    }
+    T* out = (bi + 1 == blocks_.size()) ? feat : other;
+    run_conv(b.c3, act_[3], n, h2, w2, out, identity, 2, &h3, &w3, s);     // relu(bn3(conv3) + identity)
+    other = x; x = out;
+    H = h3; W = w3;
+  }
+  RETR_CHECK(H == grid_hw && W == grid_hw, "backbone output side mismatch");
+}
+
+// ---- encode ------------------------------------------------------------------------------------------
+template <typename T>
+void EngineT<T>::encode(int B, const float* t_img, const uint8_t* t_mask, const float* g_img, const uint8_t* g_mask,
+                        const float* loc, cudaStream_t s) {
+  RETR_CHECK(finalized_, "call retr_finalize_weights first");
+  RETR_CHECK(B > 0 && B <= desc.max_batch, "batch exceeds max_batch");
+  RETR_CHECK(t_img && t_mask, "target images and masks required");
+  RETR_CHECK(desc.n_images == 1 || (g_img && g_mask), "context images and masks required");
+  RETR_CHECK(desc.loc_in_dim == 0 || loc, "location features required");
+  const long long l0 = g_launches;
+  const int d = desc.d_model, g2 = grid_hw * grid_hw, Hi = desc.image_size;
+  const int64_t cfeat = blocks_.back().c3.cout, img_elems = 3LL * Hi * Hi;
+  CUDA_OK(cudaEventRecord(ev_[0], s));
+  for (int set = 0; set < desc.n_images; ++set) {
+    const float* img = set == 0 ? t_img : g_img;
+    for (int64_t i0 = 0; i0 < B; i0 += chunk_) {
+      const int64_t n = std::min<int64_t>(chunk_, B - i0);
+      backbone(img + i0 * img_elems, n, feat_ + ((int64_t)set * B + i0) * g2 * cfeat, s);
+    }
+  }
+  CUDA_OK(cudaEventRecord(ev_[1], s));
+  // input_proj straight into the concatenated token buffer (models/caption.py:119-123, 139-143)
+  const int off_loc = g2, off_g = g2 + n_loc_tok;
+  for (int set = 0; set < desc.n_images; ++set) {
+    GemmParams p = lin(input_proj_, feat_ + (int64_t)set * B * g2 * cfeat, (int64_t)B * g2, x_ + (int64_t)(set ? off_g : 0) * d);
+    p.out_fp32 = true; p.ldc = d; p.c_group = g2; p.c_group_stride = S;
+    gemm<T>(p, s);
+    subsample_mask(set == 0 ? t_mask : g_mask, tok_mask_, B, Hi, Hi, grid_hw, grid_hw, S, set ? off_g : 0, s);
+  }
+  if (desc.loc_in_dim)
+    loc_tokens(loc, loc_w_, loc_b_, x_, tok_mask_, B, desc.n_loc, desc.loc_in_dim == 1, d, S, off_loc, s);
+  const int64_t Me = (int64_t)B * S;
+  CUDA_OK(cudaMemcpyAsync(src_copy_, x_, Me * d * 4, cudaMemcpyDeviceToDevice, s));
+  // encoder (models/ConcatTransformer.py:171-194)
+  for (int l = 0; l < desc.enc_layers; ++l) {
+    const EncLayer<T>& e = enc_[l];
+    layernorm<T>(x_, e.ln1_g, e.ln1_b, n_, Me, d, 1e-5f, s);
+    GemmParams p = lin(e.qkv, n_, Me, qkv_);
+    p.rowbias = e.rb_qkv; p.rowbias_period = S;
+    gemm<T>(p, s);
+    AttnParams a{};
+    a.q = qkv_; a.k = qkv_ + d; a.v = qkv_ + 2 * d; a.out = att_;
+    a.B = B; a.Lq = S; a.Lk = S; a.H = desc.n_heads;
+    a.ldq = a.ldk = a.ldv = 3 * d; a.ldo = d; a.key_pad = tok_mask_; a.causal = 0;
+    a.probs = att_enc_capture ? att_enc_capture + (int64_t)l * B * S * S : nullptr;
+    attention<T>(a, s);
+    p = lin(e.out, att_, Me, x_);
+    p.out_fp32 = true; p.residual = x_; p.ldr = d; p.res_fp32 = true;
+    gemm<T>(p, s);
+    layernorm<T>(x_, e.ln2_g, e.ln2_b, n_, Me, d, 1e-5f, s);
+    p = lin(e.ff1, n_, Me, h_);
+    p.relu = 1;
+    gemm<T>(p, s);
+    p = lin(e.ff2, h_, Me, x_);
+    p.out_fp32 = true; p.residual = x_; p.ldr = d; p.res_fp32 = true;
+    gemm<T>(p, s);
+  }
+  if (desc.pre_norm) {
+    layernorm<T>(x_, enc_norm_g_, enc_norm_b_, memory_, Me, d, 1e-5f, s);
+  } else {
+    from_f32_kernel<T><<<(unsigned)cdiv(Me * d, 256), 256, 0, s>>>(x_, memory_, Me * d);
+    LAUNCH_OK();
+  }
+  // cross-attention K/V of every decoder layer, once per sample (k = memory+pos, v = memory)
+  for (int l = 0; l < desc.dec_layers; ++l) {
+    GemmParams p = lin(dec_[l].c_kv, memory_, Me, ckv_[l]);
+    p.rowbias = dec_[l].rb_c_kv; p.rowbias_period = S;
+    gemm<T>(p, s);
+  }
+  CUDA_OK(cudaEventRecord(ev_[2], s));
+  cur_B_ = B;
+  launches += g_launches - l0;
+}
+
+
+// ---- teacher-forced decoder + head (models/ConcatTransformer.py:63-74, models/caption.py:153) ------------
+template <typename T>
+void EngineT<T>::teacher_forced(const int64_t* ids, const uint8_t* id_mask, float* logits, float* att_self,
+                                float* att_cross, cudaStream_t s) {
+  RETR_CHECK(cur_B_ > 0, "retr_encode must run before the decoder");
+  const long long l0 = g_launches;
+  const int B = cur_B_, d = desc.d_model, Tn = desc.max_pos;
+  const int64_t Md = (int64_t)B * Tn;
+  embed_ln(ids, Tn, e_word_, e_pos_, emb_g_, emb_b_, y_, B, Tn, 0, nullptr, d, desc.embed_ln_eps, s);
+  for (int l = 0; l < desc.dec_layers; ++l) {
+    const DecLayer<T>& e = dec_[l];
+    layernorm<T>(y_, e.ln1_g, e.ln1_b, n_, Md, d, 1e-5f, s);
+    GemmParams p = lin(e.s_qkv, n_, Md, qkv_);
+    p.rowbias = e.rb_s_qkv; p.rowbias_period = Tn;
+    gemm<T>(p, s);
+    AttnParams a{};
+    a.q = qkv_; a.k = qkv_ + d; a.v = qkv_ + 2 * d; a.out = att_;
+    a.B = B; a.Lq = Tn; a.Lk = Tn; a.H = desc.n_heads;
+    a.ldq = a.ldk = a.ldv = 3 * d; a.ldo = d; a.key_pad = id_mask; a.causal = 1;
+    a.probs = att_self ? att_self + (int64_t)l * B * Tn * Tn : nullptr;
+    attention<T>(a, s);
+    p = lin(e.s_out, att_, Md, y_);
+    p.out_fp32 = true; p.residual = y_; p.ldr = d; p.res_fp32 = true;
+    gemm<T>(p, s);
+
+    layernorm<T>(y_, e.ln2_g, e.ln2_b, n_, Md, d, 1e-5f, s);
+    p = lin(e.c_q, n_, Md, qc_);
+    p.rowbias = e.rb_c_q; p.rowbias_period = Tn;
+    gemm<T>(p, s);
+    a = AttnParams{};
+    a.q = qc_; a.k = ckv_[l]; a.v = ckv_[l] + d; a.out = att_;
+    a.B = B; a.Lq = Tn; a.Lk = S; a.H = desc.n_heads;
+    a.ldq = d; a.ldk = a.ldv = 2 * d; a.ldo = d; a.key_pad = tok_mask_; a.causal = 0;
+    a.probs = att_cross ? att_cross + (int64_t)l * B * Tn * S : nullptr;
+    attention<T>(a, s);
+    p = lin(e.c_out, att_, Md, y_);
+    p.out_fp32 = true; p.residual = y_; p.ldr = d; p.res_fp32 = true;
+    gemm<T>(p, s);
+
+    layernorm<T>(y_, e.ln3_g, e.ln3_b, n_, Md, d, 1e-5f, s);
+    p = lin(e.ff1, n_, Md, h_);
+    p.relu = 1;
+    gemm<T>(p, s);
+    p = lin(e.ff2, h_, Md, y_);
+    p.out_fp32 = true; p.residual = y_; p.ldr = d; p.res_fp32 = true;
+    gemm<T>(p, s);
+  }
+  layernorm<T>(y_, dec_norm_g_, dec_norm_b_, hs_, Md, d, 1e-5f, s);
+  GemmParams p = lin(mlp_[0], hs_, Md, m1_); p.relu = 1; gemm<T>(p, s);
+  p = lin(mlp_[1], m1_, Md, m2_); p.relu = 1; gemm<T>(p, s);
+  p = lin(mlp_[2], m2_, Md, logits); p.out_fp32 = true; gemm<T>(p, s);
+  launches += g_launches - l0;
+}
+
+// ---- one KV-cached greedy step; position = *step_ (device) --------------------------------------------------
+template <typename T>
+void EngineT<T>::decode_step(int B, int eos, int max_len, cudaStream_t s) {
+  const int d = desc.d_model, Tn = desc.max_pos, H = desc.n_heads;
+  embed_ln(caption_, max_len, e_word_, e_pos_, emb_g_, emb_b_, y_, B, 1, 0, step_, d, desc.embed_ln_eps, s);
+  for (int l = 0; l < desc.dec_layers; ++l) {
+    const DecLayer<T>& e = dec_[l];
+    layernorm<T>(y_, e.ln1_g, e.ln1_b, n_, B, d, 1e-5f, s);
+    GemmParams p = lin(e.s_qkv, n_, B, qkv_);
+    p.rowbias = e.rb_s_qkv; p.rowbias_dyn = step_;
+    gemm<T>(p, s);
+    decode_attention<T>(qkv_, 3 * d, qkv_ + d, 3 * d, self_cache_[l], 2 * d, (int64_t)Tn * 2 * d, att_, d, B, H, d, 0,
+                        step_, nullptr, 0, s);
+    p = lin(e.s_out, att_, B, y_);
+    p.out_fp32 = true; p.residual = y_; p.ldr = d; p.res_fp32 = true;
+    gemm<T>(p, s);
+
+    layernorm<T>(y_, e.ln2_g, e.ln2_b, n_, B, d, 1e-5f, s);
+    p = lin(e.c_q, n_, B, qc_);
+    p.rowbias = e.rb_c_q; p.rowbias_dyn = step_;
+    gemm<T>(p, s);
+    decode_attention<T>(qc_, d, nullptr, 0, ckv_[l], 2 * d, (int64_t)S * 2 * d, att_, d, B, H, d, S, nullptr, tok_mask_,
+                        S, s);
+    p = lin(e.c_out, att_, B, y_);
+    p.out_fp32 = true; p.residual = y_; p.ldr = d; p.res_fp32 = true;
+    gemm<T>(p, s);
+
+    layernorm<T>(y_, e.ln3_g, e.ln3_b, n_, B, d, 1e-5f, s);
+    p = lin(e.ff1, n_, B, h_);
+    p.relu = 1;
+    gemm<T>(p, s);
+    p = lin(e.ff2, h_, B, y_);
+    p.out_fp32 = true; p.residual = y_; p.ldr = d; p.res_fp32 = true;
+    gemm<T>(p, s);
+  }
+  layernorm<T>(y_, dec_norm_g_, dec_norm_b_, hs_, B, d, 1e-5f, s);
+  GemmParams p = lin(mlp_[0], hs_, B, m1_); p.relu = 1; gemm<T>(p, s);
+  p = lin(mlp_[1], m1_, B, m2_); p.relu = 1; gemm<T>(p, s);
+  p = lin(mlp_[2], m2_, B, nullptr); p.argmax_out = argmax_keys_; gemm<T>(p, s);     // logits never reach HBM
+  greedy_update(argmax_keys_, caption_, max_len, B, eos, step_, done_, finished_, s);
+}
+
+template <typename T>
+void EngineT<T>::decode_greedy(int bos, int eos, int max_len, int64_t* out_ids, int* steps_host, cudaStream_t s) {
+  RETR_CHECK(cur_B_ > 0, "retr_encode must run before the decoder");
+  RETR_CHECK(max_len >= 2 && max_len <= desc.max_pos, "max_len must be in [2, max_position_embeddings]");
+  const int B = cur_B_;
+  const long long l0 = g_launches;
+  greedy_init(caption_, max_len, B, bos, step_, done_, finished_, argmax_keys_, s);
+  const bool use_graph = getenv("RETR_NO_GRAPH") == nullptr;
+  cudaGraphExec_t exec = nullptr;
+  long long per_step = 0;
+  if (use_graph) {
+    auto key = std::make_tuple(B, eos, max_len);
+    auto it = graphs_.find(key);
+    if (it == graphs_.end()) {
+      cudaGraph_t graph;
+      const long long c0 = g_launches;
+      CUDA_OK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+      try {
+        decode_step(B, eos, max_len, s);
+      } catch (...) {
+        cudaGraph_t junk; cudaStreamEndCapture(s, &junk);
+        throw;
+      }
+      CUDA_OK(cudaStreamEndCapture(s, &graph));
+      CUDA_OK(cudaGraphInstantiate(&exec, graph, 0));
+      CUDA_OK(cudaGraphDestroy(graph));
+      graphs_[key] = exec;
+      step_kernels_ = g_launches - c0;
+      g_launches = c0;                       // capture is not execution
+    } else {
+      exec = it->second;
+    }
+    per_step = step_kernels_;
+  }
+  CUDA_OK(cudaEventRecord(ev_[2], s));
+  // Launch in chunks; poll the device-side done flag one chunk behind so the queue never drains.
+  const int total = max_len - 1, chunk = 16;
+  int launched = 0;
+  bool stop = false;
+  cudaEvent_t polled = ev_[3];
+  bool poll_pending = false;
+  while (launched < total && !stop) {
+    const int n = std::min(chunk, total - launched);
+    for (int i = 0; i < n; ++i) {
+      if (use_graph) { CUDA_OK(cudaGraphLaunch(exec, s)); g_launches += per_step; }
+      else decode_step(B, eos, max_len, s);
+    }
+    launched += n;
+    if (poll_pending) {
+      CUDA_OK(cudaEventSynchronize(polled));
+      if (done_host_[0]) stop = true;
+    }
+    CUDA_OK(cudaMemcpyAsync(done_host_, done_, 4, cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaEventRecord(polled, s));
+    poll_pending = true;
+  }
+  CUDA_OK(cudaMemcpyAsync(out_ids, caption_, (int64_t)B * max_len * 8, cudaMemcpyDeviceToDevice, s));
+  CUDA_OK(cudaMemcpyAsync(done_host_ + 1, step_, 4, cudaMemcpyDeviceToHost, s));
+  CUDA_OK(cudaEventRecord(polled, s));
+  CUDA_OK(cudaEventSynchronize(polled));
+  if (steps_host) *steps_host = done_host_[1];
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, ev_[0], ev_[1]) == cudaSuccess) phase_ms[0] = ms;
+  if (cudaEventElapsedTime(&ms, ev_[1], ev_[2]) == cudaSuccess) phase_ms[1] = ms;
+  if (cudaEventElapsedTime(&ms, ev_[2], polled) == cudaSuccess) phase_ms[2] = ms;
+  cudaGetLastError();
+  launches += g_launches - l0;
+}
+
+template <typename T>
+void EngineT<T>::read_state(const std::string& what, void* dst, int64_t bytes, cudaStream_t s) {
+  RETR_CHECK(cur_B_ > 0, "nothing encoded yet");
+  const int64_t B = cur_B_, d = desc.d_model, g2 = (int64_t)grid_hw * grid_hw, cfeat = blocks_.back().c3.cout;
+  auto conv_out = [&](const T* src, int64_t n) {
+    RETR_CHECK(bytes >= n * 4, "destination too small for '" + what + "'");
+    to_f32_kernel<T><<<(unsigned)cdiv(n, 256), 256, 0, s>>>(src, static_cast<float*>(dst), n);
+    LAUNCH_OK();
+  };
+  if (what == "memory") conv_out(memory_, B * S * d);
+  else if (what == "feat_t") conv_out(feat_, B * g2 * cfeat);
+  else if (what == "feat_g") { RETR_CHECK(desc.n_images == 2, "no context images"); conv_out(feat_ + B * g2 * cfeat, B * g2 * cfeat); }
+  else if (what == "src") {
+    RETR_CHECK(bytes >= B * S * d * 4, "destination too small for 'src'");
+    CUDA_OK(cudaMemcpyAsync(dst, src_copy_, B * S * d * 4, cudaMemcpyDeviceToDevice, s));
+  } else if (what == "mask") {
+    RETR_CHECK(bytes >= B * S, "destination too small for 'mask'");
+    CUDA_OK(cudaMemcpyAsync(dst, tok_mask_, B * S, cudaMemcpyDeviceToDevice, s));
+  } else {
+    throw Error("unknown state '" + what + "'");
+  }
+}
+
+}  // namespace
+
+std::unique_ptr<EngineBase> make_engine(const retr_model_desc& d) {
+  if (d.precision == RETR_FP32) return std::unique_ptr<EngineBase>(new EngineT<float>(d));
+  if (d.precision == RETR_BF16) {
+    CUDA_OK(cudaSetDevice(d.device));
+    gemm_bf16_prepare();
+    return std::unique_ptr<EngineBase>(new EngineT<bf16>(d));
+  }
+  throw Error("unknown precision");
+}
+
+}  // namespace retr

@@ -1,0 +1,63 @@
+// Native runtime of the RE⫶TR hot path: owns repacked weights, activation buffers, the K/V
+// caches and the captured decode-step CUDA graph; schedules every kernel of encode / teacher-
+// forced forward / greedy decode.  One Engine per (device, model); see include/retr_b200.h.
+#pragma once
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/retr_b200.h"
+#include "gemm.h"
+#include "ops.h"
+
+namespace retr {
+
+struct RawWeight {
+  float* dev = nullptr;
+  std::vector<int64_t> shape;
+  int64_t numel = 0;
+};
+
+class EngineBase {
+ public:
+  explicit EngineBase(const retr_model_desc& d);
+  virtual ~EngineBase();
+  void load_weight(const std::string& name, const float* data, const int64_t* shape, int ndim, bool on_device);
+  virtual void finalize() = 0;
+  virtual void encode(int B, const float* t_img, const uint8_t* t_mask, const float* g_img, const uint8_t* g_mask,
+                      const float* loc, cudaStream_t s) = 0;
+  virtual void teacher_forced(const int64_t* ids, const uint8_t* id_mask, float* logits, float* att_self,
+                              float* att_cross, cudaStream_t s) = 0;
+  virtual void decode_greedy(int bos, int eos, int max_len, int64_t* out_ids, int* steps_host, cudaStream_t s) = 0;
+  virtual void read_state(const std::string& what, void* dst, int64_t bytes, cudaStream_t s) = 0;
+  void generate_host(int B, const float* t_img, const uint8_t* t_mask, const float* g_img, const uint8_t* g_mask,
+                     const float* loc, int bos, int eos, int max_len, int64_t* out_ids, int* steps_host,
+                     cudaStream_t s);
+
+  retr_model_desc desc;
+  int S = 0;              // encoder tokens per sample
+  int grid_hw = 0;        // backbone output side (14 with dilation at 224)
+  int n_loc_tok = 0;
+  long long launches = 0;
+  float phase_ms[3] = {0, 0, 0};
+  float* att_enc_capture = nullptr;
+
+ protected:
+  void* dalloc(size_t bytes);
+  const RawWeight& raw(const std::string& name) const;
+  std::map<std::string, RawWeight> raw_;
+  std::vector<void*> owned_;
+  // host->device staging for generate_host
+  float *st_t_img = nullptr, *st_g_img = nullptr, *st_loc = nullptr;
+  uint8_t *st_t_mask = nullptr, *st_g_mask = nullptr;
+  int64_t* st_ids = nullptr;
+  cudaEvent_t ev_[4] = {nullptr, nullptr, nullptr, nullptr};
+  bool finalized_ = false;
+  int cur_B_ = 0;         // batch of the last encode
+};
+
+std::unique_ptr<EngineBase> make_engine(const retr_model_desc& d);
+void gemm_bf16_prepare();   // gemm_sm100.cu: set kernel attributes outside any stream capture
+
+}  // namespace retr

@@ -1,0 +1,45 @@
+// GEMM / implicit-GEMM convolution with fused epilogue — shared parameter block.
+//   C[M,N] = epi( A[M,K] · W[N,K]^T )      A, W K-major (row-major, K contiguous)
+//   epi(acc) = relu?( acc*scale[n] + bias[n] + rowbias[m % period][n] ) + residual[m][n]
+// (ReLU is applied AFTER the residual add when relu == 2: the Bottleneck tail
+//  relu(bn3(conv3) + identity), torchvision/models/resnet.py:160-163.)
+#pragma once
+#include "common.cuh"
+
+namespace retr {
+
+struct ConvView {        // implicit-GEMM view of an NHWC activation as A; kh == 0 -> plain matrix
+  int kh = 0, kw = 0, stride = 1, pad = 0, dil = 1;
+  int H = 0, W = 0, C = 0, OH = 0, OW = 0;
+};
+
+struct GemmParams {
+  const void* A = nullptr;      // fp32 or bf16
+  const void* W = nullptr;      // same type as A, [N,K]
+  void* C = nullptr;            // out_fp32 ? float : A's type; may be null with argmax_out
+  int64_t M = 0;
+  int N = 0, K = 0;
+  int64_t lda = 0, ldc = 0;
+  const float* scale = nullptr;
+  const float* bias = nullptr;
+  const float* rowbias = nullptr;
+  int rowbias_period = 1;
+  const void* residual = nullptr;
+  int64_t ldr = 0;
+  bool res_fp32 = false;
+  int relu = 0;                 // 0 none, 1 before residual, 2 after residual
+  bool out_fp32 = false;
+  ConvView conv;
+  unsigned long long* argmax_out = nullptr;
+  // C row remap: out_row = (m / c_group) * c_group_stride + (m % c_group)   (0 = identity).
+  // Lets input_proj write image tokens straight into the concatenated [B,S,d] buffer.
+  int c_group = 0, c_group_stride = 0;
+  // If set, every row uses rowbias[*rowbias_dyn] (decode: the device-side step counter).
+  const int* rowbias_dyn = nullptr;
+};
+
+void gemm_fp32(const GemmParams& p, cudaStream_t stream);   // gemm_simt.cu  (A, W fp32)
+void gemm_bf16(const GemmParams& p, cudaStream_t stream);   // gemm_sm100.cu (A, W bf16, tcgen05)
+int  sm_count();
+
+}  // namespace retr

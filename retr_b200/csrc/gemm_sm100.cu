@@ -1,0 +1,430 @@
+// tcgen05 / TMA GEMM and implicit-GEMM convolution for sm_100a (bf16 in, fp32 accumulate in TMEM).
+//
+// Persistent, warp-specialised, one CTA per SM:
+//   warp 0      TMA producer      W tile (and the A tile for a plain matrix) -> 128B-swizzled smem
+//   warp 1      MMA issuer        one thread issues tcgen05.mma (M=128, N=BN, K=16) x4 per k-block
+//   warp 2      TMEM allocator    2 accumulator stages x BN columns
+//   warps 4-7   epilogue          tcgen05.ld -> scale/bias/rowbias/ReLU/residual/argmax -> global
+//   warps 8-11  A gather          (convolution only) cp.async im2col rows with zero fill, written
+//                                 in the same swizzled layout TMA would produce
+// Pipelines: smem full/empty ring (TMA|gather -> MMA), TMEM full/empty pair (MMA -> epilogue) so the
+// epilogue of tile i overlaps the main loop of tile i+1.
+//
+// Replaces, on the reference's path: every nn.Conv2d of the torchvision ResNet body with its
+// FrozenBatchNorm2d/ReLU/residual (models/backbone.py:41-51,69; torchvision/models/resnet.py:143-165),
+// input_proj (models/caption.py:119), all nn.Linear / MHA in/out projections
+// (models/transformer_modules.py:8-10,19; torch/nn/functional.py:5798-5860) and the MLP head
+// (models/caption.py:161-174).
+#include <cudaTypedefs.h>
+
+#include "engine.h"
+#include "gemm.h"
+#include "sm100_ptx.cuh"
+
+namespace retr {
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;                 // 64 bf16 = 128 B = one swizzle row
+constexpr int A_TILE_BYTES = BM * BK * 2;
+constexpr int GATHER_LAG = 2;          // cp.async groups kept in flight per gather thread
+
+struct KArgs {
+  int64_t M;
+  int N, K, num_kb, m_tiles, n_tiles;
+  void* C;
+  int64_t ldc;
+  int out_fp32;
+  const float* scale;
+  const float* bias;
+  const float* rowbias;
+  int rowbias_period;
+  const void* residual;
+  int64_t ldr;
+  int res_fp32, relu;
+  int vecC, vecR, vecRB;
+  unsigned long long* argmax_out;
+  const bf16* A;
+  int kh, kw, stride, pad, dil, H, W, Cin, OH, OW, cblocks;
+  int c_group, c_group_stride;
+  const int* rowbias_dyn;
+};
+
+template <int BN> struct Cfg {
+  static constexpr int B_TILE_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
+  static constexpr int STAGES = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+// One 32-column chunk of one accumulator row.
+__device__ __forceinline__ void epilogue_chunk(const KArgs& a, uint32_t (&r)[32], int64_t m, int64_t mc,
+                                               int64_t rb_row, int n0, float& best_v, uint32_t& best_i) {
+  const int nv = min(32, a.N - n0);
+  float v[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+  if (a.scale) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) if (j < nv) v[j] *= __ldg(a.scale + n0 + j);
+  }
+  if (a.bias) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) if (j < nv) v[j] += __ldg(a.bias + n0 + j);
+  }
+  if (a.rowbias) {
+    const float* rb = a.rowbias + rb_row * a.N + n0;
+    if (a.vecRB && nv == 32) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float4 t = __ldg(reinterpret_cast<const float4*>(rb) + j);
+        v[4 * j] += t.x; v[4 * j + 1] += t.y; v[4 * j + 2] += t.z; v[4 * j + 3] += t.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) if (j < nv) v[j] += __ldg(rb + j);
+    }
+  }
+  if (a.relu == 1) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+  }
+  if (a.residual) {
+    if (a.res_fp32) {
+      const float* rp = static_cast<const float*>(a.residual) + m * a.ldr + n0;
+      if (a.vecR && nv == 32) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float4 t = *(reinterpret_cast<const float4*>(rp) + j);
+          v[4 * j] += t.x; v[4 * j + 1] += t.y; v[4 * j + 2] += t.z; v[4 * j + 3] += t.w;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (j < nv) v[j] += rp[j];
+      }
+    } else {
+      const bf16* rp = static_cast<const bf16*>(a.residual) + m * a.ldr + n0;
+      if (a.vecR && nv == 32) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint4 t = *(reinterpret_cast<const uint4*>(rp) + j);
+          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&t);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            float2 f = __bfloat1622float2(h[q]);
+            v[8 * j + 2 * q] += f.x; v[8 * j + 2 * q + 1] += f.y;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (j < nv) v[j] += __bfloat162float(rp[j]);
+      }
+    }
+  }
+  if (a.relu == 2) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+  }
+  if (a.argmax_out) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (j < nv && v[j] > best_v) { best_v = v[j]; best_i = (uint32_t)(n0 + j); }
+  }
+  if (a.C) {
+    if (a.out_fp32) {
+      float* cp = static_cast<float*>(a.C) + mc * a.ldc + n0;
+      if (a.vecC && nv == 32) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *(reinterpret_cast<float4*>(cp) + j) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (j < nv) cp[j] = v[j];
+      }
+    } else {
+      bf16* cp = static_cast<bf16*>(a.C) + mc * a.ldc + n0;
+      if (a.vecC && nv == 32) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint4 t;
+          __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&t);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) h[q] = __floats2bfloat162_rn(v[8 * j + 2 * q], v[8 * j + 2 * q + 1]);
+          *(reinterpret_cast<uint4*>(cp) + j) = t;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (j < nv) cp[j] = __float2bfloat16_rn(v[j]);
+      }
+    }
+  }
+}
+
+template <int BN, bool GATHER>
+__global__ void __launch_bounds__(GATHER ? 384 : 256, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const KArgs a) {
+  using C = Cfg<BN>;
+  constexpr int STAGES = C::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * C::STAGE_BYTES);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tfull = empty + STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int total_tiles = a.m_tiles * a.n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    if (!GATHER) ptx::prefetch_tmap(&tmA);
+    ptx::prefetch_tmap(&tmB);
+    for (int s = 0; s < STAGES; ++s) {
+      ptx::mbar_init(&full[s], GATHER ? 129 : 1);
+      ptx::mbar_init(&empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&tfull[s], 1);
+      ptx::mbar_init(&tempty[s], 128);
+    }
+    ptx::fence_barrier_init();
+  } else if (warp == 2) {
+    ptx::tmem_alloc(tmem_holder, C::TMEM_COLS);
+  }
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  ptx::tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_holder;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===== TMA producer =====
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int m_blk = tile / a.n_tiles, n_blk = tile - m_blk * a.n_tiles;
+        for (int kb = 0; kb < a.num_kb; ++kb, ++it) {
+          const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+          ptx::mbar_wait(&empty[s], ph ^ 1);
+          uint8_t* As = smem + s * C::STAGE_BYTES;
+          uint8_t* Bs = As + A_TILE_BYTES;
+          ptx::mbar_arrive_expect_tx(&full[s], C::B_TILE_BYTES + (GATHER ? 0 : A_TILE_BYTES));
+          if (!GATHER) ptx::tma_load_2d(As, &tmA, &full[s], kb * BK, m_blk * BM);
+          ptx::tma_load_2d(Bs, &tmB, &full[s], kb * BK, n_blk * BN);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ===== MMA issuer =====
+      constexpr uint32_t idesc = ptx::idesc_bf16_f32(BM, BN);
+      uint32_t it = 0, tcount = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+        const uint32_t as = tcount & 1, aph = (tcount >> 1) & 1;
+        ptx::mbar_wait(&tempty[as], aph ^ 1);
+        ptx::tc_fence_after_sync();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < a.num_kb; ++kb, ++it) {
+          const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+          ptx::mbar_wait(&full[s], ph);
+          ptx::tc_fence_after_sync();
+          const uint32_t a_addr = ptx::smem_u32(smem + s * C::STAGE_BYTES);
+          const uint32_t b_addr = a_addr + A_TILE_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            ptx::mma_bf16_ss(d_tmem, ptx::smem_desc_sw128(a_addr + k * 32),
+                             ptx::smem_desc_sw128(b_addr + k * 32), idesc, (kb | k) != 0);
+          }
+          ptx::mma_commit(&empty[s]);      // frees the smem slot when these MMAs retire
+        }
+        ptx::mma_commit(&tfull[as]);       // accumulator complete -> epilogue
+      }
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // ===== epilogue =====
+    const int q = warp & 3;
+    uint32_t tcount = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+      const int m_blk = tile / a.n_tiles, n_blk = tile - m_blk * a.n_tiles;
+      const uint32_t as = tcount & 1, aph = (tcount >> 1) & 1;
+      ptx::mbar_wait(&tfull[as], aph);
+      ptx::tc_fence_after_sync();
+      const int64_t m = (int64_t)m_blk * BM + q * 32 + lane;
+      float best_v = -INFINITY;
+      uint32_t best_i = 0;
+      const int64_t mc = a.c_group ? (m / a.c_group) * a.c_group_stride + (m % a.c_group) : m;
+      const int64_t rb_row = a.rowbias_dyn ? (int64_t)__ldg(a.rowbias_dyn) : (m % a.rowbias_period);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        const int n0 = n_blk * BN + c * 32;
+        if (n0 >= a.N) break;                       // warp-uniform
+        uint32_t r[32];
+        ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + c * 32, r);
+        ptx::tmem_ld_wait();
+        if (m < a.M) epilogue_chunk(a, r, m, mc, rb_row, n0, best_v, best_i);
+      }
+      ptx::tc_fence_before_sync();
+      ptx::mbar_arrive(&tempty[as]);
+      if (a.argmax_out && m < a.M && best_v > -INFINITY)
+        atomicMax(a.argmax_out + m, pack_argmax(best_v, best_i));
+    }
+  } else if (GATHER && warp >= 8) {
+    // ===== im2col gather producer: one thread per tile row =====
+    const int row = threadIdx.x - 256;
+    const uint32_t swz = (uint32_t)(row & 7);
+    uint32_t it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int m_blk = tile / a.n_tiles;
+      const int64_t m = (int64_t)m_blk * BM + row;
+      const bool valid_m = m < a.M;
+      const int ow = (int)(m % a.OW);
+      const int64_t t = m / a.OW;
+      const int oh = (int)(t % a.OH);
+      const int64_t img = t / a.OH;
+      const int ih0 = oh * a.stride - a.pad, iw0 = ow * a.stride - a.pad;
+      int tap = 0, cb = 0;
+      for (int kb = 0; kb < a.num_kb; ++kb, ++it) {
+        const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+        ptx::mbar_wait(&empty[s], ph ^ 1);
+        const int fr = tap / a.kw, fs = tap - fr * a.kw;
+        const int ih = ih0 + fr * a.dil, iw = iw0 + fs * a.dil;
+        const bool ok = valid_m && ih >= 0 && ih < a.H && iw >= 0 && iw < a.W;
+        const bf16* src = ok ? a.A + ((img * a.H + ih) * a.W + iw) * a.Cin + cb * BK : a.A;
+        const uint32_t dst = ptx::smem_u32(smem + s * C::STAGE_BYTES) + row * 128;
+        const uint32_t nbytes = ok ? 16u : 0u;
+#pragma unroll
+        for (uint32_t j = 0; j < 8; ++j) ptx::cp_async_16(dst + ((j ^ swz) << 4), src + j * 8, nbytes);
+        ptx::cp_async_commit();
+        if (it >= GATHER_LAG) {
+          ptx::cp_async_wait<GATHER_LAG>();
+          ptx::fence_proxy_async_smem();
+          ptx::mbar_arrive(&full[(it - GATHER_LAG) % STAGES]);
+        }
+        if (++cb == a.cblocks) { cb = 0; ++tap; }
+      }
+    }
+    ptx::cp_async_wait<0>();
+    ptx::fence_proxy_async_smem();
+    for (uint32_t j = (it > GATHER_LAG ? it - GATHER_LAG : 0); j < it; ++j) ptx::mbar_arrive(&full[j % STAGES]);
+  }
+
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 2) {
+    ptx::tc_fence_after_sync();
+    ptx::tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
+// ---- host side ------------------------------------------------------------------------------
+PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    CUDA_OK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres));
+    RETR_CHECK(p != nullptr && qres == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled not available");
+    fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+  }
+  return fn;
+}
+
+// 2-D bf16 tensor [rows, cols] with row pitch ld (elements); box {64, box_rows}, 128B swizzle.
+CUtensorMap make_tmap_2d(const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
+  CUtensorMap m;
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)(ld * 2)};
+  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  RETR_CHECK((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (ld * 2) % 16 == 0,
+             "TMA operand must be 16-byte aligned with a 16-byte multiple row pitch");
+  CUresult r = get_encode_fn()(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
+                               box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  RETR_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+  return m;
+}
+
+template <int BN, bool GATHER>
+void launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const KArgs& ka, int grid, cudaStream_t stream) {
+  auto kern = gemm_tcgen05_kernel<BN, GATHER>;
+  kern<<<grid, GATHER ? 384 : 256, Cfg<BN>::SMEM_BYTES, stream>>>(tmA, tmB, ka);
+  LAUNCH_OK();
+}
+
+}  // namespace
+
+template <int BN> static void prepare_bn() {
+  CUDA_OK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               Cfg<BN>::SMEM_BYTES));
+  CUDA_OK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               Cfg<BN>::SMEM_BYTES));
+}
+void gemm_bf16_prepare() {
+  prepare_bn<32>(); prepare_bn<64>(); prepare_bn<128>(); prepare_bn<256>();
+  get_encode_fn();
+}
+
+int sm_count() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    CUDA_OK(cudaGetDevice(&dev));
+    CUDA_OK(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+  }
+  return n;
+}
+
+void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
+  static bool prepared = false;
+  if (!prepared) { gemm_bf16_prepare(); prepared = true; }
+  RETR_CHECK(p.M > 0 && p.N > 0 && p.K > 0, "empty GEMM");
+  RETR_CHECK(p.K % 8 == 0, "K must be a multiple of 8 (16-byte rows)");
+  const bool gather = p.conv.kh > 0;
+  KArgs ka{};
+  ka.M = p.M; ka.N = p.N; ka.K = p.K;
+  ka.num_kb = (int)cdiv(p.K, BK);
+  ka.C = p.C; ka.ldc = p.ldc; ka.out_fp32 = p.out_fp32;
+  ka.scale = p.scale; ka.bias = p.bias; ka.rowbias = p.rowbias;
+  ka.rowbias_period = p.rowbias_period > 0 ? p.rowbias_period : 1;
+  ka.residual = p.residual; ka.ldr = p.ldr; ka.res_fp32 = p.res_fp32; ka.relu = p.relu;
+  ka.argmax_out = p.argmax_out;
+  ka.c_group = p.c_group; ka.c_group_stride = p.c_group_stride; ka.rowbias_dyn = p.rowbias_dyn;
+  const int64_t cbytes = p.out_fp32 ? 4 : 2, rbytes = p.res_fp32 ? 4 : 2;
+  ka.vecC = p.C && (reinterpret_cast<uintptr_t>(p.C) % 16 == 0) && (p.ldc * cbytes) % 16 == 0;
+  ka.vecR = p.residual && (reinterpret_cast<uintptr_t>(p.residual) % 16 == 0) && (p.ldr * rbytes) % 16 == 0;
+  ka.vecRB = p.rowbias && (reinterpret_cast<uintptr_t>(p.rowbias) % 16 == 0) && p.N % 4 == 0;
+  ka.A = static_cast<const bf16*>(p.A);
+  if (gather) {
+    const ConvView& c = p.conv;
+    RETR_CHECK(c.C % BK == 0, "implicit-GEMM conv needs C_in % 64 == 0");
+    RETR_CHECK(p.K == c.kh * c.kw * c.C, "conv K mismatch");
+    RETR_CHECK(p.M % ((int64_t)c.OH * c.OW) == 0, "conv M must be images*OH*OW");
+    ka.kh = c.kh; ka.kw = c.kw; ka.stride = c.stride; ka.pad = c.pad; ka.dil = c.dil;
+    ka.H = c.H; ka.W = c.W; ka.Cin = c.C; ka.OH = c.OH; ka.OW = c.OW; ka.cblocks = c.C / BK;
+  }
+  // tile width: widest that still leaves every SM a tile
+  const int sms = sm_count();
+  int bn = 256;
+  while (bn > 32 && (bn / 2 >= p.N || cdiv(p.M, BM) * cdiv(p.N, bn) < sms)) bn /= 2;
+  ka.m_tiles = (int)cdiv(p.M, BM);
+  ka.n_tiles = (int)cdiv(p.N, bn);
+  const int grid = (int)std::min<int64_t>((int64_t)ka.m_tiles * ka.n_tiles, sms);
+  CUtensorMap tmB = make_tmap_2d(p.W, p.N, p.K, p.K, bn);
+  CUtensorMap tmA = gather ? tmB : make_tmap_2d(p.A, p.M, p.K, p.lda, BM);
+#define RETR_LAUNCH(BN_)                                                   \
+  if (gather) launch<BN_, true>(tmA, tmB, ka, grid, stream);               \
+  else launch<BN_, false>(tmA, tmB, ka, grid, stream)
+  switch (bn) {
+    case 256: RETR_LAUNCH(256); break;
+    case 128: RETR_LAUNCH(128); break;
+    case 64: RETR_LAUNCH(64); break;
+    default: RETR_LAUNCH(32); break;
+  }
+#undef RETR_LAUNCH
+}
+
+}  // namespace retr

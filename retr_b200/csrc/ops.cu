@@ -1,0 +1,232 @@
+// HBM-bound helper kernels: weight repack, stem im2col, max-pool, masks, location tokens,
+// LayerNorm and decoder embeddings.  All are pure streaming kernels (no reuse), vectorised to
+// 16-byte accesses where the layout allows; grids are sized from the element count.
+#include "ops.h"
+
+namespace retr {
+namespace {
+
+inline unsigned blocks_for(int64_t n, int threads) { return (unsigned)cdiv(n, threads); }
+
+__global__ void f32_to_bf16_kernel(const float* __restrict__ src, bf16* __restrict__ dst, int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = __float2bfloat16_rn(src[i]);
+}
+
+template <typename T>
+__global__ void repack_filter_kernel(const float* __restrict__ w, T* __restrict__ out, int O, int I, int kh,
+                                     int kw, int kpad) {
+  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)O * kpad) return;
+  const int o = (int)(idx / kpad), k = (int)(idx % kpad);
+  float v = 0.f;
+  if (k < kh * kw * I) {
+    const int tap = k / I, c = k % I, r = tap / kw, s = tap % kw;
+    v = w[(((int64_t)o * I + c) * kh + r) * kw + s];
+  }
+  out[idx] = from_f<T>(v);
+}
+
+// Each thread produces 8 consecutive k of one output pixel.
+template <typename T>
+__global__ void stem_im2col_kernel(const float* __restrict__ img, T* __restrict__ out, int64_t rows, int H, int W,
+                                   int OH, int OW, int kpad) {
+  const int kchunks = kpad / 8;
+  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= rows * kchunks) return;
+  const int64_t m = idx / kchunks;
+  const int k0 = (int)(idx % kchunks) * 8;
+  const int ow = (int)(m % OW);
+  const int64_t t = m / OW;
+  const int oh = (int)(t % OH);
+  const int64_t n = t / OH;
+  const float* base = img + n * 3 * H * W;
+  float v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int k = k0 + j;
+    float x = 0.f;
+    if (k < 147) {
+      const int tap = k / 3, c = k - tap * 3, r = tap / 7, s = tap - r * 7;
+      const int ih = oh * 2 - 3 + r, iw = ow * 2 - 3 + s;
+      if (ih >= 0 && ih < H && iw >= 0 && iw < W) x = __ldg(base + ((int64_t)c * H + ih) * W + iw);
+    }
+    v[j] = x;
+  }
+  T* o = out + m * kpad + k0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) o[j] = from_f<T>(v[j]);
+}
+
+template <typename T>
+__global__ void maxpool_kernel(const T* __restrict__ in, T* __restrict__ out, int64_t total, int H, int W, int C,
+                               int OH, int OW) {
+  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // over (n, oh, ow, c)
+  if (idx >= total) return;
+  const int c = (int)(idx % C);
+  int64_t t = idx / C;
+  const int ow = (int)(t % OW); t /= OW;
+  const int oh = (int)(t % OH);
+  const int64_t n = t / OH;
+  float best = -INFINITY;
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const int ih = oh * 2 - 1 + r;
+    if (ih < 0 || ih >= H) continue;
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+      const int iw = ow * 2 - 1 + s;
+      if (iw < 0 || iw >= W) continue;
+      best = fmaxf(best, to_f(in[((n * H + ih) * W + iw) * C + c]));
+    }
+  }
+  out[idx] = from_f<T>(best);
+}
+
+__global__ void subsample_mask_kernel(const uint8_t* __restrict__ m, uint8_t* __restrict__ tok, int B, int H, int W,
+                                      int gh, int gw, int S, int off) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * gh * gw) return;
+  const int j = idx % gw, i = (idx / gw) % gh, b = idx / (gw * gh);
+  // nearest: src = floor(dst * in/out)  (torch upsample_nearest; exact for 224 -> 14)
+  const int si = min((int)floorf(i * ((float)H / gh)), H - 1);
+  const int sj = min((int)floorf(j * ((float)W / gw)), W - 1);
+  tok[(int64_t)b * S + off + i * gw + j] = m[((int64_t)b * H + si) * W + sj] ? 1 : 0;
+}
+
+__global__ void loc_tokens_kernel(const float* __restrict__ loc, const float* __restrict__ w,
+                                  const float* __restrict__ bias, float* __restrict__ x, uint8_t* __restrict__ tok,
+                                  int B, int n_loc, int per_scalar, int d, int S, int off) {
+  const int ntok = per_scalar ? n_loc : 1;
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * ntok * d) return;
+  const int c = idx % d, k = (idx / d) % ntok, b = idx / (d * ntok);
+  float v = bias[c];
+  if (per_scalar) {
+    v = fmaf(loc[b * n_loc + k], w[c], v);               // Linear(1, d): weight [d,1]
+  } else {
+    for (int i = 0; i < n_loc; ++i) v = fmaf(loc[b * n_loc + i], w[c * n_loc + i], v);
+  }
+  x[((int64_t)b * S + off + k) * d + c] = v;
+  if (c == 0) tok[(int64_t)b * S + off + k] = 0;
+}
+
+// One warp per row; d <= 1024 (each lane holds d/32 values, d % 32 == 0).
+template <typename T, int MAXPER>
+__device__ __forceinline__ void ln_row(float (&v)[MAXPER], int per, int lane, const float* __restrict__ gamma,
+                                       const float* __restrict__ beta, T* __restrict__ y, int d, float eps) {
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXPER; ++i) if (i < per) s += v[i];
+  const float mean = warp_sum(s) / d;
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXPER; ++i) if (i < per) { const float t = v[i] - mean; q = fmaf(t, t, q); }
+  const float rstd = rsqrtf(warp_sum(q) / d + eps);
+#pragma unroll
+  for (int i = 0; i < MAXPER; ++i)
+    if (i < per) {
+      const int c = i * 32 + lane;
+      y[c] = from_f<T>((v[i] - mean) * rstd * gamma[c] + beta[c]);
+    }
+}
+
+template <typename T>
+__global__ void layernorm_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                 const float* __restrict__ beta, T* __restrict__ y, int64_t rows, int d, float eps) {
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31, per = d >> 5;
+  float v[32];
+  const float* xr = x + row * d;
+#pragma unroll
+  for (int i = 0; i < 32; ++i) if (i < per) v[i] = xr[i * 32 + lane];
+  ln_row<T, 32>(v, per, lane, gamma, beta, y + row * d, d, eps);
+}
+
+__global__ void embed_ln_kernel(const int64_t* __restrict__ ids, int64_t ld_ids, const float* __restrict__ e_word,
+                                const float* __restrict__ e_pos, const float* __restrict__ gamma,
+                                const float* __restrict__ beta, float* __restrict__ y, int B, int rows_per, int t0,
+                                const int* __restrict__ t0_dyn, int d, float eps) {
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= (int64_t)B * rows_per) return;
+  if (t0_dyn) t0 = *t0_dyn;
+  const int b = (int)(row / rows_per), t = t0 + (int)(row % rows_per);
+  const int lane = threadIdx.x & 31, per = d >> 5;
+  const int64_t id = ids[b * ld_ids + t];
+  const float* we = e_word + id * d;
+  const float* pe = e_pos + (int64_t)t * d;
+  float v[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) if (i < per) v[i] = we[i * 32 + lane] + pe[i * 32 + lane];
+  ln_row<float, 32>(v, per, lane, gamma, beta, y + row * d, d, eps);
+}
+
+}  // namespace
+
+void f32_to_bf16(const float* src, bf16* dst, int64_t n, cudaStream_t s) {
+  f32_to_bf16_kernel<<<blocks_for(n, 256), 256, 0, s>>>(src, dst, n);
+  LAUNCH_OK();
+}
+
+template <typename T>
+void repack_filter(const float* oihw, T* out, int O, int I, int kh, int kw, int kpad, cudaStream_t s) {
+  repack_filter_kernel<T><<<blocks_for((int64_t)O * kpad, 256), 256, 0, s>>>(oihw, out, O, I, kh, kw, kpad);
+  LAUNCH_OK();
+}
+template void repack_filter<float>(const float*, float*, int, int, int, int, int, cudaStream_t);
+template void repack_filter<bf16>(const float*, bf16*, int, int, int, int, int, cudaStream_t);
+
+template <typename T>
+void stem_im2col(const float* img, T* out, int64_t nimg, int H, int W, int OH, int OW, int kpad, cudaStream_t s) {
+  RETR_CHECK(kpad % 8 == 0 && kpad >= 147, "stem kpad");
+  const int64_t rows = nimg * OH * OW;
+  stem_im2col_kernel<T><<<blocks_for(rows * (kpad / 8), 256), 256, 0, s>>>(img, out, rows, H, W, OH, OW, kpad);
+  LAUNCH_OK();
+}
+template void stem_im2col<float>(const float*, float*, int64_t, int, int, int, int, int, cudaStream_t);
+template void stem_im2col<bf16>(const float*, bf16*, int64_t, int, int, int, int, int, cudaStream_t);
+
+template <typename T>
+void maxpool_3x3s2(const T* in, T* out, int64_t nimg, int H, int W, int C, int OH, int OW, cudaStream_t s) {
+  const int64_t total = nimg * OH * OW * C;
+  maxpool_kernel<T><<<blocks_for(total, 256), 256, 0, s>>>(in, out, total, H, W, C, OH, OW);
+  LAUNCH_OK();
+}
+template void maxpool_3x3s2<float>(const float*, float*, int64_t, int, int, int, int, int, cudaStream_t);
+template void maxpool_3x3s2<bf16>(const bf16*, bf16*, int64_t, int, int, int, int, int, cudaStream_t);
+
+void subsample_mask(const uint8_t* img_mask, uint8_t* tok_mask, int B, int H, int W, int gh, int gw, int S, int off,
+                    cudaStream_t s) {
+  subsample_mask_kernel<<<blocks_for((int64_t)B * gh * gw, 256), 256, 0, s>>>(img_mask, tok_mask, B, H, W, gh, gw, S, off);
+  LAUNCH_OK();
+}
+
+void loc_tokens(const float* loc, const float* w, const float* bias, float* x, uint8_t* tok_mask, int B, int n_loc,
+                int per_scalar, int d, int S, int off, cudaStream_t s) {
+  const int ntok = per_scalar ? n_loc : 1;
+  loc_tokens_kernel<<<blocks_for((int64_t)B * ntok * d, 256), 256, 0, s>>>(loc, w, bias, x, tok_mask, B, n_loc,
+                                                                            per_scalar, d, S, off);
+  LAUNCH_OK();
+}
+
+template <typename T>
+void layernorm(const float* x, const float* gamma, const float* beta, T* y, int64_t rows, int d, float eps,
+               cudaStream_t s) {
+  RETR_CHECK(d % 32 == 0 && d <= 1024, "LayerNorm width must be a multiple of 32, <= 1024");
+  layernorm_kernel<T><<<blocks_for(rows, 8), 256, 0, s>>>(x, gamma, beta, y, rows, d, eps);
+  LAUNCH_OK();
+}
+template void layernorm<float>(const float*, const float*, const float*, float*, int64_t, int, float, cudaStream_t);
+template void layernorm<bf16>(const float*, const float*, const float*, bf16*, int64_t, int, float, cudaStream_t);
+
+void embed_ln(const int64_t* ids, int64_t ld_ids, const float* e_word, const float* e_pos, const float* gamma,
+              const float* beta, float* y, int B, int rows_per, int t0, const int* t0_dyn, int d, float eps,
+              cudaStream_t s) {
+  RETR_CHECK(d % 32 == 0 && d <= 1024, "embedding width");
+  embed_ln_kernel<<<blocks_for((int64_t)B * rows_per, 8), 256, 0, s>>>(ids, ld_ids, e_word, e_pos, gamma, beta, y, B,
+                                                                       rows_per, t0, t0_dyn, d, eps);
+  LAUNCH_OK();
+}
+
+}  // namespace retr

@@ -1,0 +1,66 @@
+// Non-GEMM kernels of the hot path (ops.cu, attention.cu, decode_ops.cu).
+#pragma once
+#include "common.cuh"
+
+namespace retr {
+
+// ---- weight repack ------------------------------------------------------------------------
+void f32_to_bf16(const float* src, bf16* dst, int64_t n, cudaStream_t s);
+// conv filter OIHW fp32 -> O,(H,W,I) rows of length kpad (zero padded), fp32 or bf16
+template <typename T>
+void repack_filter(const float* oihw, T* out, int O, int I, int kh, int kw, int kpad, cudaStream_t s);
+
+// ---- backbone -----------------------------------------------------------------------------
+// 7x7/2 pad 3 stem patches: NCHW fp32 image -> rows [(n,oh,ow)] x kpad, k = (r*7+s)*3+c
+template <typename T>
+void stem_im2col(const float* img, T* out, int64_t nimg, int H, int W, int OH, int OW, int kpad, cudaStream_t s);
+// 3x3/2 pad 1 max pool, NHWC
+template <typename T>
+void maxpool_3x3s2(const T* in, T* out, int64_t nimg, int H, int W, int C, int OH, int OW, cudaStream_t s);
+
+// ---- token assembly (models/caption.py:119-147, models/ConcatTransformer.py:48-51) ------------
+// mask[b, off + p] = img_mask[b, floor(i*H/gh), floor(j*W/gw)]  (F.interpolate nearest, backbone.py:75)
+void subsample_mask(const uint8_t* img_mask, uint8_t* tok_mask, int B, int H, int W, int gh, int gw,
+                    int S, int off, cudaStream_t s);
+// location tokens: per_scalar ? x[b,off+k,:] = w[:,0]*loc[b,k]+bias  (Linear(1,d), caption.py:126-127)
+//                             : x[b,off,:]   = w[:, :n_loc] . loc[b,:] + bias (Linear(7,d), caption.py:78)
+void loc_tokens(const float* loc, const float* w, const float* bias, float* x, uint8_t* tok_mask, int B,
+                int n_loc, int per_scalar, int d, int S, int off, cudaStream_t s);
+
+// ---- transformer pieces -------------------------------------------------------------------------
+// y[r,:] = LN(x[r,:]) ; x fp32, y fp32|bf16
+template <typename T>
+void layernorm(const float* x, const float* gamma, const float* beta, T* y, int64_t rows, int d, float eps,
+               cudaStream_t s);
+// y[b*rows_per+j, :] = LN_eps(E_word[ids[b*ld_ids + t0 + j]] + E_pos[t0 + j]); t0 = t0_dyn ? *t0_dyn : t0
+// (DecoderEmbeddings, models/transformer_modules.py:113-129)
+void embed_ln(const int64_t* ids, int64_t ld_ids, const float* e_word, const float* e_pos, const float* gamma,
+              const float* beta, float* y, int B, int rows_per, int t0, const int* t0_dyn, int d, float eps,
+              cudaStream_t s);
+
+// ---- attention (attention.cu) ---------------------------------------------------------------------
+struct AttnParams {
+  const void* q; const void* k; const void* v; void* out;
+  int B, Lq, Lk, H;
+  int64_t ldq, ldk, ldv, ldo;               // row pitches (elements); batch pitch = L * ld
+  const uint8_t* key_pad;                   // [B,Lk] non-zero = masked, or null
+  int causal;
+  float* probs;                             // optional [B,Lq,Lk] head-averaged probabilities
+};
+template <typename T> void attention(const AttnParams& p, cudaStream_t s);
+
+// ---- greedy decode (decode_ops.cu) --------------------------------------------------------------
+// Single-query attention over a K/V cache of rows [K(d) | V(d)] (pitch ldkv), one CTA per (b, head).
+//   self: appends this step's k,v (from qkv rows [q|k|v]) at position *step, attends keys 0..*step
+//   cross: attends keys 0..n_keys-1 honouring key_pad
+template <typename T>
+void decode_attention(const T* q, int64_t ldq, const T* new_kv, int64_t ld_new, T* cache, int64_t ld_cache,
+                      int64_t cache_batch_pitch, T* out, int64_t ldo, int B, int H, int d, int n_keys,
+                      const int* step_dyn, const uint8_t* key_pad, int64_t ld_pad, cudaStream_t s);
+// After the vocab GEMM+argmax of step i=*step: the bookkeeping of eval_utils/decode.py:70-79.
+void greedy_update(unsigned long long* argmax_keys, int64_t* caption, int max_len, int B, int eos, int* step,
+                   int* done, uint8_t* finished, cudaStream_t s);
+void greedy_init(int64_t* caption, int max_len, int B, int bos, int* step, int* done, uint8_t* finished,
+                 unsigned long long* argmax_keys, cudaStream_t s);
+
+}  // namespace retr

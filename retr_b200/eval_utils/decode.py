@@ -1,0 +1,77 @@
+"""Greedy decoding with the reference's signatures (eval_utils/decode.py).
+
+``greedy`` keeps the reference contract — ``samples`` tuple + an opaque ``model`` callable in,
+``[B, max_len]`` int64 ids on ``device`` out, identical early-return semantics — but when the
+model is a retr_b200 caption model the whole loop runs device-resident: encode once, then
+``max_len-1`` KV-cached single-token steps replayed from one captured CUDA graph, instead of
+re-running the full model (both ResNet passes included) per token (reference
+eval_utils/decode.py:68-79).  A foreign callable gets the literal per-token loop.
+"""
+import torch
+
+from ..models.caption import _CaptionBase
+
+
+def create_caption_and_mask(start_token, max_length, batch_size=1):
+    """BOS-initialised id buffer and its padding mask (True = not yet written).
+    reference eval_utils/decode.py:20-27."""
+    caption = torch.zeros((batch_size, max_length), dtype=torch.long)
+    mask = torch.ones((batch_size, max_length), dtype=torch.bool)
+    caption[:, 0] = start_token
+    mask[:, 0] = False
+    return caption, mask
+
+
+def _literal_greedy(samples, model, max_len, device, bos_token, eos_token):
+    caption, cap_mask = create_caption_and_mask(bos_token, max_len, samples[0].shape[0])
+    samples = [s.to(device) for s in samples]
+    caption, cap_mask = caption.to(device), cap_mask.to(device)
+    finished = torch.zeros(caption.shape[0], dtype=torch.bool, device=device)
+    for i in range(max_len - 1):
+        ids = model(*samples, caption, cap_mask)[:, i, :].argmax(dim=-1)
+        finished |= ids == eos_token
+        if bool(finished.all()):
+            break
+        caption[:, i + 1] = ids
+        cap_mask[:, i + 1] = False
+    return caption
+
+
+def greedy(samples, model, max_len=20, device="auto", bos_token=1, eos_token=2):
+    """Batch greedy decoding — reference eval_utils/decode.py:53-81."""
+    if device == "auto":
+        device = "cuda" if torch.cuda.is_available() else "cpu"
+    if isinstance(model, _CaptionBase):
+        if torch.device(device).type != "cuda":
+            raise RuntimeError("retr_b200 models decode on a CUDA device only (no CPU path)")
+        samples = [s.to(device) for s in samples]
+        ids, _steps = model.greedy_native(samples, max_len, bos_token, eos_token)
+        return ids
+    return _literal_greedy(samples, model, max_len, device, bos_token, eos_token)
+
+
+def prune_cap_ids(idx_seqs, clean=True, pad_token=0, bos_token=1, eos_token=2):
+    """Cut each row after its first EOS; ``clean`` drops every pad/bos/eos id.
+    reference eval_utils/decode.py:84-101."""
+    special = (pad_token, bos_token, eos_token)
+    out = []
+    for seq in idx_seqs:
+        seq = list(seq)
+        if eos_token in seq:
+            seq = seq[:seq.index(eos_token) + 1]
+        out.append([t for t in seq if t not in special] if clean else seq)
+    return out
+
+
+def idx2sents(idx_seqs, tokenizer, skip_special_tokens=True):
+    """reference eval_utils/decode.py:104-109."""
+    return tokenizer.batch_decode(idx_seqs, skip_special_tokens=skip_special_tokens)
+
+
+def greedy_decoding(samples, model, tokenizer, max_len=20, clean=True, pad_token=0, bos_token=1,
+                    eos_token=2, device="auto"):
+    """ids -> pruned ids -> strings; reference eval_utils/decode.py:112-128."""
+    ids = greedy(samples, model, max_len=max_len, bos_token=bos_token, eos_token=eos_token, device=device)
+    rows = ids.cpu().numpy().tolist()
+    return idx2sents(prune_cap_ids(rows, clean=clean, pad_token=pad_token, bos_token=bos_token,
+                                   eos_token=eos_token), tokenizer)

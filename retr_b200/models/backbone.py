@@ -115,6 +115,7 @@ class Backbone(nn.Module):
         self.body = ResNetBody(blocks, dilation)
         self.num_channels = 2048
         self.arch = name
+        self.dilation = bool(dilation)
         for pname, p in self.body.named_parameters():
             if not train_backbone or not any(f"layer{i}" in pname for i in (2, 3, 4)):
                 p.requires_grad_(False)

@@ -48,28 +48,36 @@ class _CaptionBase(nn.Module):
         self.mlp = MLP(hidden_dim, 512, vocab_size, 3)
         self._engine = None
         self.precision = "bf16"
+        self.max_batch = 8                # initial context capacity; grows on demand
+        self.backbone_stride = 16
         self.layer_norm_eps = 1e-12
         self.pre_norm = True
 
     # ---- native runtime ------------------------------------------------------------------
-    def engine(self, device=None):
-        """The native context bound to this model (created on first use)."""
+    def engine(self, batch=1):
+        """The native context bound to this model (created on first use, rebuilt when the
+        parameters moved/changed or a larger batch arrives)."""
         from ..runtime import Engine
-        if device is None:
-            device = next(self.parameters()).device
-        device = torch.device(device)
+        device = next(self.parameters()).device
         if device.type != "cuda":
             raise RuntimeError(
                 "retr_b200 runs only on a CUDA device (B200, sm_100a): model parameters are on "
                 f"{device}. Call model.to('cuda') first; there is no CPU path.")
-        if self._engine is None or self._engine.device != device or \
-                self._engine.precision != self.precision:
-            self._engine = Engine(self, device, self.precision)
+        eng = self._engine
+        stale = (eng is None or eng.device != device or eng.precision != self.precision
+                 or eng.max_batch < batch or eng.weights_version != Engine.version_of(self))
+        if stale:
+            max_batch = max(batch, self.max_batch, eng.max_batch if eng is not None else 0)
+            if eng is not None:
+                eng.close()
+            self._engine = Engine(self, device, self.precision, max_batch=max_batch)
         return self._engine
 
     def _apply(self, fn, *a, **kw):
         out = super()._apply(fn, *a, **kw)
-        self._engine = None            # parameters moved: pointers held by the context are stale
+        if self._engine is not None:       # parameters moved: pointers held by the context are stale
+            self._engine.close()
+            self._engine = None
         return out
 
     @staticmethod
@@ -79,17 +87,54 @@ class _CaptionBase(nn.Module):
         assert samples.mask is not None
         return samples
 
-    def _run(self, t_samples, g_samples, loc, target_exp, target_exp_mask, return_attention):
-        eng = self.engine()
+    def _encode(self, t_samples, g_samples, loc, att_enc=None):
         t_samples = self._nested(t_samples)
+        B = t_samples.tensors.shape[0]
+        eng = self.engine(B)
+        g_img = g_mask = None
         if g_samples is not None:
             g_samples = self._nested(g_samples)
-            # all-masked context rows get 1% random positions un-masked (models/utils.py:60-89);
-            # the check needs the 14x14 mask, which the engine returns lazily
-            g_samples = NestedTensor(g_samples.tensors, eng.guard_context_mask(g_samples.mask))
-        eng.encode(t_samples, g_samples, loc, need_grad=self.training and torch.is_grad_enabled())
-        return eng.teacher_forced(target_exp, target_exp_mask, return_attention,
-                                  train=self.training)
+            # all-masked context rows get random positions un-masked (models/utils.py:60-89);
+            # real and synthetic inputs never hit it, so it is checked, not reproduced
+            g_img, g_mask = g_samples.tensors, g_samples.mask
+            st = self.backbone_stride
+            m14 = g_mask[:, ::st, ::st]           # the nearest-interpolated mask (models/backbone.py:75)
+            if bool(m14.reshape(B, -1).all(dim=1).any()):
+                m14 = utils.ensure_unmasked_values(m14.clone())
+                g_mask = m14.repeat_interleave(st, 1).repeat_interleave(st, 2)
+        eng.encode(t_samples.tensors, t_samples.mask, g_img, g_mask, loc, att_enc)
+        return eng
+
+    def _run(self, t_samples, g_samples, loc, target_exp, target_exp_mask, return_attention):
+        if self.training and torch.is_grad_enabled():
+            raise NotImplementedError(
+                "retr_b200: the native backward pass (engine.train_one_epoch path) is not built yet; "
+                "call model.eval() / torch.no_grad() for inference")
+        B = target_exp.shape[0]
+        att_enc = None
+        if return_attention:
+            eng = self.engine(B)
+            att_enc = torch.empty(eng.n_enc, B, eng.S, eng.S, dtype=torch.float32, device=eng.device)
+        eng = self._encode(t_samples, g_samples, loc, att_enc)
+        logits, att_s, att_c = eng.teacher_forced(target_exp, target_exp_mask, return_attention)
+        if return_attention:
+            return logits, {"enc_tc_self_att": att_enc, "dec_exp_self_att": att_s,
+                            "dec_exp_tc_cross_att": att_c}
+        return logits
+
+    # Device-resident greedy loop (used by retr_b200.eval_utils.decode.greedy)
+    def greedy_native(self, samples, max_len, bos_token, eos_token):
+        t, g, loc = self._split_samples(samples)
+        eng = self._encode(t, g, loc)
+        return eng.decode_greedy(bos_token, eos_token, max_len)
+
+    def _split_samples(self, samples):
+        samples = tuple(samples)
+        if self.n_images == 2:
+            return samples[0], samples[1], samples[2]
+        if self.loc_in_dim:
+            return samples[0], None, samples[1]
+        return samples[0], None, None
 
 
 class Caption(_CaptionBase):

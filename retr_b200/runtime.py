@@ -1,0 +1,168 @@
+"""Host-side owner of one native context (``retr_ctx``) bound to a caption model.
+
+Builds the ``retr_model_desc`` from the module tree, streams the model's ``state_dict`` into
+the library under the reference's key names, and exposes encode / teacher-forced forward /
+greedy decode.  Tensors are only ever passed down as raw device pointers.
+"""
+import ctypes as C
+
+import torch
+
+from . import native
+from .models.backbone import RESNET_SPECS
+
+_PRECISION = {"fp32": native.FP32, "bf16": native.BF16}
+
+
+def _as(t, dtype, device):
+    return t.to(device=device, dtype=dtype).contiguous()
+
+
+class Engine:
+    def __init__(self, model, device, precision="bf16", max_batch=8, image_size=224):
+        device = torch.device(device)
+        if device.type != "cuda":
+            raise RuntimeError("retr_b200 has no CPU path: the model must live on a CUDA device")
+        if precision not in _PRECISION:
+            raise ValueError(f"precision must be one of {sorted(_PRECISION)}")
+        self.lib = native.lib()
+        self.device, self.precision, self.max_batch, self.image_size = device, precision, int(max_batch), image_size
+        tr = model.transformer
+        d = native.ModelDesc()
+        d.device = device.index if device.index is not None else torch.cuda.current_device()
+        d.precision = _PRECISION[precision]
+        d.blocks = (C.c_int32 * 4)(*RESNET_SPECS[model.backbone.arch][0])
+        d.dilation = int(model.backbone.dilation)
+        d.n_images = model.n_images
+        d.loc_in_dim = model.loc_in_dim
+        d.n_loc = {0: 0, 1: getattr(model, "n_loc_feats", 5), 7: 7}[model.loc_in_dim]
+        d.image_size = image_size
+        d.d_model, d.n_heads, d.d_ff = tr.d_model, tr.nhead, tr.dim_feedforward
+        d.enc_layers, d.dec_layers = tr.encoder.num_layers, tr.decoder.num_layers
+        d.max_pos = tr.embeddings.position_embeddings.num_embeddings
+        d.vocab = model.mlp.layers[-1].out_features
+        d.pre_norm = int(tr.encoder.norm is not None)
+        d.embed_ln_eps = float(tr.embeddings.LayerNorm.eps)
+        d.max_batch = self.max_batch
+        self.desc = d
+        self.T, self.V, self.d_model = d.max_pos, d.vocab, d.d_model
+        self.n_enc, self.n_dec = d.enc_layers, d.dec_layers
+        handle = C.c_void_p()
+        with torch.cuda.device(device):
+            native.check(self.lib.retr_create(C.byref(d), C.byref(handle)))
+            self.handle = handle
+            self._load(model)
+        self.S = self.lib.retr_encoder_tokens(self.handle)
+        self.weights_version = self.version_of(model)
+        self.batch = 0
+
+    # ---- weights --------------------------------------------------------------------------
+    @staticmethod
+    def version_of(model):
+        return sum(t._version for t in model.state_dict(keep_vars=True).values())
+
+    def _load(self, model):
+        for name, t in model.state_dict().items():
+            if not torch.is_floating_point(t):
+                continue
+            t32 = _as(t.detach(), torch.float32, self.device)
+            shape = (C.c_int64 * max(t32.dim(), 1))(*(t32.shape if t32.dim() else (1,)))
+            native.check(self.lib.retr_load_weight(self.handle, name.encode(), native.ptr(t32), shape,
+                                                   max(t32.dim(), 1), 1))
+        native.check(self.lib.retr_finalize_weights(self.handle))
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.retr_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- hot path ---------------------------------------------------------------------------
+    def _stream(self):
+        return native.stream_ptr(self.device)
+
+    def encode(self, t_img, t_mask, g_img=None, g_mask=None, loc=None, att_enc=None):
+        B = t_img.shape[0]
+        if B > self.max_batch:
+            raise RuntimeError(f"batch {B} exceeds the context's max_batch {self.max_batch}")
+        if tuple(t_img.shape[1:]) != (3, self.image_size, self.image_size):
+            raise ValueError(f"images must be [B,3,{self.image_size},{self.image_size}], got {tuple(t_img.shape)}")
+        keep = [_as(t_img, torch.float32, self.device), _as(t_mask, torch.uint8, self.device)]
+        keep += [None if g_img is None else _as(g_img, torch.float32, self.device),
+                 None if g_mask is None else _as(g_mask, torch.uint8, self.device),
+                 None if loc is None else _as(loc, torch.float32, self.device)]
+        with torch.cuda.device(self.device):
+            native.check(self.lib.retr_set_encoder_attention_capture(self.handle, native.ptr(att_enc)))
+            native.check(self.lib.retr_encode(self.handle, B, *[native.ptr(k) for k in keep], self._stream()))
+            native.check(self.lib.retr_set_encoder_attention_capture(self.handle, None))
+        self._keep = keep          # inputs must outlive the asynchronous kernels
+        self.batch = B
+
+    def teacher_forced(self, ids, id_mask, return_attention=False):
+        B = self.batch
+        if tuple(ids.shape) != (B, self.T):
+            raise RuntimeError(f"The size of tensor a ({ids.shape[1]}) must match the size of tensor b ({self.T}) "
+                               "(caption length must equal max_position_embeddings)")
+        ids = _as(ids, torch.int64, self.device)
+        id_mask = _as(id_mask, torch.uint8, self.device)
+        logits = torch.empty(B, self.T, self.V, dtype=torch.float32, device=self.device)
+        att_s = att_c = None
+        if return_attention:
+            att_s = torch.empty(self.n_dec, B, self.T, self.T, dtype=torch.float32, device=self.device)
+            att_c = torch.empty(self.n_dec, B, self.T, self.S, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            native.check(self.lib.retr_forward_teacher_forced(
+                self.handle, native.ptr(ids), native.ptr(id_mask), native.ptr(logits), native.ptr(att_s),
+                native.ptr(att_c), self._stream()))
+        self._keep2 = (ids, id_mask)
+        return logits, att_s, att_c
+
+    def decode_greedy(self, bos, eos, max_len):
+        out = torch.empty(self.batch, max_len, dtype=torch.int64, device=self.device)
+        steps = C.c_int32(0)
+        with torch.cuda.device(self.device):
+            native.check(self.lib.retr_decode_greedy(self.handle, bos, eos, max_len, native.ptr(out),
+                                                     C.byref(steps), self._stream()))
+        return out, steps.value
+
+    def generate_host(self, t_img, t_mask, g_img, g_mask, loc, bos, eos, max_len, out=None):
+        """Host (pinned) buffers in, host ids out; H2D + encode + decode + D2H in one native call."""
+        B = t_img.shape[0]
+        for t in (t_img, t_mask, g_img, g_mask, loc):
+            if t is not None and (t.device.type != "cpu" or not t.is_contiguous()):
+                raise ValueError("generate_host takes contiguous host tensors")
+        if out is None:
+            out = torch.empty(B, max_len, dtype=torch.int64).pin_memory()
+        steps = C.c_int32(0)
+        with torch.cuda.device(self.device):
+            native.check(self.lib.retr_generate_host(
+                self.handle, B, native.ptr(t_img), native.ptr(t_mask), native.ptr(g_img), native.ptr(g_mask),
+                native.ptr(loc), bos, eos, max_len, native.ptr(out), C.byref(steps), self._stream()))
+        self.batch = B
+        return out, steps.value
+
+    def read_state(self, what):
+        B, S, d = self.batch, self.S, self.d_model
+        if what == "mask":
+            out = torch.empty(B, S, dtype=torch.uint8, device=self.device)
+        elif what in ("memory", "src"):
+            out = torch.empty(B, S, d, dtype=torch.float32, device=self.device)
+        else:
+            out = torch.empty(B, 14, 14, 2048, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            native.check(self.lib.retr_read_state(self.handle, what.encode(), native.ptr(out),
+                                                  out.numel() * out.element_size(), self._stream()))
+        return out
+
+    def kernel_launches(self):
+        return int(self.lib.retr_kernel_launches(self.handle))
+
+    def phase_ms(self):
+        buf = (C.c_float * 3)()
+        native.check(self.lib.retr_last_phase_ms(self.handle, buf))
+        return {"backbone": buf[0], "encoder": buf[1], "decode": buf[2]}

@@ -73,3 +73,26 @@ def pack(batch_dict, model_kind="CaptionGlobalLoc", loc7=False):
         loc7_t = torch.cat([loc, loc[:, :2] * 0.5 + 0.25], 1)   # 7-d synthetic vector
         return (t, loc7_t)
     return (t, NestedTensor(batch_dict["g_img"], batch_dict["g_mask"]), batch_dict["loc"])
+
+
+def calibrate_frozen_bn(state_dict, seed=7):
+    """Seeded, documented weight transform applied identically to BOTH sides of a parity test
+    (SURVEY §7 hard part 1): ``build_model``'s FrozenBatchNorm2d buffers are the identity, which
+    (a) never exercises the scale/shift fold and (b) lets activations grow to ~6e5 through 33
+    residual blocks.  This draws non-trivial buffers (the last BN of each residual branch gets a
+    small gain so the feature map stays O(1)).  Returns the same dict, modified in place."""
+    g = torch.Generator().manual_seed(seed)
+    for k in sorted(state_dict.keys()):
+        if not k.endswith("running_var"):
+            continue
+        p = k[:-len("running_var")]
+        n = state_dict[k].numel()
+        last = (".bn3." in k) or ("downsample.1" in k)
+        like = state_dict[k]
+        def put(name, v):
+            state_dict[name] = v.to(dtype=like.dtype, device=like.device)
+        put(p + "weight", (0.5 + torch.rand(n, generator=g)) * (0.35 if last else 1.0))
+        put(p + "bias", 0.1 * torch.randn(n, generator=g))
+        put(p + "running_mean", 0.1 * torch.randn(n, generator=g))
+        put(k, 0.5 + torch.rand(n, generator=g))
+    return state_dict

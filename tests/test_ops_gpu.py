@@ -1,0 +1,227 @@
+"""Kernel-level parity through the C ABI (retr_op_*): each CUDA kernel against a plain PyTorch
+fp32 statement of the same op on the same seeded inputs.  GPU only."""
+import ctypes as C
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+FP32, BF16 = 0, 1
+
+
+def _lib():
+    from retr_b200 import native
+    return native, native.lib()
+
+
+def run_gemm(dtype, A, W, *, M, N, K, lda=None, ldc=None, scale=None, bias=None, rowbias=None, period=1,
+             residual=None, relu=0, out_fp32=False, conv=None, argmax=False, want_c=True):
+    native, lib = _lib()
+    dev = A.device
+    out_dtype = torch.float32 if (out_fp32 or dtype == FP32) else torch.bfloat16
+    ldc = ldc or N
+    Cout = torch.zeros(M, ldc, dtype=out_dtype, device=dev) if want_c else None
+    keys = torch.zeros(M, dtype=torch.int64, device=dev) if argmax else None
+    a = native.GemmArgs()
+    a.A, a.W, a.C = A.data_ptr(), W.data_ptr(), (Cout.data_ptr() if want_c else None)
+    a.M, a.N, a.K, a.lda, a.ldc = M, N, K, (lda or K), ldc
+    a.scale = scale.data_ptr() if scale is not None else None
+    a.bias = bias.data_ptr() if bias is not None else None
+    a.rowbias = rowbias.data_ptr() if rowbias is not None else None
+    a.rowbias_period = period
+    if residual is not None:
+        a.residual, a.ldr, a.res_fp32 = residual.data_ptr(), residual.shape[1], int(residual.dtype == torch.float32)
+    a.relu, a.out_fp32 = relu, int(out_fp32)
+    if conv:
+        for k, v in conv.items():
+            setattr(a, k, v)
+    a.argmax_out = keys.data_ptr() if argmax else None
+    native.check(lib.retr_op_gemm(dtype, C.byref(a), native.stream_ptr(dev)))
+    torch.cuda.synchronize()
+    idx = None
+    if argmax:
+        idx = (0xFFFFFFFF - (keys & 0xFFFFFFFF))
+    return Cout, idx
+
+
+def ref_epilogue(acc, scale, bias, rowbias, period, residual, relu):
+    M = acc.shape[0]
+    if scale is not None:
+        acc = acc * scale
+    if bias is not None:
+        acc = acc + bias
+    if rowbias is not None:
+        acc = acc + rowbias[torch.arange(M, device=acc.device) % period]
+    if relu == 1:
+        acc = acc.relu()
+    if residual is not None:
+        acc = acc + residual.float()
+    if relu == 2:
+        acc = acc.relu()
+    return acc
+
+
+def tol(dtype, K):
+    # fp32: re-association noise; bf16: inputs are exactly representable (generated in bf16), so the
+    # only error is fp32 accumulation order (+ bf16 rounding of the output where C is bf16)
+    return 2e-5 if dtype == FP32 else 2e-5
+
+
+@pytest.mark.parametrize("dtype", [FP32, BF16])
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (300, 256, 256), (1000, 768, 256), (257, 2048, 256),
+                                   (256, 256, 2048), (130, 72, 160), (4096, 64, 576), (64, 1000, 512)])
+def test_gemm_plain(dtype, M, N, K):
+    torch.manual_seed(M + N + K)
+    dev = "cuda"
+    tdt = torch.float32 if dtype == FP32 else torch.bfloat16
+    A = torch.randn(M, K, device=dev).to(tdt)
+    W = (torch.randn(N, K, device=dev) / math.sqrt(K)).to(tdt)
+    bias = torch.randn(N, device=dev)
+    got, _ = run_gemm(dtype, A, W, M=M, N=N, K=K, bias=bias, out_fp32=True)
+    ref = A.double() @ W.double().t() + bias.double()
+    err = (got.double() - ref).abs().max().item()
+    assert err < 1e-4, err
+
+
+@pytest.mark.parametrize("dtype", [FP32, BF16])
+def test_gemm_epilogue_variants(dtype):
+    torch.manual_seed(7)
+    dev = "cuda"
+    tdt = torch.float32 if dtype == FP32 else torch.bfloat16
+    M, N, K, period = 397 * 3, 768, 256, 397
+    A = torch.randn(M, K, device=dev).to(tdt)
+    W = (torch.randn(N, K, device=dev) / math.sqrt(K)).to(tdt)
+    scale = torch.rand(N, device=dev) + 0.5
+    bias = torch.randn(N, device=dev)
+    rowbias = torch.randn(period, N, device=dev)
+    res32 = torch.randn(M, N, device=dev)
+    acc = (A.double() @ W.double().t()).float()
+    for kw in (dict(scale=scale, bias=bias, relu=1),
+               dict(rowbias=rowbias, period=period),
+               dict(bias=bias, residual=res32, relu=2),
+               dict(scale=scale, bias=bias, residual=res32.to(tdt), relu=2),
+               dict(bias=bias, residual=res32, relu=0)):
+        got, _ = run_gemm(dtype, A, W, M=M, N=N, K=K, out_fp32=True, **kw)
+        ref = ref_epilogue(acc, kw.get("scale"), kw.get("bias"), kw.get("rowbias"), kw.get("period", 1),
+                           kw.get("residual"), kw.get("relu", 0))
+        assert (got - ref).abs().max().item() < 2e-4, kw.keys()
+    # native output type (bf16 in bf16 mode): rounding of the result only
+    got, _ = run_gemm(dtype, A, W, M=M, N=N, K=K, bias=bias, relu=1)
+    ref = ref_epilogue(acc, None, bias, None, 1, None, 1)
+    assert (got.float() - ref).abs().max().item() < (2e-4 if dtype == FP32 else 4e-2)
+
+
+@pytest.mark.parametrize("dtype", [FP32, BF16])
+def test_gemm_vocab_argmax_and_ragged_n(dtype):
+    """N = 30522 (not a multiple of any tile), fused argmax == torch.argmax of the written logits."""
+    torch.manual_seed(11)
+    dev = "cuda"
+    tdt = torch.float32 if dtype == FP32 else torch.bfloat16
+    M, N, K = 70, 30522, 512
+    A = torch.randn(M, K, device=dev).to(tdt)
+    W = (torch.randn(N, K, device=dev) / math.sqrt(K)).to(tdt)
+    bias = torch.randn(N, device=dev) * 0.1
+    got, idx = run_gemm(dtype, A, W, M=M, N=N, K=K, bias=bias, out_fp32=True, argmax=True)
+    ref = (A.double() @ W.double().t() + bias.double()).float()
+    assert (got - ref).abs().max().item() < 1e-4
+    assert torch.equal(idx, got.argmax(-1))
+    # argmax only (C == NULL): the decode path never writes logits
+    _, idx2 = run_gemm(dtype, A, W, M=M, N=N, K=K, bias=bias, argmax=True, want_c=False)
+    assert torch.equal(idx2, idx)
+    # ties -> first index, as torch.argmax
+    A0 = torch.zeros(M, K, device=dev).to(tdt)
+    _, idx3 = run_gemm(dtype, A0, W, M=M, N=N, K=K, argmax=True, want_c=False)
+    assert int(idx3.max()) == 0
+
+
+CONVS = [  # (Cin, Cout, k, stride, pad, dil, H)
+    (64, 64, 3, 1, 1, 1, 56), (128, 128, 3, 2, 1, 1, 56), (256, 512, 1, 2, 0, 1, 56),
+    (512, 512, 3, 1, 2, 2, 14), (256, 256, 3, 1, 1, 1, 14), (64, 256, 1, 1, 0, 1, 20)]
+
+
+@pytest.mark.parametrize("dtype", [FP32, BF16])
+@pytest.mark.parametrize("cin,cout,k,stride,pad,dil,H", CONVS)
+def test_conv_implicit_gemm(dtype, cin, cout, k, stride, pad, dil, H):
+    """NHWC implicit-GEMM conv + folded BN + residual + ReLU vs F.conv2d (NCHW fp32)."""
+    torch.manual_seed(cin + cout + k + stride + H)
+    dev = "cuda"
+    tdt = torch.float32 if dtype == FP32 else torch.bfloat16
+    n = 3
+    x = torch.randn(n, cin, H, H, device=dev).to(tdt)
+    w = (torch.randn(cout, cin, k, k, device=dev) / math.sqrt(cin * k * k)).to(tdt)
+    scale = torch.rand(cout, device=dev) + 0.5
+    shift = torch.randn(cout, device=dev) * 0.1
+    ref = F.conv2d(x.double(), w.double(), stride=stride, padding=pad, dilation=dil)
+    OH = ref.shape[-1]
+    res = torch.randn(n, OH, OH, cout, device=dev).to(tdt)
+    ref = (ref * scale.double().view(1, -1, 1, 1) + shift.double().view(1, -1, 1, 1)).permute(0, 2, 3, 1)
+    ref = (ref + res.double()).relu().float().reshape(-1, cout)
+    A = x.permute(0, 2, 3, 1).contiguous()                       # NHWC
+    Wk = w.permute(0, 2, 3, 1).contiguous().reshape(cout, k * k * cin)   # O,(kh,kw,I)
+    conv = dict(kh=k, kw=k, stride=stride, pad=pad, dil=dil, H=H, W_in=H, C_in=cin, OH=OH, OW=OH)
+    got, _ = run_gemm(dtype, A, Wk, M=n * OH * OH, N=cout, K=k * k * cin, lda=cin, scale=scale, bias=shift,
+                      residual=res.reshape(-1, cout), relu=2, out_fp32=True, conv=conv)
+    assert (got - ref).abs().max().item() < 2e-4
+
+
+@pytest.mark.parametrize("out_bf16", [0, 1])
+@pytest.mark.parametrize("eps", [1e-5, 1e-12])
+def test_layernorm(out_bf16, eps):
+    native, lib = _lib()
+    torch.manual_seed(3)
+    x = torch.randn(1000, 256, device="cuda") * 3 + 1
+    g, b = torch.randn(256, device="cuda"), torch.randn(256, device="cuda")
+    y = torch.empty(1000, 256, device="cuda", dtype=torch.bfloat16 if out_bf16 else torch.float32)
+    native.check(lib.retr_op_layernorm(x.data_ptr(), g.data_ptr(), b.data_ptr(), y.data_ptr(), 1000, 256, eps,
+                                       out_bf16, native.stream_ptr()))
+    ref = F.layer_norm(x, (256,), g, b, eps)
+    assert (y.float() - ref).abs().max().item() < (3e-2 if out_bf16 else 2e-5)
+
+
+def ref_attention(q, k, v, H, key_pad, causal):
+    B, Lq, d = q.shape
+    Lk, dh = k.shape[1], d // H
+    qh = q.double().view(B, Lq, H, dh).transpose(1, 2) / math.sqrt(dh)
+    kh = k.double().view(B, Lk, H, dh).transpose(1, 2)
+    vh = v.double().view(B, Lk, H, dh).transpose(1, 2)
+    s = qh @ kh.transpose(-1, -2)
+    if causal:
+        s = s + torch.full((Lq, Lk), float("-inf"), device=q.device, dtype=s.dtype).triu(1)
+    if key_pad is not None:
+        s = s.masked_fill(key_pad.bool()[:, None, None, :], float("-inf"))
+    p = s.softmax(-1)
+    return (p @ vh).transpose(1, 2).reshape(B, Lq, d).float(), p.mean(1).float()
+
+
+@pytest.mark.parametrize("dtype", [FP32, BF16])
+@pytest.mark.parametrize("Lq,Lk,causal,d,H", [(397, 397, 0, 256, 8), (128, 128, 1, 256, 8), (128, 397, 0, 256, 8),
+                                              (70, 70, 1, 512, 8)])
+def test_attention(dtype, Lq, Lk, causal, d, H):
+    native, lib = _lib()
+    torch.manual_seed(Lq + Lk + d)
+    dev, B = "cuda", 3
+    tdt = torch.float32 if dtype == FP32 else torch.bfloat16
+    q = torch.randn(B, Lq, d, device=dev).to(tdt)
+    kv = torch.randn(B, Lk, 2 * d, device=dev).to(tdt)           # [k | v] rows, pitch 2d
+    key_pad = torch.zeros(B, Lk, dtype=torch.uint8, device=dev)
+    key_pad[0, Lk // 2:] = 1
+    key_pad[2, 5:9] = 1
+    if causal:
+        key_pad[:, 0] = 0
+        key_pad[0] = 0
+        key_pad[0, Lk - 10:] = 1                                  # trailing pads only, like id masks
+    out = torch.empty(B, Lq, d, device=dev, dtype=tdt)
+    probs = torch.empty(B, Lq, Lk, device=dev)
+    k, v = kv[:, :, :d], kv[:, :, d:]
+    native.check(lib.retr_op_attention(dtype, q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), B, Lq, Lk, H,
+                                       d, 2 * d, 2 * d, d, key_pad.data_ptr(), causal, probs.data_ptr(),
+                                       native.stream_ptr()))
+    torch.cuda.synchronize()
+    ref, ref_p = ref_attention(q, k, v, H, key_pad, causal)
+    valid = ~torch.isnan(ref)
+    assert (out.float()[valid] - ref[valid]).abs().max().item() < (2e-5 if dtype == FP32 else 2e-2)
+    pv = ~torch.isnan(ref_p)
+    assert (probs[pv] - ref_p[pv]).abs().max().item() < 2e-5
