@@ -178,7 +178,10 @@ def test_layernorm(out_bf16, eps):
     native.check(lib.retr_op_layernorm(x.data_ptr(), g.data_ptr(), b.data_ptr(), y.data_ptr(), 1000, 256, eps,
                                        out_bf16, native.stream_ptr()))
     ref = F.layer_norm(x, (256,), g, b, eps)
-    assert (y.float() - ref).abs().max().item() < (3e-2 if out_bf16 else 2e-5)
+    if out_bf16:      # one bf16 rounding of the fp32 result
+        assert bool(((y.float() - ref).abs() <= ref.abs() * 2 ** -8 + 1e-6).all())
+    else:
+        assert (y - ref).abs().max().item() < 2e-5
 
 
 def ref_attention(q, k, v, H, key_pad, causal):
