@@ -72,6 +72,7 @@ class EngineT final : public EngineBase {
   ~EngineT() override {
     for (auto& kv : graphs_) cudaGraphExecDestroy(kv.second);
     if (done_host_) cudaFreeHost(done_host_);
+    if (capture_stream_) cudaStreamDestroy(capture_stream_);
   }
   void finalize() override;
   void encode(int B, const float* t_img, const uint8_t* t_mask, const float* g_img, const uint8_t* g_mask,
@@ -123,6 +124,7 @@ class EngineT final : public EngineBase {
   int* done_host_ = nullptr;                         // pinned [2]: done, step
   unsigned long long* argmax_keys_ = nullptr;
   std::map<std::tuple<int, int, int>, cudaGraphExec_t> graphs_;
+  cudaStream_t capture_stream_ = nullptr;
   long long step_kernels_ = 0;                       // kernels in one captured decode step
 };
 
@@ -555,14 +557,17 @@ void EngineT<T>::decode_greedy(int bos, int eos, int max_len, int64_t* out_ids, 
     if (it == graphs_.end()) {
       cudaGraph_t graph;
       const long long c0 = g_launches;
-      CUDA_OK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+      // capture on a private stream: the caller's stream may be the legacy default stream,
+      // which cannot be captured; nothing executes during capture, so ordering is unaffected
+      if (!capture_stream_) CUDA_OK(cudaStreamCreateWithFlags(&capture_stream_, cudaStreamNonBlocking));
+      CUDA_OK(cudaStreamBeginCapture(capture_stream_, cudaStreamCaptureModeThreadLocal));
       try {
-        decode_step(B, eos, max_len, s);
+        decode_step(B, eos, max_len, capture_stream_);
       } catch (...) {
-        cudaGraph_t junk; cudaStreamEndCapture(s, &junk);
+        cudaGraph_t junk; cudaStreamEndCapture(capture_stream_, &junk);
         throw;
       }
-      CUDA_OK(cudaStreamEndCapture(s, &graph));
+      CUDA_OK(cudaStreamEndCapture(capture_stream_, &graph));
       CUDA_OK(cudaGraphInstantiate(&exec, graph, 0));
       CUDA_OK(cudaGraphDestroy(graph));
       graphs_[key] = exec;
