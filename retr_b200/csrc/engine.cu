@@ -111,7 +111,7 @@ class EngineT final : public EngineBase {
   float *e_word_ = nullptr, *e_pos_ = nullptr, *emb_g_ = nullptr, *emb_b_ = nullptr;
   Linear<T> mlp_[3];
   // activations
-  int chunk_ = 64;                                   // images per backbone pass
+  int chunk_ = 256;                                  // images per backbone pass
   T *im2col_ = nullptr, *act_[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}, *feat_ = nullptr;
   float *x_ = nullptr, *y_ = nullptr;                // fp32 residual streams (encoder, decoder)
   T *n_ = nullptr, *qkv_ = nullptr, *att_ = nullptr, *h_ = nullptr, *memory_ = nullptr, *qc_ = nullptr;

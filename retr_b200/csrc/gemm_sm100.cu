@@ -4,7 +4,10 @@
 //   warp 0      TMA producer      W tile (and the A tile for a plain matrix) -> 128B-swizzled smem
 //   warp 1      MMA issuer        one thread issues tcgen05.mma (M=128, N=BN, K=16) x4 per k-block
 //   warp 2      TMEM allocator    2 accumulator stages x BN columns
-//   warps 4-7   epilogue          tcgen05.ld -> scale/bias/rowbias/ReLU/residual/argmax -> global
+//   warp 3      residual producer TMA loads of the residual sub-tiles (4-deep ring) ahead of the epilogue
+//   warps 4-7   epilogue          tcgen05.ld -> scale/bias/rowbias/ReLU/residual -> swizzled smem staging
+//                                 -> TMA store (128 rows x 128 B sub-tiles, double buffered); a direct
+//                                 register->global path remains for argmax-only / remapped / unaligned C
 //   warps 8-11  A gather          (convolution only) cp.async im2col rows with zero fill, written
 //                                 in the same swizzled layout TMA would produce
 // Pipelines: smem full/empty ring (TMA|gather -> MMA), TMEM full/empty pair (MMA -> epilogue) so the
@@ -49,14 +52,29 @@ struct KArgs {
   int kh, kw, stride, pad, dil, H, W, Cin, OH, OW, cblocks;
   int c_group, c_group_stride;
   const int* rowbias_dyn;
+  int stages;            // smem ring depth (runtime: depends on the epilogue staging in use)
+  int tma_epi;           // epilogue through smem staging + TMA store
+  int res_tma;           // residual sub-tiles arrive by TMA (implies tma_epi)
 };
+
+constexpr int MAX_STAGES = 8;
+constexpr int EPI_TILE_BYTES = BM * 128;     // 128 rows x 128 B (64 bf16 or 32 fp32 columns)
+constexpr int C_BUFS = 2, R_BUFS = 4;
+constexpr int SMEM_LIMIT = 232448;           // 227 KB opt-in maximum per CTA
+constexpr int BARRIER_BYTES = 512;
 
 template <int BN> struct Cfg {
   static constexpr int B_TILE_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
-  static constexpr int STAGES = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
   static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int SB_BYTES = 2 * BN * 4;
+  static int fixed_bytes(bool tma_epi, bool res_tma) {
+    return 1024 + BARRIER_BYTES + SB_BYTES + (tma_epi ? C_BUFS * EPI_TILE_BYTES : 0) + (res_tma ? R_BUFS * EPI_TILE_BYTES : 0);
+  }
+  static int stages_for(bool tma_epi, bool res_tma) {
+    const int n = (SMEM_LIMIT - fixed_bytes(tma_epi, res_tma)) / STAGE_BYTES;
+    return n > MAX_STAGES ? MAX_STAGES : n;
+  }
 };
 
 // One 32-column chunk of one accumulator row.
@@ -162,27 +180,117 @@ __device__ __forceinline__ void epilogue_chunk(const KArgs& a, uint32_t (&r)[32]
   }
 }
 
+// Scale/bias (+rowbias) -> ReLU -> residual (from the swizzled smem sub-tile) -> ReLU -> swizzled
+// staging for the TMA store.  One 32-column chunk of one accumulator row; `chunk16` is the index of
+// the first 16-byte chunk of this row segment inside the 128-byte staging row.
+template <typename OutT>
+__device__ __forceinline__ void epilogue_chunk_staged(const KArgs& a, uint32_t (&r)[32], const float* sb_scale,
+                                                      const float* sb_bias, int64_t rb_row, int n0, int row,
+                                                      int chunk16, const uint8_t* rsm, uint8_t* csm) {
+  float v[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+  if (a.scale) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float4 t = *reinterpret_cast<const float4*>(sb_scale + 4 * j);
+      v[4 * j] *= t.x; v[4 * j + 1] *= t.y; v[4 * j + 2] *= t.z; v[4 * j + 3] *= t.w;
+    }
+  }
+  if (a.bias) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float4 t = *reinterpret_cast<const float4*>(sb_bias + 4 * j);
+      v[4 * j] += t.x; v[4 * j + 1] += t.y; v[4 * j + 2] += t.z; v[4 * j + 3] += t.w;
+    }
+  }
+  if (a.rowbias) {
+    const float* rb = a.rowbias + rb_row * a.N + n0;
+    if (a.vecRB && n0 + 32 <= a.N) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(rb) + j);
+        v[4 * j] += t.x; v[4 * j + 1] += t.y; v[4 * j + 2] += t.z; v[4 * j + 3] += t.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) if (n0 + j < a.N) v[j] += __ldg(rb + j);
+    }
+  }
+  if (a.relu == 1) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+  }
+  const uint32_t swz = (uint32_t)(row & 7);
+  constexpr int NCH = sizeof(OutT) == 4 ? 8 : 4;          // 16-byte chunks covering 32 columns
+  if (rsm) {
+    const uint8_t* rrow = rsm + row * 128;
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      const uint4 t = *reinterpret_cast<const uint4*>(rrow + (((uint32_t)(chunk16 + c) ^ swz) << 4));
+      if (sizeof(OutT) == 4) {
+        v[4 * c] += __uint_as_float(t.x); v[4 * c + 1] += __uint_as_float(t.y);
+        v[4 * c + 2] += __uint_as_float(t.z); v[4 * c + 3] += __uint_as_float(t.w);
+      } else {
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&t);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float2 f = __bfloat1622float2(h[q]);
+          v[8 * c + 2 * q] += f.x; v[8 * c + 2 * q + 1] += f.y;
+        }
+      }
+    }
+  }
+  if (a.relu == 2) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+  }
+  uint8_t* crow = csm + row * 128;
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    uint4 t;
+    if (sizeof(OutT) == 4) {
+      t.x = __float_as_uint(v[4 * c]); t.y = __float_as_uint(v[4 * c + 1]);
+      t.z = __float_as_uint(v[4 * c + 2]); t.w = __float_as_uint(v[4 * c + 3]);
+    } else {
+      __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&t);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) h[q] = __floats2bfloat162_rn(v[8 * c + 2 * q], v[8 * c + 2 * q + 1]);
+    }
+    *reinterpret_cast<uint4*>(crow + (((uint32_t)(chunk16 + c) ^ swz) << 4)) = t;
+  }
+}
+
 template <int BN, bool GATHER>
 __global__ void __launch_bounds__(GATHER ? 384 : 256, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmR,
                     const KArgs a) {
   using C = Cfg<BN>;
-  constexpr int STAGES = C::STAGES;
+  const int STAGES = a.stages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * C::STAGE_BYTES);
-  uint64_t* empty = full + STAGES;
-  uint64_t* tfull = empty + STAGES;
+  uint8_t* cst = smem + STAGES * C::STAGE_BYTES;                         // C staging (TMA store source)
+  uint8_t* rst = cst + (a.tma_epi ? C_BUFS * EPI_TILE_BYTES : 0);         // residual staging (TMA load dest)
+  float* sb = reinterpret_cast<float*>(rst + (a.res_tma ? R_BUFS * EPI_TILE_BYTES : 0));
+  uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sb) + C::SB_BYTES);
+  uint64_t* empty = full + MAX_STAGES;
+  uint64_t* tfull = empty + MAX_STAGES;
   uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* rfull = tempty + 2;
+  uint64_t* rempty = rfull + R_BUFS;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(rempty + R_BUFS);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int total_tiles = a.m_tiles * a.n_tiles;
+  const int EC = a.out_fp32 ? 32 : 64;                 // columns per staged sub-tile (128 B rows)
 
   if (warp == 0 && lane == 0) {
     if (!GATHER) ptx::prefetch_tmap(&tmA);
     ptx::prefetch_tmap(&tmB);
+    if (a.tma_epi) ptx::prefetch_tmap(&tmC);
+    if (a.res_tma) ptx::prefetch_tmap(&tmR);
     for (int s = 0; s < STAGES; ++s) {
       ptx::mbar_init(&full[s], GATHER ? 129 : 1);
       ptx::mbar_init(&empty[s], 1);
@@ -190,6 +298,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull[s], 1);
       ptx::mbar_init(&tempty[s], 128);
+    }
+    for (int s = 0; s < R_BUFS; ++s) {
+      ptx::mbar_init(&rfull[s], 1);
+      ptx::mbar_init(&rempty[s], 128);
     }
     ptx::fence_barrier_init();
   } else if (warp == 2) {
@@ -203,17 +315,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == 0) {
     if (lane == 0) {
       // ===== TMA producer =====
-      uint32_t it = 0;
+      uint32_t s = 0, ph = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int m_blk = tile / a.n_tiles, n_blk = tile - m_blk * a.n_tiles;
-        for (int kb = 0; kb < a.num_kb; ++kb, ++it) {
-          const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+        for (int kb = 0; kb < a.num_kb; ++kb) {
           ptx::mbar_wait(&empty[s], ph ^ 1);
           uint8_t* As = smem + s * C::STAGE_BYTES;
           uint8_t* Bs = As + A_TILE_BYTES;
           ptx::mbar_arrive_expect_tx(&full[s], C::B_TILE_BYTES + (GATHER ? 0 : A_TILE_BYTES));
           if (!GATHER) ptx::tma_load_2d(As, &tmA, &full[s], kb * BK, m_blk * BM);
           ptx::tma_load_2d(Bs, &tmB, &full[s], kb * BK, n_blk * BN);
+          if (++s == (uint32_t)STAGES) { s = 0; ph ^= 1; }
         }
       }
     }
@@ -221,14 +333,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (lane == 0) {
       // ===== MMA issuer =====
       constexpr uint32_t idesc = ptx::idesc_bf16_f32(BM, BN);
-      uint32_t it = 0, tcount = 0;
+      uint32_t s = 0, ph = 0, tcount = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
         const uint32_t as = tcount & 1, aph = (tcount >> 1) & 1;
         ptx::mbar_wait(&tempty[as], aph ^ 1);
         ptx::tc_fence_after_sync();
         const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kb = 0; kb < a.num_kb; ++kb, ++it) {
-          const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+        for (int kb = 0; kb < a.num_kb; ++kb) {
           ptx::mbar_wait(&full[s], ph);
           ptx::tc_fence_after_sync();
           const uint32_t a_addr = ptx::smem_u32(smem + s * C::STAGE_BYTES);
@@ -239,43 +350,109 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                              ptx::smem_desc_sw128(b_addr + k * 32), idesc, (kb | k) != 0);
           }
           ptx::mma_commit(&empty[s]);      // frees the smem slot when these MMAs retire
+          if (++s == (uint32_t)STAGES) { s = 0; ph ^= 1; }
         }
         ptx::mma_commit(&tfull[as]);       // accumulator complete -> epilogue
+      }
+    }
+  } else if (warp == 3) {
+    if (lane == 0 && a.res_tma) {
+      // ===== residual producer: sub-tiles in the order the epilogue consumes them =====
+      uint32_t rb = 0, rph = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int m_blk = tile / a.n_tiles, n_blk = tile - m_blk * a.n_tiles;
+        for (int n0 = n_blk * BN; n0 < min(a.N, (n_blk + 1) * BN); n0 += EC) {
+          ptx::mbar_wait(&rempty[rb], rph ^ 1);
+          ptx::mbar_arrive_expect_tx(&rfull[rb], EPI_TILE_BYTES);
+          ptx::tma_load_2d(rst + rb * EPI_TILE_BYTES, &tmR, &rfull[rb], n0, m_blk * BM);
+          if (++rb == R_BUFS) { rb = 0; rph ^= 1; }
+        }
       }
     }
   } else if (warp >= 4 && warp < 8) {
     // ===== epilogue =====
     const int q = warp & 3;
-    uint32_t tcount = 0;
+    const int row = q * 32 + lane;                   // row inside the tile == TMEM lane
+    const int tid_e = threadIdx.x - 128;
+    uint32_t tcount = 0, cit = 0, rb = 0, rph = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
       const int m_blk = tile / a.n_tiles, n_blk = tile - m_blk * a.n_tiles;
       const uint32_t as = tcount & 1, aph = (tcount >> 1) & 1;
-      ptx::mbar_wait(&tfull[as], aph);
-      ptx::tc_fence_after_sync();
-      const int64_t m = (int64_t)m_blk * BM + q * 32 + lane;
-      float best_v = -INFINITY;
-      uint32_t best_i = 0;
-      const int64_t mc = a.c_group ? (m / a.c_group) * a.c_group_stride + (m % a.c_group) : m;
+      const int64_t m = (int64_t)m_blk * BM + row;
       const int64_t rb_row = a.rowbias_dyn ? (int64_t)__ldg(a.rowbias_dyn) : (m % a.rowbias_period);
+      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
+      if (a.tma_epi) {
+        // per-tile column parameters -> smem (all 128 epilogue threads)
+        ptx::named_bar_sync(2, 128);
+        for (int i = tid_e; i < BN; i += 128) {
+          const int n = n_blk * BN + i;
+          sb[i] = (a.scale && n < a.N) ? __ldg(a.scale + n) : 1.f;
+          sb[BN + i] = (a.bias && n < a.N) ? __ldg(a.bias + n) : 0.f;
+        }
+        ptx::named_bar_sync(2, 128);
+        ptx::mbar_wait(&tfull[as], aph);
+        ptx::tc_fence_after_sync();
+        for (int n0 = n_blk * BN; n0 < min(a.N, (n_blk + 1) * BN); n0 += EC, ++cit) {
+          const int col = n0 - n_blk * BN;
+          uint8_t* cbuf = cst + (cit & 1) * EPI_TILE_BYTES;
+          const uint8_t* rbuf = nullptr;
+          if (a.res_tma) {
+            ptx::mbar_wait(&rfull[rb], rph);
+            rbuf = rst + rb * EPI_TILE_BYTES;
+          }
+          if (tid_e == 0) ptx::bulk_wait_read<1>();        // the store that used cbuf two sub-tiles ago
+          ptx::named_bar_sync(1, 128);
+          for (int c = 0; c < EC / 32; ++c) {
+            uint32_t r[32];
+            ptx::tmem_ld_32x32(t_row + col + c * 32, r);
+            ptx::tmem_ld_wait();
+            if (a.out_fp32)
+              epilogue_chunk_staged<float>(a, r, sb + col + c * 32, sb + BN + col + c * 32, rb_row, n0 + c * 32, row,
+                                           0, rbuf, cbuf);
+            else
+              epilogue_chunk_staged<bf16>(a, r, sb + col + c * 32, sb + BN + col + c * 32, rb_row, n0 + c * 32, row,
+                                          c * 4, rbuf, cbuf);
+          }
+          if (a.res_tma) {
+            ptx::mbar_arrive(&rempty[rb]);
+            if (++rb == R_BUFS) { rb = 0; rph ^= 1; }
+          }
+          ptx::fence_proxy_async_smem();
+          ptx::named_bar_sync(1, 128);
+          if (tid_e == 0) {
+            ptx::tma_store_2d(&tmC, cbuf, n0, m_blk * BM);
+            ptx::bulk_commit();
+          }
+        }
+        ptx::tc_fence_before_sync();
+        ptx::mbar_arrive(&tempty[as]);
+      } else {
+        ptx::mbar_wait(&tfull[as], aph);
+        ptx::tc_fence_after_sync();
+        float best_v = -INFINITY;
+        uint32_t best_i = 0;
+        const int64_t mc = a.c_group ? (m / a.c_group) * a.c_group_stride + (m % a.c_group) : m;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        const int n0 = n_blk * BN + c * 32;
-        if (n0 >= a.N) break;                       // warp-uniform
-        uint32_t r[32];
-        ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + c * 32, r);
-        ptx::tmem_ld_wait();
-        if (m < a.M) epilogue_chunk(a, r, m, mc, rb_row, n0, best_v, best_i);
+        for (int c = 0; c < BN / 32; ++c) {
+          const int n0 = n_blk * BN + c * 32;
+          if (n0 >= a.N) break;                       // warp-uniform
+          uint32_t r[32];
+          ptx::tmem_ld_32x32(t_row + c * 32, r);
+          ptx::tmem_ld_wait();
+          if (m < a.M) epilogue_chunk(a, r, m, mc, rb_row, n0, best_v, best_i);
+        }
+        ptx::tc_fence_before_sync();
+        ptx::mbar_arrive(&tempty[as]);
+        if (a.argmax_out && m < a.M && best_v > -INFINITY)
+          atomicMax(a.argmax_out + m, pack_argmax(best_v, best_i));
       }
-      ptx::tc_fence_before_sync();
-      ptx::mbar_arrive(&tempty[as]);
-      if (a.argmax_out && m < a.M && best_v > -INFINITY)
-        atomicMax(a.argmax_out + m, pack_argmax(best_v, best_i));
     }
+    if (a.tma_epi && tid_e == 0) ptx::bulk_wait_read<0>();   // smem must outlive the last store's read
   } else if (GATHER && warp >= 8) {
     // ===== im2col gather producer: one thread per tile row =====
     const int row = threadIdx.x - 256;
     const uint32_t swz = (uint32_t)(row & 7);
-    uint32_t it = 0;
+    uint32_t it = 0, s = 0, ph = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int m_blk = tile / a.n_tiles;
       const int64_t m = (int64_t)m_blk * BM + row;
@@ -287,7 +464,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const int ih0 = oh * a.stride - a.pad, iw0 = ow * a.stride - a.pad;
       int tap = 0, cb = 0;
       for (int kb = 0; kb < a.num_kb; ++kb, ++it) {
-        const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
         ptx::mbar_wait(&empty[s], ph ^ 1);
         const int fr = tap / a.kw, fs = tap - fr * a.kw;
         const int ih = ih0 + fr * a.dil, iw = iw0 + fs * a.dil;
@@ -304,6 +480,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           ptx::mbar_arrive(&full[(it - GATHER_LAG) % STAGES]);
         }
         if (++cb == a.cblocks) { cb = 0; ++tap; }
+        if (++s == (uint32_t)STAGES) { s = 0; ph ^= 1; }
       }
     }
     ptx::cp_async_wait<0>();
@@ -332,36 +509,40 @@ PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
   return fn;
 }
 
-// 2-D bf16 tensor [rows, cols] with row pitch ld (elements); box {64, box_rows}, 128B swizzle.
-CUtensorMap make_tmap_2d(const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
+// 2-D tensor [rows, cols] with row pitch ld (elements); box {box_cols, box_rows} with 128-byte inner
+// extent, 128B swizzle.
+CUtensorMap make_tmap_2d(const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows, bool fp32 = false) {
   CUtensorMap m;
+  const int esize = fp32 ? 4 : 2;
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)(ld * 2)};
-  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  cuuint64_t strides[1] = {(cuuint64_t)(ld * esize)};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / esize), (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  RETR_CHECK((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (ld * 2) % 16 == 0,
+  RETR_CHECK((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (ld * esize) % 16 == 0,
              "TMA operand must be 16-byte aligned with a 16-byte multiple row pitch");
-  CUresult r = get_encode_fn()(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
-                               box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = get_encode_fn()(&m, fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                               const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   RETR_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
   return m;
 }
 
 template <int BN, bool GATHER>
-void launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const KArgs& ka, int grid, cudaStream_t stream) {
-  auto kern = gemm_tcgen05_kernel<BN, GATHER>;
-  kern<<<grid, GATHER ? 384 : 256, Cfg<BN>::SMEM_BYTES, stream>>>(tmA, tmB, ka);
+void launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const CUtensorMap& tmR,
+            KArgs& ka, int grid, cudaStream_t stream) {
+  ka.stages = Cfg<BN>::stages_for(ka.tma_epi, ka.res_tma);
+  RETR_CHECK(ka.stages >= (GATHER ? GATHER_LAG + 1 : 2), "not enough shared memory for the pipeline");
+  const int smem = Cfg<BN>::fixed_bytes(ka.tma_epi, ka.res_tma) + ka.stages * Cfg<BN>::STAGE_BYTES;
+  gemm_tcgen05_kernel<BN, GATHER><<<grid, GATHER ? 384 : 256, smem, stream>>>(tmA, tmB, tmC, tmR, ka);
   LAUNCH_OK();
 }
 
 }  // namespace
 
 template <int BN> static void prepare_bn() {
-  CUDA_OK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               Cfg<BN>::SMEM_BYTES));
-  CUDA_OK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               Cfg<BN>::SMEM_BYTES));
+  CUDA_OK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  CUDA_OK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
 }
 void gemm_bf16_prepare() {
   prepare_bn<32>(); prepare_bn<64>(); prepare_bn<128>(); prepare_bn<256>();
@@ -410,14 +591,22 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
   const int sms = sm_count();
   int bn = 256;
   while (bn > 32 && (bn / 2 >= p.N || cdiv(p.M, BM) * cdiv(p.N, bn) < sms)) bn /= 2;
+  // epilogue route: staged TMA store whenever C is a plain, 16-byte aligned matrix (a staged
+  // sub-tile is 128 B wide, so a bf16 C needs BN >= 64)
+  const bool force_direct = getenv("RETR_GEMM_DIRECT_EPILOGUE") != nullptr;
+  ka.tma_epi = !force_direct && ka.vecC && !p.argmax_out && !p.c_group && (p.out_fp32 || bn >= 64) &&
+               (!p.residual || (ka.vecR && p.res_fp32 == p.out_fp32));
+  ka.res_tma = ka.tma_epi && p.residual;
   ka.m_tiles = (int)cdiv(p.M, BM);
   ka.n_tiles = (int)cdiv(p.N, bn);
   const int grid = (int)std::min<int64_t>((int64_t)ka.m_tiles * ka.n_tiles, sms);
   CUtensorMap tmB = make_tmap_2d(p.W, p.N, p.K, p.K, bn);
   CUtensorMap tmA = gather ? tmB : make_tmap_2d(p.A, p.M, p.K, p.lda, BM);
+  CUtensorMap tmC = ka.tma_epi ? make_tmap_2d(p.C, p.M, p.N, p.ldc, BM, p.out_fp32) : tmB;
+  CUtensorMap tmR = ka.res_tma ? make_tmap_2d(p.residual, p.M, p.N, p.ldr, BM, p.res_fp32) : tmB;
 #define RETR_LAUNCH(BN_)                                                   \
-  if (gather) launch<BN_, true>(tmA, tmB, ka, grid, stream);               \
-  else launch<BN_, false>(tmA, tmB, ka, grid, stream)
+  if (gather) launch<BN_, true>(tmA, tmB, tmC, tmR, ka, grid, stream);     \
+  else launch<BN_, false>(tmA, tmB, tmC, tmR, ka, grid, stream)
   switch (bn) {
     case 256: RETR_LAUNCH(256); break;
     case 128: RETR_LAUNCH(128); break;
