@@ -10,6 +10,8 @@
 // Online softmax in chunks of 4 keys.
 #include "ops.h"
 
+#include <type_traits>
+
 namespace retr {
 namespace {
 
@@ -152,7 +154,9 @@ void attention(const AttnParams& p, cudaStream_t s) {
   dim3 grid((unsigned)cdiv(p.Lq, QT), (unsigned)p.H, (unsigned)p.B);
   const int dh = (int)(p.ldo / p.H);
   RETR_CHECK(dh == 32 || dh == 64, "head dim must be 32 or 64 (ldo = n_heads * head_dim)");
-  if (p.out) {
+  if (p.out && std::is_same<T, bf16>::value && getenv("RETR_ATTN_SIMT") == nullptr) {
+    flash_attention_bf16(p, dh, s);                    // tensor-core path (attention_mma.cu)
+  } else if (p.out) {
     if (dh == 32) attention_kernel<T, 32><<<grid, QT, 0, s>>>(p);
     else attention_kernel<T, 64><<<grid, QT, 0, s>>>(p);
     LAUNCH_OK();

@@ -11,6 +11,9 @@ constexpr int DA_WARPS = 4;
 template <typename T> struct Vec16;
 template <> struct Vec16<float> {
   static constexpr int N = 4;
+  typedef float4 Raw;
+  __device__ static Raw load_raw(const float* p) { return *reinterpret_cast<const float4*>(p); }
+  __device__ static void unpack(const Raw& t, float (&o)[4]) { o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = t.w; }
   __device__ static void load(const float* p, float (&o)[4]) {
     const float4 t = *reinterpret_cast<const float4*>(p);
     o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = t.w;
@@ -21,6 +24,13 @@ template <> struct Vec16<float> {
 };
 template <> struct Vec16<bf16> {
   static constexpr int N = 8;
+  typedef uint4 Raw;
+  __device__ static Raw load_raw(const bf16* p) { return *reinterpret_cast<const uint4*>(p); }
+  __device__ static void unpack(const Raw& t, float (&o)[8]) {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&t);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { const float2 f = __bfloat1622float2(h[i]); o[2 * i] = f.x; o[2 * i + 1] = f.y; }
+  }
   __device__ static void load(const bf16* p, float (&o)[8]) {
     const uint4 t = *reinterpret_cast<const uint4*>(p);
     const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&t);
@@ -49,19 +59,22 @@ __device__ __forceinline__ void merge_state(float& m, float& l, float (&acc)[N],
   m = mn;
 }
 
-// grid (H, B), 4 warps.  LPK lanes cooperate on one key (each holds a 16-byte slice of the head
-// dim); a warp scores 32/LPK keys per iteration, UNROLL iterations in flight.
+// One warp per (sample, head): no shared memory, no block barrier.  LPK lanes cooperate on one key
+// (each holds a 16-byte slice of the head dim); a warp scores 32/LPK keys per load instruction and keeps
+// UNROLL instructions (K and V) in flight.  The K/V rows of a (b, h) pair are 2*DH-byte pieces at pitch
+// ld_cache; the 8 warps of neighbouring heads read the neighbouring pieces of the same rows.
 template <typename T, int DH>
-__global__ void __launch_bounds__(DA_WARPS * 32)
+__global__ void __launch_bounds__(DA_WARPS * 32, 4)
 decode_attention_kernel(const T* __restrict__ q, int64_t ldq, const T* __restrict__ new_kv, int64_t ld_new,
                         T* __restrict__ cache, int64_t ld_cache, int64_t cache_bp, T* __restrict__ out, int64_t ldo,
-                        int d, int n_keys, const int* __restrict__ step_dyn, const uint8_t* __restrict__ key_pad,
-                        int64_t ld_pad) {
+                        int d, int H, int n_pairs, int n_keys, const int* __restrict__ step_dyn,
+                        const uint8_t* __restrict__ key_pad, int64_t ld_pad) {
   using V = Vec16<T>;
-  constexpr int VN = V::N, LPK = DH / VN, KPI = 32 / LPK, UNROLL = 4;
-  __shared__ float sm_m[DA_WARPS], sm_l[DA_WARPS], sm_acc[DA_WARPS][DH];
-  const int h = blockIdx.x, b = blockIdx.y;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int VN = V::N, LPK = DH / VN, KPI = 32 / LPK, UNROLL = sizeof(T) == 2 ? 8 : 4;
+  const int gw = blockIdx.x * DA_WARPS + (threadIdx.x >> 5);
+  if (gw >= n_pairs) return;                                // warp-uniform
+  const int b = gw / H, h = gw - b * H;
+  const int lane = threadIdx.x & 31;
   const int sub = lane % LPK, grp = lane / LPK;
   const int e0 = h * DH + sub * VN;                         // this lane's slice of the model dim
   T* kc = cache + (int64_t)b * cache_bp + e0;               // K part; V part at + d
@@ -88,7 +101,7 @@ decode_attention_kernel(const T* __restrict__ q, int64_t ldq, const T* __restric
     for (int i = 0; i < VN; ++i) s = fmaf(qv[i], kn[i], s);
 #pragma unroll
     for (int o = LPK / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);   // all lanes converged
-    if (warp == 0 && grp == 0) {
+    if (grp == 0) {
       V::store(kc + (int64_t)step * ld_cache, kn);
       V::store(kc + (int64_t)step * ld_cache + d, vn);
       m = s; l = 1.f;
@@ -97,29 +110,30 @@ decode_attention_kernel(const T* __restrict__ q, int64_t ldq, const T* __restric
     }
   }
 
-  const int stride = DA_WARPS * KPI;
-  // loop bound is warp-uniform (base), so the segment shuffles below run converged
-  for (int base = warp * KPI; base < n_cached; base += stride * UNROLL) {
-    const int j0 = base + grp;
-    float kk[UNROLL][VN], vv[UNROLL][VN];
+  const uint8_t* pad = key_pad ? key_pad + (int64_t)b * ld_pad : nullptr;
+  for (int base = 0; base < n_cached; base += KPI * UNROLL) {      // warp-uniform trip count
+    typename V::Raw kraw[UNROLL], vraw[UNROLL];
     bool ok[UNROLL];
 #pragma unroll
     for (int u = 0; u < UNROLL; ++u) {
-      const int j = j0 + u * stride;
-      ok[u] = j < n_cached && !(key_pad && key_pad[(int64_t)b * ld_pad + j]);
+      const int j = base + u * KPI + grp;
+      ok[u] = j < n_cached && !(pad && pad[j]);
       if (ok[u]) {
-        V::load(kc + (int64_t)j * ld_cache, kk[u]);
-        V::load(kc + (int64_t)j * ld_cache + d, vv[u]);
+        kraw[u] = V::load_raw(kc + (int64_t)j * ld_cache);
+        vraw[u] = V::load_raw(kc + (int64_t)j * ld_cache + d);
       }
     }
 #pragma unroll
     for (int u = 0; u < UNROLL; ++u) {
       float s = 0.f;
+      float kf[VN], vf[VN];
       if (ok[u]) {
+        V::unpack(kraw[u], kf);
+        V::unpack(vraw[u], vf);
 #pragma unroll
-        for (int i = 0; i < VN; ++i) s = fmaf(qv[i], kk[u][i], s);
+        for (int i = 0; i < VN; ++i) s = fmaf(qv[i], kf[i], s);
       }
-      // all LPK lanes of a group share j, hence ok[u]: the segment shuffle is converged
+      // the LPK lanes of a group share j, hence ok[u]: the segment shuffle runs converged
 #pragma unroll
       for (int o = LPK / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
       if (ok[u]) {
@@ -127,7 +141,7 @@ decode_attention_kernel(const T* __restrict__ q, int64_t ldq, const T* __restric
         const float corr = __expf(m - mn), pr = __expf(s - mn);
         l = l * corr + pr;
 #pragma unroll
-        for (int i = 0; i < VN; ++i) acc[i] = fmaf(pr, vv[u][i], acc[i] * corr);
+        for (int i = 0; i < VN; ++i) acc[i] = fmaf(pr, vf[i], acc[i] * corr);
         m = mn;
       }
     }
@@ -142,24 +156,10 @@ decode_attention_kernel(const T* __restrict__ q, int64_t ldq, const T* __restric
     merge_state<VN>(m, l, acc, m2, l2, a2);
   }
   if (grp == 0) {
-    sm_m[warp] = m; sm_l[warp] = l;
+    const float inv = 1.f / l;
 #pragma unroll
-    for (int i = 0; i < VN; ++i) sm_acc[warp][sub * VN + i] = acc[i];
-  }
-  __syncthreads();
-  if (threadIdx.x < DH) {
-    const int c = threadIdx.x;
-    float mm = -INFINITY;
-#pragma unroll
-    for (int w = 0; w < DA_WARPS; ++w) mm = fmaxf(mm, sm_m[w]);
-    float ll = 0.f, aa = 0.f;
-#pragma unroll
-    for (int w = 0; w < DA_WARPS; ++w) {
-      const float f = sm_m[w] == -INFINITY ? 0.f : __expf(sm_m[w] - mm);
-      ll = fmaf(sm_l[w], f, ll);
-      aa = fmaf(sm_acc[w][c], f, aa);
-    }
-    out[(int64_t)b * ldo + h * DH + c] = from_f<T>(aa / ll);
+    for (int i = 0; i < VN; ++i) acc[i] *= inv;
+    V::store(out + (int64_t)b * ldo + e0, acc);
   }
 }
 
@@ -208,15 +208,16 @@ void decode_attention(const T* q, int64_t ldq, const T* new_kv, int64_t ld_new, 
   const int dh = d / H;
   RETR_CHECK(dh == 32 || dh == 64, "head dim must be 32 or 64");
   RETR_CHECK(!new_kv || step_dyn, "self-attention needs the step counter");
-  dim3 grid((unsigned)H, (unsigned)B);
+  const int pairs = B * H;
+  const unsigned grid = (unsigned)cdiv(pairs, DA_WARPS);
   if (dh == 32)
     decode_attention_kernel<T, 32><<<grid, DA_WARPS * 32, 0, s>>>(q, ldq, new_kv, ld_new, cache, ld_cache,
-                                                                   cache_batch_pitch, out, ldo, d, n_keys, step_dyn,
-                                                                   key_pad, ld_pad);
+                                                                   cache_batch_pitch, out, ldo, d, H, pairs, n_keys,
+                                                                   step_dyn, key_pad, ld_pad);
   else
     decode_attention_kernel<T, 64><<<grid, DA_WARPS * 32, 0, s>>>(q, ldq, new_kv, ld_new, cache, ld_cache,
-                                                                   cache_batch_pitch, out, ldo, d, n_keys, step_dyn,
-                                                                   key_pad, ld_pad);
+                                                                   cache_batch_pitch, out, ldo, d, H, pairs, n_keys,
+                                                                   step_dyn, key_pad, ld_pad);
   LAUNCH_OK();
 }
 template void decode_attention<float>(const float*, int64_t, const float*, int64_t, float*, int64_t, int64_t, float*,

@@ -48,6 +48,7 @@ struct AttnParams {
   float* probs;                             // optional [B,Lq,Lk] head-averaged probabilities
 };
 template <typename T> void attention(const AttnParams& p, cudaStream_t s);
+void flash_attention_bf16(const AttnParams& p, int dh, cudaStream_t s);   // attention_mma.cu
 
 // ---- greedy decode (decode_ops.cu) --------------------------------------------------------------
 // Single-query attention over a K/V cache of rows [K(d) | V(d)] (pitch ldkv), one CTA per (b, head).
