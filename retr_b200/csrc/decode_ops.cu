@@ -1,12 +1,15 @@
 // Kernels of the KV-cached greedy loop that replaces eval_utils/decode.py:68-79's full-prefix
 // recompute: single-query attention over the self / cross K-V caches and the per-step token
 // bookkeeping.  The step index lives in device memory so one captured CUDA graph serves every step.
+#include "gemm.h"
 #include "ops.h"
+#include "sm100_ptx.cuh"
 
 namespace retr {
 namespace {
 
 constexpr int DA_WARPS = 4;
+constexpr int DA_MAX_KEYS = 1024;       // the sine table bounds the encoder length at 1024
 
 template <typename T> struct Vec16;
 template <> struct Vec16<float> {
@@ -59,41 +62,63 @@ __device__ __forceinline__ void merge_state(float& m, float& l, float (&acc)[N],
   m = mn;
 }
 
-// One warp per (sample, head): no shared memory, no block barrier.  LPK lanes cooperate on one key
-// (each holds a 16-byte slice of the head dim); a warp scores 32/LPK keys per load instruction and keeps
-// UNROLL instructions (K and V) in flight.  The K/V rows of a (b, h) pair are 2*DH-byte pieces at pitch
-// ld_cache; the 8 warps of neighbouring heads read the neighbouring pieces of the same rows.
+// One CTA per (sample, head).  The K and V blocks of a (b, h) pair are CONTIGUOUS in the head-major
+// caches ([B][H][rows][DH]), so one thread streams them into shared memory with two bulk-async copies
+// (cp.async.bulk, completion on an mbarrier) — the whole block is in flight at once, 4 CTAs per SM —
+// and the 4 warps then score keys from shared memory: LPK lanes cooperate on one key (16-byte slice
+// each, conflict-free), online softmax per lane group, merged by shuffles and one smem pass.
+// (A persistent double-buffered variant measured slower on B200: 38 us vs 35 us per cross-attention
+// launch at B=256; see profiles/.)
 template <typename T, int DH>
-__global__ void __launch_bounds__(DA_WARPS * 32, 4)
+__global__ void __launch_bounds__(DA_WARPS * 32)
 decode_attention_kernel(const T* __restrict__ q, int64_t ldq, const T* __restrict__ new_kv, int64_t ld_new,
-                        T* __restrict__ cache, int64_t ld_cache, int64_t cache_bp, T* __restrict__ out, int64_t ldo,
-                        int d, int H, int n_pairs, int n_keys, const int* __restrict__ step_dyn,
+                        T* __restrict__ kcache, T* __restrict__ vcache, int cache_rows, T* __restrict__ out,
+                        int64_t ldo, int d, int H, int n_keys, const int* __restrict__ step_dyn,
                         const uint8_t* __restrict__ key_pad, int64_t ld_pad) {
   using V = Vec16<T>;
-  constexpr int VN = V::N, LPK = DH / VN, KPI = 32 / LPK, UNROLL = sizeof(T) == 2 ? 8 : 4;
-  const int gw = blockIdx.x * DA_WARPS + (threadIdx.x >> 5);
-  if (gw >= n_pairs) return;                                // warp-uniform
-  const int b = gw / H, h = gw - b * H;
-  const int lane = threadIdx.x & 31;
+  constexpr int VN = V::N, LPK = DH / VN, KPI = 32 / LPK;
+  extern __shared__ __align__(128) uint8_t da_smem[];
+  T* Ks = reinterpret_cast<T*>(da_smem);
+  T* Vs = Ks + (size_t)cache_rows * DH;
+  __shared__ __align__(8) uint64_t bar[2];                  // K landed, V landed
+  __shared__ float sm_m[DA_WARPS], sm_l[DA_WARPS], sm_acc[DA_WARPS][DH];
+  __shared__ float sc[DA_MAX_KEYS];                         // scores (masked keys: -inf)
+  const int bh = blockIdx.x, b = bh / H, h = bh - b * H;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int sub = lane % LPK, grp = lane / LPK;
   const int e0 = h * DH + sub * VN;                         // this lane's slice of the model dim
-  T* kc = cache + (int64_t)b * cache_bp + e0;               // K part; V part at + d
+  T* kg = kcache + (size_t)bh * cache_rows * DH;
+  T* vg = vcache + (size_t)bh * cache_rows * DH;
+  const int n_cached = new_kv ? *step_dyn : n_keys;
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(&bar[0], 1);
+    ptx::mbar_init(&bar[1], 1);
+    ptx::fence_barrier_init();
+    if (n_cached > 0) {
+      const uint32_t bytes = (uint32_t)n_cached * DH * sizeof(T);
+      ptx::mbar_arrive_expect_tx(&bar[0], bytes);
+      ptx::bulk_load(Ks, kg, bytes, &bar[0]);
+      ptx::mbar_arrive_expect_tx(&bar[1], bytes);
+      ptx::bulk_load(Vs, vg, bytes, &bar[1]);
+    }
+  }
+  // small operands: one global round trip, overlapped with the bulk copies.  The padding bytes go
+  // straight into the score array as 0 / -inf.
+  if (key_pad) {
+    const uint8_t* pad = key_pad + (int64_t)b * ld_pad;
+    for (int j = threadIdx.x; j < n_cached; j += DA_WARPS * 32) sc[j] = pad[j] ? -INFINITY : 0.f;
+  } else {
+    for (int j = threadIdx.x; j < n_cached; j += DA_WARPS * 32) sc[j] = 0.f;
+  }
   float qv[VN];
   V::load(q + (int64_t)b * ldq + e0, qv);
   const float scale = rsqrtf((float)DH);
 #pragma unroll
   for (int i = 0; i < VN; ++i) qv[i] *= scale;
-
-  int n_cached = n_keys;
-  float m = -INFINITY, l = 0.f, acc[VN];
-#pragma unroll
-  for (int i = 0; i < VN; ++i) acc[i] = 0.f;
-
+  float s_new = -INFINITY, vn[VN];
   if (new_kv) {
     // self-attention: this step's key/value come from the projection output and are appended
-    const int step = *step_dyn;
-    n_cached = step;
-    float kn[VN], vn[VN];
+    float kn[VN];
     V::load(new_kv + (int64_t)b * ld_new + e0, kn);
     V::load(new_kv + (int64_t)b * ld_new + d + e0, vn);
     float s = 0.f;
@@ -101,66 +126,99 @@ decode_attention_kernel(const T* __restrict__ q, int64_t ldq, const T* __restric
     for (int i = 0; i < VN; ++i) s = fmaf(qv[i], kn[i], s);
 #pragma unroll
     for (int o = LPK / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);   // all lanes converged
-    if (grp == 0) {
-      V::store(kc + (int64_t)step * ld_cache, kn);
-      V::store(kc + (int64_t)step * ld_cache + d, vn);
-      m = s; l = 1.f;
-#pragma unroll
-      for (int i = 0; i < VN; ++i) acc[i] = vn[i];
+    s_new = s;
+    if (warp == 0 && grp == 0) {
+      V::store(kg + (size_t)n_cached * DH + sub * VN, kn);
+      V::store(vg + (size_t)n_cached * DH + sub * VN, vn);
     }
   }
-
-  const uint8_t* pad = key_pad ? key_pad + (int64_t)b * ld_pad : nullptr;
-  for (int base = 0; base < n_cached; base += KPI * UNROLL) {      // warp-uniform trip count
-    typename V::Raw kraw[UNROLL], vraw[UNROLL];
-    bool ok[UNROLL];
+  __syncthreads();                                          // barrier init + mask values visible
+  // pass 1: scores (independent per key: no serial softmax chain), running max per lane
+  float mx = s_new;
+  if (n_cached > 0) ptx::mbar_wait(&bar[0], 0);
+  for (int base = warp * KPI; base < n_cached; base += DA_WARPS * KPI) {     // warp-uniform trip count
+    const int j = base + grp;
+    float s = 0.f;
+    if (j < n_cached) {
+      float kf[VN];
+      V::load(Ks + (size_t)j * DH + sub * VN, kf);
 #pragma unroll
-    for (int u = 0; u < UNROLL; ++u) {
-      const int j = base + u * KPI + grp;
-      ok[u] = j < n_cached && !(pad && pad[j]);
-      if (ok[u]) {
-        kraw[u] = V::load_raw(kc + (int64_t)j * ld_cache);
-        vraw[u] = V::load_raw(kc + (int64_t)j * ld_cache + d);
-      }
+      for (int i = 0; i < VN; ++i) s = fmaf(qv[i], kf[i], s);
     }
 #pragma unroll
-    for (int u = 0; u < UNROLL; ++u) {
-      float s = 0.f;
-      float kf[VN], vf[VN];
-      if (ok[u]) {
-        V::unpack(kraw[u], kf);
-        V::unpack(vraw[u], vf);
-#pragma unroll
-        for (int i = 0; i < VN; ++i) s = fmaf(qv[i], kf[i], s);
-      }
-      // the LPK lanes of a group share j, hence ok[u]: the segment shuffle runs converged
-#pragma unroll
-      for (int o = LPK / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-      if (ok[u]) {
-        const float mn = fmaxf(m, s);
-        const float corr = __expf(m - mn), pr = __expf(s - mn);
-        l = l * corr + pr;
-#pragma unroll
-        for (int i = 0; i < VN; ++i) acc[i] = fmaf(pr, vf[i], acc[i] * corr);
-        m = mn;
-      }
+    for (int o = LPK / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (j < n_cached) {
+      s += sc[j];                                           // -inf for padded keys
+      if (sub == 0) sc[j] = s;
+      mx = fmaxf(mx, s);
     }
   }
-  // merge the KPI key groups of the warp
+  mx = warp_max(mx);
+  if (lane == 0) sm_m[warp] = mx;
+  __syncthreads();                                          // scores + per-warp maxima visible
+  float M = sm_m[0];
+#pragma unroll
+  for (int w = 1; w < DA_WARPS; ++w) M = fmaxf(M, sm_m[w]);
+  // pass 2: p = exp(s - M), l += p, acc += p v   (no rescaling needed)
+  float l = 0.f, acc[VN];
+#pragma unroll
+  for (int i = 0; i < VN; ++i) acc[i] = 0.f;
+  if (new_kv && warp == 0 && grp == 0) {
+    const float pr = __expf(s_new - M);
+    l = pr;
+#pragma unroll
+    for (int i = 0; i < VN; ++i) acc[i] = pr * vn[i];
+  }
+  if (n_cached > 0) ptx::mbar_wait(&bar[1], 0);
+  for (int base = warp * KPI; base < n_cached; base += DA_WARPS * KPI) {
+    const int j = base + grp;
+    if (j < n_cached) {
+      const float pr = __expf(sc[j] - M);
+      float vf[VN];
+      V::load(Vs + (size_t)j * DH + sub * VN, vf);
+      l += pr;
+#pragma unroll
+      for (int i = 0; i < VN; ++i) acc[i] = fmaf(pr, vf[i], acc[i]);
+    }
+  }
+  // sum the KPI key groups of the warp, then the warps
 #pragma unroll
   for (int o = LPK; o < 32; o <<= 1) {
-    const float m2 = __shfl_xor_sync(0xffffffffu, m, o), l2 = __shfl_xor_sync(0xffffffffu, l, o);
-    float a2[VN];
+    l += __shfl_xor_sync(0xffffffffu, l, o);
 #pragma unroll
-    for (int i = 0; i < VN; ++i) a2[i] = __shfl_xor_sync(0xffffffffu, acc[i], o);
-    merge_state<VN>(m, l, acc, m2, l2, a2);
+    for (int i = 0; i < VN; ++i) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o);
   }
   if (grp == 0) {
-    const float inv = 1.f / l;
+    if (sub == 0) sm_l[warp] = l;
 #pragma unroll
-    for (int i = 0; i < VN; ++i) acc[i] *= inv;
-    V::store(out + (int64_t)b * ldo + e0, acc);
+    for (int i = 0; i < VN; ++i) sm_acc[warp][sub * VN + i] = acc[i];
   }
+  __syncthreads();
+  if (threadIdx.x < DH) {
+    const int c = threadIdx.x;
+    float ll = 0.f, aa = 0.f;
+#pragma unroll
+    for (int w = 0; w < DA_WARPS; ++w) { ll += sm_l[w]; aa += sm_acc[w][c]; }
+    out[(int64_t)b * ldo + h * DH + c] = from_f<T>(aa / ll);
+  }
+}
+
+// [B*rows, 2d] rows of [K(d) | V(d)]  ->  head-major K[B][H][rows][DH], V[B][H][rows][DH]; 16-byte chunks
+template <typename T>
+__global__ void kv_to_head_major_kernel(const T* __restrict__ kv, T* __restrict__ kh, T* __restrict__ vh, int B,
+                                        int rows, int H, int dh) {
+  constexpr int VN = 16 / sizeof(T);
+  const int cpr = 2 * H * dh / VN;                          // chunks per source row
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)B * rows * cpr) return;
+  const int c = (int)(idx % cpr);
+  const int64_t br = idx / cpr;
+  const int r = (int)(br % rows), b = (int)(br / rows);
+  const int e = c * VN, isv = e >= H * dh, eh = isv ? e - H * dh : e;
+  const int h = eh / dh, w = eh % dh;
+  const uint4 val = *reinterpret_cast<const uint4*>(kv + br * (2 * H * dh) + e);
+  T* dst = (isv ? vh : kh) + (((size_t)b * H + h) * rows + r) * dh + w;
+  *reinterpret_cast<uint4*>(dst) = val;
 }
 
 __global__ void greedy_init_kernel(int64_t* caption, int max_len, int B, int bos, int* step, int* done,
@@ -202,28 +260,41 @@ __global__ void greedy_update_kernel(unsigned long long* keys, int64_t* caption,
 }  // namespace
 
 template <typename T>
-void decode_attention(const T* q, int64_t ldq, const T* new_kv, int64_t ld_new, T* cache, int64_t ld_cache,
-                      int64_t cache_batch_pitch, T* out, int64_t ldo, int B, int H, int d, int n_keys,
-                      const int* step_dyn, const uint8_t* key_pad, int64_t ld_pad, cudaStream_t s) {
+void decode_attention(const T* q, int64_t ldq, const T* new_kv, int64_t ld_new, T* kcache, T* vcache, int cache_rows,
+                      T* out, int64_t ldo, int B, int H, int d, int n_keys, const int* step_dyn,
+                      const uint8_t* key_pad, int64_t ld_pad, cudaStream_t s) {
   const int dh = d / H;
   RETR_CHECK(dh == 32 || dh == 64, "head dim must be 32 or 64");
   RETR_CHECK(!new_kv || step_dyn, "self-attention needs the step counter");
-  const int pairs = B * H;
-  const unsigned grid = (unsigned)cdiv(pairs, DA_WARPS);
-  if (dh == 32)
-    decode_attention_kernel<T, 32><<<grid, DA_WARPS * 32, 0, s>>>(q, ldq, new_kv, ld_new, cache, ld_cache,
-                                                                   cache_batch_pitch, out, ldo, d, H, pairs, n_keys,
-                                                                   step_dyn, key_pad, ld_pad);
-  else
-    decode_attention_kernel<T, 64><<<grid, DA_WARPS * 32, 0, s>>>(q, ldq, new_kv, ld_new, cache, ld_cache,
-                                                                   cache_batch_pitch, out, ldo, d, H, pairs, n_keys,
-                                                                   step_dyn, key_pad, ld_pad);
+  const size_t smem = (size_t)2 * cache_rows * dh * sizeof(T);        // K block + V block
+  RETR_CHECK(smem <= 220 * 1024 && cache_rows <= DA_MAX_KEYS, "K/V block does not fit in shared memory");
+  auto kern = dh == 32 ? decode_attention_kernel<T, 32> : decode_attention_kernel<T, 64>;
+  kern<<<(unsigned)(B * H), DA_WARPS * 32, smem, s>>>(q, ldq, new_kv, ld_new, kcache, vcache, cache_rows, out, ldo, d, H,
+                                                      n_keys, step_dyn, key_pad, ld_pad);
   LAUNCH_OK();
 }
-template void decode_attention<float>(const float*, int64_t, const float*, int64_t, float*, int64_t, int64_t, float*,
-                                      int64_t, int, int, int, int, const int*, const uint8_t*, int64_t, cudaStream_t);
-template void decode_attention<bf16>(const bf16*, int64_t, const bf16*, int64_t, bf16*, int64_t, int64_t, bf16*,
-                                     int64_t, int, int, int, int, const int*, const uint8_t*, int64_t, cudaStream_t);
+template <typename T>
+void decode_attention_configure(int max_rows, int dh) {
+  auto kern = dh == 32 ? decode_attention_kernel<T, 32> : decode_attention_kernel<T, 64>;
+  CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * max_rows * dh * (int)sizeof(T)));
+  CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  CUDA_OK(cudaFuncSetAttribute(greedy_update_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+}
+template void decode_attention_configure<float>(int, int);
+template void decode_attention_configure<bf16>(int, int);
+template void decode_attention<float>(const float*, int64_t, const float*, int64_t, float*, float*, int, float*, int64_t,
+                                      int, int, int, int, const int*, const uint8_t*, int64_t, cudaStream_t);
+template void decode_attention<bf16>(const bf16*, int64_t, const bf16*, int64_t, bf16*, bf16*, int, bf16*, int64_t, int,
+                                     int, int, int, const int*, const uint8_t*, int64_t, cudaStream_t);
+
+template <typename T>
+void kv_to_head_major(const T* kv, T* kh, T* vh, int B, int rows, int H, int dh, cudaStream_t s) {
+  const int64_t n = (int64_t)B * rows * (2 * H * dh / (16 / (int)sizeof(T)));
+  kv_to_head_major_kernel<T><<<(unsigned)cdiv(n, 256), 256, 0, s>>>(kv, kh, vh, B, rows, H, dh);
+  LAUNCH_OK();
+}
+template void kv_to_head_major<float>(const float*, float*, float*, int, int, int, int, cudaStream_t);
+template void kv_to_head_major<bf16>(const bf16*, bf16*, bf16*, int, int, int, int, cudaStream_t);
 
 void greedy_update(unsigned long long* argmax_keys, int64_t* caption, int max_len, int B, int eos, int* step,
                    int* done, uint8_t* finished, cudaStream_t s) {

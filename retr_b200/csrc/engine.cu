@@ -117,7 +117,8 @@ class EngineT final : public EngineBase {
   T *n_ = nullptr, *qkv_ = nullptr, *att_ = nullptr, *h_ = nullptr, *memory_ = nullptr, *qc_ = nullptr;
   T *hs_ = nullptr, *m1_ = nullptr, *m2_ = nullptr;
   float* src_copy_ = nullptr;                        // encoder input tokens kept for read_state
-  std::vector<T*> ckv_, self_cache_;
+  std::vector<T*> ckv_;                              // per layer [B*S, 2d] rows of [K|V] (teacher-forced path)
+  std::vector<T*> ck_, cv_, sk_, sv_;                // head-major decode caches [B][H][rows][dh]
   uint8_t *tok_mask_ = nullptr, *finished_ = nullptr;
   int64_t* caption_ = nullptr;
   int *step_ = nullptr, *done_ = nullptr;
@@ -302,7 +303,10 @@ void EngineT<T>::alloc_buffers() {
   m2_ = static_cast<T*>(dalloc(Md * mlp_[1].out * sizeof(T)));
   for (int l = 0; l < desc.dec_layers; ++l) {
     ckv_.push_back(static_cast<T*>(dalloc(Me * 2 * d * sizeof(T))));
-    self_cache_.push_back(static_cast<T*>(dalloc(Md * 2 * d * sizeof(T))));
+    ck_.push_back(static_cast<T*>(dalloc(Me * d * sizeof(T))));
+    cv_.push_back(static_cast<T*>(dalloc(Me * d * sizeof(T))));
+    sk_.push_back(static_cast<T*>(dalloc(Md * d * sizeof(T))));
+    sv_.push_back(static_cast<T*>(dalloc(Md * d * sizeof(T))));
   }
   tok_mask_ = static_cast<uint8_t*>(dalloc(Me));
   finished_ = static_cast<uint8_t*>(dalloc(B));
@@ -312,6 +316,8 @@ void EngineT<T>::alloc_buffers() {
   argmax_keys_ = static_cast<unsigned long long*>(dalloc(Md * 8));
   CUDA_OK(cudaMemset(argmax_keys_, 0, Md * 8));
   CUDA_OK(cudaMallocHost(&done_host_, 16));
+  if (getenv("RETR_NO_CARVEOUT_HINT") == nullptr) ops_prefer_max_shared();
+  decode_attention_configure<T>(std::max<int>(S, (int)Tn), (int)(d / desc.n_heads));
 }
 
 // ---- backbone --------------------------------------------------------------------------------------
@@ -438,6 +444,7 @@ void EngineT<T>::encode(int B, const float* t_img, const uint8_t* t_mask, const 
     GemmParams p = lin(dec_[l].c_kv, memory_, Me, ckv_[l]);
     p.rowbias = dec_[l].rb_c_kv; p.rowbias_period = S;
     gemm<T>(p, s);
+    kv_to_head_major<T>(ckv_[l], ck_[l], cv_[l], B, S, desc.n_heads, d / desc.n_heads, s);
   }
   CUDA_OK(cudaEventRecord(ev_[2], s));
   cur_B_ = B;
@@ -510,8 +517,7 @@ void EngineT<T>::decode_step(int B, int eos, int max_len, cudaStream_t s) {
     GemmParams p = lin(e.s_qkv, n_, B, qkv_);
     p.rowbias = e.rb_s_qkv; p.rowbias_dyn = step_;
     gemm<T>(p, s);
-    decode_attention<T>(qkv_, 3 * d, qkv_ + d, 3 * d, self_cache_[l], 2 * d, (int64_t)Tn * 2 * d, att_, d, B, H, d, 0,
-                        step_, nullptr, 0, s);
+    decode_attention<T>(qkv_, 3 * d, qkv_ + d, 3 * d, sk_[l], sv_[l], Tn, att_, d, B, H, d, 0, step_, nullptr, 0, s);
     p = lin(e.s_out, att_, B, y_);
     p.out_fp32 = true; p.residual = y_; p.ldr = d; p.res_fp32 = true;
     gemm<T>(p, s);
@@ -520,8 +526,7 @@ void EngineT<T>::decode_step(int B, int eos, int max_len, cudaStream_t s) {
     p = lin(e.c_q, n_, B, qc_);
     p.rowbias = e.rb_c_q; p.rowbias_dyn = step_;
     gemm<T>(p, s);
-    decode_attention<T>(qc_, d, nullptr, 0, ckv_[l], 2 * d, (int64_t)S * 2 * d, att_, d, B, H, d, S, nullptr, tok_mask_,
-                        S, s);
+    decode_attention<T>(qc_, d, nullptr, 0, ck_[l], cv_[l], S, att_, d, B, H, d, S, nullptr, tok_mask_, S, s);
     p = lin(e.c_out, att_, B, y_);
     p.out_fp32 = true; p.residual = y_; p.ldr = d; p.res_fp32 = true;
     gemm<T>(p, s);

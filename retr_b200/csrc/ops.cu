@@ -164,6 +164,15 @@ __global__ void embed_ln_kernel(const int64_t* __restrict__ ids, int64_t ld_ids,
 
 }  // namespace
 
+// Every kernel of the decode step asks for the maximum shared-memory carveout so that consecutive
+// launches (227 KB GEMMs, zero-smem LayerNorms) never force an SM L1/shared reconfiguration.
+void ops_prefer_max_shared() {
+  const int v = cudaSharedmemCarveoutMaxShared;
+  CUDA_OK(cudaFuncSetAttribute(layernorm_kernel<float>, cudaFuncAttributePreferredSharedMemoryCarveout, v));
+  CUDA_OK(cudaFuncSetAttribute(layernorm_kernel<bf16>, cudaFuncAttributePreferredSharedMemoryCarveout, v));
+  CUDA_OK(cudaFuncSetAttribute(embed_ln_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, v));
+}
+
 void f32_to_bf16(const float* src, bf16* dst, int64_t n, cudaStream_t s) {
   f32_to_bf16_kernel<<<blocks_for(n, 256), 256, 0, s>>>(src, dst, n);
   LAUNCH_OK();

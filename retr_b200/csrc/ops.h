@@ -4,6 +4,8 @@
 
 namespace retr {
 
+void ops_prefer_max_shared();   // ops.cu: see the definition
+
 // ---- weight repack ------------------------------------------------------------------------
 void f32_to_bf16(const float* src, bf16* dst, int64_t n, cudaStream_t s);
 // conv filter OIHW fp32 -> O,(H,W,I) rows of length kpad (zero padded), fp32 or bf16
@@ -51,13 +53,18 @@ template <typename T> void attention(const AttnParams& p, cudaStream_t s);
 void flash_attention_bf16(const AttnParams& p, int dh, cudaStream_t s);   // attention_mma.cu
 
 // ---- greedy decode (decode_ops.cu) --------------------------------------------------------------
-// Single-query attention over a K/V cache of rows [K(d) | V(d)] (pitch ldkv), one CTA per (b, head).
+// Single-query attention over head-major K/V caches ([B][H][cache_rows][dh] each), one CTA per (b, head).
 //   self: appends this step's k,v (from qkv rows [q|k|v]) at position *step, attends keys 0..*step
 //   cross: attends keys 0..n_keys-1 honouring key_pad
 template <typename T>
-void decode_attention(const T* q, int64_t ldq, const T* new_kv, int64_t ld_new, T* cache, int64_t ld_cache,
-                      int64_t cache_batch_pitch, T* out, int64_t ldo, int B, int H, int d, int n_keys,
-                      const int* step_dyn, const uint8_t* key_pad, int64_t ld_pad, cudaStream_t s);
+void decode_attention(const T* q, int64_t ldq, const T* new_kv, int64_t ld_new, T* kcache, T* vcache, int cache_rows,
+                      T* out, int64_t ldo, int B, int H, int d, int n_keys, const int* step_dyn,
+                      const uint8_t* key_pad, int64_t ld_pad, cudaStream_t s);
+// opt in to the dynamic shared memory the kernel needs (call once, outside stream capture)
+template <typename T> void decode_attention_configure(int max_rows, int dh);
+// rows of [K(d) | V(d)] -> head-major K and V blocks
+template <typename T>
+void kv_to_head_major(const T* kv, T* kh, T* vh, int B, int rows, int H, int dh, cudaStream_t s);
 // After the vocab GEMM+argmax of step i=*step: the bookkeeping of eval_utils/decode.py:70-79.
 void greedy_update(unsigned long long* argmax_keys, int64_t* caption, int max_len, int B, int eos, int* step,
                    int* done, uint8_t* finished, cudaStream_t s);
