@@ -1,0 +1,115 @@
+"""CPU-side checks: the C-ABI library loads and exports every symbol include/retr_b200.h declares
+(no compute calls), and the host-side mirrors of the reference's helper functions behave like
+the reference (eval_utils/decode.py, engine.py, models/utils.py)."""
+import os
+import re
+
+import pytest
+import torch
+
+from conftest import ROOT, build_product_model
+from oracle import retr_oracle as O
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "retr_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(retr_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_are_exported_and_bound():
+    import __graft_entry__
+    __graft_entry__.build()
+    from retr_b200 import native
+    lib = native.lib()
+    names = declared_symbols()
+    assert len(names) >= 18
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/retr_b200.h but not exported"
+        assert n in native.SIGNATURES, f"{n} has no ctypes signature"
+    assert sorted(native.SIGNATURES) == names
+    assert lib.retr_abi_version() == 1
+    assert isinstance(lib.retr_last_error(), bytes)
+
+
+def test_no_cuda_means_loud_failure():
+    """The product path has no CPU fallback: a CPU-resident model refuses to run."""
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    model, _, _ = build_product_model("Caption")
+    from retr_b200 import synthetic
+    data = synthetic.make_batch(1, train=True)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        model.eval()(*synthetic.pack(data, "Caption"), data["caps"][:, :-1], data["cap_masks"][:, :-1])
+    from retr_b200.eval_utils import decode
+    with pytest.raises(RuntimeError, match="CUDA"):
+        decode.greedy(synthetic.pack(data, "Caption"), model, max_len=128, device="cpu", bos_token=101, eos_token=102)
+
+
+def test_product_never_imports_oracle():
+    """oracle/ is test infrastructure: nothing under retr_b200/ may import it."""
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "retr_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in text and "from oracle" not in text, os.path.join(dirpath, f)
+
+
+def test_create_caption_and_mask_and_prune():
+    from retr_b200.eval_utils import decode
+    cap, msk = decode.create_caption_and_mask(101, 128, 3)
+    rcap, rmsk = O.create_caption_and_mask(101, 128, 3)
+    assert torch.equal(cap, rcap) and torch.equal(msk, rmsk)
+    rows = [[101, 5, 6, 102, 7, 0], [101, 9, 0, 0, 0, 0], [101, 102, 5, 5, 5, 5], [101, 7, 7, 7, 7, 7]]
+    for clean in (True, False):
+        assert decode.prune_cap_ids(rows, clean, 0, 101, 102) == O.prune_cap_ids(rows, clean, 0, 101, 102)
+    assert decode.prune_cap_ids(rows, True, 0, 101, 102) == [[5, 6], [9], [], [7, 7, 7, 7, 7]]
+
+
+def test_literal_greedy_with_foreign_callable():
+    """A callable that is not a retr_b200 model gets the reference's literal loop, including the
+    early return before the last EOS is written (eval_utils/decode.py:73-79)."""
+    from retr_b200.eval_utils import decode
+    from retr_b200.models.utils import NestedTensor
+    V = 50
+    script = {0: [7, 9, 102], 1: [8, 102, 4]}        # row -> token per step
+
+    def stub(samples, caption, cap_mask):
+        B, T = caption.shape
+        out = torch.zeros(B, T, V + 60)
+        filled = int((~cap_mask[0]).sum())            # positions written so far
+        for b in range(B):
+            tok = script[b][min(filled - 1, 2)]
+            out[b, filled - 1, tok] = 1.0
+        return out
+
+    s = (NestedTensor(torch.zeros(2, 3, 4, 4), torch.zeros(2, 4, 4, dtype=torch.bool)),)
+    ids = decode.greedy(s, stub, max_len=8, device="cpu", bos_token=101, eos_token=102)
+    # row 1 finishes at step 1 (EOS written), row 0 at step 2 -> return without writing step 2
+    assert ids.tolist() == [[101, 7, 9, 0, 0, 0, 0, 0], [101, 8, 102, 0, 0, 0, 0, 0]]
+
+
+def test_pack_encoder_inputs_shapes():
+    from retr_b200 import engine
+    t, tm = torch.zeros(2, 3, 8, 8), torch.zeros(2, 8, 8, dtype=torch.bool)
+    loc = torch.zeros(2, 5)
+    assert len(engine.pack_encoder_inputs((t, tm), False, False)) == 1
+    out = engine.pack_encoder_inputs((t, tm, loc), False, True)
+    assert len(out) == 2 and out[1].shape == (2, 5)
+    out = engine.pack_encoder_inputs((t, tm, t, tm), True, False)
+    assert len(out) == 2 and out[1].shape == tm.shape            # NestedTensor.shape is the mask shape
+    out = engine.pack_encoder_inputs((t, tm, t, tm, loc), True, True)
+    assert len(out) == 3 and out[0].shape[0] == 2
+
+
+def test_build_model_flag_matrix():
+    from retr_b200.configuration import Config
+    from retr_b200.models import caption
+    with pytest.raises(NotImplementedError):
+        caption.build_model(Config(use_global_features=True, use_location_features=False))
+    for kind, n_img, loc in (("Caption", 1, 0), ("CaptionLoc", 1, 7), ("CaptionGlobalLoc", 2, 1)):
+        m, crit, _ = build_product_model(kind)
+        assert m.__class__.__name__ == kind and m.n_images == n_img and m.loc_in_dim == loc
+        assert isinstance(crit, torch.nn.CrossEntropyLoss)
+        frozen = [n for n, p in m.named_parameters() if not p.requires_grad]
+        assert all("backbone.body.conv1" in n or "backbone.body.layer1" in n for n in frozen) and frozen
