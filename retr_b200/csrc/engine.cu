@@ -13,6 +13,7 @@
 // (q=k=LN(x)+pos, q=LN(y)+query_pos, k=memory+pos) is folded into a per-position bias table,
 // W(x+p)+b = Wx + (Wp+b), computed once in fp32 at weight-load time (rowbias epilogue).
 #include "engine.h"
+#include "small_gemm.h"
 
 #include <tuple>
 #include <type_traits>
@@ -93,6 +94,9 @@ class EngineT final : public EngineBase {
   void backbone(const float* img, int64_t n, T* feat, cudaStream_t s);
   void decoder_layers_full(int B, const uint8_t* id_mask, float* att_self, float* att_cross, cudaStream_t s);
   void decode_step(int B, int eos, int max_len, cudaStream_t s);
+  void decode_step_fused(int B, int eos, int max_len, cudaStream_t s);
+  void dgemm(const Linear<T>& l, const T* A, const float* X, const float* g, const float* b, void* C, bool out_fp32,
+             int B, const float* rowbias, int relu, const float* residual, int split_k, cudaStream_t s);
   void alloc_buffers();
   GemmParams lin(const Linear<T>& l, const void* A, int64_t M, void* C) {
     GemmParams p;
@@ -126,7 +130,10 @@ class EngineT final : public EngineBase {
   unsigned long long* argmax_keys_ = nullptr;
   std::map<std::tuple<int, int, int>, cudaGraphExec_t> graphs_;
   cudaStream_t capture_stream_ = nullptr;
-  long long step_kernels_ = 0;                       // kernels in one captured decode step
+  long long step_kernels_ = 0;
+  float* splitk_scratch_ = nullptr;                  // [4][B][d] partial sums of the FFN second linear
+  unsigned* splitk_tickets_ = nullptr;
+  bool fast_decode_ = false;                         // bf16: small_gemm (LN fused) for the decode step                       // kernels in one captured decode step
 };
 
 // ---- weight preparation -------------------------------------------------------------------------
@@ -316,6 +323,12 @@ void EngineT<T>::alloc_buffers() {
   argmax_keys_ = static_cast<unsigned long long*>(dalloc(Md * 8));
   CUDA_OK(cudaMemset(argmax_keys_, 0, Md * 8));
   CUDA_OK(cudaMallocHost(&done_host_, 16));
+  splitk_scratch_ = static_cast<float*>(dalloc((size_t)4 * B * std::max<int64_t>(d, 512) * 4));
+  splitk_tickets_ = static_cast<unsigned*>(dalloc(4096 * 4));
+  CUDA_OK(cudaMemset(splitk_tickets_, 0, 4096 * 4));
+  fast_decode_ = std::is_same<T, bf16>::value && getenv("RETR_NO_FAST_DECODE") == nullptr && (d == 256 || d == 512) &&
+                 ff % 256 == 0;
+  if (fast_decode_) small_gemm_configure();
   if (getenv("RETR_NO_CARVEOUT_HINT") == nullptr) ops_prefer_max_shared();
   decode_attention_configure<T>(std::max<int>(S, (int)Tn), (int)(d / desc.n_heads));
 }
@@ -509,6 +522,7 @@ void EngineT<T>::teacher_forced(const int64_t* ids, const uint8_t* id_mask, floa
 // ---- one KV-cached greedy step; position = *step_ (device) --------------------------------------------------
 template <typename T>
 void EngineT<T>::decode_step(int B, int eos, int max_len, cudaStream_t s) {
+  if (fast_decode_) return decode_step_fused(B, eos, max_len, s);
   const int d = desc.d_model, Tn = desc.max_pos, H = desc.n_heads;
   embed_ln(caption_, max_len, e_word_, e_pos_, emb_g_, emb_b_, y_, B, 1, 0, step_, d, desc.embed_ln_eps, s);
   for (int l = 0; l < desc.dec_layers; ++l) {
@@ -543,6 +557,51 @@ void EngineT<T>::decode_step(int B, int eos, int max_len, cudaStream_t s) {
   GemmParams p = lin(mlp_[0], hs_, B, m1_); p.relu = 1; gemm<T>(p, s);
   p = lin(mlp_[1], m1_, B, m2_); p.relu = 1; gemm<T>(p, s);
   p = lin(mlp_[2], m2_, B, nullptr); p.argmax_out = argmax_keys_; gemm<T>(p, s);     // logits never reach HBM
+  greedy_update(argmax_keys_, caption_, max_len, B, eos, step_, done_, finished_, s);
+}
+
+// bf16 decode GEMM through small_gemm.cu: A (bf16) or LayerNorm(X) as the left operand.
+template <>
+void EngineT<float>::dgemm(const Linear<float>&, const float*, const float*, const float*, const float*, void*, bool, int,
+                           const float*, int, const float*, int, cudaStream_t) {
+  throw Error("fused decode step is a bf16-only path");
+}
+template <>
+void EngineT<bf16>::dgemm(const Linear<bf16>& l, const bf16* A, const float* X, const float* g, const float* b, void* C,
+                          bool out_fp32, int B, const float* rowbias, int relu, const float* residual, int split_k,
+                          cudaStream_t s) {
+  SmallGemmParams p;
+  p.A = A; p.lda = l.in; p.X = X; p.ldx = l.in; p.gamma = g; p.beta = b; p.eps = 1e-5f;
+  p.W = l.w; p.C = C; p.ldc = l.out; p.out_fp32 = out_fp32;
+  p.M = B; p.N = l.out; p.K = l.in;
+  p.bias = l.b; p.rowbias = rowbias; p.rowbias_dyn = rowbias ? step_ : nullptr;
+  p.residual = residual; p.ldr = l.out; p.relu = relu;
+  p.split_k = split_k; p.scratch = splitk_scratch_; p.tickets = splitk_tickets_;
+  small_gemm(p, s);
+}
+
+// One KV-cached greedy step, bf16: every pre-norm LayerNorm is the prologue of the GEMM it feeds
+// (8 kernels per decoder layer instead of 11), small-M mma.sync GEMMs, deterministic split-K for FFN2.
+template <typename T>
+void EngineT<T>::decode_step_fused(int B, int eos, int max_len, cudaStream_t s) {
+  const int d = desc.d_model, Tn = desc.max_pos, H = desc.n_heads;
+  const int kpan = desc.d_ff / 256;
+  const int split = kpan % 4 == 0 ? 4 : (kpan % 2 == 0 ? 2 : 1);
+  embed_ln(caption_, max_len, e_word_, e_pos_, emb_g_, emb_b_, y_, B, 1, 0, step_, d, desc.embed_ln_eps, s);
+  for (int l = 0; l < desc.dec_layers; ++l) {
+    const DecLayer<T>& e = dec_[l];
+    dgemm(e.s_qkv, nullptr, y_, e.ln1_g, e.ln1_b, qkv_, false, B, e.rb_s_qkv, 0, nullptr, 1, s);
+    decode_attention<T>(qkv_, 3 * d, qkv_ + d, 3 * d, sk_[l], sv_[l], Tn, att_, d, B, H, d, 0, step_, nullptr, 0, s);
+    dgemm(e.s_out, att_, nullptr, nullptr, nullptr, y_, true, B, nullptr, 0, y_, 1, s);
+    dgemm(e.c_q, nullptr, y_, e.ln2_g, e.ln2_b, qc_, false, B, e.rb_c_q, 0, nullptr, 1, s);
+    decode_attention<T>(qc_, d, nullptr, 0, ck_[l], cv_[l], S, att_, d, B, H, d, S, nullptr, tok_mask_, S, s);
+    dgemm(e.c_out, att_, nullptr, nullptr, nullptr, y_, true, B, nullptr, 0, y_, 1, s);
+    dgemm(e.ff1, nullptr, y_, e.ln3_g, e.ln3_b, h_, false, B, nullptr, 1, nullptr, 1, s);
+    dgemm(e.ff2, h_, nullptr, nullptr, nullptr, y_, true, B, nullptr, 0, y_, split, s);
+  }
+  dgemm(mlp_[0], nullptr, y_, dec_norm_g_, dec_norm_b_, m1_, false, B, nullptr, 1, nullptr, 1, s);
+  dgemm(mlp_[1], m1_, nullptr, nullptr, nullptr, m2_, false, B, nullptr, 1, nullptr, 1, s);
+  GemmParams p = lin(mlp_[2], m2_, B, nullptr); p.argmax_out = argmax_keys_; gemm<T>(p, s);     // logits never reach HBM
   greedy_update(argmax_keys_, caption_, max_len, B, eos, step_, done_, finished_, s);
 }
 

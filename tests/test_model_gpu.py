@@ -182,3 +182,33 @@ def test_generate_host_matches_device_path():
     assert steps == 127
     assert torch.equal(out, ids)
     assert eng.kernel_launches() > 0
+
+
+def test_scaled_variant_d512_heads64():
+    """BASELINE.json configs[4] geometry in miniature: hidden_dim 512 (head dim 64), a different Bottleneck
+    ResNet, fewer layers so the CPU oracle stays fast — exercises the dh=64 attention kernels, the K=512
+    LayerNorm-prologue GEMM and the S/T-dependent buffers."""
+    from retr_b200.configuration import Config
+    from retr_b200.models import caption
+    cfg = Config(use_global_features=True, use_location_features=True, backbone="ResNet50", hidden_dim=512,
+                 enc_layers=2, dec_layers=2)
+    torch.manual_seed(7)
+    model, _ = caption.build_model(cfg)
+    model.load_state_dict(synthetic.calibrate_frozen_bn(model.state_dict()))
+    sd = {k: v.clone() for k, v in model.state_dict().items()}
+    kind = "CaptionGlobalLoc"
+    data, enc_in = synthetic_samples(kind, 2, shard=4)
+    caps, cm = data["caps"], data["cap_masks"]
+    with torch.no_grad():
+        ref = O.forward(sd, cfg, *enc_in, caps[:, :-1], cm[:, :-1])
+        ref_ids, _ = O.greedy(sd, cfg, *enc_in, max_len=128, bos_token=101, eos_token=102, literal=False, max_steps=12)
+    model = model.to("cuda").eval()
+    for precision, tol_rel in (("fp32", 1e-4), ("bf16", BF16_LOGIT_TOL)):
+        model.precision = precision
+        with torch.no_grad():
+            logits = model(*samples_of(kind, enc_in), caps[:, :-1].cuda(), cm[:, :-1].cuda()).cpu()
+            ids = decode.greedy(samples_of(kind, enc_in, "cpu"), model, max_len=128, device="cuda", bos_token=101,
+                                eos_token=102).cpu()
+        assert (logits - ref).abs().max().item() <= tol_rel * ref.abs().max().item(), precision
+        if precision == "fp32":
+            assert torch.equal(ids[:, :13], ref_ids[:, :13])
