@@ -6,6 +6,10 @@ namespace retr {
 thread_local long long g_launches = 0;
 static thread_local std::string g_error;
 void set_error(const std::string& msg) { g_error = msg; }
+bool pdl_enabled() {
+  static const bool on = getenv("RETR_NO_PDL") == nullptr;
+  return on;
+}
 }  // namespace retr
 
 using namespace retr;

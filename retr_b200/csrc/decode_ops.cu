@@ -89,6 +89,8 @@ decode_attention_kernel(const T* __restrict__ q, int64_t ldq, const T* __restric
   const int e0 = h * DH + sub * VN;                         // this lane's slice of the model dim
   T* kg = kcache + (size_t)bh * cache_rows * DH;
   T* vg = vcache + (size_t)bh * cache_rows * DH;
+  pdl_launch_dependents();
+  pdl_wait();
   const int n_cached = new_kv ? *step_dyn : n_keys;
   if (threadIdx.x == 0) {
     ptx::mbar_init(&bar[0], 1);
@@ -234,6 +236,7 @@ __global__ void greedy_init_kernel(int64_t* caption, int max_len, int B, int bos
 __global__ void greedy_update_kernel(unsigned long long* keys, int64_t* caption, int max_len, int B, int eos,
                                      int* step, int* done, uint8_t* finished) {
   __shared__ int unfinished;
+  pdl_wait();
   if (*done) return;
   const int i = *step;
   if (threadIdx.x == 0) unfinished = 0;
@@ -269,9 +272,8 @@ void decode_attention(const T* q, int64_t ldq, const T* new_kv, int64_t ld_new, 
   const size_t smem = (size_t)2 * cache_rows * dh * sizeof(T);        // K block + V block
   RETR_CHECK(smem <= 220 * 1024 && cache_rows <= DA_MAX_KEYS, "K/V block does not fit in shared memory");
   auto kern = dh == 32 ? decode_attention_kernel<T, 32> : decode_attention_kernel<T, 64>;
-  kern<<<(unsigned)(B * H), DA_WARPS * 32, smem, s>>>(q, ldq, new_kv, ld_new, kcache, vcache, cache_rows, out, ldo, d, H,
-                                                      n_keys, step_dyn, key_pad, ld_pad);
-  LAUNCH_OK();
+  launch_pdl(kern, dim3((unsigned)(B * H)), dim3(DA_WARPS * 32), smem, s, q, ldq, new_kv, ld_new, kcache, vcache,
+             cache_rows, out, ldo, d, H, n_keys, step_dyn, key_pad, ld_pad);
 }
 template <typename T>
 void decode_attention_configure(int max_rows, int dh) {
@@ -298,8 +300,7 @@ template void kv_to_head_major<bf16>(const bf16*, bf16*, bf16*, int, int, int, i
 
 void greedy_update(unsigned long long* argmax_keys, int64_t* caption, int max_len, int B, int eos, int* step,
                    int* done, uint8_t* finished, cudaStream_t s) {
-  greedy_update_kernel<<<1, 1024, 0, s>>>(argmax_keys, caption, max_len, B, eos, step, done, finished);
-  LAUNCH_OK();
+  launch_pdl(greedy_update_kernel, dim3(1), dim3(1024), 0, s, argmax_keys, caption, max_len, B, eos, step, done, finished);
 }
 
 void greedy_init(int64_t* caption, int max_len, int B, int bos, int* step, int* done, uint8_t* finished,

@@ -148,6 +148,8 @@ __global__ void embed_ln_kernel(const int64_t* __restrict__ ids, int64_t ld_ids,
                                 const float* __restrict__ e_pos, const float* __restrict__ gamma,
                                 const float* __restrict__ beta, float* __restrict__ y, int B, int rows_per, int t0,
                                 const int* __restrict__ t0_dyn, int d, float eps) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= (int64_t)B * rows_per) return;
   if (t0_dyn) t0 = *t0_dyn;
@@ -233,9 +235,8 @@ void embed_ln(const int64_t* ids, int64_t ld_ids, const float* e_word, const flo
               const float* beta, float* y, int B, int rows_per, int t0, const int* t0_dyn, int d, float eps,
               cudaStream_t s) {
   RETR_CHECK(d % 32 == 0 && d <= 1024, "embedding width");
-  embed_ln_kernel<<<blocks_for((int64_t)B * rows_per, 8), 256, 0, s>>>(ids, ld_ids, e_word, e_pos, gamma, beta, y, B,
-                                                                       rows_per, t0, t0_dyn, d, eps);
-  LAUNCH_OK();
+  launch_pdl(embed_ln_kernel, dim3(blocks_for((int64_t)B * rows_per, 8)), dim3(256), 0, s, ids, ld_ids, e_word, e_pos,
+             gamma, beta, y, B, rows_per, t0, t0_dyn, d, eps);
 }
 
 }  // namespace retr

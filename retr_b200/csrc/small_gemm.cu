@@ -62,7 +62,9 @@ __global__ void __launch_bounds__(SM_THREADS) small_gemm_kernel(const SmallGemmP
     }
   };
 
-  load_w(0, 0);
+  pdl_launch_dependents();
+  load_w(0, 0);                                     // weights do not depend on the previous kernel
+  pdl_wait();                                       // ... activations, step counter and residual do
   if (!p.X) load_a(0, 0);
   asm volatile("cp.async.commit_group;" ::: "memory");
   // Epilogue operands are fetched NOW (same memory round trip as the operand panels) so the tail of the
@@ -253,9 +255,8 @@ void small_gemm(const SmallGemmParams& p_in, cudaStream_t s) {
   RETR_CHECK(p.split_k == 1 || (p.scratch && p.tickets), "small_gemm: split-K needs scratch and tickets");
   RETR_CHECK(p.N % 2 == 0 && p.ldc % 2 == 0, "small_gemm: even N / ldc");
   dim3 grid((unsigned)cdiv(p.N, SM_BN), (unsigned)cdiv(p.M, SM_BM), (unsigned)p.split_k);
-  if (kc == 512) small_gemm_kernel<512><<<grid, SM_THREADS, sg_smem_bytes<512>(), s>>>(p);
-  else small_gemm_kernel<256><<<grid, SM_THREADS, sg_smem_bytes<256>(), s>>>(p);
-  LAUNCH_OK();
+  if (kc == 512) launch_pdl(small_gemm_kernel<512>, grid, dim3(SM_THREADS), sg_smem_bytes<512>(), s, p);
+  else launch_pdl(small_gemm_kernel<256>, grid, dim3(SM_THREADS), sg_smem_bytes<256>(), s, p);
 }
 
 }  // namespace retr
