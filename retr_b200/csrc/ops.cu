@@ -3,6 +3,8 @@
 // 16-byte accesses where the layout allows; grids are sized from the element count.
 #include "ops.h"
 
+#include <algorithm>
+
 namespace retr {
 namespace {
 
@@ -54,21 +56,35 @@ __global__ void stem_im2col_kernel(const float* __restrict__ img, T* __restrict_
     v[j] = x;
   }
   T* o = out + m * kpad + k0;
+  if (sizeof(T) == 2) {                              // one 16-byte store per thread
+    uint4 t;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&t);
 #pragma unroll
-  for (int j = 0; j < 8; ++j) o[j] = from_f<T>(v[j]);
+    for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+    *reinterpret_cast<uint4*>(o) = t;
+  } else {
+    float* of = reinterpret_cast<float*>(o);
+    *reinterpret_cast<float4*>(of) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(of + 4) = make_float4(v[4], v[5], v[6], v[7]);
+  }
 }
 
+// 16 bytes of channels per thread (8 bf16 / 4 fp32): 9 vector loads, one vector store.
 template <typename T>
 __global__ void maxpool_kernel(const T* __restrict__ in, T* __restrict__ out, int64_t total, int H, int W, int C,
                                int OH, int OW) {
-  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // over (n, oh, ow, c)
+  constexpr int VN = 16 / sizeof(T);
+  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // over (n, oh, ow, c / VN)
   if (idx >= total) return;
-  const int c = (int)(idx % C);
-  int64_t t = idx / C;
+  const int cv = C / VN;
+  const int c = (int)(idx % cv) * VN;
+  int64_t t = idx / cv;
   const int ow = (int)(t % OW); t /= OW;
   const int oh = (int)(t % OH);
   const int64_t n = t / OH;
-  float best = -INFINITY;
+  float best[VN];
+#pragma unroll
+  for (int i = 0; i < VN; ++i) best[i] = -INFINITY;
 #pragma unroll
   for (int r = 0; r < 3; ++r) {
     const int ih = oh * 2 - 1 + r;
@@ -77,10 +93,17 @@ __global__ void maxpool_kernel(const T* __restrict__ in, T* __restrict__ out, in
     for (int s = 0; s < 3; ++s) {
       const int iw = ow * 2 - 1 + s;
       if (iw < 0 || iw >= W) continue;
-      best = fmaxf(best, to_f(in[((n * H + ih) * W + iw) * C + c]));
+      const uint4 raw = *reinterpret_cast<const uint4*>(in + ((n * H + ih) * W + iw) * C + c);
+      const T* e = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+      for (int i = 0; i < VN; ++i) best[i] = fmaxf(best[i], to_f(e[i]));
     }
   }
-  out[idx] = from_f<T>(best);
+  uint4 o;
+  T* e = reinterpret_cast<T*>(&o);
+#pragma unroll
+  for (int i = 0; i < VN; ++i) e[i] = from_f<T>(best[i]);
+  *reinterpret_cast<uint4*>(out + (((n * OH + oh) * OW + ow) * C + c)) = o;
 }
 
 __global__ void subsample_mask_kernel(const uint8_t* __restrict__ m, uint8_t* __restrict__ tok, int B, int H, int W,
@@ -129,6 +152,52 @@ __device__ __forceinline__ void ln_row(float (&v)[MAXPER], int per, int lane, co
       const int c = i * 32 + lane;
       y[c] = from_f<T>((v[i] - mean) * rstd * gamma[c] + beta[c]);
     }
+}
+
+// One warp per row, float4 loads (lane holds columns j*128 + lane*4 .. +3), d % 128 == 0.
+template <typename T, int D>
+__global__ void layernorm_vec_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                     const float* __restrict__ beta, T* __restrict__ y, int64_t rows, float eps) {
+  constexpr int NV = D / 128;
+  const int lane = threadIdx.x & 31;
+  float4 g[NV], be[NV];
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    g[j] = __ldg(reinterpret_cast<const float4*>(gamma + j * 128 + lane * 4));
+    be[j] = __ldg(reinterpret_cast<const float4*>(beta + j * 128 + lane * 4));
+  }
+  const int64_t wstride = (int64_t)gridDim.x * (blockDim.x >> 5);
+  for (int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < rows; row += wstride) {
+    float4 v[NV];
+#pragma unroll
+    for (int j = 0; j < NV; ++j) v[j] = *reinterpret_cast<const float4*>(x + row * D + j * 128 + lane * 4);
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) s += v[j].x + v[j].y + v[j].z + v[j].w;
+    const float mean = warp_sum(s) * (1.f / D);
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const float a = v[j].x - mean, b2 = v[j].y - mean, c = v[j].z - mean, d2 = v[j].w - mean;
+      q += a * a + b2 * b2 + c * c + d2 * d2;
+    }
+    const float rstd = rsqrtf(warp_sum(q) * (1.f / D) + eps);
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const float o0 = (v[j].x - mean) * rstd * g[j].x + be[j].x, o1 = (v[j].y - mean) * rstd * g[j].y + be[j].y;
+      const float o2 = (v[j].z - mean) * rstd * g[j].z + be[j].z, o3 = (v[j].w - mean) * rstd * g[j].w + be[j].w;
+      T* dst = y + row * D + j * 128 + lane * 4;
+      if (sizeof(T) == 4) {
+        *reinterpret_cast<float4*>(dst) = make_float4(o0, o1, o2, o3);
+      } else {
+        __nv_bfloat162 lo = __floats2bfloat162_rn(o0, o1), hi = __floats2bfloat162_rn(o2, o3);
+        uint2 pk;
+        pk.x = *reinterpret_cast<uint32_t*>(&lo);
+        pk.y = *reinterpret_cast<uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(dst) = pk;
+      }
+    }
+  }
 }
 
 template <typename T>
@@ -200,7 +269,8 @@ template void stem_im2col<bf16>(const float*, bf16*, int64_t, int, int, int, int
 
 template <typename T>
 void maxpool_3x3s2(const T* in, T* out, int64_t nimg, int H, int W, int C, int OH, int OW, cudaStream_t s) {
-  const int64_t total = nimg * OH * OW * C;
+  RETR_CHECK(C % (16 / (int)sizeof(T)) == 0, "maxpool channel count");
+  const int64_t total = nimg * OH * OW * (C / (16 / (int)sizeof(T)));
   maxpool_kernel<T><<<blocks_for(total, 256), 256, 0, s>>>(in, out, total, H, W, C, OH, OW);
   LAUNCH_OK();
 }
@@ -225,6 +295,13 @@ template <typename T>
 void layernorm(const float* x, const float* gamma, const float* beta, T* y, int64_t rows, int d, float eps,
                cudaStream_t s) {
   RETR_CHECK(d % 32 == 0 && d <= 1024, "LayerNorm width must be a multiple of 32, <= 1024");
+  if (d == 256 || d == 512) {
+    const unsigned grid = (unsigned)std::min<int64_t>(cdiv(rows, 8), 148 * 8);     // grid-stride, 8 warps per CTA
+    if (d == 256) layernorm_vec_kernel<T, 256><<<grid, 256, 0, s>>>(x, gamma, beta, y, rows, eps);
+    else layernorm_vec_kernel<T, 512><<<grid, 256, 0, s>>>(x, gamma, beta, y, rows, eps);
+    LAUNCH_OK();
+    return;
+  }
   layernorm_kernel<T><<<blocks_for(rows, 8), 256, 0, s>>>(x, gamma, beta, y, rows, d, eps);
   LAUNCH_OK();
 }
