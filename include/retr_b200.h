@@ -129,6 +129,44 @@ int retr_op_attention(int32_t dtype, const void* q, const void* k, const void* v
                       int64_t ldk, int64_t ldv, int64_t ldo, const uint8_t* key_pad,
                       int32_t causal, float* probs, void* stream);
 
+/* ---- training step (engine.py:52-87 train_one_epoch; optimiser recipe main.py:30-40) ------------- */
+typedef struct retr_trainer retr_trainer;
+
+/* replaces: model.train() + the module tree as seen by loss.backward().  `pad_token_id` is the
+ * nn.Embedding padding_idx whose row receives no gradient (models/transformer_modules.py:103-105). */
+int  retr_train_create(const retr_model_desc* desc, int32_t pad_token_id, retr_trainer** out);
+void retr_train_destroy(retr_trainer* tr);
+/* Bind one reference state_dict entry (SURVEY Appendix B key).  `param`: fp32 device memory that the
+ * trainer READS at every step (nothing is copied: an optimiser may update it in place).  `grad`: fp32
+ * device memory of the same shape that retr_train_backward overwrites, or NULL for a frozen parameter or
+ * a buffer (requires_grad False: conv1/layer1, models/backbone.py:58-60; FrozenBatchNorm2d buffers). */
+int retr_train_bind(retr_trainer* tr, const char* name, float* param, float* grad, const int64_t* shape,
+                    int32_t ndim);
+int retr_train_finalize(retr_trainer* tr);
+/* replaces: outputs = model(*samples, caps[:, :-1], cap_masks[:, :-1]) in train mode (engine.py:70):
+ * dropout `dropout_p` at the reference's sites (embeddings, attention probabilities, residual branches)
+ * from a counter-based Philox stream keyed by `seed`; activations are kept for the backward pass.
+ * logits fp32 [B,T,vocab]. */
+int retr_train_forward(retr_trainer* tr, int32_t batch, const float* t_img, const uint8_t* t_mask,
+                       const float* g_img, const uint8_t* g_mask, const float* loc, const int64_t* ids,
+                       const uint8_t* id_mask, float* logits, float dropout_p, uint64_t seed, void* stream);
+/* replaces: loss.backward() (engine.py:80) below the logits: dlogits fp32 [B,T,vocab] -> bound grads. */
+int retr_train_backward(retr_trainer* tr, const float* dlogits, void* stream);
+/* replaces: engine.py:70-80 in one call — forward, CrossEntropyLoss (mean over all B*T positions, pads
+ * included, models/caption.py:210) against targets int64 [B,T], backward.  loss_sum_dev (device fp32)
+ * receives the SUM of the per-position losses (divide by B*T); the logits never leave bf16/HBM. */
+int retr_train_loss_and_grads(retr_trainer* tr, int32_t batch, const float* t_img, const uint8_t* t_mask,
+                              const float* g_img, const uint8_t* g_mask, const float* loc, const int64_t* ids,
+                              const uint8_t* id_mask, const int64_t* targets, float dropout_p, uint64_t seed,
+                              float* loss_sum_dev, void* stream);
+/* replaces: clip_grad_norm_(model.parameters(), max_norm) + AdamW.step() (engine.py:81-83, main.py:30-40):
+ * entries whose name contains "backbone" use lr_backbone.  step is the 1-based update count.
+ * grad_sumsq_dev (optional, device fp32): squared global gradient norm before clipping. */
+int retr_train_clip_adamw(retr_trainer* tr, float max_norm, float lr, float lr_backbone, float beta1,
+                          float beta2, float eps, float weight_decay, int32_t step, float* grad_sumsq_dev,
+                          void* stream);
+int64_t retr_train_kernel_launches(const retr_trainer* tr);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,6 +1,7 @@
 // extern "C" surface declared in include/retr_b200.h.  Every entry point converts C++ exceptions
 // into a non-zero status + retr_last_error(); there is no CPU fallback behind any of them.
 #include "engine.h"
+#include "train.h"
 
 namespace retr {
 thread_local long long g_launches = 0;
@@ -16,6 +17,10 @@ using namespace retr;
 
 struct retr_ctx {
   std::unique_ptr<EngineBase> eng;
+};
+struct retr_trainer {
+  std::unique_ptr<TrainerBase> tr;
+  int device = 0;
 };
 
 #define API_BEGIN try {
@@ -172,5 +177,84 @@ int retr_op_attention(int32_t dtype, const void* q, const void* k, const void* v
   else throw Error("unknown dtype");
   API_END
 }
+
+// ---- training ------------------------------------------------------------------------------------------
+int retr_train_create(const retr_model_desc* desc, int32_t pad_token_id, retr_trainer** out) {
+  API_BEGIN
+  RETR_CHECK(desc && out, "null argument");
+  int ndev = 0;
+  CUDA_OK(cudaGetDeviceCount(&ndev));
+  RETR_CHECK(desc->device >= 0 && desc->device < ndev, "no such CUDA device");
+  cudaDeviceProp prop;
+  CUDA_OK(cudaGetDeviceProperties(&prop, desc->device));
+  RETR_CHECK(prop.major == 10, std::string("retr_b200 is built for sm_100a only; device is sm_") +
+                                   std::to_string(prop.major) + std::to_string(prop.minor));
+  retr_trainer* t = new retr_trainer;
+  try {
+    t->tr = make_trainer(*desc, pad_token_id);
+    t->device = desc->device;
+  } catch (...) {
+    delete t;
+    throw;
+  }
+  *out = t;
+  API_END
+}
+
+void retr_train_destroy(retr_trainer* tr) { delete tr; }
+
+int retr_train_bind(retr_trainer* tr, const char* name, float* param, float* grad, const int64_t* shape, int32_t ndim) {
+  API_BEGIN
+  RETR_CHECK(tr && name && param && shape, "null argument");
+  tr->tr->bind(name, param, grad, shape, ndim);
+  API_END
+}
+
+int retr_train_finalize(retr_trainer* tr) {
+  API_BEGIN
+  RETR_CHECK(tr, "null trainer");
+  CUDA_OK(cudaSetDevice(tr->device));
+  tr->tr->finalize();
+  API_END
+}
+
+int retr_train_forward(retr_trainer* tr, int32_t batch, const float* t_img, const uint8_t* t_mask, const float* g_img,
+                       const uint8_t* g_mask, const float* loc, const int64_t* ids, const uint8_t* id_mask, float* logits,
+                       float dropout_p, uint64_t seed, void* stream) {
+  API_BEGIN
+  RETR_CHECK(tr && logits, "null argument");
+  tr->tr->forward(batch, t_img, t_mask, g_img, g_mask, loc, ids, id_mask, logits, dropout_p, seed,
+                  static_cast<cudaStream_t>(stream));
+  API_END
+}
+
+int retr_train_backward(retr_trainer* tr, const float* dlogits, void* stream) {
+  API_BEGIN
+  RETR_CHECK(tr, "null trainer");
+  tr->tr->backward(dlogits, static_cast<cudaStream_t>(stream));
+  API_END
+}
+
+int retr_train_loss_and_grads(retr_trainer* tr, int32_t batch, const float* t_img, const uint8_t* t_mask,
+                              const float* g_img, const uint8_t* g_mask, const float* loc, const int64_t* ids,
+                              const uint8_t* id_mask, const int64_t* targets, float dropout_p, uint64_t seed,
+                              float* loss_sum_dev, void* stream) {
+  API_BEGIN
+  RETR_CHECK(tr, "null trainer");
+  tr->tr->loss_and_grads(batch, t_img, t_mask, g_img, g_mask, loc, ids, id_mask, targets, dropout_p, seed, loss_sum_dev,
+                         static_cast<cudaStream_t>(stream));
+  API_END
+}
+
+int retr_train_clip_adamw(retr_trainer* tr, float max_norm, float lr, float lr_backbone, float beta1, float beta2,
+                          float eps, float weight_decay, int32_t step, float* grad_sumsq_dev, void* stream) {
+  API_BEGIN
+  RETR_CHECK(tr && step >= 1, "bad argument");
+  tr->tr->clip_adamw(max_norm, lr, lr_backbone, beta1, beta2, eps, weight_decay, step, grad_sumsq_dev,
+                     static_cast<cudaStream_t>(stream));
+  API_END
+}
+
+int64_t retr_train_kernel_launches(const retr_trainer* tr) { return tr ? tr->tr->launches : -1; }
 
 }  // extern "C"

@@ -299,8 +299,13 @@ template void kv_to_head_major<float>(const float*, float*, float*, int, int, in
 template void kv_to_head_major<bf16>(const bf16*, bf16*, bf16*, int, int, int, int, cudaStream_t);
 
 void greedy_update(unsigned long long* argmax_keys, int64_t* caption, int max_len, int B, int eos, int* step,
-                   int* done, uint8_t* finished, cudaStream_t s) {
-  launch_pdl(greedy_update_kernel, dim3(1), dim3(1024), 0, s, argmax_keys, caption, max_len, B, eos, step, done, finished);
+                   int* done, uint8_t* finished, cudaStream_t s, bool allow_pdl) {
+  if (allow_pdl) {
+    launch_pdl(greedy_update_kernel, dim3(1), dim3(1024), 0, s, argmax_keys, caption, max_len, B, eos, step, done, finished);
+  } else {      // joins several parallel branches: a plain (full) dependency on every one of them
+    greedy_update_kernel<<<1, 1024, 0, s>>>(argmax_keys, caption, max_len, B, eos, step, done, finished);
+    LAUNCH_OK();
+  }
 }
 
 void greedy_init(int64_t* caption, int max_len, int B, int bos, int* step, int* done, uint8_t* finished,

@@ -36,6 +36,13 @@ struct GemmParams {
   int c_group = 0, c_group_stride = 0;
   // If set, every row uses rowbias[*rowbias_dyn] (decode: the device-side step counter).
   const int* rowbias_dyn = nullptr;
+  // Weight-gradient shape (small M x N, very long K): split the contraction over split_k CTAs per output
+  // tile (0 = choose from the SM count), fp32 partial tiles in split_ws ([split_k*M, N] floats), summed into C
+  // (C += sum when accumulate).  Requires a plain fp32 C with ldc == N and no epilogue operands.
+  int split_k = 1;
+  float* split_ws = nullptr;
+  int64_t split_ws_floats = 0;
+  bool accumulate = false;
 };
 
 void gemm_fp32(const GemmParams& p, cudaStream_t stream);   // gemm_simt.cu  (A, W fp32)

@@ -23,6 +23,7 @@
 #include "engine.h"
 #include "gemm.h"
 #include "sm100_ptx.cuh"
+#include "train_ops.h"
 
 namespace retr {
 
@@ -55,6 +56,10 @@ struct KArgs {
   int stages;            // smem ring depth (runtime: depends on the epilogue staging in use)
   int tma_epi;           // epilogue through smem staging + TMA store
   int res_tma;           // residual sub-tiles arrive by TMA (implies tma_epi)
+  // split-K (weight-gradient GEMMs: tiny M x N, contraction over every token/pixel): tile t covers
+  // k-blocks [sp*kb_per_split, ...) of output tile t / splits and writes an fp32 partial tile at row
+  // offset sp*M of C (C = workspace [splits*M, N]); splitk_reduce() sums the partials.
+  int splits, kb_per_split;
 };
 
 constexpr int MAX_STAGES = 8;
@@ -76,6 +81,18 @@ template <int BN> struct Cfg {
     return n > MAX_STAGES ? MAX_STAGES : n;
   }
 };
+
+struct TileCoord { int m_blk, n_blk, sp, kb0, kb1; };
+__device__ __forceinline__ TileCoord tile_coord(const KArgs& a, int tile) {
+  TileCoord t;
+  t.sp = tile % a.splits;
+  const int t2 = tile / a.splits;
+  t.m_blk = t2 / a.n_tiles;
+  t.n_blk = t2 - t.m_blk * a.n_tiles;
+  t.kb0 = t.sp * a.kb_per_split;
+  t.kb1 = min(a.num_kb, t.kb0 + a.kb_per_split);
+  return t;
+}
 
 // One 32-column chunk of one accumulator row.
 __device__ __forceinline__ void epilogue_chunk(const KArgs& a, uint32_t (&r)[32], int64_t m, int64_t mc,
@@ -283,7 +300,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int total_tiles = a.m_tiles * a.n_tiles;
+  const int total_tiles = a.m_tiles * a.n_tiles * a.splits;
   const int EC = a.out_fp32 ? 32 : 64;                 // columns per staged sub-tile (128 B rows)
 
   if (warp == 0 && lane == 0) {
@@ -317,8 +334,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       // ===== TMA producer =====
       uint32_t s = 0, ph = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int m_blk = tile / a.n_tiles, n_blk = tile - m_blk * a.n_tiles;
-        for (int kb = 0; kb < a.num_kb; ++kb) {
+        const TileCoord tc = tile_coord(a, tile);
+        const int m_blk = tc.m_blk, n_blk = tc.n_blk;
+        for (int kb = tc.kb0; kb < tc.kb1; ++kb) {
           ptx::mbar_wait(&empty[s], ph ^ 1);
           uint8_t* As = smem + s * C::STAGE_BYTES;
           uint8_t* Bs = As + A_TILE_BYTES;
@@ -339,7 +357,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         ptx::mbar_wait(&tempty[as], aph ^ 1);
         ptx::tc_fence_after_sync();
         const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kb = 0; kb < a.num_kb; ++kb) {
+        const TileCoord tc = tile_coord(a, tile);
+        for (int kb = tc.kb0; kb < tc.kb1; ++kb) {
           ptx::mbar_wait(&full[s], ph);
           ptx::tc_fence_after_sync();
           const uint32_t a_addr = ptx::smem_u32(smem + s * C::STAGE_BYTES);
@@ -347,7 +366,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             ptx::mma_bf16_ss(d_tmem, ptx::smem_desc_sw128(a_addr + k * 32),
-                             ptx::smem_desc_sw128(b_addr + k * 32), idesc, (kb | k) != 0);
+                             ptx::smem_desc_sw128(b_addr + k * 32), idesc, ((kb - tc.kb0) | k) != 0);
           }
           ptx::mma_commit(&empty[s]);      // frees the smem slot when these MMAs retire
           if (++s == (uint32_t)STAGES) { s = 0; ph ^= 1; }
@@ -360,7 +379,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       // ===== residual producer: sub-tiles in the order the epilogue consumes them =====
       uint32_t rb = 0, rph = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int m_blk = tile / a.n_tiles, n_blk = tile - m_blk * a.n_tiles;
+        const TileCoord tc = tile_coord(a, tile);
+        const int m_blk = tc.m_blk, n_blk = tc.n_blk;
         for (int n0 = n_blk * BN; n0 < min(a.N, (n_blk + 1) * BN); n0 += EC) {
           ptx::mbar_wait(&rempty[rb], rph ^ 1);
           ptx::mbar_arrive_expect_tx(&rfull[rb], EPI_TILE_BYTES);
@@ -376,7 +396,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int tid_e = threadIdx.x - 128;
     uint32_t tcount = 0, cit = 0, rb = 0, rph = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
-      const int m_blk = tile / a.n_tiles, n_blk = tile - m_blk * a.n_tiles;
+      const TileCoord tc = tile_coord(a, tile);
+      const int m_blk = tc.m_blk, n_blk = tc.n_blk;
       const uint32_t as = tcount & 1, aph = (tcount >> 1) & 1;
       const int64_t m = (int64_t)m_blk * BM + row;
       const int64_t rb_row = a.rowbias_dyn ? (int64_t)__ldg(a.rowbias_dyn) : (m % a.rowbias_period);
@@ -431,7 +452,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         ptx::tc_fence_after_sync();
         float best_v = -INFINITY;
         uint32_t best_i = 0;
-        const int64_t mc = a.c_group ? (m / a.c_group) * a.c_group_stride + (m % a.c_group) : m;
+        const int64_t mc = a.c_group ? (m / a.c_group) * a.c_group_stride + (m % a.c_group) : m + (int64_t)tc.sp * a.M;
 #pragma unroll 1
         for (int c = 0; c < BN / 32; ++c) {
           const int n0 = n_blk * BN + c * 32;
@@ -454,7 +475,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const uint32_t swz = (uint32_t)(row & 7);
     uint32_t it = 0, s = 0, ph = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const int m_blk = tile / a.n_tiles;
+      const TileCoord tc = tile_coord(a, tile);
+      const int m_blk = tc.m_blk;
       const int64_t m = (int64_t)m_blk * BM + row;
       const bool valid_m = m < a.M;
       const int ow = (int)(m % a.OW);
@@ -462,8 +484,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const int oh = (int)(t % a.OH);
       const int64_t img = t / a.OH;
       const int ih0 = oh * a.stride - a.pad, iw0 = ow * a.stride - a.pad;
-      int tap = 0, cb = 0;
-      for (int kb = 0; kb < a.num_kb; ++kb, ++it) {
+      int tap = tc.kb0 / a.cblocks, cb = tc.kb0 - tap * a.cblocks;
+      for (int kb = tc.kb0; kb < tc.kb1; ++kb, ++it) {
         ptx::mbar_wait(&empty[s], ph ^ 1);
         const int fr = tap / a.kw, fs = tap - fr * a.kw;
         const int ih = ih0 + fr * a.dil, iw = iw0 + fs * a.dil;
@@ -590,20 +612,40 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
   // tile width: widest that still leaves every SM a tile
   const int sms = sm_count();
   int bn = 256;
-  while (bn > 32 && (bn / 2 >= p.N || cdiv(p.M, BM) * cdiv(p.N, bn) < sms)) bn /= 2;
+  int splits = 1;
+  if (p.split_k != 1) {
+    RETR_CHECK(p.out_fp32 && p.C && p.ldc == p.N && !p.scale && !p.bias && !p.rowbias && !p.residual && !p.relu &&
+                   !p.argmax_out && !p.c_group,
+               "split-K GEMM takes a plain fp32 C and no epilogue operands");
+    while (bn > 32 && bn / 2 >= p.N) bn /= 2;
+    const int64_t tiles = cdiv(p.M, BM) * cdiv(p.N, bn);
+    splits = p.split_k > 1 ? p.split_k : (int)std::max<int64_t>(1, (2 * sms) / tiles);
+    splits = std::min(splits, std::max(1, ka.num_kb / 4));
+    if (p.split_ws) splits = (int)std::min<int64_t>(splits, p.split_ws_floats / std::max<int64_t>(1, p.M * p.N));
+    else splits = 1;
+    splits = std::max(splits, 1);
+  } else {
+    while (bn > 32 && (bn / 2 >= p.N || cdiv(p.M, BM) * cdiv(p.N, bn) < sms)) bn /= 2;
+  }
+  ka.kb_per_split = (int)cdiv(ka.num_kb, splits);
+  splits = (int)cdiv(ka.num_kb, ka.kb_per_split);          // no empty split
+  ka.splits = splits;
+  const bool acc_in_place = p.split_k != 1 && splits == 1 && p.accumulate;
+  if (splits > 1) ka.C = p.split_ws;
+  if (acc_in_place) { ka.residual = p.C; ka.ldr = p.ldc; ka.res_fp32 = 1; ka.vecR = ka.vecC; }
   // epilogue route: staged TMA store whenever C is a plain, 16-byte aligned matrix (a staged
   // sub-tile is 128 B wide, so a bf16 C needs BN >= 64)
   const bool force_direct = getenv("RETR_GEMM_DIRECT_EPILOGUE") != nullptr;
-  ka.tma_epi = !force_direct && ka.vecC && !p.argmax_out && !p.c_group && (p.out_fp32 || bn >= 64) &&
-               (!p.residual || (ka.vecR && p.res_fp32 == p.out_fp32));
-  ka.res_tma = ka.tma_epi && p.residual;
+  ka.tma_epi = !force_direct && splits == 1 && ka.vecC && !p.argmax_out && !p.c_group && (p.out_fp32 || bn >= 64) &&
+               (!ka.residual || (ka.vecR && ka.res_fp32 == p.out_fp32));
+  ka.res_tma = ka.tma_epi && ka.residual;
   ka.m_tiles = (int)cdiv(p.M, BM);
   ka.n_tiles = (int)cdiv(p.N, bn);
-  const int grid = (int)std::min<int64_t>((int64_t)ka.m_tiles * ka.n_tiles, sms);
+  const int grid = (int)std::min<int64_t>((int64_t)ka.m_tiles * ka.n_tiles * splits, sms);
   CUtensorMap tmB = make_tmap_2d(p.W, p.N, p.K, p.K, bn);
   CUtensorMap tmA = gather ? tmB : make_tmap_2d(p.A, p.M, p.K, p.lda, BM);
   CUtensorMap tmC = ka.tma_epi ? make_tmap_2d(p.C, p.M, p.N, p.ldc, BM, p.out_fp32) : tmB;
-  CUtensorMap tmR = ka.res_tma ? make_tmap_2d(p.residual, p.M, p.N, p.ldr, BM, p.res_fp32) : tmB;
+  CUtensorMap tmR = ka.res_tma ? make_tmap_2d(ka.residual, p.M, p.N, ka.ldr, BM, ka.res_fp32 != 0) : tmB;
 #define RETR_LAUNCH(BN_)                                                   \
   if (gather) launch<BN_, true>(tmA, tmB, tmC, tmR, ka, grid, stream);     \
   else launch<BN_, false>(tmA, tmB, tmC, tmR, ka, grid, stream)
@@ -614,6 +656,7 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
     default: RETR_LAUNCH(32); break;
   }
 #undef RETR_LAUNCH
+  if (splits > 1) splitk_reduce(p.split_ws, static_cast<float*>(p.C), p.M * p.N, splits, p.accumulate ? 1 : 0, stream);
 }
 
 }  // namespace retr

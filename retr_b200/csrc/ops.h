@@ -67,7 +67,7 @@ template <typename T>
 void kv_to_head_major(const T* kv, T* kh, T* vh, int B, int rows, int H, int dh, cudaStream_t s);
 // After the vocab GEMM+argmax of step i=*step: the bookkeeping of eval_utils/decode.py:70-79.
 void greedy_update(unsigned long long* argmax_keys, int64_t* caption, int max_len, int B, int eos, int* step,
-                   int* done, uint8_t* finished, cudaStream_t s);
+                   int* done, uint8_t* finished, cudaStream_t s, bool allow_pdl = true);
 void greedy_init(int64_t* caption, int max_len, int B, int bos, int* step, int* done, uint8_t* finished,
                  unsigned long long* argmax_keys, cudaStream_t s);
 

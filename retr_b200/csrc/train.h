@@ -1,0 +1,42 @@
+// Trainer: the teacher-forced training step of the reference (engine.py:52-87 train_one_epoch,
+// main.py:30-40 optimiser recipe) — train-mode forward (dropout, activations kept), backward into
+// bound fp32 gradient buffers, and the fused clip + AdamW update.  See train.cu.
+#pragma once
+#include <memory>
+#include <string>
+
+#include "../../include/retr_b200.h"
+#include "common.cuh"
+
+namespace retr {
+
+class TrainerBase {
+ public:
+  virtual ~TrainerBase() {}
+  // bind a reference state_dict entry: `param` fp32 device memory read at every step (never copied),
+  // `grad` (may be null = frozen / buffer) fp32 device memory the backward pass writes
+  virtual void bind(const std::string& name, float* param, float* grad, const int64_t* shape, int ndim) = 0;
+  virtual void finalize() = 0;
+  // train-mode forward; logits_out (optional) fp32 [B,T,V]
+  virtual void forward(int B, const float* t_img, const uint8_t* t_mask, const float* g_img, const uint8_t* g_mask,
+                       const float* loc, const int64_t* ids, const uint8_t* id_mask, float* logits_out, float dropout_p,
+                       unsigned long long seed, cudaStream_t s) = 0;
+  // backward of the last forward from dL/dlogits (fp32 [B,T,V]); every bound grad is overwritten
+  virtual void backward(const float* dlogits, cudaStream_t s) = 0;
+  // forward + mean cross-entropy against targets [B,T] + backward in one call; the loss stays on the device
+  // (loss_dev, fp32) so the caller decides when to synchronise
+  virtual void loss_and_grads(int B, const float* t_img, const uint8_t* t_mask, const float* g_img,
+                              const uint8_t* g_mask, const float* loc, const int64_t* ids, const uint8_t* id_mask,
+                              const int64_t* targets, float dropout_p, unsigned long long seed, float* loss_dev,
+                              cudaStream_t s) = 0;
+  // clip_grad_norm_(all grads, max_norm) + AdamW over every trainable tensor; names containing "backbone" use
+  // lr_backbone (main.py:31-36).  `step` is the 1-based update count (bias correction).
+  virtual void clip_adamw(float max_norm, float lr, float lr_backbone, float beta1, float beta2, float eps,
+                          float weight_decay, int step, float* grad_norm_dev, cudaStream_t s) = 0;
+  long long launches = 0;
+};
+
+// pad_token_id: nn.Embedding(padding_idx=...) row that receives no gradient (models/transformer_modules.py:103-105)
+std::unique_ptr<TrainerBase> make_trainer(const retr_model_desc& d, int pad_token_id);
+
+}  // namespace retr

@@ -55,6 +55,27 @@ def train_one_epoch(model, criterion, data_loader, optimizer, device, epoch, max
     return epoch_loss / total
 
 
+def train_step_native(model, samples, caps, cap_masks, max_norm, lr, lr_backbone, weight_decay=1e-4,
+                      betas=(0.9, 0.999), eps=1e-8):
+    """One step of the loop body above (engine.py:64-83) entirely in native kernels: train-mode forward,
+    fused cross-entropy (bf16 logits never leave the device), backward, NCCL all-reduce of the flat gradient
+    buffer when a process group is up, clip_grad_norm_ + AdamW (main.py:30-40 recipe: parameters whose name
+    contains "backbone" use lr_backbone).  Returns (mean loss, pre-clip gradient norm) as 0-d device tensors —
+    no host synchronisation."""
+    import torch.distributed as dist
+    t, g, loc = model._split_samples(samples)
+    inputs = model._train_inputs(t, g, loc, caps[:, :-1], cap_masks[:, :-1])
+    tr = model.trainer(inputs[0].shape[0])
+    seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+    p = float(model.dropout_p) if model.training else 0.0
+    loss = tr.loss_and_grads(*inputs, caps[:, 1:], dropout_p=p, seed=seed)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(tr.gflat)
+        tr.gflat.div_(dist.get_world_size())
+    norm = tr.clip_adamw(max_norm, lr, lr_backbone, betas=betas, eps=eps, weight_decay=weight_decay)
+    return loss, norm
+
+
 @torch.no_grad()
 def evaluate(model, criterion, data_loader, device):
     """Validation loss — reference engine.py:89-114 (same forward, no backward)."""

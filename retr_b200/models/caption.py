@@ -33,6 +33,29 @@ class MLP(nn.Module):
         self.layers = nn.ModuleList(nn.Linear(a, b) for a, b in zip(dims[:-1], dims[1:]))
 
 
+class _NativeTrainForward(torch.autograd.Function):
+    """Train-mode forward/backward through the native trainer (reference engine.py:70,80:
+    ``outputs = model(...)`` / ``loss.backward()``).  The trainable parameters are inputs of the Function
+    only so that autograd routes their gradients; the arithmetic reads them by pointer."""
+
+    @staticmethod
+    def forward(ctx, model, inputs, p_drop, seed, *params):
+        trainer = model.trainer(inputs[0].shape[0])
+        ctx.trainer, ctx.names = trainer, trainer.trainable
+        return trainer.forward(*inputs, dropout_p=p_drop, seed=seed)
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        trainer = ctx.trainer
+        grads = trainer.backward(dlogits)
+        if torch.distributed.is_available() and torch.distributed.is_initialized() \
+                and torch.distributed.get_world_size() > 1:
+            # data parallel: one all-reduce of the flat gradient buffer (NCCL over NVLink), mean over ranks
+            torch.distributed.all_reduce(trainer.gflat)
+            trainer.gflat.div_(torch.distributed.get_world_size())
+        return (None, None, None, None) + tuple(grads[n] for n in ctx.names)
+
+
 class _CaptionBase(nn.Module):
     n_images = 1          # backbone passes per sample
     loc_in_dim = 0        # 0: no location input
@@ -47,6 +70,9 @@ class _CaptionBase(nn.Module):
         self.transformer = transformer
         self.mlp = MLP(hidden_dim, 512, vocab_size, 3)
         self._engine = None
+        self._trainer = None
+        self.dropout_p = 0.1              # config.dropout (configuration_template.py:48)
+        self.pad_token_id = 0
         self.precision = "bf16"
         self.max_batch = 8                # initial context capacity; grows on demand
         self.backbone_stride = 16
@@ -73,12 +99,43 @@ class _CaptionBase(nn.Module):
             self._engine = Engine(self, device, self.precision, max_batch=max_batch)
         return self._engine
 
+    def trainer(self, batch=1):
+        """The native trainer bound (by pointer) to this model's parameters; rebuilt when a parameter
+        tensor was replaced, a FrozenBatchNorm2d buffer was rewritten, or a larger batch arrives."""
+        from ..runtime import Trainer
+        device = next(self.parameters()).device
+        if device.type != "cuda":
+            raise RuntimeError(
+                "retr_b200 runs only on a CUDA device (B200, sm_100a): model parameters are on "
+                f"{device}. Call model.to('cuda') first; there is no CPU path.")
+        tr = self._trainer
+        stale = (tr is None or tr.device != device or tr.precision != self.precision or tr.max_batch < batch
+                 or tr.signature != Trainer.signature_of(self))
+        if stale:
+            max_batch = max(batch, tr.max_batch if tr is not None else 0)
+            if tr is not None:
+                tr.close()
+            self._trainer = Trainer(self, device, self.precision, max_batch=max_batch,
+                                    pad_token_id=self.pad_token_id)
+        return self._trainer
+
     def _apply(self, fn, *a, **kw):
         out = super()._apply(fn, *a, **kw)
         if self._engine is not None:       # parameters moved: pointers held by the context are stale
             self._engine.close()
             self._engine = None
+        if self._trainer is not None:
+            self._trainer.close()
+            self._trainer = None
         return out
+
+    def _train_inputs(self, t_samples, g_samples, loc, target_exp, target_exp_mask):
+        t_samples = self._nested(t_samples)
+        g_img = g_mask = None
+        if g_samples is not None:
+            g_samples = self._nested(g_samples)
+            g_img, g_mask = g_samples.tensors, g_samples.mask
+        return (t_samples.tensors, t_samples.mask, g_img, g_mask, loc, target_exp, target_exp_mask)
 
     @staticmethod
     def _nested(samples):
@@ -106,10 +163,14 @@ class _CaptionBase(nn.Module):
         return eng
 
     def _run(self, t_samples, g_samples, loc, target_exp, target_exp_mask, return_attention):
-        if self.training and torch.is_grad_enabled():
-            raise NotImplementedError(
-                "retr_b200: the native backward pass (engine.train_one_epoch path) is not built yet; "
-                "call model.eval() / torch.no_grad() for inference")
+        if self.training:
+            # train mode: dropout active, activations kept, autograd-capable logits (engine.py:70)
+            if return_attention:
+                raise NotImplementedError("return_attention=True is served by the eval path (model.eval())")
+            inputs = self._train_inputs(t_samples, g_samples, loc, target_exp, target_exp_mask)
+            seed = int(torch.randint(0, 2 ** 62, (1,)).item())       # drawn from torch's CPU generator
+            params = [p for p in self.parameters() if p.requires_grad]
+            return _NativeTrainForward.apply(self, inputs, float(self.dropout_p), seed, *params)
         B = target_exp.shape[0]
         att_enc = None
         if return_attention:
@@ -170,6 +231,8 @@ def build_model(config):
         (bool(use_global), bool(use_location))]
     model = Model(backbone, transformer, None, config.hidden_dim, config.vocab_size)
     model.precision = getattr(config, "precision", "bf16")
+    model.dropout_p = float(config.dropout)
+    model.pad_token_id = int(config.pad_token_id)
     model.layer_norm_eps = config.layer_norm_eps
     model.pre_norm = bool(config.pre_norm)
     print(f"Built {model.__class__.__name__} model with {transformer.__class__.__name__}")

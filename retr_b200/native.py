@@ -56,6 +56,16 @@ SIGNATURES = {
     "retr_last_phase_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "retr_op_gemm": (C.c_int, [C.c_int32, C.POINTER(GemmArgs), C.c_void_p]),
     "retr_op_layernorm": (C.c_int, [C.c_void_p] * 4 + [C.c_int64, C.c_int32, C.c_float, C.c_int32, C.c_void_p]),
+    "retr_train_create": (C.c_int, [C.POINTER(ModelDesc), C.c_int32, C.POINTER(C.c_void_p)]),
+    "retr_train_destroy": (None, [C.c_void_p]),
+    "retr_train_bind": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int64), C.c_int32]),
+    "retr_train_finalize": (C.c_int, [C.c_void_p]),
+    "retr_train_forward": (C.c_int, [C.c_void_p, C.c_int32] + [C.c_void_p] * 8 + [C.c_float, C.c_uint64, C.c_void_p]),
+    "retr_train_backward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "retr_train_loss_and_grads": (C.c_int, [C.c_void_p, C.c_int32] + [C.c_void_p] * 8 +
+                                  [C.c_float, C.c_uint64, C.c_void_p, C.c_void_p]),
+    "retr_train_clip_adamw": (C.c_int, [C.c_void_p] + [C.c_float] * 7 + [C.c_int32, C.c_void_p, C.c_void_p]),
+    "retr_train_kernel_launches": (C.c_int64, [C.c_void_p]),
     "retr_op_attention": (C.c_int, [C.c_int32] + [C.c_void_p] * 4 + [C.c_int32] * 4 + [C.c_int64] * 4 +
                           [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
 }

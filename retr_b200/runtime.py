@@ -18,6 +18,28 @@ def _as(t, dtype, device):
     return t.to(device=device, dtype=dtype).contiguous()
 
 
+def model_desc(model, device, precision, max_batch, image_size=224):
+    """``retr_model_desc`` of a caption model: the attributes build_model reads from Config."""
+    tr = model.transformer
+    d = native.ModelDesc()
+    d.device = device.index if device.index is not None else torch.cuda.current_device()
+    d.precision = _PRECISION[precision]
+    d.blocks = (C.c_int32 * 4)(*RESNET_SPECS[model.backbone.arch][0])
+    d.dilation = int(model.backbone.dilation)
+    d.n_images = model.n_images
+    d.loc_in_dim = model.loc_in_dim
+    d.n_loc = {0: 0, 1: getattr(model, "n_loc_feats", 5), 7: 7}[model.loc_in_dim]
+    d.image_size = image_size
+    d.d_model, d.n_heads, d.d_ff = tr.d_model, tr.nhead, tr.dim_feedforward
+    d.enc_layers, d.dec_layers = tr.encoder.num_layers, tr.decoder.num_layers
+    d.max_pos = tr.embeddings.position_embeddings.num_embeddings
+    d.vocab = model.mlp.layers[-1].out_features
+    d.pre_norm = int(tr.encoder.norm is not None)
+    d.embed_ln_eps = float(tr.embeddings.LayerNorm.eps)
+    d.max_batch = int(max_batch)
+    return d
+
+
 class Engine:
     def __init__(self, model, device, precision="bf16", max_batch=8, image_size=224):
         device = torch.device(device)
@@ -27,23 +49,7 @@ class Engine:
             raise ValueError(f"precision must be one of {sorted(_PRECISION)}")
         self.lib = native.lib()
         self.device, self.precision, self.max_batch, self.image_size = device, precision, int(max_batch), image_size
-        tr = model.transformer
-        d = native.ModelDesc()
-        d.device = device.index if device.index is not None else torch.cuda.current_device()
-        d.precision = _PRECISION[precision]
-        d.blocks = (C.c_int32 * 4)(*RESNET_SPECS[model.backbone.arch][0])
-        d.dilation = int(model.backbone.dilation)
-        d.n_images = model.n_images
-        d.loc_in_dim = model.loc_in_dim
-        d.n_loc = {0: 0, 1: getattr(model, "n_loc_feats", 5), 7: 7}[model.loc_in_dim]
-        d.image_size = image_size
-        d.d_model, d.n_heads, d.d_ff = tr.d_model, tr.nhead, tr.dim_feedforward
-        d.enc_layers, d.dec_layers = tr.encoder.num_layers, tr.decoder.num_layers
-        d.max_pos = tr.embeddings.position_embeddings.num_embeddings
-        d.vocab = model.mlp.layers[-1].out_features
-        d.pre_norm = int(tr.encoder.norm is not None)
-        d.embed_ln_eps = float(tr.embeddings.LayerNorm.eps)
-        d.max_batch = self.max_batch
+        d = model_desc(model, device, precision, self.max_batch, image_size)
         self.desc = d
         self.T, self.V, self.d_model = d.max_pos, d.vocab, d.d_model
         self.n_enc, self.n_dec = d.enc_layers, d.dec_layers
@@ -166,3 +172,123 @@ class Engine:
         buf = (C.c_float * 3)()
         native.check(self.lib.retr_last_phase_ms(self.handle, buf))
         return {"backbone": buf[0], "encoder": buf[1], "decode": buf[2]}
+
+
+class Trainer:
+    """Host-side owner of one native ``retr_trainer``: the training step of the reference
+    (engine.py:52-87).  The model's parameters are bound BY POINTER (the native side reads the fp32
+    masters at every step, so an optimiser updating them in place needs no re-upload); gradients
+    land in one flat fp32 buffer of which ``self.grads[name]`` are views."""
+
+    def __init__(self, model, device, precision="bf16", max_batch=8, image_size=224, pad_token_id=0):
+        device = torch.device(device)
+        if device.type != "cuda":
+            raise RuntimeError("retr_b200 has no CPU path: the model must live on a CUDA device")
+        self.lib = native.lib()
+        self.device, self.precision, self.max_batch, self.image_size = device, precision, int(max_batch), image_size
+        d = model_desc(model, device, precision, self.max_batch, image_size)
+        if not d.pre_norm:
+            raise NotImplementedError("retr_b200 training implements pre_norm=True (configuration_template.py:51)")
+        self.desc, self.T, self.V = d, d.max_pos, d.vocab
+        sd = model.state_dict(keep_vars=True)
+        self.names = [n for n, t in sd.items() if torch.is_floating_point(t)]
+        self.tensors = {n: sd[n] for n in self.names}
+        for n, t in self.tensors.items():
+            if t.dtype != torch.float32 or not t.is_contiguous() or t.device != device:
+                raise RuntimeError(f"parameter {n} must be a contiguous fp32 tensor on {device}")
+        self.trainable = [n for n in self.names if isinstance(sd[n], torch.nn.Parameter) and sd[n].requires_grad]
+        total = sum(self.tensors[n].numel() for n in self.trainable)
+        self.gflat = torch.zeros(total, dtype=torch.float32, device=device)
+        self.grads, off = {}, 0
+        for n in self.trainable:
+            k = self.tensors[n].numel()
+            self.grads[n] = self.gflat[off:off + k].view(self.tensors[n].shape)
+            off += k
+        handle = C.c_void_p()
+        with torch.cuda.device(device):
+            native.check(self.lib.retr_train_create(C.byref(d), int(pad_token_id), C.byref(handle)))
+            self.handle = handle
+            for n in self.names:
+                t = self.tensors[n]
+                shape = (C.c_int64 * max(t.dim(), 1))(*(t.shape if t.dim() else (1,)))
+                native.check(self.lib.retr_train_bind(self.handle, n.encode(), native.ptr(t.data), native.ptr(self.grads.get(n)),
+                                                      shape, max(t.dim(), 1)))
+            native.check(self.lib.retr_train_finalize(self.handle))
+        self.signature = self.signature_of(model)
+        self.batch, self.step_count = 0, 0
+        self._loss = torch.zeros(1, dtype=torch.float32, device=device)
+        self._sumsq = torch.zeros(1, dtype=torch.float32, device=device)
+
+    @staticmethod
+    def signature_of(model):
+        """Changes when a bound pointer moved or a folded buffer (FrozenBatchNorm2d) was rewritten."""
+        ptrs = tuple(t.data_ptr() for t in model.state_dict(keep_vars=True).values())
+        return ptrs, sum(b._version for b in model.buffers())
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.retr_train_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _inputs(self, t_img, t_mask, g_img, g_mask, loc, ids, id_mask):
+        B = t_img.shape[0]
+        if B > self.max_batch:
+            raise RuntimeError(f"batch {B} exceeds the trainer's max_batch {self.max_batch}")
+        if tuple(ids.shape) != (B, self.T):
+            raise RuntimeError(f"The size of tensor a ({ids.shape[1]}) must match the size of tensor b ({self.T}) "
+                               "(caption length must equal max_position_embeddings)")
+        keep = [_as(t_img, torch.float32, self.device), _as(t_mask, torch.uint8, self.device),
+                None if g_img is None else _as(g_img, torch.float32, self.device),
+                None if g_mask is None else _as(g_mask, torch.uint8, self.device),
+                None if loc is None else _as(loc, torch.float32, self.device),
+                _as(ids, torch.int64, self.device), _as(id_mask, torch.uint8, self.device)]
+        self._keep = keep
+        self.batch = B
+        return B, keep
+
+    def forward(self, t_img, t_mask, g_img, g_mask, loc, ids, id_mask, dropout_p=0.0, seed=0):
+        B, keep = self._inputs(t_img, t_mask, g_img, g_mask, loc, ids, id_mask)
+        logits = torch.empty(B, self.T, self.V, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            native.check(self.lib.retr_train_forward(self.handle, B, *[native.ptr(k) for k in keep], native.ptr(logits),
+                                                     float(dropout_p), int(seed), native.stream_ptr(self.device)))
+        return logits
+
+    def backward(self, dlogits):
+        dlogits = _as(dlogits, torch.float32, self.device)
+        if tuple(dlogits.shape) != (self.batch, self.T, self.V):
+            raise RuntimeError(f"dlogits must be [{self.batch},{self.T},{self.V}], got {tuple(dlogits.shape)}")
+        with torch.cuda.device(self.device):
+            native.check(self.lib.retr_train_backward(self.handle, native.ptr(dlogits), native.stream_ptr(self.device)))
+        self._keep_d = dlogits
+        return self.grads
+
+    def loss_and_grads(self, t_img, t_mask, g_img, g_mask, loc, ids, id_mask, targets, dropout_p=0.0, seed=0):
+        """Fused forward + mean CE + backward; returns the mean loss as a 0-d device tensor (no sync)."""
+        B, keep = self._inputs(t_img, t_mask, g_img, g_mask, loc, ids, id_mask)
+        targets = _as(targets, torch.int64, self.device)
+        self._keep.append(targets)
+        with torch.cuda.device(self.device):
+            native.check(self.lib.retr_train_loss_and_grads(
+                self.handle, B, *[native.ptr(k) for k in keep], native.ptr(targets), float(dropout_p), int(seed),
+                native.ptr(self._loss), native.stream_ptr(self.device)))
+        return self._loss[0] / (B * self.T)
+
+    def clip_adamw(self, max_norm, lr, lr_backbone, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-4):
+        """clip_grad_norm_ + AdamW in native kernels; returns the pre-clip gradient norm (0-d device tensor)."""
+        self.step_count += 1
+        with torch.cuda.device(self.device):
+            native.check(self.lib.retr_train_clip_adamw(self.handle, float(max_norm), float(lr), float(lr_backbone),
+                                                        float(betas[0]), float(betas[1]), float(eps), float(weight_decay),
+                                                        self.step_count, native.ptr(self._sumsq),
+                                                        native.stream_ptr(self.device)))
+        return self._sumsq[0].sqrt()
+
+    def kernel_launches(self):
+        return int(self.lib.retr_train_kernel_launches(self.handle))
