@@ -273,7 +273,7 @@ class Trainer:
         """Fused forward + mean CE + backward; returns the mean loss as a 0-d device tensor (no sync)."""
         B, keep = self._inputs(t_img, t_mask, g_img, g_mask, loc, ids, id_mask)
         targets = _as(targets, torch.int64, self.device)
-        self._keep.append(targets)
+        self._keep = keep + [targets]
         with torch.cuda.device(self.device):
             native.check(self.lib.retr_train_loss_and_grads(
                 self.handle, B, *[native.ptr(k) for k in keep], native.ptr(targets), float(dropout_p), int(seed),
