@@ -66,6 +66,7 @@ template <typename T> struct TEnc {
   float *gin_b = nullptr;                                            // in_proj_bias grad [3d]
   float *xa, *xb;                                                    // fp32 stream before each sublayer
   T *n1, *n1p, *qkv, *P, *att, *n2, *h;
+  float* lse = nullptr;
 };
 template <typename T> struct TDec {
   float *g1, *b1, *g2, *b2, *g3, *b3, *gg1, *gb1, *gg2, *gb2, *gg3, *gb3;
@@ -73,6 +74,7 @@ template <typename T> struct TDec {
   float *gs_b = nullptr, *gc_b = nullptr;                            // in_proj_bias grads [3d]
   float *ya, *yb, *yc;
   T *n1, *n1p, *qkv, *Ps, *att_s, *n2p, *qc, *ckv, *Pc, *att_c, *n3, *h;
+  float *lse_s = nullptr, *lse_c = nullptr;
 };
 
 __global__ void cast_rows_kernel(const float* __restrict__ in, int64_t ld_in, bf16* __restrict__ out, int64_t ld_out,
@@ -178,9 +180,10 @@ class TrainerT final : public TrainerBase {
                float* bias_grad, cudaStream_t s);
   void conv_bwd(const TConv<T>& c, const T* g, const T* x, int64_t nimg, int H, int OH, T* dx, const T* dx_add,
                 bool need_dx, cudaStream_t s);
-  void attn_fwd(const T* q, int64_t ldq, const T* k, const T* v, int64_t ldkv, T* out, T* probs, int Lq, int Lk,
-                const uint8_t* pad, int causal, unsigned site, cudaStream_t s);
-  void attn_bwd(const T* q, int64_t ldq, const T* k, const T* v, int64_t ldkv, const T* probs, const T* dout, T* dq,
+  void attn_fwd(const T* q, int64_t ldq, const T* k, const T* v, int64_t ldkv, T* out, T* probs, float* lse, int Lq,
+                int Lk, const uint8_t* pad, int causal, unsigned site, cudaStream_t s);
+  void attn_bwd(const T* q, int64_t ldq, const T* k, const T* v, int64_t ldkv, const T* probs, const float* lse,
+                const T* out, const T* dout, T* dq,
                 int64_t lddq, T* dk, T* dv, int64_t lddkv, int Lq, int Lk, const uint8_t* pad, int causal, unsigned site,
                 cudaStream_t s);
   void forward_impl(int B, const float* t_img, const uint8_t* t_mask, const float* g_img, const uint8_t* g_mask,
@@ -227,7 +230,9 @@ class TrainerT final : public TrainerBase {
   T *tA_ = nullptr, *tB_ = nullptr, *dcol_ = nullptr;
   int64_t tA_cap_ = 0, tB_cap_ = 0;
   T *bb_[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // backbone gradient buffers
-  float *dwk_ = nullptr, *ws_ = nullptr, *sumsq_ = nullptr;
+  float *dwk_ = nullptr, *ws_ = nullptr, *sumsq_ = nullptr, *delta_ = nullptr;
+  // bf16: tensor-core flash attention (log-sum-exp kept, probabilities recomputed in the backward pass)
+  bool flash_ = std::is_same<T, bf16>::value && getenv("RETR_TRAIN_SIMT_ATTENTION") == nullptr;
   int64_t ws_floats_ = 0;
   int cur_B_ = 0;
   float drop_p_ = 0.f;
@@ -368,7 +373,8 @@ void TrainerT<T>::finalize() {
     e.ff2 = lin(p + "ff.sublayer.2.weight", p + "ff.sublayer.2.bias");
     e.xa = alloc<float>(Me * d); e.xb = alloc<float>(Me * d);
     e.n1 = alloc<T>(Me * d); e.n1p = alloc<T>(Me * d); e.qkv = alloc<T>(Me * 3 * d);
-    e.P = alloc<T>(B * H * (int64_t)S * S); e.att = alloc<T>(Me * d); e.n2 = alloc<T>(Me * d); e.h = alloc<T>(Me * ff);
+    e.P = flash_ ? nullptr : alloc<T>(B * H * (int64_t)S * S); e.lse = flash_ ? alloc<float>(B * H * (int64_t)S) : nullptr;
+    e.att = alloc<T>(Me * d); e.n2 = alloc<T>(Me * d); e.h = alloc<T>(Me * ff);
     enc_.push_back(e);
   }
   enc_ng_ = P("transformer.encoder.norm.weight").p; g_enc_ng_ = P("transformer.encoder.norm.weight").g;
@@ -396,9 +402,10 @@ void TrainerT<T>::finalize() {
     e.ff2 = lin(p + "ff.sublayer.2.weight", p + "ff.sublayer.2.bias");
     e.ya = alloc<float>(Md * d); e.yb = alloc<float>(Md * d); e.yc = alloc<float>(Md * d);
     e.n1 = alloc<T>(Md * d); e.n1p = alloc<T>(Md * d); e.qkv = alloc<T>(Md * 3 * d);
-    e.Ps = alloc<T>(B * H * (int64_t)Tn * Tn); e.att_s = alloc<T>(Md * d);
+    e.Ps = flash_ ? nullptr : alloc<T>(B * H * (int64_t)Tn * Tn); e.att_s = alloc<T>(Md * d);
+    e.lse_s = flash_ ? alloc<float>(B * H * (int64_t)Tn) : nullptr; e.lse_c = e.lse_s ? alloc<float>(B * H * (int64_t)Tn) : nullptr;
     e.n2p = alloc<T>(Md * d); e.qc = alloc<T>(Md * d); e.ckv = alloc<T>(Me * 2 * d);
-    e.Pc = alloc<T>(B * H * (int64_t)Tn * S); e.att_c = alloc<T>(Md * d); e.n3 = alloc<T>(Md * d); e.h = alloc<T>(Md * ff);
+    e.Pc = flash_ ? nullptr : alloc<T>(B * H * (int64_t)Tn * S); e.att_c = alloc<T>(Md * d); e.n3 = alloc<T>(Md * d); e.h = alloc<T>(Md * ff);
     dec_.push_back(e);
   }
   dec_ng_ = P("transformer.decoder.norm.weight").p; g_dec_ng_ = P("transformer.decoder.norm.weight").g;
@@ -420,7 +427,8 @@ void TrainerT<T>::finalize() {
   tmpf_ = alloc<float>(Mx * d); tmpf2_ = alloc<float>(Mx * d); embtmp_ = alloc<float>(2 * Md * d);
   gb_ = alloc<T>(Mx * d); dh_ = alloc<T>(Mx * std::max<int64_t>(ff, 512)); datt_ = alloc<T>(Mx * d);
   dqkv_ = alloc<T>(Mx * 3 * d); dckv_ = alloc<T>(Me * 2 * d);
-  dS_ = alloc<T>(B * H * (int64_t)std::max(S, Tn) * std::max(S, Tn));
+  dS_ = flash_ ? nullptr : alloc<T>(B * H * (int64_t)std::max(S, Tn) * std::max(S, Tn));
+  delta_ = alloc<float>(B * H * (int64_t)std::max(S, Tn));
   dtok_ = alloc<T>(NI * g2 * d);
   const int64_t Mdp = rup(Md, 16), Mep = rup(Me, 16), Mtp = rup(NI * g2, 16);
   tA_cap_ = std::max({max_tA, (int64_t)desc.vocab * Mdp, std::max(ff, (int64_t)3 * d) * std::max(Mdp, Mep), (int64_t)d * Mtp});
@@ -503,20 +511,21 @@ void TrainerT<T>::branch_out(const TLin<T>& l, const T* A, int64_t M, const floa
 }
 
 template <typename T>
-void TrainerT<T>::attn_fwd(const T* q, int64_t ldq, const T* k, const T* v, int64_t ldkv, T* out, T* probs, int Lq, int Lk,
-                           const uint8_t* pad, int causal, unsigned site, cudaStream_t s) {
+void TrainerT<T>::attn_fwd(const T* q, int64_t ldq, const T* k, const T* v, int64_t ldkv, T* out, T* probs, float* lse,
+                           int Lq, int Lk, const uint8_t* pad, int causal, unsigned site, cudaStream_t s) {
   AttnTrainParams a{};
-  a.q = q; a.k = k; a.v = v; a.ldq = ldq; a.ldk = a.ldv = ldkv; a.out = out; a.ldo = desc.d_model; a.probs = probs;
+  a.q = q; a.k = k; a.v = v; a.ldq = ldq; a.ldk = a.ldv = ldkv; a.out = out; a.ldo = desc.d_model; a.probs = probs; a.lse = lse;
   a.B = cur_B_; a.Lq = Lq; a.Lk = Lk; a.H = desc.n_heads; a.dh = desc.d_model / desc.n_heads;
   a.key_pad = pad; a.causal = causal; a.drop = drop(site);
   attention_train_fwd<T>(a, s);
 }
 template <typename T>
-void TrainerT<T>::attn_bwd(const T* q, int64_t ldq, const T* k, const T* v, int64_t ldkv, const T* probs, const T* dout,
-                           T* dq, int64_t lddq, T* dk, T* dv, int64_t lddkv, int Lq, int Lk, const uint8_t* pad,
+void TrainerT<T>::attn_bwd(const T* q, int64_t ldq, const T* k, const T* v, int64_t ldkv, const T* probs, const float* lse,
+                           const T* out, const T* dout, T* dq, int64_t lddq, T* dk, T* dv, int64_t lddkv, int Lq, int Lk, const uint8_t* pad,
                            int causal, unsigned site, cudaStream_t s) {
   AttnBwdParams b{};
   b.f.q = q; b.f.k = k; b.f.v = v; b.f.ldq = ldq; b.f.ldk = b.f.ldv = ldkv; b.f.probs = const_cast<T*>(probs);
+  b.f.lse = const_cast<float*>(lse); b.f.out = const_cast<T*>(out); b.f.ldo = desc.d_model; b.delta = delta_;
   b.f.B = cur_B_; b.f.Lq = Lq; b.f.Lk = Lk; b.f.H = desc.n_heads; b.f.dh = desc.d_model / desc.n_heads;
   b.f.key_pad = pad; b.f.causal = causal; b.f.drop = drop(site);
   b.dout = dout; b.lddo = desc.d_model; b.ds = dS_;
@@ -607,7 +616,7 @@ void TrainerT<T>::forward_impl(int B, const float* t_img, const uint8_t* t_mask,
     layernorm_pos<T>(e.xa, e.g1, e.b1, e.n1, e.n1p, pe_, S, Me, d, 1e-5f, s);
     gemmT<T>(lp(e.qk, e.n1p, d, Me, e.qkv, 3 * d), s);
     gemmT<T>(lp(e.v, e.n1, d, Me, e.qkv + 2 * d, 3 * d), s);
-    attn_fwd(e.qkv, 3 * d, e.qkv + d, e.qkv + 2 * d, 3 * d, e.att, e.P, S, S, tok_mask_, 0, 10 + 4 * l, s);
+    attn_fwd(e.qkv, 3 * d, e.qkv + d, e.qkv + 2 * d, 3 * d, e.att, e.P, e.lse, S, S, tok_mask_, 0, 10 + 4 * l, s);
     branch_out(e.o, e.att, Me, e.xa, e.xb, drop(11 + 4 * l), s);
     layernorm_pos<T>(e.xb, e.g2, e.b2, e.n2, nullptr, nullptr, 1, Me, d, 1e-5f, s);
     GemmParams p = lp(e.ff1, e.n2, d, Me, e.h, e.ff1.out);
@@ -625,13 +634,13 @@ void TrainerT<T>::forward_impl(int B, const float* t_img, const uint8_t* t_mask,
     layernorm_pos<T>(e.ya, e.g1, e.b1, e.n1, e.n1p, e_pos_, Tn, Md, d, 1e-5f, s);
     gemmT<T>(lp(e.s_qk, e.n1p, d, Md, e.qkv, 3 * d), s);
     gemmT<T>(lp(e.s_v, e.n1, d, Md, e.qkv + 2 * d, 3 * d), s);
-    attn_fwd(e.qkv, 3 * d, e.qkv + d, e.qkv + 2 * d, 3 * d, e.att_s, e.Ps, Tn, Tn, id_mask_, 1, 100 + 8 * l, s);
+    attn_fwd(e.qkv, 3 * d, e.qkv + d, e.qkv + 2 * d, 3 * d, e.att_s, e.Ps, e.lse_s, Tn, Tn, id_mask_, 1, 100 + 8 * l, s);
     branch_out(e.s_o, e.att_s, Md, e.ya, e.yb, drop(101 + 8 * l), s);
     layernorm_pos<T>(e.yb, e.g2, e.b2, nullptr, e.n2p, e_pos_, Tn, Md, d, 1e-5f, s);
     gemmT<T>(lp(e.c_q, e.n2p, d, Md, e.qc, d), s);
     gemmT<T>(lp(e.c_k, memp_, d, Me, e.ckv, 2 * d), s);
     gemmT<T>(lp(e.c_v, memory_, d, Me, e.ckv + d, 2 * d), s);
-    attn_fwd(e.qc, d, e.ckv, e.ckv + d, 2 * d, e.att_c, e.Pc, Tn, S, tok_mask_, 0, 102 + 8 * l, s);
+    attn_fwd(e.qc, d, e.ckv, e.ckv + d, 2 * d, e.att_c, e.Pc, e.lse_c, Tn, S, tok_mask_, 0, 102 + 8 * l, s);
     branch_out(e.c_o, e.att_c, Md, e.yb, e.yc, drop(103 + 8 * l), s);
     layernorm_pos<T>(e.yc, e.g3, e.b3, e.n3, nullptr, nullptr, 1, Md, d, 1e-5f, s);
     GemmParams p = lp(e.ff1, e.n3, d, Md, e.h, e.ff1.out);
@@ -782,7 +791,7 @@ void TrainerT<T>::backward_impl(cudaStream_t s) {
     // cross attention: yc = yb + drop(Wo att(q = Wq(LN2(yb)+E_pos), k = Wk(mem+pos), v = Wv mem))
     dropout_bwd_cast<T>(dY_, gb_, Md * d, drop(103 + 8 * l), s);
     lin_bwd(e.c_o, gb_, d, e.att_c, d, Md, datt_, false, e.c_o.gb, s);
-    attn_bwd(e.qc, d, e.ckv, e.ckv + d, 2 * d, e.Pc, datt_, dqkv_, d, dckv_, dckv_ + d, 2 * d, Tn, S, tok_mask_, 0,
+    attn_bwd(e.qc, d, e.ckv, e.ckv + d, 2 * d, e.Pc, e.lse_c, e.att_c, datt_, dqkv_, d, dckv_, dckv_ + d, 2 * d, Tn, S, tok_mask_, 0,
              102 + 8 * l, s);
     lin_bwd(e.c_q, dqkv_, d, e.n2p, d, Md, tmpf_, true, e.gc_b, s);
     if (g_e_pos_) pos_grad_accumulate(tmpf_, g_e_pos_, B, Tn, d, s);
@@ -802,7 +811,7 @@ void TrainerT<T>::backward_impl(cudaStream_t s) {
     // self attention: yb = ya + drop(Wo att(q = k = LN1(ya)+E_pos, v = LN1(ya)))
     dropout_bwd_cast<T>(dY_, gb_, Md * d, drop(101 + 8 * l), s);
     lin_bwd(e.s_o, gb_, d, e.att_s, d, Md, datt_, false, e.s_o.gb, s);
-    attn_bwd(e.qkv, 3 * d, e.qkv + d, e.qkv + 2 * d, 3 * d, e.Ps, datt_, dqkv_, 3 * d, dqkv_ + d, dqkv_ + 2 * d, 3 * d, Tn,
+    attn_bwd(e.qkv, 3 * d, e.qkv + d, e.qkv + 2 * d, 3 * d, e.Ps, e.lse_s, e.att_s, datt_, dqkv_, 3 * d, dqkv_ + d, dqkv_ + 2 * d, 3 * d, Tn,
              Tn, id_mask_, 1, 100 + 8 * l, s);
     if (e.gs_b) colsum<T>(dqkv_, 3 * d, e.gs_b, Md, 3 * d, 0, s);
     lin_bwd(e.s_qk, dqkv_, 3 * d, e.n1p, d, Md, tmpf_, true, nullptr, s);
@@ -825,7 +834,7 @@ void TrainerT<T>::backward_impl(cudaStream_t s) {
     layernorm_bwd(e.xb, e.g2, tmpf_, nullptr, dX_, 1, e.gg2, e.gb2, Me, d, 1e-5f, s);
     dropout_bwd_cast<T>(dX_, gb_, Me * d, drop(11 + 4 * l), s);
     lin_bwd(e.o, gb_, d, e.att, d, Me, datt_, false, e.o.gb, s);
-    attn_bwd(e.qkv, 3 * d, e.qkv + d, e.qkv + 2 * d, 3 * d, e.P, datt_, dqkv_, 3 * d, dqkv_ + d, dqkv_ + 2 * d, 3 * d, S, S,
+    attn_bwd(e.qkv, 3 * d, e.qkv + d, e.qkv + 2 * d, 3 * d, e.P, e.lse, e.att, datt_, dqkv_, 3 * d, dqkv_ + d, dqkv_ + 2 * d, 3 * d, S, S,
              tok_mask_, 0, 10 + 4 * l, s);
     if (e.gin_b) colsum<T>(dqkv_, 3 * d, e.gin_b, Me, 3 * d, 0, s);
     lin_bwd(e.qk, dqkv_, 3 * d, e.n1p, d, Me, tmpf_, true, nullptr, s);

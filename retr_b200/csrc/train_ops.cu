@@ -4,34 +4,15 @@
 // through the tcgen05 GEMM (gemm_sm100.cu) after the layout helpers below have made the contraction
 // dimension contiguous.
 #include "train_ops.h"
+#include "dropout.cuh"
+
+#include <type_traits>
 
 namespace retr {
 namespace {
 
 constexpr int EW_THREADS = 256;
 inline unsigned ew_blocks(int64_t n) { return (unsigned)std::min<int64_t>(cdiv(n, EW_THREADS), 148 * 16); }
-
-// ---- Philox4x32-10 ------------------------------------------------------------------------------
-__device__ __forceinline__ uint4 philox4(uint2 key, uint4 ctr) {
-  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
-#pragma unroll
-  for (int i = 0; i < 10; ++i) {
-    const uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
-    const uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
-    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
-    key.x += W0; key.y += W1;
-  }
-  return ctr;
-}
-// 0 for a dropped element, 1/(1-p) for a kept one; a pure function of (seed, site, idx)
-__device__ __forceinline__ float drop_scale(const DropCfg& dc, uint64_t idx) {
-  if (dc.p <= 0.f) return 1.f;
-  const uint4 r = philox4(make_uint2((uint32_t)dc.seed, (uint32_t)(dc.seed >> 32)),
-                          make_uint4((uint32_t)(idx >> 2), (uint32_t)(idx >> 34), dc.site, 0u));
-  const uint32_t sel = (uint32_t)idx & 3u;
-  const uint32_t w = sel == 0 ? r.x : (sel == 1 ? r.y : (sel == 2 ? r.z : r.w));
-  return ((float)w * 2.3283064365386963e-10f >= dc.p) ? 1.f / (1.f - dc.p) : 0.f;
-}
 
 template <typename T> struct V16;
 template <> struct V16<float> {
@@ -807,6 +788,7 @@ void layernorm_bwd(const float* x, const float* gamma, const float* dy1, const f
 
 template <typename T>
 void attention_train_fwd(const AttnTrainParams& p, cudaStream_t s) {
+  if (std::is_same<T, bf16>::value && p.lse) return flash_train_fwd_bf16(p, s);      // tensor-core path
   RETR_CHECK(p.dh == 32 || p.dh == 64, "head dim must be 32 or 64");
   dim3 grid((unsigned)cdiv(p.Lq, AT_ROWS), (unsigned)p.H, (unsigned)p.B);
   if (p.dh == 32) {
@@ -827,6 +809,7 @@ template void attention_train_fwd<bf16>(const AttnTrainParams&, cudaStream_t);
 template <typename T>
 void attention_train_bwd(const AttnBwdParams& bp, cudaStream_t s) {
   const AttnTrainParams& p = bp.f;
+  if (std::is_same<T, bf16>::value && p.lse) return flash_train_bwd_bf16(bp, s);       // tensor-core path
   RETR_CHECK(p.dh == 32 || p.dh == 64, "head dim must be 32 or 64");
   dim3 gq((unsigned)cdiv(p.Lq, AT_ROWS), (unsigned)p.H, (unsigned)p.B);
   dim3 gk((unsigned)cdiv(p.Lk, 32), (unsigned)p.H, (unsigned)p.B);

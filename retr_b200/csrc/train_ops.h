@@ -62,7 +62,8 @@ struct AttnTrainParams {
   const void* q; const void* k; const void* v;      // T, rows [b*L + i], heads side by side
   int64_t ldq, ldk, ldv;
   void* out; int64_t ldo;                           // T [B*Lq, d]
-  void* probs;                                      // T [B,H,Lq,Lk]  softmax probabilities BEFORE dropout
+  void* probs;                                      // T [B,H,Lq,Lk]  softmax probabilities BEFORE dropout (SIMT path)
+  float* lse;                                       // fp32 [B,H,Lq] log2-sum-exp per query row (tensor-core path)
   int B, Lq, Lk, H, dh;
   const uint8_t* key_pad;                           // [B,Lk] non-zero = masked
   int causal;
@@ -72,11 +73,16 @@ template <typename T> void attention_train_fwd(const AttnTrainParams& p, cudaStr
 struct AttnBwdParams {
   AttnTrainParams f;                                // forward operands (out unused)
   const void* dout; int64_t lddo;                   // T [B*Lq, d]
-  void* ds;                                         // T [B,H,Lq,Lk] scratch: softmax-backward scores
+  void* ds;                                         // T [B,H,Lq,Lk] scratch: softmax-backward scores (SIMT path)
+  float* delta;                                     // fp32 [B,H,Lq] scratch: rowsum(dO o O) (tensor-core path)
   void* dq; void* dk; void* dv;                     // T, same pitches as q, k, v
   int64_t lddq, lddk, lddv;
 };
 template <typename T> void attention_train_bwd(const AttnBwdParams& p, cudaStream_t s);
+// bf16 tensor-core (mma.sync) flash variants, attention_train_mma.cu: nothing of size [Lq,Lk] reaches HBM.
+// f.out must hold the forward output (delta = rowsum(dO o O)).
+void flash_train_fwd_bf16(const AttnTrainParams& p, cudaStream_t s);
+void flash_train_bwd_bf16(const AttnBwdParams& p, cudaStream_t s);
 
 // ---- embeddings ------------------------------------------------------------------------------------------
 // y = dropout(LN_eps(E_word[ids] + E_pos[t]));  pre = the LN input kept for the backward pass
