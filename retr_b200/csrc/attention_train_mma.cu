@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(128) flash_train_fwd_kernel(const AttnTrainPar
   const int g = lane >> 2, c4 = lane & 3;
   const int qrow0 = q0 + warp * 16 + g;
   const float sl2 = rsqrtf((float)DH) * 1.4426950408889634f;
-  const int64_t prow0 = (((int64_t)b * p.H + h) * p.Lq + qrow0) * p.Lk, prow1 = prow0 + (int64_t)8 * p.Lk;
+  const int64_t prow0 = ((int64_t)b * p.H + h) * p.Lq + qrow0, prow1 = prow0 + 8;     // dropout row ids
   uint32_t qa[DH / 16][4];
   float o[NT][4];
 #pragma unroll
@@ -176,13 +176,11 @@ __global__ void __launch_bounds__(128) flash_train_fwd_kernel(const AttnTrainPar
     l0 = l0 * cr0 + rs0; l1 = l1 * cr1 + rs1;          // the normaliser is that of the un-dropped softmax
     if (p.drop.p > 0.f) {
 #pragma unroll
-      for (int nt = 0; nt < 8; ++nt)
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-          const int j = kbase + nt * 8 + c4 * 2 + e;
-          s[nt][e] *= drop_scale(p.drop, (uint64_t)(prow0 + j));
-          s[nt][2 + e] *= drop_scale(p.drop, (uint64_t)(prow1 + j));
-        }
+      for (int nt = 0; nt < 8; ++nt) {
+        const uint32_t j = (uint32_t)(kbase + nt * 8 + c4 * 2);
+        const float2 k0 = drop_scale_cols2(p.drop, (uint64_t)prow0, j), k1 = drop_scale_cols2(p.drop, (uint64_t)prow1, j);
+        s[nt][0] *= k0.x; s[nt][1] *= k0.y; s[nt][2] *= k1.x; s[nt][3] *= k1.y;
+      }
     }
 #pragma unroll
     for (int i = 0; i < NT; ++i) { o[i][0] *= cr0; o[i][1] *= cr0; o[i][2] *= cr1; o[i][3] *= cr1; }
@@ -244,7 +242,7 @@ __global__ void __launch_bounds__(128) flash_train_bwd_dq_kernel(const AttnBwdPa
   const int qrow0 = q0 + warp * 16 + g;
   const float scale = rsqrtf((float)DH), sl2 = scale * 1.4426950408889634f;
   const int64_t bh = (int64_t)b * p.H + h;
-  const int64_t prow0 = (bh * p.Lq + qrow0) * p.Lk, prow1 = prow0 + (int64_t)8 * p.Lk;
+  const int64_t prow0 = bh * p.Lq + qrow0, prow1 = prow0 + 8;                          // dropout row ids
   const float lse0 = qrow0 < p.Lq ? p.lse[bh * p.Lq + qrow0] : INFINITY;
   const float lse1 = qrow0 + 8 < p.Lq ? p.lse[bh * p.Lq + qrow0 + 8] : INFINITY;
   uint32_t qa[DH / 16][4], da[DH / 16][4];
@@ -286,7 +284,10 @@ __global__ void __launch_bounds__(128) flash_train_bwd_dq_kernel(const AttnBwdPa
     mma_a_tileT<DH>(dp, da, Vs[buf], lane);
     const int kbase = t * TK;
 #pragma unroll
-    for (int nt = 0; nt < 8; ++nt)
+    for (int nt = 0; nt < 8; ++nt) {
+      const uint32_t jb = (uint32_t)(kbase + nt * 8 + c4 * 2);
+      const float2 ka = drop_scale_cols2(p.drop, (uint64_t)prow0, jb), kb = drop_scale_cols2(p.drop, (uint64_t)prow1, jb);
+      const float ks0[2] = {ka.x, ka.y}, ks1[2] = {kb.x, kb.y};
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
         const int kl = nt * 8 + c4 * 2 + e;
@@ -295,14 +296,10 @@ __global__ void __launch_bounds__(128) flash_train_bwd_dq_kernel(const AttnBwdPa
         const bool d0 = dead || (p.causal && j > qrow0), d1 = dead || (p.causal && j > qrow0 + 8);
         const float p0 = d0 ? 0.f : exp2f(s[nt][e] * sl2 - lse0);
         const float p1 = d1 ? 0.f : exp2f(s[nt][2 + e] * sl2 - lse1);
-        float g0 = dp[nt][e], g1 = dp[nt][2 + e];
-        if (p.drop.p > 0.f) {
-          g0 *= drop_scale(p.drop, (uint64_t)(prow0 + j));
-          g1 *= drop_scale(p.drop, (uint64_t)(prow1 + j));
-        }
-        s[nt][e] = p0 * (g0 - delta0);
-        s[nt][2 + e] = p1 * (g1 - delta1);
+        s[nt][e] = p0 * (dp[nt][e] * ks0[e] - delta0);
+        s[nt][2 + e] = p1 * (dp[nt][2 + e] * ks1[e] - delta1);
       }
+    }
     mma_p_tile<DH>(dq, s, Ks[buf], lane);               // dQ += dS K
     __syncthreads();
   }
@@ -376,7 +373,19 @@ __global__ void __launch_bounds__(128) flash_train_bwd_kv_kernel(const AttnBwdPa
     mma_a_tileT<DH>(dpt, va, dOs[buf], lane);             // dP^T
     const int qbase = t * TK;
 #pragma unroll
-    for (int nt = 0; nt < 8; ++nt)
+    for (int nt = 0; nt < 8; ++nt) {
+      // queries i (even) and i + 1 of this thread: one Philox evaluation per key row.  (bh*Lq + i) keeps the parity
+      // of i only when bh*Lq is even, so the pair is split into two single lookups otherwise.
+      const int64_t prow_e = bh * p.Lq + qbase + nt * 8 + c4 * 2;
+      float ms0[2], ms1[2];
+      if (prow_e & 1) {
+        ms0[0] = drop_scale_rc(p.drop, (uint64_t)prow_e, (uint32_t)krow0); ms0[1] = drop_scale_rc(p.drop, (uint64_t)prow_e + 1, (uint32_t)krow0);
+        ms1[0] = drop_scale_rc(p.drop, (uint64_t)prow_e, (uint32_t)(krow0 + 8)); ms1[1] = drop_scale_rc(p.drop, (uint64_t)prow_e + 1, (uint32_t)(krow0 + 8));
+      } else {
+        const float2 a0 = drop_scale_rows2(p.drop, (uint64_t)prow_e, (uint32_t)krow0);
+        const float2 a1 = drop_scale_rows2(p.drop, (uint64_t)prow_e, (uint32_t)(krow0 + 8));
+        ms0[0] = a0.x; ms0[1] = a0.y; ms1[0] = a1.x; ms1[1] = a1.y;
+      }
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
         const int ql = nt * 8 + c4 * 2 + e;
@@ -385,18 +394,14 @@ __global__ void __launch_bounds__(128) flash_train_bwd_kv_kernel(const AttnBwdPa
         const bool d0 = dead0 || (p.causal && krow0 > i), d1 = dead1 || (p.causal && krow0 + 8 > i);
         const float p0 = d0 ? 0.f : exp2f(st[nt][e] * sl2 - lse);
         const float p1 = d1 ? 0.f : exp2f(st[nt][2 + e] * sl2 - lse);
-        float m0 = 1.f, m1 = 1.f;
-        if (p.drop.p > 0.f) {
-          const int64_t prow = (bh * p.Lq + i) * p.Lk;
-          m0 = drop_scale(p.drop, (uint64_t)(prow + krow0));
-          m1 = drop_scale(p.drop, (uint64_t)(prow + krow0 + 8));
-        }
+        const float m0 = ms0[e], m1 = ms1[e];
         const float g0 = dpt[nt][e] * m0, g1 = dpt[nt][2 + e] * m1;
         st[nt][e] = p0 * m0;                              // (P o mask)^T  -> dV
         st[nt][2 + e] = p1 * m1;
         dpt[nt][e] = p0 * (g0 - dl);                      // dS^T          -> dK
         dpt[nt][2 + e] = p1 * (g1 - dl);
       }
+    }
     mma_p_tile<DH>(dv, st, dOs[buf], lane);
     mma_p_tile<DH>(dk, dpt, Qs[buf], lane);
     __syncthreads();

@@ -91,6 +91,70 @@ __global__ void im2col_T_kernel(const T* __restrict__ x, T* __restrict__ colT, i
   }
 }
 
+// bf16 fast paths of the two layout helpers: 64x64 tiles, 4-byte (bf16x2) accesses in both directions so every
+// warp instruction moves 128 contiguous bytes; smem pitch 66 elements keeps the transposed reads 2-way at worst.
+__global__ void __launch_bounds__(256) transpose_bf16x2_kernel(const bf16* __restrict__ in, int64_t ld_in,
+                                                               bf16* __restrict__ out, int64_t ldo, int64_t M, int N) {
+  __shared__ __align__(4) bf16 t[64][66];
+  const int64_t m0 = (int64_t)blockIdx.x * 64;
+  const int n0 = blockIdx.y * 64;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int r = w; r < 64; r += 8) {
+    const int64_t m = m0 + r;
+    const int n = n0 + lane * 2;
+    __nv_bfloat162 v = __floats2bfloat162_rn(0.f, 0.f);
+    if (m < M && n < N) v = *reinterpret_cast<const __nv_bfloat162*>(in + m * ld_in + n);
+    *reinterpret_cast<__nv_bfloat162*>(&t[r][lane * 2]) = v;
+  }
+  __syncthreads();
+  for (int c = w; c < 64; c += 8) {
+    const int n = n0 + c;
+    const int64_t m = m0 + lane * 2;
+    if (n < N && m < ldo) {
+      __nv_bfloat162 v;
+      v.x = t[lane * 2][c];
+      v.y = t[lane * 2 + 1][c];
+      *reinterpret_cast<__nv_bfloat162*>(out + (int64_t)n * ldo + m) = v;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) im2col_T_bf16x2_kernel(const bf16* __restrict__ x, bf16* __restrict__ colT,
+                                                              int64_t ldm, int64_t M, int H, int W, int C, int k,
+                                                              int stride, int pad, int dil, int OH, int OW) {
+  __shared__ __align__(4) bf16 t[64][66];
+  const int tap = blockIdx.z, fr = tap / k, fs = tap - fr * k;
+  const int64_t m0 = (int64_t)blockIdx.x * 64;
+  const int c0 = blockIdx.y * 64;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int r = w; r < 64; r += 8) {
+    const int64_t m = m0 + r;
+    const int c = c0 + lane * 2;
+    __nv_bfloat162 v = __floats2bfloat162_rn(0.f, 0.f);
+    if (m < M && c < C) {
+      const int ow = (int)(m % OW);
+      const int64_t q = m / OW;
+      const int oh = (int)(q % OH);
+      const int64_t img = q / OH;
+      const int ih = oh * stride - pad + fr * dil, iw = ow * stride - pad + fs * dil;
+      if (ih >= 0 && ih < H && iw >= 0 && iw < W)
+        v = *reinterpret_cast<const __nv_bfloat162*>(x + ((img * H + ih) * W + iw) * C + c);
+    }
+    *reinterpret_cast<__nv_bfloat162*>(&t[r][lane * 2]) = v;
+  }
+  __syncthreads();
+  for (int cc = w; cc < 64; cc += 8) {
+    const int c = c0 + cc;
+    const int64_t m = m0 + lane * 2;
+    if (c < C && m < ldm) {
+      __nv_bfloat162 v;
+      v.x = t[lane * 2][cc];
+      v.y = t[lane * 2 + 1][cc];
+      *reinterpret_cast<__nv_bfloat162*>(colT + ((int64_t)tap * C + c) * ldm + m) = v;
+    }
+  }
+}
+
 template <typename T>
 __global__ void col2im_kernel(const T* __restrict__ dcol, T* __restrict__ dx, const T* __restrict__ add,
                               int64_t total, int H, int W, int C, int k, int stride, int pad, int dil, int OH, int OW) {
@@ -228,7 +292,7 @@ __global__ void relu_bwd_kernel(T* __restrict__ g, const T* __restrict__ h, int6
 // ---- LayerNorm (warp per row, d a multiple of 32, d <= 1024) --------------------------------------------
 constexpr int LN_MAX_PER = 32;       // d <= 1024
 
-template <typename T>
+template <typename T, int MAXP>
 __global__ void layernorm_pos_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                                      const float* __restrict__ beta, T* __restrict__ y, T* __restrict__ y2,
                                      const float* __restrict__ pos, int period, int64_t rows, int d, float eps) {
@@ -236,20 +300,20 @@ __global__ void layernorm_pos_kernel(const float* __restrict__ x, const float* _
   const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int per = d >> 5;
-  float v[LN_MAX_PER];
+  float v[MAXP];
   float s = 0.f;
 #pragma unroll
-  for (int j = 0; j < LN_MAX_PER; ++j)
+  for (int j = 0; j < MAXP; ++j)
     if (j < per) { v[j] = x[row * d + j * 32 + lane]; s += v[j]; }
   const float mean = warp_sum(s) / d;
   float q = 0.f;
 #pragma unroll
-  for (int j = 0; j < LN_MAX_PER; ++j)
+  for (int j = 0; j < MAXP; ++j)
     if (j < per) { const float t = v[j] - mean; q = fmaf(t, t, q); }
   const float rstd = rsqrtf(warp_sum(q) / d + eps);
   const float* pr = pos ? pos + (row % period) * d : nullptr;
 #pragma unroll
-  for (int j = 0; j < LN_MAX_PER; ++j)
+  for (int j = 0; j < MAXP; ++j)
     if (j < per) {
       const int c = j * 32 + lane;
       const float o = (v[j] - mean) * rstd * gamma[c] + beta[c];
@@ -258,6 +322,7 @@ __global__ void layernorm_pos_kernel(const float* __restrict__ x, const float* _
     }
 }
 
+template <int MAXP>
 __global__ void layernorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                                      const float* __restrict__ dy1, const float* __restrict__ dy2,
                                      float* __restrict__ dx, int accumulate_dx, float* __restrict__ dgamma,
@@ -267,14 +332,14 @@ __global__ void layernorm_bwd_kernel(const float* __restrict__ x, const float* _
   const int per = d >> 5;
   for (int i = threadIdx.x; i < 2 * d; i += blockDim.x) ln_red[i] = 0.f;
   __syncthreads();
-  float ag[LN_MAX_PER], ab[LN_MAX_PER];
+  float ag[MAXP], ab[MAXP];
 #pragma unroll
-  for (int j = 0; j < LN_MAX_PER; ++j) ag[j] = ab[j] = 0.f;
+  for (int j = 0; j < MAXP; ++j) ag[j] = ab[j] = 0.f;
   for (int64_t row = (int64_t)blockIdx.x * nwarp + warp; row < rows; row += (int64_t)gridDim.x * nwarp) {
-    float v[LN_MAX_PER], g[LN_MAX_PER];
+    float v[MAXP], g[MAXP];
     float s = 0.f;
 #pragma unroll
-    for (int j = 0; j < LN_MAX_PER; ++j)
+    for (int j = 0; j < MAXP; ++j)
       if (j < per) {
         const int64_t o = row * d + j * 32 + lane;
         v[j] = x[o];
@@ -284,12 +349,12 @@ __global__ void layernorm_bwd_kernel(const float* __restrict__ x, const float* _
     const float mean = warp_sum(s) / d;
     float q = 0.f;
 #pragma unroll
-    for (int j = 0; j < LN_MAX_PER; ++j)
+    for (int j = 0; j < MAXP; ++j)
       if (j < per) { const float t = v[j] - mean; q = fmaf(t, t, q); }
     const float rstd = rsqrtf(warp_sum(q) / d + eps);
     float c1 = 0.f, c2 = 0.f;
 #pragma unroll
-    for (int j = 0; j < LN_MAX_PER; ++j)
+    for (int j = 0; j < MAXP; ++j)
       if (j < per) {
         const int c = j * 32 + lane;
         const float xh = (v[j] - mean) * rstd;
@@ -303,7 +368,7 @@ __global__ void layernorm_bwd_kernel(const float* __restrict__ x, const float* _
     c1 = warp_sum(c1) / d;
     c2 = warp_sum(c2) / d;
 #pragma unroll
-    for (int j = 0; j < LN_MAX_PER; ++j)
+    for (int j = 0; j < MAXP; ++j)
       if (j < per) {
         const int64_t o = row * d + j * 32 + lane;
         const float r = rstd * (g[j] - c1 - v[j] * c2);
@@ -311,7 +376,7 @@ __global__ void layernorm_bwd_kernel(const float* __restrict__ x, const float* _
       }
   }
 #pragma unroll
-  for (int j = 0; j < LN_MAX_PER; ++j)
+  for (int j = 0; j < MAXP; ++j)
     if (j < per) {
       atomicAdd(&ln_red[j * 32 + lane], ag[j]);
       atomicAdd(&ln_red[d + j * 32 + lane], ab[j]);
@@ -383,7 +448,7 @@ __global__ void __launch_bounds__(AT_WARPS * 32) attn_train_fwd_kernel(const Att
       const float pv = pr[j] * inv;
       if (probs) probs[prow_off + j] = from_f<T>(pv);
       // the stored (rounded) probability is what the backward pass sees: use it here too
-      pr[j] = to_f(from_f<T>(pv)) * drop_scale(p.drop, (uint64_t)(prow_off + j));
+      pr[j] = to_f(from_f<T>(pv)) * drop_scale_rc(p.drop, (uint64_t)(prow_off / p.Lk), (uint32_t)j);
     }
     __syncwarp();
     for (int c = lane; c < DH; c += 32) {
@@ -425,7 +490,7 @@ __global__ void __launch_bounds__(AT_WARPS * 32) attn_train_bwd_q_kernel(const A
       float dp = 0.f;
 #pragma unroll
       for (int c = 0; c < DH; ++c) dp = fmaf(dor[c], Vs[j * (DH + 1) + c], dp);
-      dp *= drop_scale(p.drop, (uint64_t)(prow_off + j));
+      dp *= drop_scale_rc(p.drop, (uint64_t)(prow_off / p.Lk), (uint32_t)j);
       const float pv = to_f(probs[prow_off + j]);
       pr[j] = dp;
       delta = fmaf(dp, pv, delta);
@@ -473,7 +538,7 @@ __global__ void __launch_bounds__(128) attn_train_bwd_kv_kernel(const AttnBwdPar
       float pv = 0.f, sv = 0.f;
       if (i < p.Lq && j < p.Lk) {
         const int64_t o = (((int64_t)b * p.H + h) * p.Lq + i) * p.Lk + j;
-        pv = to_f(probs[o]) * drop_scale(p.drop, (uint64_t)o);
+        pv = to_f(probs[o]) * drop_scale_rc(p.drop, (uint64_t)(o / p.Lk), (uint32_t)j);
         sv = to_f(ds[o]);
       }
       Ps[ii][jj] = pv;
@@ -529,6 +594,7 @@ template <int DH> size_t attn_smem(int Lk) {
 }
 
 // ---- embeddings ---------------------------------------------------------------------------------------------
+template <int MAXP>
 __global__ void embed_ln_train_kernel(const int64_t* __restrict__ ids, const float* __restrict__ e_word,
                                       const float* __restrict__ e_pos, const float* __restrict__ gamma,
                                       const float* __restrict__ beta, float* __restrict__ pre, float* __restrict__ y,
@@ -539,10 +605,10 @@ __global__ void embed_ln_train_kernel(const int64_t* __restrict__ ids, const flo
   const int per = d >> 5;
   const int t = (int)(row % Tn);
   const int64_t id = ids[row];
-  float v[LN_MAX_PER];
+  float v[MAXP];
   float s = 0.f;
 #pragma unroll
-  for (int j = 0; j < LN_MAX_PER; ++j)
+  for (int j = 0; j < MAXP; ++j)
     if (j < per) {
       const int c = j * 32 + lane;
       v[j] = e_word[id * d + c] + e_pos[(int64_t)t * d + c];
@@ -552,11 +618,11 @@ __global__ void embed_ln_train_kernel(const int64_t* __restrict__ ids, const flo
   const float mean = warp_sum(s) / d;
   float q = 0.f;
 #pragma unroll
-  for (int j = 0; j < LN_MAX_PER; ++j)
+  for (int j = 0; j < MAXP; ++j)
     if (j < per) { const float u = v[j] - mean; q = fmaf(u, u, q); }
   const float rstd = rsqrtf(warp_sum(q) / d + eps);
 #pragma unroll
-  for (int j = 0; j < LN_MAX_PER; ++j)
+  for (int j = 0; j < MAXP; ++j)
     if (j < per) {
       const int c = j * 32 + lane;
       y[row * d + c] = ((v[j] - mean) * rstd * gamma[c] + beta[c]) * drop_scale(dc, (uint64_t)(row * d + c));
@@ -680,6 +746,13 @@ __global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g,
 // ================================== host wrappers ===================================================
 template <typename TI, typename TO>
 void transpose_pad(const TI* in, int64_t ld_in, TO* out, int64_t ldo, int64_t M, int N, cudaStream_t s) {
+  if (std::is_same<TI, bf16>::value && std::is_same<TO, bf16>::value && N % 2 == 0 && ld_in % 2 == 0 && ldo % 2 == 0 &&
+      reinterpret_cast<uintptr_t>(in) % 4 == 0 && reinterpret_cast<uintptr_t>(out) % 4 == 0) {
+    dim3 g2((unsigned)cdiv(ldo, 64), (unsigned)cdiv(N, 64));
+    transpose_bf16x2_kernel<<<g2, 256, 0, s>>>(reinterpret_cast<const bf16*>(in), ld_in, reinterpret_cast<bf16*>(out), ldo, M, N);
+    LAUNCH_OK();
+    return;
+  }
   dim3 grid((unsigned)cdiv(ldo, 32), (unsigned)cdiv(N, 32));
   transpose_pad_kernel<TI, TO><<<grid, dim3(32, 8), 0, s>>>(in, ld_in, out, ldo, M, N);
   LAUNCH_OK();
@@ -692,6 +765,13 @@ template <typename T>
 void im2col_T(const T* x, T* colT, int64_t ldm, int64_t nimg, int H, int W, int C, int k, int stride, int pad, int dil,
               int OH, int OW, cudaStream_t s) {
   const int64_t M = nimg * OH * OW;
+  if (std::is_same<T, bf16>::value && C % 2 == 0 && ldm % 2 == 0) {
+    dim3 g2((unsigned)cdiv(ldm, 64), (unsigned)cdiv(C, 64), (unsigned)(k * k));
+    im2col_T_bf16x2_kernel<<<g2, 256, 0, s>>>(reinterpret_cast<const bf16*>(x), reinterpret_cast<bf16*>(colT), ldm, M, H, W, C, k,
+                                              stride, pad, dil, OH, OW);
+    LAUNCH_OK();
+    return;
+  }
   dim3 grid((unsigned)cdiv(ldm, 32), (unsigned)cdiv(C, 32), (unsigned)(k * k));
   im2col_T_kernel<T><<<grid, dim3(32, 8), 0, s>>>(x, colT, ldm, M, H, W, C, k, stride, pad, dil, OH, OW);
   LAUNCH_OK();
@@ -768,8 +848,11 @@ template <typename T>
 void layernorm_pos(const float* x, const float* gamma, const float* beta, T* y, T* y2, const float* pos, int period,
                    int64_t rows, int d, float eps, cudaStream_t s) {
   RETR_CHECK(d % 32 == 0 && d <= 32 * LN_MAX_PER, "layernorm: d must be a multiple of 32, at most 1024");
-  layernorm_pos_kernel<T><<<(unsigned)cdiv(rows, 8), 256, 0, s>>>(x, gamma, beta, y, y2, pos, period > 0 ? period : 1,
-                                                                  rows, d, eps);
+  const unsigned grid = (unsigned)cdiv(rows, 8);
+  const int per = period > 0 ? period : 1;
+  if (d <= 256) layernorm_pos_kernel<T, 8><<<grid, 256, 0, s>>>(x, gamma, beta, y, y2, pos, per, rows, d, eps);
+  else if (d <= 512) layernorm_pos_kernel<T, 16><<<grid, 256, 0, s>>>(x, gamma, beta, y, y2, pos, per, rows, d, eps);
+  else layernorm_pos_kernel<T, 32><<<grid, 256, 0, s>>>(x, gamma, beta, y, y2, pos, per, rows, d, eps);
   LAUNCH_OK();
 }
 template void layernorm_pos<float>(const float*, const float*, const float*, float*, float*, const float*, int, int64_t,
@@ -781,8 +864,10 @@ void layernorm_bwd(const float* x, const float* gamma, const float* dy1, const f
                    float* dgamma, float* dbeta, int64_t rows, int d, float eps, cudaStream_t s) {
   RETR_CHECK(d % 32 == 0 && d <= 32 * LN_MAX_PER, "layernorm_bwd: d must be a multiple of 32, at most 1024");
   const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(rows, 8), 148 * 4);
-  layernorm_bwd_kernel<<<blocks, 256, (size_t)2 * d * 4, s>>>(x, gamma, dy1, dy2, dx, accumulate_dx, dgamma, dbeta, rows,
-                                                             d, eps);
+  const size_t sm = (size_t)2 * d * 4;
+  if (d <= 256) layernorm_bwd_kernel<8><<<blocks, 256, sm, s>>>(x, gamma, dy1, dy2, dx, accumulate_dx, dgamma, dbeta, rows, d, eps);
+  else if (d <= 512) layernorm_bwd_kernel<16><<<blocks, 256, sm, s>>>(x, gamma, dy1, dy2, dx, accumulate_dx, dgamma, dbeta, rows, d, eps);
+  else layernorm_bwd_kernel<32><<<blocks, 256, sm, s>>>(x, gamma, dy1, dy2, dx, accumulate_dx, dgamma, dbeta, rows, d, eps);
   LAUNCH_OK();
 }
 
@@ -836,7 +921,10 @@ void embed_ln_train(const int64_t* ids, const float* e_word, const float* e_pos,
                     float* pre, float* y, int B, int Tn, int d, float eps, DropCfg dc, cudaStream_t s) {
   RETR_CHECK(d % 32 == 0 && d <= 32 * LN_MAX_PER, "embed_ln: d must be a multiple of 32, at most 1024");
   const int64_t rows = (int64_t)B * Tn;
-  embed_ln_train_kernel<<<(unsigned)cdiv(rows, 8), 256, 0, s>>>(ids, e_word, e_pos, gamma, beta, pre, y, rows, Tn, d, eps, dc);
+  const unsigned grid = (unsigned)cdiv(rows, 8);
+  if (d <= 256) embed_ln_train_kernel<8><<<grid, 256, 0, s>>>(ids, e_word, e_pos, gamma, beta, pre, y, rows, Tn, d, eps, dc);
+  else if (d <= 512) embed_ln_train_kernel<16><<<grid, 256, 0, s>>>(ids, e_word, e_pos, gamma, beta, pre, y, rows, Tn, d, eps, dc);
+  else embed_ln_train_kernel<32><<<grid, 256, 0, s>>>(ids, e_word, e_pos, gamma, beta, pre, y, rows, Tn, d, eps, dc);
   LAUNCH_OK();
 }
 

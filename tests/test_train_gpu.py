@@ -9,6 +9,7 @@ Dropout cannot be RNG-matched with torch, so parity runs use dropout 0 (SURVEY Â
 path is checked for determinism, keep-rate and train/eval consistency.
 """
 import copy
+import os
 import sys
 
 import pytest
@@ -154,6 +155,64 @@ def test_dropout_path():
     assert float((d - e).abs().max()) <= 2e-2 * scale        # p = 0 train forward == eval forward (bf16 tolerance)
     # the dropped forward is a perturbation of the clean one, not garbage
     assert float((a - d).abs().max()) <= 0.75 * scale + 1.0
+
+
+def _fused_inputs(model, enc_in, data):
+    t, g, loc = model._split_samples(samples_of(enc_in))
+    return model._train_inputs(t, g, loc, data["caps"][:, :-1].cuda(), data["cap_masks"][:, :-1].cuda())
+
+
+def test_dropout_backward_matches_finite_differences_fp32():
+    """With a fixed Philox seed the dropped forward is a deterministic function of the weights, so the backward
+    pass (which REGENERATES every mask) must agree with a central finite difference of the loss."""
+    kind = "CaptionGlobalLoc"
+    model, sd, cfg = train_model(kind, "fp32", dropout=0.1)
+    data, enc_in = synthetic_samples(kind, 2, shard=8)
+    tr = model.trainer(2)
+    inputs = _fused_inputs(model, enc_in, data)
+    targets = data["caps"][:, 1:].cuda()
+
+    def loss():
+        return float(tr.loss_and_grads(*inputs, targets, dropout_p=0.1, seed=1234))
+
+    loss()
+    g = {n: tr.grads[n].clone() for n in tr.trainable}
+    gnorm = sum(float(v.double().pow(2).sum()) for v in g.values()) ** 0.5
+    params = dict(model.named_parameters())
+    eps = 2e-2
+    with torch.no_grad():
+        for n, v in g.items():
+            params[n].add_(v, alpha=eps / gnorm)
+        lp = loss()
+        for n, v in g.items():
+            params[n].add_(v, alpha=-2 * eps / gnorm)
+        lm = loss()
+    fd = (lp - lm) / (2 * eps)
+    assert abs(fd - gnorm) <= 0.03 * gnorm, (fd, gnorm)
+
+
+def test_flash_training_attention_matches_simt_with_dropout():
+    """Same seed, same mask function: the tensor-core flash attention (bf16 default) and the stored-probability
+    SIMT kernels (RETR_TRAIN_SIMT_ATTENTION=1) must give the same loss and gradients up to bf16 rounding."""
+    kind = "CaptionGlobalLoc"
+    data, enc_in = synthetic_samples(kind, 2, shard=9)
+    targets = data["caps"][:, 1:].cuda()
+    out = {}
+    for mode in ("simt", "flash"):
+        if mode == "simt":
+            os.environ["RETR_TRAIN_SIMT_ATTENTION"] = "1"
+        try:
+            model, sd, cfg = train_model(kind, "bf16", dropout=0.1)
+            tr = model.trainer(2)
+        finally:
+            os.environ.pop("RETR_TRAIN_SIMT_ATTENTION", None)
+        l = float(tr.loss_and_grads(*_fused_inputs(model, enc_in, data), targets, dropout_p=0.1, seed=77))
+        out[mode] = (l, {n: tr.grads[n].clone().cpu() for n in tr.trainable})
+    assert abs(out["simt"][0] - out["flash"][0]) <= 2e-3 * abs(out["simt"][0]), (out["simt"][0], out["flash"][0])
+    rows = compare(out["simt"][1], out["flash"][1])
+    num = sum((r[1] * r[2]) ** 2 for r in rows) ** 0.5
+    den = sum(r[1] ** 2 for r in rows) ** 0.5
+    assert num / den <= 5e-2, num / den
 
 
 class _FakeLoader:
