@@ -279,11 +279,15 @@ __device__ __forceinline__ void epilogue_chunk_staged(const KArgs& a, uint32_t (
 }
 
 template <int BN, bool GATHER>
-__global__ void __launch_bounds__(GATHER ? 384 : 256, 1)
+__global__ void __launch_bounds__(384, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmR,
                     const KArgs a) {
   using C = Cfg<BN>;
+  // epilogue warp groups: a plain GEMM has two (warps 4-7 and 8-11) that take alternate 128-byte column
+  // sub-tiles of the accumulator — tiles with K <= 1024 are epilogue-bound with one; the convolution variant
+  // keeps one and uses warps 8-11 for the im2col gather (its K >= 576 tiles are main-loop bound).
+  constexpr int EG = GATHER ? 1 : 2;
   const int STAGES = a.stages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -314,7 +318,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull[s], 1);
-      ptx::mbar_init(&tempty[s], 128);
+      ptx::mbar_init(&tempty[s], 128 * EG);
     }
     for (int s = 0; s < R_BUFS; ++s) {
       ptx::mbar_init(&rfull[s], 1);
@@ -389,12 +393,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
       }
     }
-  } else if (warp >= 4 && warp < 8) {
+  } else if (warp >= 4 && warp < 4 + 4 * EG) {
     // ===== epilogue =====
     const int q = warp & 3;
+    const int grp = (warp - 4) >> 2;                 // epilogue warp group
     const int row = q * 32 + lane;                   // row inside the tile == TMEM lane
-    const int tid_e = threadIdx.x - 128;
-    uint32_t tcount = 0, cit = 0, rb = 0, rph = 0;
+    const int tid_e = (threadIdx.x - 128) & 127;     // thread inside its group
+    const int tid_all = threadIdx.x - 128;
+    uint32_t tcount = 0, cit = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
       const TileCoord tc = tile_coord(a, tile);
       const int m_blk = tc.m_blk, n_blk = tc.n_blk;
@@ -403,26 +409,31 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const int64_t rb_row = a.rowbias_dyn ? (int64_t)__ldg(a.rowbias_dyn) : (m % a.rowbias_period);
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
       if (a.tma_epi) {
-        // per-tile column parameters -> smem (all 128 epilogue threads)
-        ptx::named_bar_sync(2, 128);
-        for (int i = tid_e; i < BN; i += 128) {
+        // per-tile column parameters -> smem (all epilogue threads)
+        ptx::named_bar_sync(2, 128 * EG);
+        for (int i = tid_all; i < BN; i += 128 * EG) {
           const int n = n_blk * BN + i;
           sb[i] = (a.scale && n < a.N) ? __ldg(a.scale + n) : 1.f;
           sb[BN + i] = (a.bias && n < a.N) ? __ldg(a.bias + n) : 0.f;
         }
-        ptx::named_bar_sync(2, 128);
+        ptx::named_bar_sync(2, 128 * EG);
         ptx::mbar_wait(&tfull[as], aph);
         ptx::tc_fence_after_sync();
         for (int n0 = n_blk * BN; n0 < min(a.N, (n_blk + 1) * BN); n0 += EC, ++cit) {
+          if (EG == 2 && (int)(cit & 1) != grp) continue;        // the other group's sub-tile
           const int col = n0 - n_blk * BN;
-          uint8_t* cbuf = cst + (cit & 1) * EPI_TILE_BYTES;
+          uint8_t* cbuf = cst + (EG == 2 ? grp : (int)(cit & 1)) * EPI_TILE_BYTES;
           const uint8_t* rbuf = nullptr;
+          const uint32_t rb = cit % R_BUFS, rph = (cit / R_BUFS) & 1;
           if (a.res_tma) {
             ptx::mbar_wait(&rfull[rb], rph);
             rbuf = rst + rb * EPI_TILE_BYTES;
           }
-          if (tid_e == 0) ptx::bulk_wait_read<1>();        // the store that used cbuf two sub-tiles ago
-          ptx::named_bar_sync(1, 128);
+          if (tid_e == 0) {                                   // the store that last used cbuf has read it
+            if (EG == 2) ptx::bulk_wait_read<0>();
+            else ptx::bulk_wait_read<1>();
+          }
+          ptx::named_bar_sync(1 + 2 * grp, 128);
           for (int c = 0; c < EC / 32; ++c) {
             uint32_t r[32];
             ptx::tmem_ld_32x32(t_row + col + c * 32, r);
@@ -434,12 +445,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               epilogue_chunk_staged<bf16>(a, r, sb + col + c * 32, sb + BN + col + c * 32, rb_row, n0 + c * 32, row,
                                           c * 4, rbuf, cbuf);
           }
-          if (a.res_tma) {
-            ptx::mbar_arrive(&rempty[rb]);
-            if (++rb == R_BUFS) { rb = 0; rph ^= 1; }
-          }
+          if (a.res_tma) ptx::mbar_arrive(&rempty[rb]);
           ptx::fence_proxy_async_smem();
-          ptx::named_bar_sync(1, 128);
+          ptx::named_bar_sync(1 + 2 * grp, 128);
           if (tid_e == 0) {
             ptx::tma_store_2d(&tmC, cbuf, n0, m_blk * BM);
             ptx::bulk_commit();
@@ -454,7 +462,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         uint32_t best_i = 0;
         const int64_t mc = a.c_group ? (m / a.c_group) * a.c_group_stride + (m % a.c_group) : m + (int64_t)tc.sp * a.M;
 #pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
+        for (int c = grp; c < BN / 32; c += EG) {     // 32-column chunks alternate between the groups
           const int n0 = n_blk * BN + c * 32;
           if (n0 >= a.N) break;                       // warp-uniform
           uint32_t r[32];
@@ -556,7 +564,7 @@ void launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& t
   ka.stages = Cfg<BN>::stages_for(ka.tma_epi, ka.res_tma);
   RETR_CHECK(ka.stages >= (GATHER ? GATHER_LAG + 1 : 2), "not enough shared memory for the pipeline");
   const int smem = Cfg<BN>::fixed_bytes(ka.tma_epi, ka.res_tma) + ka.stages * Cfg<BN>::STAGE_BYTES;
-  gemm_tcgen05_kernel<BN, GATHER><<<grid, GATHER ? 384 : 256, smem, stream>>>(tmA, tmB, tmC, tmR, ka);
+  gemm_tcgen05_kernel<BN, GATHER><<<grid, 384, smem, stream>>>(tmA, tmB, tmC, tmR, ka);
   LAUNCH_OK();
 }
 
