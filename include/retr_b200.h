@@ -142,6 +142,11 @@ void retr_train_destroy(retr_trainer* tr);
  * a buffer (requires_grad False: conv1/layer1, models/backbone.py:58-60; FrozenBatchNorm2d buffers). */
 int retr_train_bind(retr_trainer* tr, const char* name, float* param, float* grad, const int64_t* shape,
                     int32_t ndim);
+/* Optional (before finalize): declare that every bound trainable parameter / gradient is a slice of two flat
+ * fp32 arenas with the same element order, the first n_backbone elements being the "backbone" learning-rate
+ * group (main.py:31-36).  The step then zeroes the gradients with one memset, takes the global norm with one
+ * kernel and runs AdamW in two launches; without it the same work is done tensor by tensor. */
+int retr_train_set_arena(retr_trainer* tr, float* params, float* grads, int64_t n_total, int64_t n_backbone);
 int retr_train_finalize(retr_trainer* tr);
 /* replaces: outputs = model(*samples, caps[:, :-1], cap_masks[:, :-1]) in train mode (engine.py:70):
  * dropout `dropout_p` at the reference's sites (embeddings, attention probabilities, residual branches)

@@ -210,6 +210,13 @@ int retr_train_bind(retr_trainer* tr, const char* name, float* param, float* gra
   API_END
 }
 
+int retr_train_set_arena(retr_trainer* tr, float* params, float* grads, int64_t n_total, int64_t n_backbone) {
+  API_BEGIN
+  RETR_CHECK(tr && params && grads && n_total > 0 && n_backbone >= 0 && n_backbone <= n_total, "bad arena");
+  tr->tr->set_arena(params, grads, n_total, n_backbone);
+  API_END
+}
+
 int retr_train_finalize(retr_trainer* tr) {
   API_BEGIN
   RETR_CHECK(tr, "null trainer");

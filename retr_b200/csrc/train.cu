@@ -138,6 +138,9 @@ class TrainerT final : public TrainerBase {
     RETR_CHECK(!finalized_, "bind after finalize");
     params_[name] = b;
   }
+  void set_arena(float* params, float* grads, int64_t n_total, int64_t n_backbone) override {
+    arena_p_ = params; arena_g_ = grads; arena_n_ = n_total; arena_nb_ = n_backbone;
+  }
   void finalize() override;
   void forward(int B, const float* t_img, const uint8_t* t_mask, const float* g_img, const uint8_t* g_mask,
                const float* loc, const int64_t* ids, const uint8_t* id_mask, float* logits_out, float dropout_p,
@@ -234,6 +237,8 @@ class TrainerT final : public TrainerBase {
   // bf16: tensor-core flash attention (log-sum-exp kept, probabilities recomputed in the backward pass)
   bool flash_ = std::is_same<T, bf16>::value && getenv("RETR_TRAIN_SIMT_ATTENTION") == nullptr;
   int64_t ws_floats_ = 0;
+  float *arena_p_ = nullptr, *arena_g_ = nullptr, *arena_m_ = nullptr, *arena_v_ = nullptr;
+  int64_t arena_n_ = 0, arena_nb_ = 0;
   int cur_B_ = 0;
   float drop_p_ = 0.f;
   unsigned long long seed_ = 0;
@@ -767,8 +772,12 @@ void TrainerT<T>::backward_impl(cudaStream_t s) {
   const int B = cur_B_, d = desc.d_model, Tn = desc.max_pos;
   const int64_t Me = (int64_t)B * S, Md = (int64_t)B * Tn, ff = desc.d_ff;
   const int64_t NI = (int64_t)B * desc.n_images, g2 = (int64_t)grid_hw * grid_hw;
-  for (auto& kv : params_)
-    if (kv.second.g) CUDA_OK(cudaMemsetAsync(kv.second.g, 0, kv.second.numel * 4, s));
+  if (arena_g_) {
+    CUDA_OK(cudaMemsetAsync(arena_g_, 0, arena_n_ * 4, s));
+  } else {
+    for (auto& kv : params_)
+      if (kv.second.g) CUDA_OK(cudaMemsetAsync(kv.second.g, 0, kv.second.numel * 4, s));
+  }
 
   // ---- head ----
   lin_bwd(mlp_[2], dlg_, Vp, m2_, mlp_[1].out, Md, dh_, false, mlp_[2].gb, s);          // dh_ = d m2 [Md,512]
@@ -885,6 +894,23 @@ void TrainerT<T>::clip_adamw(float max_norm, float lr, float lr_backbone, float 
                              float weight_decay, int step, float* grad_norm_dev, cudaStream_t s) {
   const long long l0 = g_launches;
   CUDA_OK(cudaMemsetAsync(sumsq_, 0, 4, s));
+  if (arena_g_) {
+    grad_sumsq(arena_g_, arena_n_, sumsq_, s);
+    if (grad_norm_dev) CUDA_OK(cudaMemcpyAsync(grad_norm_dev, sumsq_, 4, cudaMemcpyDeviceToDevice, s));
+    if (!arena_m_) {
+      arena_m_ = alloc<float>(arena_n_); arena_v_ = alloc<float>(arena_n_);
+      CUDA_OK(cudaMemsetAsync(arena_m_, 0, arena_n_ * 4, s));
+      CUDA_OK(cudaMemsetAsync(arena_v_, 0, arena_n_ * 4, s));
+    }
+    if (arena_nb_ > 0)
+      adamw_step(arena_p_, arena_g_, arena_m_, arena_v_, arena_nb_, sumsq_, max_norm, lr_backbone, beta1, beta2, eps,
+                 weight_decay, step, s);
+    if (arena_n_ > arena_nb_)
+      adamw_step(arena_p_ + arena_nb_, arena_g_ + arena_nb_, arena_m_ + arena_nb_, arena_v_ + arena_nb_,
+                 arena_n_ - arena_nb_, sumsq_, max_norm, lr, beta1, beta2, eps, weight_decay, step, s);
+    launches += g_launches - l0;
+    return;
+  }
   for (auto& kv : params_)
     if (kv.second.g) grad_sumsq(kv.second.g, kv.second.numel, sumsq_, s);
   if (grad_norm_dev) CUDA_OK(cudaMemcpyAsync(grad_norm_dev, sumsq_, 4, cudaMemcpyDeviceToDevice, s));

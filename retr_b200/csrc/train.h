@@ -16,6 +16,9 @@ class TrainerBase {
   // bind a reference state_dict entry: `param` fp32 device memory read at every step (never copied),
   // `grad` (may be null = frozen / buffer) fp32 device memory the backward pass writes
   virtual void bind(const std::string& name, float* param, float* grad, const int64_t* shape, int ndim) = 0;
+  // optional: all trainable parameters / gradients live in two flat fp32 arenas (same element order), the first
+  // n_backbone elements being the backbone group -> one memset, one norm kernel, two AdamW launches per step
+  virtual void set_arena(float* params, float* grads, int64_t n_total, int64_t n_backbone) = 0;
   virtual void finalize() = 0;
   // train-mode forward; logits_out (optional) fp32 [B,T,V]
   virtual void forward(int B, const float* t_img, const uint8_t* t_mask, const float* g_img, const uint8_t* g_mask,

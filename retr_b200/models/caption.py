@@ -39,9 +39,9 @@ class _NativeTrainForward(torch.autograd.Function):
     only so that autograd routes their gradients; the arithmetic reads them by pointer."""
 
     @staticmethod
-    def forward(ctx, model, inputs, p_drop, seed, *params):
+    def forward(ctx, model, inputs, p_drop, seed, names, *params):
         trainer = model.trainer(inputs[0].shape[0])
-        ctx.trainer, ctx.names = trainer, trainer.trainable
+        ctx.trainer, ctx.names = trainer, names               # names[i] is the state_dict key of params[i]
         return trainer.forward(*inputs, dropout_p=p_drop, seed=seed)
 
     @staticmethod
@@ -53,7 +53,7 @@ class _NativeTrainForward(torch.autograd.Function):
             # data parallel: one all-reduce of the flat gradient buffer (NCCL over NVLink), mean over ranks
             torch.distributed.all_reduce(trainer.gflat)
             trainer.gflat.div_(torch.distributed.get_world_size())
-        return (None, None, None, None) + tuple(grads[n] for n in ctx.names)
+        return (None, None, None, None, None) + tuple(grads[n] for n in ctx.names)
 
 
 class _CaptionBase(nn.Module):
@@ -169,8 +169,9 @@ class _CaptionBase(nn.Module):
                 raise NotImplementedError("return_attention=True is served by the eval path (model.eval())")
             inputs = self._train_inputs(t_samples, g_samples, loc, target_exp, target_exp_mask)
             seed = int(torch.randint(0, 2 ** 62, (1,)).item())       # drawn from torch's CPU generator
-            params = [p for p in self.parameters() if p.requires_grad]
-            return _NativeTrainForward.apply(self, inputs, float(self.dropout_p), seed, *params)
+            named = [(n, p) for n, p in self.named_parameters() if p.requires_grad]
+            return _NativeTrainForward.apply(self, inputs, float(self.dropout_p), seed, [n for n, _ in named],
+                                             *[p for _, p in named])
         B = target_exp.shape[0]
         att_enc = None
         if return_attention:

@@ -59,6 +59,7 @@ SIGNATURES = {
     "retr_train_create": (C.c_int, [C.POINTER(ModelDesc), C.c_int32, C.POINTER(C.c_void_p)]),
     "retr_train_destroy": (None, [C.c_void_p]),
     "retr_train_bind": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int64), C.c_int32]),
+    "retr_train_set_arena": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64]),
     "retr_train_finalize": (C.c_int, [C.c_void_p]),
     "retr_train_forward": (C.c_int, [C.c_void_p, C.c_int32] + [C.c_void_p] * 8 + [C.c_float, C.c_uint64, C.c_void_p]),
     "retr_train_backward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),

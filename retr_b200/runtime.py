@@ -196,14 +196,25 @@ class Trainer:
         for n, t in self.tensors.items():
             if t.dtype != torch.float32 or not t.is_contiguous() or t.device != device:
                 raise RuntimeError(f"parameter {n} must be a contiguous fp32 tensor on {device}")
-        self.trainable = [n for n in self.names if isinstance(sd[n], torch.nn.Parameter) and sd[n].requires_grad]
+        trainable = [n for n in self.names if isinstance(sd[n], torch.nn.Parameter) and sd[n].requires_grad]
+        # flat arenas: backbone group first (its own learning rate, main.py:31-36), then everything else.  The
+        # parameters are RE-POINTED into the arena (p.data = view), so the model, any torch optimiser and the
+        # native kernels all see the same storage.
+        self.trainable = [n for n in trainable if "backbone" in n] + [n for n in trainable if "backbone" not in n]
         total = sum(self.tensors[n].numel() for n in self.trainable)
+        self.n_backbone = sum(self.tensors[n].numel() for n in self.trainable if "backbone" in n)
+        self.pflat = torch.empty(total, dtype=torch.float32, device=device)
         self.gflat = torch.zeros(total, dtype=torch.float32, device=device)
         self.grads, off = {}, 0
-        for n in self.trainable:
-            k = self.tensors[n].numel()
-            self.grads[n] = self.gflat[off:off + k].view(self.tensors[n].shape)
-            off += k
+        with torch.no_grad():
+            for n in self.trainable:
+                t = self.tensors[n]
+                k = t.numel()
+                view = self.pflat[off:off + k].view(t.shape)
+                view.copy_(t.data)
+                t.data = view
+                self.grads[n] = self.gflat[off:off + k].view(t.shape)
+                off += k
         handle = C.c_void_p()
         with torch.cuda.device(device):
             native.check(self.lib.retr_train_create(C.byref(d), int(pad_token_id), C.byref(handle)))
@@ -213,6 +224,8 @@ class Trainer:
                 shape = (C.c_int64 * max(t.dim(), 1))(*(t.shape if t.dim() else (1,)))
                 native.check(self.lib.retr_train_bind(self.handle, n.encode(), native.ptr(t.data), native.ptr(self.grads.get(n)),
                                                       shape, max(t.dim(), 1)))
+            native.check(self.lib.retr_train_set_arena(self.handle, native.ptr(self.pflat), native.ptr(self.gflat), total,
+                                                       self.n_backbone))
             native.check(self.lib.retr_train_finalize(self.handle))
         self.signature = self.signature_of(model)
         self.batch, self.step_count = 0, 0

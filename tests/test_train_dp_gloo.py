@@ -57,8 +57,9 @@ def _worker(rank, world, port, q):
     model.train()
     inputs = (torch.zeros(2, 3, 8, 8), torch.zeros(2, 8, 8, dtype=torch.bool), None, None, None,
               torch.zeros(2, 128, dtype=torch.long), torch.zeros(2, 128, dtype=torch.bool))
-    params = [p for p in model.parameters() if p.requires_grad]
-    out = _NativeTrainForward.apply(model, inputs, 0.0, 0, *params)
+    named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
+    params = [p for _, p in named]
+    out = _NativeTrainForward.apply(model, inputs, 0.0, 0, [n for n, _ in named], *params)
     out.sum().backward()
     ok_autograd = all(torch.allclose(p.grad, torch.full_like(p, 1.5)) for p in params)
     frozen_untouched = all(p.grad is None for p in model.parameters() if not p.requires_grad)
