@@ -115,6 +115,27 @@ def cpu_reference_throughput(batch, steps):
     return batch / (per_step * (MAX_LEN - 1)), cores, per_step, ran
 
 
+def reference_eager_on_gpu(batch, steps, dev):
+    """Secondary bar: the reference's ALGORITHM — full model recompute per token, stock
+    torch eager ops (cuDNN/cuBLAS fp32) — on the same B200, via the oracle port with every tensor on the
+    device.  Bounded sample, extrapolated x127 like the CPU leg."""
+    from oracle import retr_oracle as O
+    from retr_b200 import synthetic
+    model, cfg = build_model("fp32")
+    sd = {k: v.to(dev) for k, v in model.state_dict().items()}
+    data = synthetic.make_batch(batch, shard=0)
+    enc = tuple(data[k].to(dev) for k in ("t_img", "t_mask", "g_img", "g_mask", "loc"))
+    with torch.no_grad():
+        O.greedy(sd, cfg, *enc, max_len=MAX_LEN, bos_token=BOS, eos_token=EOS, literal=True, max_steps=2)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        _, ran = O.greedy(sd, cfg, *enc, max_len=MAX_LEN, bos_token=BOS, eos_token=EOS, literal=True, max_steps=steps)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+    per_step = dt / ran
+    return batch / (per_step * (MAX_LEN - 1)), per_step, ran
+
+
 def run_reference(args, rank):
     if rank != 0:
         return
@@ -266,6 +287,14 @@ def main():
             line["cpu_baseline"] = {"value": v, "unit": "expr/s", "cores": cores, "kind": "port",
                                     "sample": f"oracle port of the reference loop (full forward per token), batch 8, "
                                               f"{ran} timed steps at {per_step:.2f} s/step, extrapolated x127"}
+            try:
+                v2, ps2, ran2 = reference_eager_on_gpu(64, 4, dev)
+                line["reference_algorithm_eager_b200"] = {
+                    "value": v2, "unit": "expr/s", "kind": "port",
+                    "sample": f"oracle port on cuda (torch eager fp32, full forward per token), batch 64, {ran2} timed "
+                              f"steps at {ps2 * 1000:.0f} ms/step, extrapolated x127"}
+            except Exception as e:          # a reported extra, never a reason to lose the bench line
+                line["reference_algorithm_eager_b200"] = {"unavailable": str(e)[:200]}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

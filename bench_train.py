@@ -23,6 +23,36 @@ sys.path.insert(0, ROOT)
 GFLOP_PER_SAMPLE_STEP = 3 * 54.65
 
 
+def cpu_reference_train(cfg, batch=4, steps=2):
+    """The reference's train step on the host cores (oracle port of engine.py:64-83: autograd + clip + torch AdamW)."""
+    import time
+    from oracle import retr_oracle as O
+    from retr_b200 import synthetic
+    from retr_b200.models import caption
+    torch.manual_seed(cfg.seed)
+    with contextlib.redirect_stdout(io.StringIO()):
+        model, _ = caption.build_model(cfg)
+    sd = synthetic.calibrate_frozen_bn(model.state_dict())
+    names = [n for n, p in model.named_parameters() if p.requires_grad]
+    sd = {k: v.clone().requires_grad_(k in names) for k, v in sd.items()}
+    opt = torch.optim.AdamW([{"params": [sd[n] for n in names if "backbone" not in n]},
+                             {"params": [sd[n] for n in names if "backbone" in n], "lr": cfg.lr_backbone}],
+                            lr=cfg.lr, weight_decay=cfg.weight_decay)
+    data = synthetic.make_batch(batch, shard=0, train=True)
+    enc = (data["t_img"], data["t_mask"], data["g_img"], data["g_mask"], data["loc"])
+    times = []
+    for i in range(steps + 1):
+        t0 = time.perf_counter()
+        loss = O.train_loss(sd, cfg, *enc, data["caps"], data["cap_masks"], drop_p=cfg.dropout)
+        opt.zero_grad()
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_([sd[n] for n in names], cfg.clip_max_norm)
+        opt.step()
+        times.append(time.perf_counter() - t0)
+    per_step = sum(times[1:]) / steps
+    return batch / per_step, per_step, torch.get_num_threads()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -31,6 +61,7 @@ def main():
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--dropout", type=float, default=0.1)
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -93,7 +124,13 @@ def main():
         if os.path.exists(p):
             peak = json.load(open(p)).get("bf16_tflops_sustained", peak)
         tf = value * GFLOP_PER_SAMPLE_STEP / 1000.0 / world
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            v, ps, cores = cpu_reference_train(cfg)
+            cpu = {"value": v, "unit": "samples/s", "cores": cores, "kind": "port",
+                   "sample": f"oracle port of engine.py:64-83 (autograd, clip, torch AdamW), batch 4, 2 timed steps at {ps:.2f} s/step"}
         print(json.dumps({
+            "cpu_baseline": cpu,
             "metric": "training samples/sec (teacher-forced step: fwd + CE + bwd + clip + AdamW)", "value": value,
             "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "dtype": args.precision,

@@ -214,7 +214,7 @@ def encoder_inputs(sd: SD, cfg, t_img, t_mask, g_img=None, g_mask=None, loc=None
         else:                                     # CaptionLoc: whole vector -> one token
             loc_tok = F.linear(loc, w, b).unsqueeze(1)
         src = torch.cat([src, loc_tok], 1)
-        mask = torch.cat([mask, torch.zeros(B, loc_tok.shape[1], dtype=torch.bool)], 1)
+        mask = torch.cat([mask, torch.zeros(B, loc_tok.shape[1], dtype=torch.bool, device=mask.device)], 1)
     if g_img is not None:
         g_src, g_m = image_tokens(g_img, g_mask, sd, cfg)
         assert bool((~g_m).any(1).all()), "all-masked context row: ensure_unmasked_values path (models/utils.py:60-89)"
@@ -268,7 +268,8 @@ def greedy(sd: SD, cfg, t_img, t_mask, g_img, g_mask, loc, max_len=128, bos_toke
     ``max_steps`` bounds the loop for timing samples.  Returns (caption [B,max_len], steps run)."""
     B = t_img.shape[0]
     cap, msk = create_caption_and_mask(bos_token, max_len, B)
-    finished = torch.zeros(B, dtype=torch.bool)
+    cap, msk = cap.to(t_img.device), msk.to(t_img.device)      # decode.py:62 moves the samples; ids live beside them
+    finished = torch.zeros(B, dtype=torch.bool, device=t_img.device)
     enc = None if literal else encode(sd, cfg, t_img, t_mask, g_img, g_mask, loc)
     steps = 0
     for i in range(max_len - 1):

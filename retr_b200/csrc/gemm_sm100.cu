@@ -32,7 +32,11 @@ namespace {
 constexpr int BM = 128;
 constexpr int BK = 64;                 // 64 bf16 = 128 B = one swizzle row
 constexpr int A_TILE_BYTES = BM * BK * 2;
-constexpr int GATHER_LAG = 2;          // cp.async groups kept in flight per gather thread
+// cp.async groups a gather thread keeps in flight.  The thread signals stage `it - lag` only after it has issued
+// group `it`, which needs stage it % S empty, so MMA(j) cannot start before MMA(j + lag - S) has retired plus one
+// mbarrier round trip (~1 us): with S = 3, lag = 2 (round-1 first cut) the 3x3 convolutions ran fully serialised at
+// 1.48 us per k-block (22 % tensor pipe).  Keep S - lag >= 3: lag 1 up to 5 stages, lag 2 from 6.
+constexpr int MAX_GATHER_LAG = 2;
 
 struct KArgs {
   int64_t M;
@@ -64,7 +68,7 @@ struct KArgs {
 
 constexpr int MAX_STAGES = 8;
 constexpr int EPI_TILE_BYTES = BM * 128;     // 128 rows x 128 B (64 bf16 or 32 fp32 columns)
-constexpr int C_BUFS = 2, R_BUFS = 4;
+constexpr int C_BUFS = 2, R_BUFS = 4;      // C staging: 2 buffers (1 in the gather variant: one more pipeline stage)
 constexpr int SMEM_LIMIT = 232448;           // 227 KB opt-in maximum per CTA
 constexpr int BARRIER_BYTES = 512;
 
@@ -73,11 +77,12 @@ template <int BN> struct Cfg {
   static constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
   static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
   static constexpr int SB_BYTES = 2 * BN * 4;
-  static int fixed_bytes(bool tma_epi, bool res_tma) {
-    return 1024 + BARRIER_BYTES + SB_BYTES + (tma_epi ? C_BUFS * EPI_TILE_BYTES : 0) + (res_tma ? R_BUFS * EPI_TILE_BYTES : 0);
+  static int fixed_bytes(bool tma_epi, bool res_tma, bool gather) {
+    return 1024 + BARRIER_BYTES + SB_BYTES + (tma_epi ? (gather ? 1 : C_BUFS) * EPI_TILE_BYTES : 0) +
+           (res_tma ? R_BUFS * EPI_TILE_BYTES : 0);
   }
-  static int stages_for(bool tma_epi, bool res_tma) {
-    const int n = (SMEM_LIMIT - fixed_bytes(tma_epi, res_tma)) / STAGE_BYTES;
+  static int stages_for(bool tma_epi, bool res_tma, bool gather) {
+    const int n = (SMEM_LIMIT - fixed_bytes(tma_epi, res_tma, gather)) / STAGE_BYTES;
     return n > MAX_STAGES ? MAX_STAGES : n;
   }
 };
@@ -292,7 +297,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* cst = smem + STAGES * C::STAGE_BYTES;                         // C staging (TMA store source)
-  uint8_t* rst = cst + (a.tma_epi ? C_BUFS * EPI_TILE_BYTES : 0);         // residual staging (TMA load dest)
+  uint8_t* rst = cst + (a.tma_epi ? (GATHER ? 1 : C_BUFS) * EPI_TILE_BYTES : 0);   // residual staging (TMA load dest)
   float* sb = reinterpret_cast<float*>(rst + (a.res_tma ? R_BUFS * EPI_TILE_BYTES : 0));
   uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sb) + C::SB_BYTES);
   uint64_t* empty = full + MAX_STAGES;
@@ -422,7 +427,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         for (int n0 = n_blk * BN; n0 < min(a.N, (n_blk + 1) * BN); n0 += EC, ++cit) {
           if (EG == 2 && (int)(cit & 1) != grp) continue;        // the other group's sub-tile
           const int col = n0 - n_blk * BN;
-          uint8_t* cbuf = cst + (EG == 2 ? grp : (int)(cit & 1)) * EPI_TILE_BYTES;
+          uint8_t* cbuf = cst + (EG == 2 ? grp : 0) * EPI_TILE_BYTES;       // one staging buffer per group
           const uint8_t* rbuf = nullptr;
           const uint32_t rb = cit % R_BUFS, rph = (cit / R_BUFS) & 1;
           if (a.res_tma) {
@@ -430,8 +435,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             rbuf = rst + rb * EPI_TILE_BYTES;
           }
           if (tid_e == 0) {                                   // the store that last used cbuf has read it
-            if (EG == 2) ptx::bulk_wait_read<0>();
-            else ptx::bulk_wait_read<1>();
+            ptx::bulk_wait_read<0>();
           }
           ptx::named_bar_sync(1 + 2 * grp, 128);
           for (int c = 0; c < EC / 32; ++c) {
@@ -481,6 +485,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // ===== im2col gather producer: one thread per tile row =====
     const int row = threadIdx.x - 256;
     const uint32_t swz = (uint32_t)(row & 7);
+    const uint32_t lag = STAGES >= 6 ? 2u : 1u;
     uint32_t it = 0, s = 0, ph = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const TileCoord tc = tile_coord(a, tile);
@@ -504,10 +509,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
         for (uint32_t j = 0; j < 8; ++j) ptx::cp_async_16(dst + ((j ^ swz) << 4), src + j * 8, nbytes);
         ptx::cp_async_commit();
-        if (it >= GATHER_LAG) {
-          ptx::cp_async_wait<GATHER_LAG>();
+        if (it >= lag) {
+          if (lag == 2) ptx::cp_async_wait<2>();
+          else ptx::cp_async_wait<1>();
           ptx::fence_proxy_async_smem();
-          ptx::mbar_arrive(&full[(it - GATHER_LAG) % STAGES]);
+          ptx::mbar_arrive(&full[(it - lag) % STAGES]);
         }
         if (++cb == a.cblocks) { cb = 0; ++tap; }
         if (++s == (uint32_t)STAGES) { s = 0; ph ^= 1; }
@@ -515,7 +521,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     ptx::cp_async_wait<0>();
     ptx::fence_proxy_async_smem();
-    for (uint32_t j = (it > GATHER_LAG ? it - GATHER_LAG : 0); j < it; ++j) ptx::mbar_arrive(&full[j % STAGES]);
+    for (uint32_t j = (it > lag ? it - lag : 0); j < it; ++j) ptx::mbar_arrive(&full[j % STAGES]);
   }
 
   ptx::tc_fence_before_sync();
@@ -561,9 +567,9 @@ CUtensorMap make_tmap_2d(const void* base, int64_t rows, int64_t cols, int64_t l
 template <int BN, bool GATHER>
 void launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const CUtensorMap& tmR,
             KArgs& ka, int grid, cudaStream_t stream) {
-  ka.stages = Cfg<BN>::stages_for(ka.tma_epi, ka.res_tma);
-  RETR_CHECK(ka.stages >= (GATHER ? GATHER_LAG + 1 : 2), "not enough shared memory for the pipeline");
-  const int smem = Cfg<BN>::fixed_bytes(ka.tma_epi, ka.res_tma) + ka.stages * Cfg<BN>::STAGE_BYTES;
+  ka.stages = Cfg<BN>::stages_for(ka.tma_epi, ka.res_tma, GATHER);
+  RETR_CHECK(ka.stages >= (GATHER ? 3 : 2), "not enough shared memory for the pipeline");
+  const int smem = Cfg<BN>::fixed_bytes(ka.tma_epi, ka.res_tma, GATHER) + ka.stages * Cfg<BN>::STAGE_BYTES;
   gemm_tcgen05_kernel<BN, GATHER><<<grid, 384, smem, stream>>>(tmA, tmB, tmC, tmR, ka);
   LAUNCH_OK();
 }
