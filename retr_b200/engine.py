@@ -89,3 +89,46 @@ def evaluate(model, criterion, data_loader, device):
         outputs = model(*samples, caps[:, :-1], cap_masks[:, :-1])
         loss_sum += criterion(outputs.permute(0, 2, 1), caps[:, 1:]).item()
     return loss_sum / total
+
+
+def normalize_with_tokenizer(sent, tokenizer):
+    """reference engine.py:116-121."""
+    return tokenizer.decode(tokenizer.encode(sent), skip_special_tokens=True)
+
+
+def eval_model(model, data_loader, tokenizer, config, metrics_to_omit=(), print_samples=False, compute_metrics=None):
+    """Decode a split and score it — the loop shell of reference engine.py:125-187.  The decode is the native
+    KV-cached greedy loop (any batch size); the string metrics stay on the host and are DELEGATED: pass
+    ``compute_metrics(ref_list=..., hyp_list=...) -> dict`` (e.g. ``nlgeval.NLGEval(...).compute_metrics``, which is
+    what the reference constructs at engine.py:135-137).  Without it the metrics dict is empty — nlgeval (java METEOR
+    jar) is out of scope and not imported here.
+    Returns (metrics_dict, [{'ann_id', 'expression'}, ...]) like the reference."""
+    from collections import defaultdict
+
+    from .eval_utils.decode import greedy_decoding
+    model.eval()
+    annotations = defaultdict(list)
+    for a in data_loader.dataset.annot:
+        annotations[a[0]].append(a[2])
+    hypotheses, ids_hypotheses, references = [], [], []
+    pad_id = tokenizer.convert_tokens_to_ids(tokenizer.pad_token)
+    bos_id = tokenizer.convert_tokens_to_ids(tokenizer.cls_token)
+    eos_id = tokenizer.convert_tokens_to_ids(tokenizer.sep_token)
+    use_global, use_loc = _flags(data_loader)
+    with torch.no_grad():
+        for ann_ids, *encoder_input, _caps, _cap_masks in data_loader:
+            samples = pack_encoder_inputs(encoder_input, use_global, use_loc)
+            hyps = greedy_decoding(samples, model, tokenizer, max_len=config.max_position_embeddings, clean=True,
+                                   pad_token=pad_id, bos_token=bos_id, eos_token=eos_id, device="auto")
+            hypotheses += hyps
+            ann_list = ann_ids.tolist() if hasattr(ann_ids, "tolist") else list(ann_ids)
+            ids_hyps = [{"ann_id": i, "expression": h} for i, h in zip(ann_list, hyps)]
+            ids_hypotheses += ids_hyps
+            if print_samples:
+                print(*ids_hyps, sep="\n")
+            references += [[normalize_with_tokenizer(r, tokenizer) for r in annotations[i]] for i in ann_list]
+    metrics = {}
+    if compute_metrics is not None:
+        transposed = list(map(list, zip(*references)))
+        metrics = compute_metrics(ref_list=transposed, hyp_list=hypotheses)
+    return metrics, ids_hypotheses

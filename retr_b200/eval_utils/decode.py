@@ -75,3 +75,54 @@ def greedy_decoding(samples, model, tokenizer, max_len=20, clean=True, pad_token
     rows = ids.cpu().numpy().tolist()
     return idx2sents(prune_cap_ids(rows, clean=clean, pad_token=pad_token, bos_token=bos_token,
                                    eos_token=eos_token), tokenizer)
+
+
+def greedy_with_att(model, sample, tokenizer, start_token=1, end_token=2, max_pos_embeddings=128, return_raw=True,
+                    device="auto"):
+    """Single-sample greedy decoding that also returns, per generated token, the attention dict of the
+    forward that produced it — reference eval_utils/decode.py:131-167 (literal: one full
+    ``return_attention=True`` forward per token; EOS IS written before the loop stops)."""
+    if device == "auto":
+        device = "cuda" if torch.cuda.is_available() else "cpu"
+    caption, cap_mask = create_caption_and_mask(start_token, max_pos_embeddings)
+    sample = [s.to(device) for s in sample]
+    caption, cap_mask = caption.to(device), cap_mask.to(device)
+    atts = []
+    with torch.no_grad():
+        model.eval()
+        for i in range(max_pos_embeddings - 1):
+            predictions, att = model(*sample, caption, cap_mask, return_attention=True)
+            predicted_id = torch.argmax(predictions[:, i, :], axis=-1)
+            caption[:, i + 1] = predicted_id[0]
+            cap_mask[:, i + 1] = False
+            atts.append(att)
+            if predicted_id[0] == end_token:
+                break
+    token_ids = caption[0][~cap_mask[0]][1:]            # exclude BOS
+    if return_raw:
+        return token_ids, atts
+    return tokenizer.decode(token_ids, skip_special_tokens=True), atts
+
+
+def greedy_single(model, image, tokenizer, start_token, end_token, max_pos_embeddings):
+    """Greedy decoding of one image with the target-only ``Caption`` model — reference
+    eval_utils/decode.py:30-50: stops WITHOUT writing EOS and decodes the whole id buffer.  A retr_b200 model runs the
+    device-resident KV-cached loop (for a batch of one the early-return rule of ``greedy`` is this very rule);
+    a foreign callable gets the literal loop."""
+    if isinstance(model, _CaptionBase):
+        device = next(model.parameters()).device
+        with torch.no_grad():
+            model.eval()
+            ids, _ = model.greedy_native([image.to(device) if hasattr(image, "to") else image], max_pos_embeddings,
+                                         start_token, end_token)
+        return tokenizer.decode(ids[0].cpu(), skip_special_tokens=True)
+    caption, cap_mask = create_caption_and_mask(start_token, max_pos_embeddings)
+    with torch.no_grad():
+        model.eval()
+        for i in range(max_pos_embeddings - 1):
+            predicted_id = torch.argmax(model(image, caption, cap_mask)[:, i, :], axis=-1)
+            if predicted_id[0] == end_token:
+                break
+            caption[:, i + 1] = predicted_id[0]
+            cap_mask[:, i + 1] = False
+    return tokenizer.decode(caption[0], skip_special_tokens=True)

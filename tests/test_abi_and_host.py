@@ -113,3 +113,84 @@ def test_build_model_flag_matrix():
         assert isinstance(crit, torch.nn.CrossEntropyLoss)
         frozen = [n for n, p in m.named_parameters() if not p.requires_grad]
         assert all("backbone.body.conv1" in n or "backbone.body.layer1" in n for n in frozen) and frozen
+
+
+class _StubTok:
+    pad_token, cls_token, sep_token = "[PAD]", "[CLS]", "[SEP]"
+    _ids = {"[PAD]": 0, "[CLS]": 101, "[SEP]": 102}
+
+    def convert_tokens_to_ids(self, t):
+        return self._ids[t]
+
+    def decode(self, ids, skip_special_tokens=True):
+        ids = [int(i) for i in ids]
+        return " ".join(f"w{i}" for i in ids if not (skip_special_tokens and i in (0, 101, 102)))
+
+    def batch_decode(self, rows, skip_special_tokens=True):
+        return [self.decode(r, skip_special_tokens) for r in rows]
+
+    def encode(self, s):
+        return [101] + [int(w[1:]) for w in s.split()] + [102]
+
+
+def _scripted(script, V=200, with_att=False):
+    """Foreign callable emitting script[b][step] at the position being predicted."""
+    def stub(*args, return_attention=False):
+        caption, cap_mask = args[-2], args[-1]
+        B, T = caption.shape
+        out = torch.zeros(B, T, V)
+        filled = int((~cap_mask[0]).sum())
+        for b in range(B):
+            out[b, filled - 1, script[b][min(filled - 1, len(script[b]) - 1)]] = 1.0
+        if return_attention:
+            return out, {"step": filled - 1}
+        return out
+    stub.eval = lambda: stub
+    return stub
+
+
+def test_greedy_with_att_and_greedy_single_stop_rules():
+    """greedy_with_att WRITES the EOS and returns ids without BOS (decode.py:153-163); greedy_single stops before
+    writing it and decodes the whole buffer (decode.py:40-50)."""
+    from retr_b200.eval_utils import decode
+    from retr_b200.models.utils import NestedTensor
+    tok = _StubTok()
+    s = (NestedTensor(torch.zeros(1, 3, 4, 4), torch.zeros(1, 4, 4, dtype=torch.bool)),)
+    ids, atts = decode.greedy_with_att(_scripted({0: [7, 9, 102, 5]}), s, tok, 101, 102, 8, device="cpu")
+    assert ids.tolist() == [7, 9, 102] and [a["step"] for a in atts] == [0, 1, 2]
+    text, atts = decode.greedy_with_att(_scripted({0: [7, 9, 102, 5]}), s, tok, 101, 102, 8, return_raw=False,
+                                        device="cpu")
+    assert text == "w7 w9" and len(atts) == 3
+    # never emits EOS -> runs to the end of the buffer
+    ids, atts = decode.greedy_with_att(_scripted({0: [4]}), s, tok, 101, 102, 6, device="cpu")
+    assert ids.tolist() == [4] * 5 and len(atts) == 5
+    assert decode.greedy_single(_scripted({0: [7, 9, 102, 5]}), s[0], tok, 101, 102, 8) == "w7 w9"
+
+
+def test_eval_model_shell_collects_hypotheses_and_references():
+    from types import SimpleNamespace
+
+    from retr_b200 import engine
+    tok = _StubTok()
+    t, tm = torch.zeros(2, 3, 4, 4), torch.zeros(2, 4, 4, dtype=torch.bool)
+    batches = [(torch.tensor([11, 12]), t, tm, None, None), (torch.tensor([13, 11]), t, tm, None, None)]
+
+    class Loader(list):
+        dataset = SimpleNamespace(annot=[(11, 0, "w5 w6"), (11, 0, "w5"), (12, 0, "w8"), (12, 0, "w8 w8"),
+                                         (13, 0, "w1"), (13, 0, "w2")],
+                                  return_global_context=False, return_location_features=False)
+    seen = {}
+
+    def metrics(ref_list, hyp_list):
+        seen.update(ref=ref_list, hyp=hyp_list)
+        return {"n": len(hyp_list)}
+
+    model = _scripted({0: [7, 9, 102], 1: [8, 102, 4]})
+    out, ids_hyps = engine.eval_model(model, Loader(batches), tok, SimpleNamespace(max_position_embeddings=8),
+                                      compute_metrics=metrics)
+    assert out == {"n": 4}
+    assert ids_hyps == [{"ann_id": 11, "expression": "w7 w9"}, {"ann_id": 12, "expression": "w8"},
+                        {"ann_id": 13, "expression": "w7 w9"}, {"ann_id": 11, "expression": "w8"}]
+    assert seen["hyp"] == ["w7 w9", "w8", "w7 w9", "w8"]
+    assert seen["ref"] == [["w5 w6", "w8", "w1", "w5 w6"], ["w5", "w8 w8", "w2", "w5"]]   # transposed (engine.py:180)
+    assert engine.eval_model(model, Loader(batches), tok, SimpleNamespace(max_position_embeddings=8))[0] == {}
