@@ -83,7 +83,12 @@ def backbone(img, mask, sd: SD, cfg):
 # --------------------------------------------------------------------------------------------
 def sine_table(sd: SD, length: int):
     """PositionalEncoding buffer rows 0..length-1 — models/position_encoding.py:13-35. [length, d]"""
-    return sd["transformer.positional_encoding.pe"][:length, 0]
+    k = "transformer.positional_encoding."
+    if k + "pe" in sd:
+        return sd[k + "pe"][:length, 0]
+    # learned variant ('v3'/'learned'), models/position_encoding.py:38-63 in eval mode (dropout = identity)
+    return F.layer_norm(sd[k + "pos_embed.weight"][:length], (sd[k + "pos_embed.weight"].shape[1],),
+                        sd[k + "LayerNorm.weight"], sd[k + "LayerNorm.bias"], 1e-5)
 
 
 def sine_table_fresh(length: int, d: int):

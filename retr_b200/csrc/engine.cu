@@ -244,8 +244,21 @@ void EngineT<T>::finalize() {
   RETR_CHECK(input_proj_.out == d, "input_proj width");
   if (desc.loc_in_dim) { loc_w_ = raw("loc_proj.weight").dev; loc_b_ = raw("loc_proj.bias").dev; }
 
-  const float* pe = raw("transformer.positional_encoding.pe").dev;     // [1024,1,d]
-  RETR_CHECK(raw("transformer.positional_encoding.pe").shape[0] >= S, "sequence longer than the sine table");
+  // position table of the concatenated sequence: the sine buffer ('v2'/'sine', position_encoding.py:7-35) or, for the
+  // learned variant ('v3'/'learned', position_encoding.py:38-63), LayerNorm(pos_embed.weight[:S]) — in eval mode a
+  // constant of the weights, so it is evaluated once here (its dropout is the identity outside training).
+  const float* pe = nullptr;
+  const std::string pk = "transformer.positional_encoding.";
+  if (raw_.count(pk + "pe")) {
+    pe = raw(pk + "pe").dev;                                           // [1024,1,d]
+    RETR_CHECK(raw(pk + "pe").shape[0] >= S, "sequence longer than the sine table");
+  } else {
+    const RawWeight& pw = raw(pk + "pos_embed.weight");                // [1024,d]
+    RETR_CHECK(pw.shape[0] >= S && pw.shape[1] == d, "sequence longer than the learned position table");
+    float* t = static_cast<float*>(dalloc((size_t)S * d * 4));
+    layernorm<float>(pw.dev, raw(pk + "LayerNorm.weight").dev, raw(pk + "LayerNorm.bias").dev, t, S, d, 1e-5f, 0);
+    pe = t;
+  }
   e_word_ = raw("transformer.embeddings.word_embeddings.weight").dev;
   e_pos_ = raw("transformer.embeddings.position_embeddings.weight").dev;
   emb_g_ = raw("transformer.embeddings.LayerNorm.weight").dev;

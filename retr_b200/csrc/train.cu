@@ -354,6 +354,9 @@ void TrainerT<T>::finalize() {
     loc_w_ = P("loc_proj.weight").p; loc_b_ = P("loc_proj.bias").p;
     g_loc_w_ = P("loc_proj.weight").g; g_loc_b_ = P("loc_proj.bias").g;
   }
+  RETR_CHECK(params_.count("transformer.positional_encoding.pe") > 0,
+             "the training path implements the sine position table only (position_embedding 'v2'/'sine'); the learned "
+             "variant is served for inference");
   pe_ = P("transformer.positional_encoding.pe").p;
   RETR_CHECK(P("transformer.positional_encoding.pe").shape[0] >= S, "sequence longer than the sine table");
   const std::string em = "transformer.embeddings.";

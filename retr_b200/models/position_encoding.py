@@ -26,10 +26,27 @@ class PositionalEncoding(nn.Module):
         return self.pe[:s, 0].t().unsqueeze(0).expand(b, -1, -1)
 
 
+class PositionalEmbedding(nn.Module):
+    """Learned position table of the concatenated sequence ('v3'/'learned'; reference
+    models/position_encoding.py:38-63): ``dropout(LayerNorm(pos_embed[0:S]))``.  The module carries the parameters
+    (state_dict-compatible); the native engine evaluates the table once per weight version for inference.  Training
+    with this variant is not built (the trainer fails loudly on the missing sine buffer)."""
+
+    def __init__(self, embedding_dim, dropout=0.1, max_position_embeddings=5000):
+        super().__init__()
+        self.pos_embed = nn.Embedding(num_embeddings=max_position_embeddings, embedding_dim=embedding_dim)
+        self.LayerNorm = nn.LayerNorm(embedding_dim)
+        self.dropout = nn.Dropout(dropout)
+
+    def forward(self, x):
+        raise RuntimeError("the position table is evaluated by the native engine; this module only holds parameters")
+
+
 def build_position_encoding(config):
     if config.position_embedding in ("v2", "sine"):
         print("Using sine/cosine positional encodings")
         return PositionalEncoding(config.hidden_dim, max_len=1024)
     if config.position_embedding in ("v3", "learned"):
-        raise NotImplementedError("learned position embedding: SURVEY 8(f) item 4, not built yet")
+        print("Using learned positional encodings")
+        return PositionalEmbedding(config.hidden_dim, max_position_embeddings=1024, dropout=0.1)
     raise ValueError(f"not supported {config.position_embedding}")

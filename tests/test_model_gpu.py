@@ -21,8 +21,8 @@ KINDS = ["CaptionGlobalLoc", "Caption", "CaptionLoc"]
 BF16_LOGIT_TOL = 2e-2          # relative to max|logit|
 
 
-def gpu_model(kind, precision, calibrated):
-    model, _, cfg = build_product_model(kind)
+def gpu_model(kind, precision, calibrated, **cfg_over):
+    model, _, cfg = build_product_model(kind, **cfg_over)
     model = copy.deepcopy(model)
     if calibrated:
         model.load_state_dict(synthetic.calibrate_frozen_bn(model.state_dict()))
@@ -119,6 +119,64 @@ def test_greedy_early_exit_semantics():
         got = decode.greedy(samples_of(kind, enc_in, "cpu"), model, max_len=128, device="cuda", bos_token=101,
                             eos_token=eos).cpu()
     assert torch.equal(got, ref)
+
+
+def test_learned_position_variant_matches_reference_fixture_and_oracle():
+    """position_embedding='learned' (models/position_encoding.py:38-63): the engine evaluates LN(pos_embed[:S]) once;
+    fp32 logits vs the reference fixture, greedy ids vs the oracle; training with it fails loudly."""
+    kind = "CaptionGlobalLoc"
+    model, sd, cfg = gpu_model(kind, "fp32", calibrated=False, position_embedding="learned")
+    fx = golden("CaptionGlobalLoc_learned")
+    data, enc_in = synthetic_samples(kind, fx["batch"])
+    caps, cm = data["caps"].cuda(), data["cap_masks"].cuda()
+    with torch.no_grad():
+        logits = model(*samples_of(kind, enc_in), caps[:, :-1], cm[:, :-1]).cpu()
+    scale = fx["logits_absmax"]
+    got = logits[:, :12, :][:, :, fx["vocab_idx"]]
+    assert (got - fx["logits_slice"]).abs().max().item() <= 1e-4 * scale
+    sure = fx["margin"] > 2e-4 * scale
+    assert torch.equal(logits.argmax(-1)[sure], fx["argmax"][sure])
+    model, sd, cfg = gpu_model(kind, "fp32", calibrated=True, position_embedding="learned")
+    _, enc_in = synthetic_samples(kind, 2, shard=5, train=False)
+    with torch.no_grad():
+        ids = decode.greedy(samples_of(kind, enc_in, "cpu"), model, max_len=128, device="cuda", bos_token=101,
+                            eos_token=102).cpu()
+        ref, _ = O.greedy(sd, cfg, *enc_in, max_len=128, bos_token=101, eos_token=102, literal=False)
+    assert torch.equal(ids, ref)
+    model.train()
+    with pytest.raises(RuntimeError):
+        model(*samples_of(kind, enc_in), data["caps"][:, :-1].cuda(), data["cap_masks"][:, :-1].cuda())
+    model.eval()
+
+
+def test_greedy_with_att_and_single_native():
+    """greedy_with_att (decode.py:131-167) and greedy_single (decode.py:30-50) over the native model: ids equal the
+    oracle's greedy prefix for the same sample; one attention dict per generated token with the fixture's shapes."""
+    class Tok:
+        def decode(self, ids, skip_special_tokens=True):
+            return " ".join(str(int(i)) for i in ids if not (skip_special_tokens and int(i) in (0, 101, 102)))
+
+    kind = "CaptionGlobalLoc"
+    model, sd, cfg = gpu_model(kind, "fp32", calibrated=True)
+    _, enc_in = synthetic_samples(kind, 1, shard=5, train=False)
+    with torch.no_grad():
+        free, _ = O.greedy(sd, cfg, *enc_in, max_len=128, bos_token=101, eos_token=102, literal=False)
+        eos = int(free[0, 5])                                   # declare the 5th generated token to be EOS
+        first = free[0, 1:].tolist().index(eos)                 # it may already occur earlier
+        ids, atts = decode.greedy_with_att(model, samples_of(kind, enc_in, "cpu"), Tok(), 101, eos, 128, device="cuda")
+    assert ids.cpu().tolist() == free[0, 1:first + 2].tolist() and ids[-1] == eos
+    assert len(atts) == first + 1
+    assert set(atts[0]) == set(golden(kind)["att_shapes"])
+    kind = "Caption"
+    model, sd, cfg = gpu_model(kind, "fp32", calibrated=True)
+    _, enc_in = synthetic_samples(kind, 1, shard=6, train=False)
+    with torch.no_grad():
+        free, _ = O.greedy(sd, cfg, *enc_in, max_len=128, bos_token=101, eos_token=102, literal=False)
+        eos = int(free[0, 4])
+        first = free[0, 1:].tolist().index(eos)
+        text = decode.greedy_single(model, samples_of(kind, enc_in, "cpu")[0], Tok(), 101, eos, 128)
+    want = [t for t in free[0, 1:first + 1].tolist() if t not in (0, 101, 102)]
+    assert text == " ".join(str(t) for t in want)
 
 
 @pytest.mark.parametrize("kind", ["CaptionGlobalLoc", "Caption"])

@@ -87,3 +87,25 @@ def test_prune_cap_ids_semantics():
     rows = [[101, 5, 6, 102, 7, 0], [101, 9, 0, 0, 0, 0]]
     assert O.prune_cap_ids(rows, True, 0, 101, 102) == [[5, 6], [9]]
     assert O.prune_cap_ids(rows, False, 0, 101, 102) == [[101, 5, 6, 102], [101, 9, 0, 0, 0, 0]]
+
+
+def test_learned_position_variant_init_and_oracle_forward():
+    """position_embedding='learned' (models/position_encoding.py:38-63): init replay and the
+    oracle's eval-mode forward against the fixture recorded from the unmodified reference."""
+    model, _, cfg = build_product_model("CaptionGlobalLoc", position_embedding="learned")
+    sd = model.state_dict()
+    fx = golden("CaptionGlobalLoc_learned")
+    fp = fx["fingerprint"]
+    assert sorted(sd.keys()) == fp["keys"]
+    assert "transformer.positional_encoding.pos_embed.weight" in sd
+    for k, s in fp["sums"].items():
+        assert float(sd[k].double().sum()) == s, k
+    assert float(sum(sd[k].double().abs().sum() for k in sorted(sd.keys()))) == fp["abs_sum_total"]
+    data, enc_in = synthetic_samples("CaptionGlobalLoc", fx["batch"])
+    with torch.no_grad():
+        logits = O.forward(sd, cfg, *enc_in, data["caps"][:, :-1], data["cap_masks"][:, :-1])
+    scale = fx["logits_absmax"]
+    got = logits[:, :12, :][:, :, fx["vocab_idx"]]
+    assert (got - fx["logits_slice"]).abs().max() <= 2e-5 * scale
+    sure = fx["margin"] > 1e-4 * scale
+    assert torch.equal(logits.argmax(-1)[sure], fx["argmax"][sure])
