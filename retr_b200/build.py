@@ -18,7 +18,7 @@ OBJ = os.path.join(CSRC, "build")
 LIB = os.path.join(HERE, "libretr_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-         "-Xcompiler", "-fPIC", "-cudart", "shared"]
+         "-Xcompiler", "-fPIC", "-cudart", "shared"] + os.environ.get("RETR_EXTRA_NVCC_FLAGS", "").split()
 
 
 def _digest(paths):

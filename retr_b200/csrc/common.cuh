@@ -53,14 +53,50 @@ template <typename... KArgs, typename... Args>
 inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cfg.numAttrs = na;
   CUDA_OK(cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...));
   ++g_launches;
 }
+
+// ---- in-graph timeline (diagnostic builds only: -DRETR_TRACE) --------------------------------------
+// The first and the last CTA of a traced kernel record {id, grid, globaltimer at entry/exit, SM, tag}.  ncu serialises
+// launches, so this is the only view of how the branches of the decode graph overlap.  Compiled out of the product.
+#ifdef RETR_TRACE
+#define RETR_TRACE_DECL static __device__ unsigned long long* trace_buf_ = nullptr;
+__device__ __forceinline__ unsigned long long trace_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define TRACE_BEGIN()                                                                                                 \
+  const unsigned trace_lin_ = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);                        \
+  const unsigned trace_n_ = gridDim.x * gridDim.y * gridDim.z;                                                       \
+  const bool trace_on_ = trace_buf_ && threadIdx.x == 0 && (trace_lin_ == 0 || trace_lin_ == trace_n_ - 1);          \
+  const unsigned long long trace_t0_ = trace_on_ ? trace_now() : 0ull;
+#define TRACE_END(id, tag)                                                                                            \
+  if (trace_on_) {                                                                                                    \
+    const unsigned long long slot_ = atomicAdd(trace_buf_, 1ull);                                                     \
+    if (slot_ < (1ull << 18)) {                                                                                       \
+      unsigned long long* r_ = trace_buf_ + 8 + 8 * slot_;                                                            \
+      unsigned smid_;                                                                                                 \
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid_));                                                              \
+      r_[0] = (unsigned long long)(id); r_[1] = trace_n_; r_[2] = trace_lin_; r_[3] = trace_t0_;                      \
+      r_[4] = trace_now(); r_[5] = smid_; r_[6] = (unsigned long long)(tag);                                          \
+    }                                                                                                                 \
+  }
+#else
+#define RETR_TRACE_DECL
+#define TRACE_BEGIN()
+#define TRACE_END(id, tag)
+#endif
 
 // ---- device helpers ---------------------------------------------------------------------
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }

@@ -7,6 +7,7 @@
 
 namespace retr {
 namespace {
+RETR_TRACE_DECL
 
 constexpr int DA_WARPS = 4;
 constexpr int DA_MAX_KEYS = 1024;       // the sine table bounds the encoder length at 1024
@@ -67,8 +68,9 @@ __device__ __forceinline__ void merge_state(float& m, float& l, float (&acc)[N],
 // (cp.async.bulk, completion on an mbarrier) — the whole block is in flight at once, 4 CTAs per SM —
 // and the 4 warps then score keys from shared memory: LPK lanes cooperate on one key (16-byte slice
 // each, conflict-free), online softmax per lane group, merged by shuffles and one smem pass.
-// (A persistent double-buffered variant measured slower on B200: 38 us vs 35 us per cross-attention
-// launch at B=256; see profiles/.)
+// (Persistent variants measured slower inside the decode graph on B200 at B=256 — a CTA-wide ring with one producer
+// warp: 68-74 ms decode vs 62.5; one warp per unit with private rings: 64.5-83 — each needs ~100 KB per SM in flight
+// AND several units' dependent load->compute chains overlapped, which is exactly what 4 resident one-unit CTAs give.)
 template <typename T, int DH>
 __global__ void __launch_bounds__(DA_WARPS * 32)
 decode_attention_kernel(const T* __restrict__ q, int64_t ldq, const T* __restrict__ new_kv, int64_t ld_new,
@@ -89,6 +91,7 @@ decode_attention_kernel(const T* __restrict__ q, int64_t ldq, const T* __restric
   const int e0 = h * DH + sub * VN;                         // this lane's slice of the model dim
   T* kg = kcache + (size_t)bh * cache_rows * DH;
   T* vg = vcache + (size_t)bh * cache_rows * DH;
+  TRACE_BEGIN();
   pdl_launch_dependents();
   pdl_wait();
   const int n_cached = new_kv ? *step_dyn : n_keys;
@@ -99,9 +102,17 @@ decode_attention_kernel(const T* __restrict__ q, int64_t ldq, const T* __restric
     if (n_cached > 0) {
       const uint32_t bytes = (uint32_t)n_cached * DH * sizeof(T);
       ptx::mbar_arrive_expect_tx(&bar[0], bytes);
-      ptx::bulk_load(Ks, kg, bytes, &bar[0]);
       ptx::mbar_arrive_expect_tx(&bar[1], bytes);
-      ptx::bulk_load(Vs, vg, bytes, &bar[1]);
+      if (new_kv) {
+        ptx::bulk_load(Ks, kg, bytes, &bar[0]);
+        ptx::bulk_load(Vs, vg, bytes, &bar[1]);
+      } else {
+        // cross-attention K/V: 0.6 GB per step over all layers, each byte read once per step — stream it past the
+        // L2 so the ~35 MB of decoder weights and activations every step re-reads stay resident
+        const uint64_t pol = ptx::policy_evict_first();
+        ptx::bulk_load_hint(Ks, kg, bytes, &bar[0], pol);
+        ptx::bulk_load_hint(Vs, vg, bytes, &bar[1], pol);
+      }
     }
   }
   // small operands: one global round trip, overlapped with the bulk copies.  The padding bytes go
@@ -203,6 +214,7 @@ decode_attention_kernel(const T* __restrict__ q, int64_t ldq, const T* __restric
     for (int w = 0; w < DA_WARPS; ++w) { ll += sm_l[w]; aa += sm_acc[w][c]; }
     out[(int64_t)b * ldo + h * DH + c] = from_f<T>(aa / ll);
   }
+  TRACE_END(new_kv ? 2 : 3, out);
 }
 
 // [B*rows, 2d] rows of [K(d) | V(d)]  ->  head-major K[B][H][rows][DH], V[B][H][rows][DH]; 16-byte chunks
@@ -236,6 +248,7 @@ __global__ void greedy_init_kernel(int64_t* caption, int max_len, int B, int bos
 __global__ void greedy_update_kernel(unsigned long long* keys, int64_t* caption, int max_len, int B, int eos,
                                      int* step, int* done, uint8_t* finished) {
   __shared__ int unfinished;
+  TRACE_BEGIN();
   pdl_wait();
   if (*done) return;
   const int i = *step;
@@ -258,9 +271,14 @@ __global__ void greedy_update_kernel(unsigned long long* keys, int64_t* caption,
     *step = i + 1;                      // == number of model evaluations so far
     if (all_done || i + 1 >= max_len - 1) *done = 1;
   }
+  TRACE_END(6, 0);
 }
 
 }  // namespace
+
+#ifdef RETR_TRACE
+void decode_ops_set_trace(unsigned long long* buf) { CUDA_OK(cudaMemcpyToSymbol(trace_buf_, &buf, sizeof(buf))); }
+#endif
 
 template <typename T>
 void decode_attention(const T* q, int64_t ldq, const T* new_kv, int64_t ld_new, T* kcache, T* vcache, int cache_rows,

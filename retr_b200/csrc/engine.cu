@@ -13,12 +13,18 @@
 // (q=k=LN(x)+pos, q=LN(y)+query_pos, k=memory+pos) is folded into a per-position bias table,
 // W(x+p)+b = Wx + (Wp+b), computed once in fp32 at weight-load time (rowbias epilogue).
 #include "engine.h"
+#include "ffn_fused.h"
 #include "small_gemm.h"
 
 #include <tuple>
 #include <type_traits>
 
 namespace retr {
+#ifdef RETR_TRACE
+void small_gemm_set_trace(unsigned long long* buf);
+void decode_ops_set_trace(unsigned long long* buf);
+void ffn_fused_set_trace(unsigned long long* buf);
+#endif
 namespace {
 
 template <typename T> void gemm(const GemmParams& p, cudaStream_t s);
@@ -145,6 +151,8 @@ class EngineT final : public EngineBase {
   std::vector<cudaStream_t> gstreams_;
   std::vector<cudaEvent_t> gjoin_;
   cudaEvent_t gfork_ = nullptr;
+  int cur_G_ = 1;                                    // row groups of the step being captured
+  bool ffn_fused_ = false;                           // FFN sublayer of the decode step as one cluster kernel (ffn_fused.cu)
   size_t splitk_group_stride_ = 0;                   // floats of split-K scratch per group
 };
 
@@ -349,7 +357,10 @@ void EngineT<T>::alloc_buffers() {
   CUDA_OK(cudaMemset(argmax_keys_, 0, Md * 8));
   CUDA_OK(cudaMallocHost(&done_host_, 16));
   if (const char* e = getenv("RETR_DECODE_GROUPS")) groups_ = std::min(16, std::max(1, atoi(e)));
-  splitk_group_stride_ = (size_t)4 * B * std::max<int64_t>(d, 512);
+  ffn_fused_ = std::is_same<T, bf16>::value && ffn_fused_supported((int)d, (int)desc.d_ff) &&
+               !(getenv("RETR_FFN_FUSED") && atoi(getenv("RETR_FFN_FUSED")) == 0);
+  if (ffn_fused_) ffn_fused_configure();
+  splitk_group_stride_ = (size_t)8 * B * std::max<int64_t>(d, 512);
   splitk_scratch_ = static_cast<float*>(dalloc((size_t)groups_ * splitk_group_stride_ * 4));
   splitk_tickets_ = static_cast<unsigned*>(dalloc((size_t)groups_ * 1024 * 4));
   CUDA_OK(cudaMemset(splitk_tickets_, 0, (size_t)groups_ * 1024 * 4));
@@ -623,7 +634,8 @@ void EngineT<T>::decode_rows_fused(int r0, int n, int group, int max_len, cudaSt
   const int d = desc.d_model, Tn = desc.max_pos, H = desc.n_heads;
   const int64_t ff = desc.d_ff;
   const int kpan = desc.d_ff / 256;
-  const int split = kpan % 4 == 0 ? 4 : (kpan % 2 == 0 ? 2 : 1);
+  int split = kpan % 4 == 0 ? 4 : (kpan % 2 == 0 ? 2 : 1);
+  if (const char* e = getenv("RETR_FF2_SPLIT")) { const int v = atoi(e); if (v >= 1 && v <= 8 && kpan % v == 0) split = v; }
   cur_group_ = group;
   float* y = y_ + (int64_t)r0 * d;
   T* qkv = qkv_ + (int64_t)r0 * 3 * d;
@@ -646,8 +658,17 @@ void EngineT<T>::decode_rows_fused(int r0, int n, int group, int max_len, cudaSt
     dgemm(e.c_q, nullptr, y, e.ln2_g, e.ln2_b, qc, false, n, e.rb_c_q, 0, nullptr, 1, s);
     decode_attention<T>(qc, d, nullptr, 0, ck, cv, S, att, d, n, H, d, S, nullptr, tok_mask_ + (int64_t)r0 * S, S, s);
     dgemm(e.c_out, att, nullptr, nullptr, nullptr, y, true, n, nullptr, 0, y, 1, s);
-    dgemm(e.ff1, nullptr, y, e.ln3_g, e.ln3_b, h, false, n, nullptr, 1, nullptr, 1, s);
-    dgemm(e.ff2, h, nullptr, nullptr, nullptr, y, true, n, nullptr, 0, y, split, s);
+    if (ffn_fused_) {
+      if constexpr (std::is_same<T, bf16>::value) {
+        FfnFusedParams fp;
+        fp.Y = y; fp.gamma = e.ln3_g; fp.beta = e.ln3_b; fp.W1 = e.ff1.w; fp.b1 = e.ff1.b; fp.W2 = e.ff2.w; fp.b2 = e.ff2.b;
+        fp.M = n; fp.d_ff = (int)ff;
+        ffn_fused(fp, s);
+      }
+    } else {
+      dgemm(e.ff1, nullptr, y, e.ln3_g, e.ln3_b, h, false, n, nullptr, 1, nullptr, 1, s);
+      dgemm(e.ff2, h, nullptr, nullptr, nullptr, y, true, n, nullptr, 0, y, split, s);
+    }
   }
   dgemm(mlp_[0], nullptr, y, dec_norm_g_, dec_norm_b_, m1, false, n, nullptr, 1, nullptr, 1, s);
   dgemm(mlp_[1], m1, nullptr, nullptr, nullptr, m2, false, n, nullptr, 1, nullptr, 1, s);
@@ -660,6 +681,7 @@ void EngineT<T>::decode_step_fused(int B, int eos, int max_len, cudaStream_t s) 
   int rows = (int)cdiv(B, groups_);
   rows = (int)cdiv(std::max(rows, group_rows_min_), 32) * 32;
   const int G = (int)cdiv(B, rows);
+  cur_G_ = G;
   if (G > 1) {
     CUDA_OK(cudaEventRecord(gfork_, s));
     for (int g = 1; g < G; ++g) {
@@ -680,6 +702,17 @@ void EngineT<T>::decode_greedy(int bos, int eos, int max_len, int64_t* out_ids, 
   RETR_CHECK(max_len >= 2 && max_len <= desc.max_pos, "max_len must be in [2, max_position_embeddings]");
   const int B = cur_B_;
   const long long l0 = g_launches;
+#ifdef RETR_TRACE
+  static unsigned long long* trace_dev = nullptr;
+  const size_t trace_bytes = (size_t)8 * ((1u << 18) + 1) * 8;
+  if (!trace_dev) {
+    CUDA_OK(cudaMalloc(&trace_dev, trace_bytes));
+    small_gemm_set_trace(trace_dev);
+    decode_ops_set_trace(trace_dev);
+    ffn_fused_set_trace(trace_dev);
+  }
+  CUDA_OK(cudaMemsetAsync(trace_dev, 0, 64, s));
+#endif
   greedy_init(caption_, max_len, B, bos, step_, done_, finished_, argmax_keys_, s);
   const bool use_graph = getenv("RETR_NO_GRAPH") == nullptr;
   cudaGraphExec_t exec = nullptr;
@@ -738,6 +771,13 @@ void EngineT<T>::decode_greedy(int bos, int eos, int max_len, int64_t* out_ids, 
   CUDA_OK(cudaEventRecord(polled, s));
   CUDA_OK(cudaEventSynchronize(polled));
   if (steps_host) *steps_host = done_host_[1];
+#ifdef RETR_TRACE
+  if (const char* f = getenv("RETR_TRACE_FILE")) {
+    std::vector<unsigned long long> host(trace_bytes / 8);
+    CUDA_OK(cudaMemcpy(host.data(), trace_dev, trace_bytes, cudaMemcpyDeviceToHost));
+    if (FILE* fp = fopen(f, "wb")) { fwrite(host.data(), 8, 8 + 8 * std::min<size_t>(host[0], 1u << 18), fp); fclose(fp); }
+  }
+#endif
   float ms = 0.f;
   if (cudaEventElapsedTime(&ms, ev_[0], ev_[1]) == cudaSuccess) phase_ms[0] = ms;
   if (cudaEventElapsedTime(&ms, ev_[1], ev_[2]) == cudaSuccess) phase_ms[1] = ms;

@@ -1,0 +1,318 @@
+// Feed-forward sublayer of one decode step as ONE kernel (pre-norm, models/transformer_modules.py:84-97):
+//     y <- y + W2 · relu(W1 · LN(y) + b1) + b2          d_model = 256, d_ff = 256 * CL (CL <= 8)
+// In the decode graph this sublayer used to be two dependent launches (LN+FF1, then split-K FF2 with a ticketed
+// reduction through global memory): ~22 us of dependent latency per layer for 0.5 GFLOP.  Here a thread-block
+// cluster of CL CTAs owns a 32-row block: CTA r takes the r-th 256-wide slice of the hidden dimension, computes
+// h_r = relu(LN(y) W1[r]^T + b1[r]) (bf16, stays in shared memory) and its partial y_r = h_r W2[:, r]^T, whose 32-column
+// slices it PUSHES into the shared memory of the CTA that owns those columns (st.shared::cluster, fire and forget).
+// After one cluster barrier every CTA sums its eight slots in a fixed order (deterministic), adds b2 and the residual
+// and writes y in place.  No HBM round trip for h, no atomics, no second launch, no remote-load latency.
+// Both GEMMs are the same shape — A[32 x 256] (LN(y) or h_r) times a 64-row weight panel — so one cp.async ring of
+// 64 x 256 panels feeds all eight of them; the first panels are in flight before griddepcontrol.wait (weights do not
+// depend on the previous kernel).
+#include "ffn_fused.h"
+
+#include <cuda_runtime.h>
+
+namespace retr {
+namespace {
+RETR_TRACE_DECL
+
+constexpr int FF_BM = 32, FF_D = 256, FF_PANEL = 64, FF_LDS = FF_D + 8, FF_THREADS = 256, FF_NST = 4;
+constexpr int FF_PANELS = 2 * FF_D / FF_PANEL;                 // 4 of W1[r], 4 of W2[:, r]
+
+__device__ __forceinline__ void ff_ldsm_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+}
+__device__ __forceinline__ void ff_mma(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void ff_cp16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ uint32_t ff_cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void ff_cluster_arrive() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void ff_cluster_wait() {
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void ff_st_peer(uint32_t local_addr, uint32_t rank, float2 v) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(rank));
+  asm volatile("st.shared::cluster.v2.f32 [%0], {%1,%2};" ::"r"(remote), "f"(v.x), "f"(v.y) : "memory");
+}
+
+struct FfSmem {
+  bf16 As[FF_BM][FF_LDS];                    // LN(y) rows
+  bf16 Hs[FF_BM][FF_LDS];                    // relu(W1[r] LN(y) + b1[r])
+  bf16 Wr[FF_NST][FF_PANEL][FF_LDS];         // weight panel ring
+  float Ps[8][FF_BM][FF_D / 8];              // partials of THIS CTA's 32 output columns, one slot per source CTA
+  float red[4][FF_BM][16];                   // K-half exchange between the two warp groups
+};
+
+__global__ void __launch_bounds__(FF_THREADS) ffn_fused_kernel(const FfnFusedParams p) {
+  extern __shared__ __align__(128) uint8_t ff_raw[];
+  FfSmem& sm = *reinterpret_cast<FfSmem*>(ff_raw);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int rank = (int)ff_cluster_rank(), CL = (int)gridDim.x;
+  const int m0 = blockIdx.y * FF_BM;
+  const int d_ff = CL * FF_D;
+
+  auto load_panel = [&](int pi, int buf) {
+    // pi < 4: rows [rank*256 + pi*64, +64) of W1 [d_ff, 256];  pi >= 4: rows [(pi-4)*64, +64) of W2 [256, d_ff],
+    // columns [rank*256, +256)
+    const bf16* base = pi < 4 ? p.W1 + ((int64_t)rank * FF_D + pi * FF_PANEL) * FF_D
+                              : p.W2 + (int64_t)(pi - 4) * FF_PANEL * d_ff + (int64_t)rank * FF_D;
+    const int64_t ld = pi < 4 ? FF_D : d_ff;
+#pragma unroll
+    for (int k = 0; k < FF_PANEL * (FF_D / 8) / FF_THREADS; ++k) {
+      const int idx = tid + k * FF_THREADS, r = idx / (FF_D / 8), ch = idx % (FF_D / 8);
+      ff_cp16((uint32_t)__cvta_generic_to_shared(&sm.Wr[buf][r][ch * 8]), base + r * ld + ch * 8);
+    }
+  };
+
+  TRACE_BEGIN();
+  pdl_launch_dependents();
+  ff_cluster_arrive();                                              // phase 1: "my shared memory exists" (waited on before
+                                                                    // the first remote store, five panels from now)
+#pragma unroll
+  for (int s = 0; s < FF_NST; ++s) {
+    load_panel(s, s);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  // epilogue operands that do not depend on the previous kernel: this thread's bias values of the four W1 panels
+  const int g = lane >> 2, c4 = lane & 3;
+  // warp tile: all 32 rows x 16 columns (cg) of the panel output over one half of K (kh); the A fragments of that
+  // K half stay in registers for the four panels of a GEMM, so a panel costs one pass over its own 32 KB and nothing
+  // else — with 16 x 16 tiles re-reading A the loop was bound by shared-memory bandwidth (1.1 us per panel).
+  const int kh = warp >> 2, cg = warp & 3, wc = cg * 16;
+  float b1r[4][2][2];
+#pragma unroll
+  for (int pi = 0; pi < 4; ++pi)
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+      const int col = rank * FF_D + pi * FF_PANEL + wc + nt * 8 + c4 * 2;
+      b1r[pi][nt][0] = __ldg(p.b1 + col);
+      b1r[pi][nt][1] = __ldg(p.b1 + col + 1);
+    }
+  float4 gam[2], bet[2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    gam[j] = __ldg(reinterpret_cast<const float4*>(p.gamma + j * 128 + lane * 4));
+    bet[j] = __ldg(reinterpret_cast<const float4*>(p.beta + j * 128 + lane * 4));
+  }
+  pdl_wait();                                                       // y is the previous kernel's output
+#ifdef RETR_TRACE
+  unsigned long long tp[12];
+  int tpn = 0;
+  if (trace_on_) tp[tpn++] = trace_now();
+#endif
+
+  // LayerNorm prologue: warp w normalises rows 4w .. 4w+3 into As (bf16)
+  {
+    float v[4][8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int m = m0 + warp * 4 + i;
+      const float* xr = p.Y + (int64_t)(m < p.M ? m : 0) * FF_D;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const float4 t = *reinterpret_cast<const float4*>(xr + j * 128 + lane * 4);
+        v[i][4 * j] = t.x; v[i][4 * j + 1] = t.y; v[i][4 * j + 2] = t.z; v[i][4 * j + 3] = t.w;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float s = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s += v[i][j];
+      const float mean = warp_sum(s) * (1.f / FF_D);
+      float q = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { const float t = v[i][j] - mean; q = fmaf(t, t, q); }
+      const float rstd = rsqrtf(warp_sum(q) * (1.f / FF_D) + p.eps);
+      bf16* dst = &sm.As[warp * 4 + i][0];
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const float4 ga = gam[j], be = bet[j];
+        __nv_bfloat162 lo = __floats2bfloat162_rn((v[i][4 * j] - mean) * rstd * ga.x + be.x,
+                                                  (v[i][4 * j + 1] - mean) * rstd * ga.y + be.y);
+        __nv_bfloat162 hi = __floats2bfloat162_rn((v[i][4 * j + 2] - mean) * rstd * ga.z + be.z,
+                                                  (v[i][4 * j + 3] - mean) * rstd * ga.w + be.w);
+        uint2 pk;
+        pk.x = *reinterpret_cast<uint32_t*>(&lo);
+        pk.y = *reinterpret_cast<uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(dst + j * 128 + lane * 4) = pk;
+      }
+    }
+  }
+
+  uint32_t af[2][8][4];
+#pragma unroll 1
+  for (int pi = 0; pi < FF_PANELS; ++pi) {
+    const int buf = pi % FF_NST;
+    asm volatile("cp.async.wait_group %0;" ::"n"(FF_NST - 1) : "memory");
+    __syncthreads();                                                // panel pi landed; As / Hs complete
+    if (pi == 4) ff_cluster_wait();                                 // every CTA of the cluster is running (remote stores ahead)
+    if (pi == 0 || pi == 4) {                                       // (re)load this warp's A fragments
+      const bf16(*A)[FF_LDS] = pi < 4 ? sm.As : sm.Hs;
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          ff_ldsm_x4((uint32_t)__cvta_generic_to_shared(&A[mt * 16 + (lane & 15)][kh * 128 + ks * 16 + (lane >> 4) * 8]),
+                     af[mt][ks][0], af[mt][ks][1], af[mt][ks][2], af[mt][ks][3]);
+    }
+    float acc[2][2][4];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 2; ++nt) acc[mt][nt][0] = acc[mt][nt][1] = acc[mt][nt][2] = acc[mt][nt][3] = 0.f;
+    const uint32_t b_base = (uint32_t)__cvta_generic_to_shared(
+        &sm.Wr[buf][wc + (lane >> 4) * 8 + (lane & 7)][kh * 128 + ((lane >> 3) & 1) * 8]);
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks) {
+      uint32_t b0, b1, b2, b3;
+      ff_ldsm_x4(b_base + ks * 32, b0, b1, b2, b3);
+      ff_mma(acc[0][0], af[0][ks], b0, b1);
+      ff_mma(acc[0][1], af[0][ks], b2, b3);
+      ff_mma(acc[1][0], af[1][ks], b0, b1);
+      ff_mma(acc[1][1], af[1][ks], b2, b3);
+    }
+    if (kh == 1) {
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+          *reinterpret_cast<float2*>(&sm.red[cg][mt * 16 + g][nt * 8 + c4 * 2]) = make_float2(acc[mt][nt][0], acc[mt][nt][1]);
+          *reinterpret_cast<float2*>(&sm.red[cg][mt * 16 + g + 8][nt * 8 + c4 * 2]) = make_float2(acc[mt][nt][2], acc[mt][nt][3]);
+        }
+    }
+    __syncthreads();                                                // K halves exchanged; ring slot `buf` is free
+    if (pi + FF_NST < FF_PANELS) load_panel(pi + FF_NST, buf);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    if (kh == 0) {
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+          const float2 lo = *reinterpret_cast<const float2*>(&sm.red[cg][mt * 16 + g][nt * 8 + c4 * 2]);
+          const float2 hi = *reinterpret_cast<const float2*>(&sm.red[cg][mt * 16 + g + 8][nt * 8 + c4 * 2]);
+          acc[mt][nt][0] += lo.x; acc[mt][nt][1] += lo.y; acc[mt][nt][2] += hi.x; acc[mt][nt][3] += hi.y;
+        }
+      if (pi < 4) {
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+          const int col = pi * FF_PANEL + wc + nt * 8 + c4 * 2;
+          const float bb0 = pi == 0 ? b1r[0][nt][0] : pi == 1 ? b1r[1][nt][0] : pi == 2 ? b1r[2][nt][0] : b1r[3][nt][0];
+          const float bb1 = pi == 0 ? b1r[0][nt][1] : pi == 1 ? b1r[1][nt][1] : pi == 2 ? b1r[2][nt][1] : b1r[3][nt][1];
+#pragma unroll
+          for (int mt = 0; mt < 2; ++mt) {
+            *reinterpret_cast<__nv_bfloat162*>(&sm.Hs[mt * 16 + g][col]) =
+                __floats2bfloat162_rn(fmaxf(acc[mt][nt][0] + bb0, 0.f), fmaxf(acc[mt][nt][1] + bb1, 0.f));
+            *reinterpret_cast<__nv_bfloat162*>(&sm.Hs[mt * 16 + g + 8][col]) =
+                __floats2bfloat162_rn(fmaxf(acc[mt][nt][2] + bb0, 0.f), fmaxf(acc[mt][nt][3] + bb1, 0.f));
+          }
+        }
+      } else {
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+          const int col = (pi - 4) * FF_PANEL + wc + nt * 8 + c4 * 2;  // output column; owner CTA = col / 32
+          const uint32_t owner = (uint32_t)(col >> 5);
+          const int lc = col & 31;
+#pragma unroll
+          for (int mt = 0; mt < 2; ++mt) {
+            ff_st_peer((uint32_t)__cvta_generic_to_shared(&sm.Ps[rank][mt * 16 + g][lc]), owner, make_float2(acc[mt][nt][0], acc[mt][nt][1]));
+            ff_st_peer((uint32_t)__cvta_generic_to_shared(&sm.Ps[rank][mt * 16 + g + 8][lc]), owner, make_float2(acc[mt][nt][2], acc[mt][nt][3]));
+          }
+        }
+      }
+    }
+#ifdef RETR_TRACE
+    if (trace_on_) tp[tpn++] = trace_now();
+#endif
+  }
+
+  // ---- reduction: this CTA owns columns [rank*32, +32) of the 32-row block; its eight partial slots were filled by
+  // remote stores, visible after the cluster barrier.  One float4 per thread, slots summed in a fixed order.
+  const int row = tid >> 3, lc = (tid & 7) * 4, col = rank * 32 + lc;
+  const float4 bias2 = __ldg(reinterpret_cast<const float4*>(p.b2 + col));
+  float4 resid = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (m0 + row < p.M) resid = *reinterpret_cast<const float4*>(p.Y + (int64_t)(m0 + row) * FF_D + col);
+  ff_cluster_arrive();
+  ff_cluster_wait();
+  {
+    float4 s = make_float4(bias2.x + resid.x, bias2.y + resid.y, bias2.z + resid.z, bias2.w + resid.w);
+    float4 t[8];
+#pragma unroll
+    for (int src = 0; src < 8; ++src) t[src] = *reinterpret_cast<const float4*>(&sm.Ps[src][row][lc]);
+    float4 part = t[0];
+#pragma unroll
+    for (int src = 1; src < 8; ++src) { part.x += t[src].x; part.y += t[src].y; part.z += t[src].z; part.w += t[src].w; }
+    s.x += part.x; s.y += part.y; s.z += part.z; s.w += part.w;
+    if (m0 + row < p.M) *reinterpret_cast<float4*>(p.Y + (int64_t)(m0 + row) * FF_D + col) = s;
+  }
+#ifdef RETR_TRACE
+  if (trace_on_) {
+    tp[tpn++] = trace_now();
+    const unsigned long long slot_ = atomicAdd(trace_buf_, 2ull);
+    if (slot_ + 1 < (1ull << 18)) {
+      unsigned long long* r_ = trace_buf_ + 8 + 8 * slot_;
+      r_[0] = 9; r_[1] = trace_n_; r_[2] = trace_lin_; r_[3] = trace_t0_;
+      r_[4] = tp[0]; r_[5] = tp[1]; r_[6] = tp[2]; r_[7] = tp[3];
+      r_[8] = 10; r_[9] = tp[4]; r_[10] = tp[5]; r_[11] = tp[6]; r_[12] = tp[7]; r_[13] = tp[8]; r_[14] = tp[9];
+      r_[15] = trace_lin_;
+    }
+  }
+#endif
+  TRACE_END(8, p.Y);
+}
+
+}  // namespace
+
+#ifdef RETR_TRACE
+void ffn_fused_set_trace(unsigned long long* buf) { CUDA_OK(cudaMemcpyToSymbol(trace_buf_, &buf, sizeof(buf))); }
+#endif
+
+void ffn_fused_configure() {
+  CUDA_OK(cudaFuncSetAttribute(ffn_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FfSmem)));
+}
+
+bool ffn_fused_supported(int d_model, int d_ff) {
+  if (d_model != FF_D || d_ff % FF_D != 0) return false;
+  return d_ff / FF_D == 8;                              // one 32-column slice per CTA and thread-per-float4 reduction
+}
+
+void ffn_fused(const FfnFusedParams& p, cudaStream_t s) {
+  RETR_CHECK(ffn_fused_supported(FF_D, p.d_ff), "ffn_fused: unsupported shape");
+  const int cl = p.d_ff / FF_D;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)cl, (unsigned)cdiv(p.M, FF_BM), 1);
+  cfg.blockDim = dim3(FF_THREADS);
+  cfg.dynamicSmemBytes = sizeof(FfSmem);
+  cfg.stream = s;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  attr[na].id = cudaLaunchAttributeClusterDimension;
+  attr[na].val.clusterDim.x = (unsigned)cl; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+  ++na;
+  if (pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  CUDA_OK(cudaLaunchKernelEx(&cfg, ffn_fused_kernel, p));
+  ++g_launches;
+}
+
+}  // namespace retr

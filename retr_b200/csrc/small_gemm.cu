@@ -12,6 +12,7 @@
 
 namespace retr {
 namespace {
+RETR_TRACE_DECL
 
 constexpr int SM_BM = 64, SM_BN = 32, SM_THREADS = 128, SM_PAD = 8;
 
@@ -35,12 +36,13 @@ __global__ void __launch_bounds__(SM_THREADS) small_gemm_kernel(const SmallGemmP
   constexpr int LDS = KC + SM_PAD;                  // padded row (elements): conflict-free ldmatrix
   constexpr int CPR = KC / 8;                       // 16-byte chunks per row
   extern __shared__ __align__(16) uint8_t sg_smem[];
-  bf16* As = reinterpret_cast<bf16*>(sg_smem);      // [2][64][LDS]
-  bf16* Ws = As + 2 * SM_BM * LDS;                  // [2][32][LDS]
+  const int chunks = p.K / KC / p.split_k;          // K panels handled by this CTA
+  const int nbuf = chunks > 1 ? 2 : 1;              // one panel: no double buffer (half the smem -> co-residency)
+  bf16* As = reinterpret_cast<bf16*>(sg_smem);      // [nbuf][64][LDS]
+  bf16* Ws = As + nbuf * SM_BM * LDS;               // [nbuf][32][LDS]
   __shared__ int s_ticket;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int m0 = blockIdx.y * SM_BM, n0 = blockIdx.x * SM_BN;
-  const int chunks = p.K / KC / p.split_k;          // K panels handled by this CTA
   const int kc0 = blockIdx.z * chunks;
 
   auto load_w = [&](int c, int buf) {
@@ -62,6 +64,7 @@ __global__ void __launch_bounds__(SM_THREADS) small_gemm_kernel(const SmallGemmP
     }
   };
 
+  TRACE_BEGIN();
   pdl_launch_dependents();
   load_w(0, 0);                                     // weights do not depend on the previous kernel
   pdl_wait();                                       // ... activations, step counter and residual do
@@ -192,7 +195,7 @@ __global__ void __launch_bounds__(SM_THREADS) small_gemm_kernel(const SmallGemmP
     __syncthreads();
     if (tid == 0) s_ticket = (int)atomicAdd(p.tickets + blockIdx.y * gridDim.x + blockIdx.x, 1u);
     __syncthreads();
-    if (s_ticket != p.split_k - 1) return;
+    if (s_ticket != p.split_k - 1) { TRACE_END(1, p.C); return; }
     __threadfence();
     if (tid == 0) p.tickets[blockIdx.y * gridDim.x + blockIdx.x] = 0;      // ready for the next launch
 #pragma unroll
@@ -229,11 +232,16 @@ __global__ void __launch_bounds__(SM_THREADS) small_gemm_kernel(const SmallGemmP
       else *reinterpret_cast<__nv_bfloat162*>(static_cast<bf16*>(p.C) + (int64_t)m * p.ldc + n) = __floats2bfloat162_rn(v0, v1);
     }
   }
+  TRACE_END(1, p.C);
 }
 
-template <int KC> size_t sg_smem_bytes() { return (size_t)2 * (SM_BM + SM_BN) * (KC + SM_PAD) * sizeof(bf16); }
+template <int KC> size_t sg_smem_bytes(int nbuf = 2) { return (size_t)nbuf * (SM_BM + SM_BN) * (KC + SM_PAD) * sizeof(bf16); }
 
 }  // namespace
+
+#ifdef RETR_TRACE
+void small_gemm_set_trace(unsigned long long* buf) { CUDA_OK(cudaMemcpyToSymbol(trace_buf_, &buf, sizeof(buf))); }
+#endif
 
 void small_gemm_configure() {
   CUDA_OK(cudaFuncSetAttribute(small_gemm_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sg_smem_bytes<256>()));
@@ -255,8 +263,9 @@ void small_gemm(const SmallGemmParams& p_in, cudaStream_t s) {
   RETR_CHECK(p.split_k == 1 || (p.scratch && p.tickets), "small_gemm: split-K needs scratch and tickets");
   RETR_CHECK(p.N % 2 == 0 && p.ldc % 2 == 0, "small_gemm: even N / ldc");
   dim3 grid((unsigned)cdiv(p.N, SM_BN), (unsigned)cdiv(p.M, SM_BM), (unsigned)p.split_k);
-  if (kc == 512) launch_pdl(small_gemm_kernel<512>, grid, dim3(SM_THREADS), sg_smem_bytes<512>(), s, p);
-  else launch_pdl(small_gemm_kernel<256>, grid, dim3(SM_THREADS), sg_smem_bytes<256>(), s, p);
+  const int nbuf = p.K / kc / p.split_k > 1 ? 2 : 1;
+  if (kc == 512) launch_pdl(small_gemm_kernel<512>, grid, dim3(SM_THREADS), sg_smem_bytes<512>(nbuf), s, p);
+  else launch_pdl(small_gemm_kernel<256>, grid, dim3(SM_THREADS), sg_smem_bytes<256>(nbuf), s, p);
 }
 
 }  // namespace retr

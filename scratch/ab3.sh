@@ -1,0 +1,16 @@
+run() {
+  echo -n "$*  "
+  env "$@" python bench.py --steps 3 --warmup 3 --no-cpu-baseline 2>/dev/null | python -c "
+import sys,json
+for l in sys.stdin:
+    if l.startswith('{'):
+        d=json.loads(l); print(round(d['value']), round(d['phases_ms_per_step']['decode'],2))"
+}
+run A=1
+run RETR_FF2_SPLIT=8
+run RETR_FF2_SPLIT=8 RETR_DECODE_PRIO=-3
+run RETR_FF2_SPLIT=8 RETR_DECODE_PRIO=-3 RETR_DECODE_GROUPS=3
+run RETR_FF2_SPLIT=8 RETR_DECODE_PRIO=-3 RETR_DECODE_GROUPS=4
+run RETR_FF2_SPLIT=8 RETR_DECODE_GROUPS=4
+run RETR_FF2_SPLIT=8 RETR_DECODE_PRIO=-3 RETR_DECODE_GROUPS=8
+run RETR_FF2_SPLIT=8 RETR_DECODE_PRIO=-3 RETR_DECODE_GROUPS=1

@@ -1,0 +1,18 @@
+python -m pytest tests/test_model_gpu.py -x -q 2>&1 | tail -3
+run() {
+  echo -n "$*  "
+  env "$@" python bench.py --steps 3 --warmup 3 --no-cpu-baseline 2>/dev/null | python -c "
+import sys,json
+for l in sys.stdin:
+    if l.startswith('{'):
+        d=json.loads(l); print(round(d['value']), round(d['phases_ms_per_step']['decode'],2))"
+}
+run RETR_CROSS_STREAM=0
+run A=1
+run RETR_DECODE_GROUPS=3
+run RETR_DECODE_GROUPS=4
+run RETR_DECODE_GROUPS=1
+run RETR_CROSS_STAGES=14
+run RETR_CROSS_STAGES=6
+run RETR_DECODE_GROUPS=4 RETR_CROSS_STAGES=6
+RETR_TRACE_FILE=gpurun_out/trace2.bin python bench.py --steps 1 --warmup 3 --no-cpu-baseline > /dev/null 2>&1
