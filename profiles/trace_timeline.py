@@ -13,7 +13,7 @@ from collections import defaultdict
 
 import numpy as np
 
-NAMES = {1: "small_gemm", 2: "self_attn", 3: "cross_attn", 6: "greedy_update", 8: "ffn_fused"}
+NAMES = {1: "small_gemm", 2: "self_attn", 3: "cross_attn", 6: "greedy_update", 8: "ffn_fused", 11: "out_ln_proj"}
 
 
 def main():
@@ -24,7 +24,7 @@ def main():
     upd = rec[rec[:, 0] == 6]
     upd = upd[np.argsort(upd[:, 3])]
     t_lo, t_hi = int(upd[step - 1, 4]), int(upd[step, 4])
-    sel = rec[(rec[:, 3] >= t_lo) & (rec[:, 3] < t_hi) & np.isin(rec[:, 0], [1, 2, 3, 8])]
+    sel = rec[(rec[:, 3] >= t_lo) & (rec[:, 3] < t_hi) & np.isin(rec[:, 0], [1, 2, 3, 8, 11])]
     # group launches: key = (id, grid, tag) within the step, ordered by time; first+last CTA records pair up
     launches = defaultdict(list)
     for r in sel:

@@ -133,6 +133,7 @@ class EngineT final : public EngineBase {
   float* src_copy_ = nullptr;                        // encoder input tokens kept for read_state
   std::vector<T*> ckv_;                              // per layer [B*S, 2d] rows of [K|V] (teacher-forced path)
   std::vector<T*> ck_, cv_, sk_, sv_;                // head-major decode caches [B][H][rows][dh]
+  int *cross_dst_ = nullptr, *cross_nvalid_ = nullptr;   // cross caches hold only the unpadded keys (decode_ops.cu)
   uint8_t *tok_mask_ = nullptr, *finished_ = nullptr;
   int64_t* caption_ = nullptr;
   int *step_ = nullptr, *done_ = nullptr;
@@ -349,6 +350,8 @@ void EngineT<T>::alloc_buffers() {
     sv_.push_back(static_cast<T*>(dalloc(Md * d * sizeof(T))));
   }
   tok_mask_ = static_cast<uint8_t*>(dalloc(Me));
+  cross_dst_ = static_cast<int*>(dalloc(Me * 4));
+  cross_nvalid_ = static_cast<int*>(dalloc((size_t)B * 4));
   finished_ = static_cast<uint8_t*>(dalloc(B));
   caption_ = static_cast<int64_t*>(dalloc(Md * 8));
   step_ = static_cast<int*>(dalloc(16));
@@ -502,7 +505,8 @@ void EngineT<T>::encode(int B, const float* t_img, const uint8_t* t_mask, const 
     GemmParams p = lin(dec_[l].c_kv, memory_, Me, ckv_[l]);
     p.rowbias = dec_[l].rb_c_kv; p.rowbias_period = S;
     gemm<T>(p, s);
-    kv_to_head_major<T>(ckv_[l], ck_[l], cv_[l], B, S, desc.n_heads, d / desc.n_heads, s);
+    if (l == 0) key_compaction(tok_mask_, B, S, cross_dst_, cross_nvalid_, s);
+    kv_to_head_major<T>(ckv_[l], ck_[l], cv_[l], B, S, desc.n_heads, d / desc.n_heads, s, cross_dst_);
   }
   CUDA_OK(cudaEventRecord(ev_[2], s));
   cur_B_ = B;
@@ -585,7 +589,7 @@ void EngineT<T>::decode_step(int B, int eos, int max_len, cudaStream_t s) {
     p = lin(e.c_q, n_, B, qc_);
     p.rowbias = e.rb_c_q; p.rowbias_dyn = step_;
     gemm<T>(p, s);
-    decode_attention<T>(qc_, d, nullptr, 0, ck_[l], cv_[l], S, att_, d, B, H, d, S, nullptr, tok_mask_, S, s);
+    decode_attention<T>(qc_, d, nullptr, 0, ck_[l], cv_[l], S, att_, d, B, H, d, S, nullptr, nullptr, 0, s, cross_nvalid_);
     p = lin(e.c_out, att_, B, y_);
     p.out_fp32 = true; p.residual = y_; p.ldr = d; p.res_fp32 = true;
     gemm<T>(p, s);
@@ -654,13 +658,27 @@ void EngineT<T>::decode_rows_fused(int r0, int n, int group, int max_len, cudaSt
     T* cv = cv_[l] + (int64_t)r0 * S * d;
     dgemm(e.s_qkv, nullptr, y, e.ln1_g, e.ln1_b, qkv, false, n, e.rb_s_qkv, 0, nullptr, 1, s);
     decode_attention<T>(qkv, 3 * d, qkv + d, 3 * d, sk, sv, Tn, att, d, n, H, d, 0, step_, nullptr, 0, s);
-    dgemm(e.s_out, att, nullptr, nullptr, nullptr, y, true, n, nullptr, 0, y, 1, s);
-    dgemm(e.c_q, nullptr, y, e.ln2_g, e.ln2_b, qc, false, n, e.rb_c_q, 0, nullptr, 1, s);
-    decode_attention<T>(qc, d, nullptr, 0, ck, cv, S, att, d, n, H, d, S, nullptr, tok_mask_ + (int64_t)r0 * S, S, s);
-    dgemm(e.c_out, att, nullptr, nullptr, nullptr, y, true, n, nullptr, 0, y, 1, s);
+    bool fused_sq = false;
+    if constexpr (std::is_same<T, bf16>::value) {
+      if (ffn_fused_) {                              // out-proj + residual + LN + cross-attention query projection, one kernel
+        AttnOutProjParams ap;
+        ap.att = att; ap.ld_att = d; ap.Wo = e.s_out.w; ap.bo = e.s_out.b; ap.Y = y;
+        ap.gamma = e.ln2_g; ap.beta = e.ln2_b; ap.Wq = e.c_q.w; ap.bq = e.c_q.b;
+        ap.rowbias = e.rb_c_q; ap.rowbias_dyn = step_; ap.Q = qc; ap.ld_q = d; ap.M = n;
+        attn_out_ln_proj(ap, s);
+        fused_sq = true;
+      }
+    }
+    if (!fused_sq) {
+      dgemm(e.s_out, att, nullptr, nullptr, nullptr, y, true, n, nullptr, 0, y, 1, s);
+      dgemm(e.c_q, nullptr, y, e.ln2_g, e.ln2_b, qc, false, n, e.rb_c_q, 0, nullptr, 1, s);
+    }
+    decode_attention<T>(qc, d, nullptr, 0, ck, cv, S, att, d, n, H, d, S, nullptr, nullptr, 0, s, cross_nvalid_ + r0);
+    if (!ffn_fused_) dgemm(e.c_out, att, nullptr, nullptr, nullptr, y, true, n, nullptr, 0, y, 1, s);
     if (ffn_fused_) {
       if constexpr (std::is_same<T, bf16>::value) {
         FfnFusedParams fp;
+        fp.att = att; fp.ld_att = d; fp.Wo = e.c_out.w; fp.bo = e.c_out.b;      // cross-attention out-proj rides along
         fp.Y = y; fp.gamma = e.ln3_g; fp.beta = e.ln3_b; fp.W1 = e.ff1.w; fp.b1 = e.ff1.b; fp.W2 = e.ff2.w; fp.b2 = e.ff2.b;
         fp.M = n; fp.d_ff = (int)ff;
         ffn_fused(fp, s);

@@ -50,6 +50,26 @@ __device__ __forceinline__ void ff_st_peer(uint32_t local_addr, uint32_t rank, f
   asm volatile("st.shared::cluster.v2.f32 [%0], {%1,%2};" ::"r"(remote), "f"(v.x), "f"(v.y) : "memory");
 }
 
+// one m16n8 output tile per warp (mt = warp & 1, nt = warp >> 1) over K = 256; two accumulator sets over alternate k
+__device__ __forceinline__ void ap_tile_mma(const bf16 (*A)[FF_LDS], const bf16 (*W)[FF_LDS], int mt, int nt, int lane,
+                                            float (&acc)[4]) {
+  float acc2[4] = {0.f, 0.f, 0.f, 0.f};
+  acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
+  const uint32_t a_base = (uint32_t)__cvta_generic_to_shared(&A[mt * 16 + (lane & 15)][(lane >> 4) * 8]);
+  const uint32_t b_base = (uint32_t)__cvta_generic_to_shared(&W[nt * 8 + (lane & 7)][((lane >> 3) & 3) * 8]);
+#pragma unroll
+  for (int ks = 0; ks < FF_D / 16; ks += 2) {
+    uint32_t a[4], a2[4], b0, b1, b2, b3;
+    ff_ldsm_x4(a_base + ks * 32, a[0], a[1], a[2], a[3]);
+    ff_ldsm_x4(a_base + (ks + 1) * 32, a2[0], a2[1], a2[2], a2[3]);
+    ff_ldsm_x4(b_base + ks * 32, b0, b1, b2, b3);               // 8 rows x k [ks*16, +32): fragments of two k-steps
+    ff_mma(acc, a, b0, b1);
+    ff_mma(acc2, a2, b2, b3);
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) acc[k] += acc2[k];
+}
+
 struct FfSmem {
   bf16 As[FF_BM][FF_LDS];                    // LN(y) rows
   bf16 Hs[FF_BM][FF_LDS];                    // relu(W1[r] LN(y) + b1[r])
@@ -83,6 +103,14 @@ __global__ void __launch_bounds__(FF_THREADS) ffn_fused_kernel(const FfnFusedPar
   pdl_launch_dependents();
   ff_cluster_arrive();                                              // phase 1: "my shared memory exists" (waited on before
                                                                     // the first remote store, five panels from now)
+  if (p.att) {                                                      // stage 0 weights: rows [32 rank, +32) of Wo -> As
+#pragma unroll
+    for (int k = 0; k < 32 * (FF_D / 8) / FF_THREADS; ++k) {
+      const int idx = tid + k * FF_THREADS, r = idx / (FF_D / 8), ch = idx % (FF_D / 8);
+      ff_cp16((uint32_t)__cvta_generic_to_shared(&sm.As[r][ch * 8]), p.Wo + (int64_t)(rank * 32 + r) * FF_D + ch * 8);
+    }
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");              // (possibly empty) group older than the ring's
 #pragma unroll
   for (int s = 0; s < FF_NST; ++s) {
     load_panel(s, s);
@@ -116,13 +144,47 @@ __global__ void __launch_bounds__(FF_THREADS) ffn_fused_kernel(const FfnFusedPar
   if (trace_on_) tp[tpn++] = trace_now();
 #endif
 
+  // ---- stage 0 (optional): y <- y + Wo att + bo for this block, each CTA one 32-column slice, slices pushed to every
+  // peer (the LayerNorm below needs whole rows).  The assembled block lives in the Ps area until it is consumed.
+  float(*Yfull)[FF_D] = reinterpret_cast<float(*)[FF_D]>(&sm.Ps[0][0][0]);
+  if (p.att) {
+#pragma unroll
+    for (int k = 0; k < FF_BM * (FF_D / 8) / FF_THREADS; ++k) {
+      const int idx = tid + k * FF_THREADS, r = idx / (FF_D / 8), ch = idx % (FF_D / 8);
+      const int m = m0 + r < p.M ? m0 + r : 0;
+      *reinterpret_cast<uint4*>(&sm.Hs[r][ch * 8]) = *reinterpret_cast<const uint4*>(p.att + (int64_t)m * p.ld_att + ch * 8);
+    }
+    const int mt = warp & 1, nt = warp >> 1, col = rank * 32 + nt * 8 + c4 * 2;
+    const int r_lo = m0 + mt * 16 + g, r_hi = r_lo + 8;
+    const float bo0 = __ldg(p.bo + col), bo1 = __ldg(p.bo + col + 1);
+    float2 res_lo = make_float2(0.f, 0.f), res_hi = res_lo;
+    if (r_lo < p.M) res_lo = *reinterpret_cast<const float2*>(p.Y + (int64_t)r_lo * FF_D + col);
+    if (r_hi < p.M) res_hi = *reinterpret_cast<const float2*>(p.Y + (int64_t)r_hi * FF_D + col);
+    asm volatile("cp.async.wait_group %0;" ::"n"(FF_NST) : "memory");   // the Wo slice; the ring may still be in flight
+    __syncthreads();
+    float acc0[4];
+    ap_tile_mma(sm.Hs, sm.As, mt, nt, lane, acc0);
+    const float2 y_lo = make_float2(acc0[0] + bo0 + res_lo.x, acc0[1] + bo1 + res_lo.y);
+    const float2 y_hi = make_float2(acc0[2] + bo0 + res_hi.x, acc0[3] + bo1 + res_hi.y);
+    ff_cluster_wait();                                              // phase 1: every CTA of the cluster is running
+    const uint32_t a_lo = (uint32_t)__cvta_generic_to_shared(&Yfull[mt * 16 + g][col]);
+    const uint32_t a_hi = (uint32_t)__cvta_generic_to_shared(&Yfull[mt * 16 + g + 8][col]);
+#pragma unroll
+    for (int dst = 0; dst < 8; ++dst) {
+      ff_st_peer(a_lo, (uint32_t)dst, y_lo);
+      ff_st_peer(a_hi, (uint32_t)dst, y_hi);
+    }
+    ff_cluster_arrive();
+    ff_cluster_wait();                                              // phase 2: whole rows of the new y are here
+  }
+
   // LayerNorm prologue: warp w normalises rows 4w .. 4w+3 into As (bf16)
   {
     float v[4][8];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int m = m0 + warp * 4 + i;
-      const float* xr = p.Y + (int64_t)(m < p.M ? m : 0) * FF_D;
+      const float* xr = p.att ? &Yfull[warp * 4 + i][0] : p.Y + (int64_t)(m < p.M ? m : 0) * FF_D;
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
         const float4 t = *reinterpret_cast<const float4*>(xr + j * 128 + lane * 4);
@@ -155,13 +217,19 @@ __global__ void __launch_bounds__(FF_THREADS) ffn_fused_kernel(const FfnFusedPar
     }
   }
 
+  float4 resid = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (p.att) {                                                      // the residual of the final sum is this CTA's own slice
+    resid = *reinterpret_cast<const float4*>(&Yfull[tid >> 3][rank * 32 + (tid & 7) * 4]);
+    ff_cluster_arrive();                                            // phase 3: this CTA no longer reads the assembled block
+  }
   uint32_t af[2][8][4];
 #pragma unroll 1
   for (int pi = 0; pi < FF_PANELS; ++pi) {
     const int buf = pi % FF_NST;
     asm volatile("cp.async.wait_group %0;" ::"n"(FF_NST - 1) : "memory");
     __syncthreads();                                                // panel pi landed; As / Hs complete
-    if (pi == 4) ff_cluster_wait();                                 // every CTA of the cluster is running (remote stores ahead)
+    if (pi == 4) ff_cluster_wait();                                 // phase 1 (or 3): peers are running and done with the Ps
+                                                                    // area as "assembled y" — remote partial stores ahead
     if (pi == 0 || pi == 4) {                                       // (re)load this warp's A fragments
       const bf16(*A)[FF_LDS] = pi < 4 ? sm.As : sm.Hs;
 #pragma unroll
@@ -245,8 +313,7 @@ __global__ void __launch_bounds__(FF_THREADS) ffn_fused_kernel(const FfnFusedPar
   // remote stores, visible after the cluster barrier.  One float4 per thread, slots summed in a fixed order.
   const int row = tid >> 3, lc = (tid & 7) * 4, col = rank * 32 + lc;
   const float4 bias2 = __ldg(reinterpret_cast<const float4*>(p.b2 + col));
-  float4 resid = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (m0 + row < p.M) resid = *reinterpret_cast<const float4*>(p.Y + (int64_t)(m0 + row) * FF_D + col);
+  if (!p.att && m0 + row < p.M) resid = *reinterpret_cast<const float4*>(p.Y + (int64_t)(m0 + row) * FF_D + col);
   ff_cluster_arrive();
   ff_cluster_wait();
   {
@@ -276,6 +343,125 @@ __global__ void __launch_bounds__(FF_THREADS) ffn_fused_kernel(const FfnFusedPar
   TRACE_END(8, p.Y);
 }
 
+
+// ---- attention output projection + residual + LayerNorm + next projection, one cluster kernel ----------------
+//     y <- y + Wo · att + bo ;   q = Wq · LN(y) + bq + rowbias[*step]
+// (self-attention out-proj followed by the cross-attention query projection of a decoder layer,
+// models/transformer_modules.py:58-83 in pre-norm form).  Two dependent 5-8 us launches in the decode graph; here the
+// eight CTAs of a cluster each compute a 32-column slice of y for a 32-row block, push it to every peer's shared
+// memory (the LayerNorm needs whole rows), and after one cluster barrier each computes a 32-column slice of q.
+struct ApSmem {
+  bf16 A0[FF_BM][FF_LDS];                    // att rows
+  bf16 W0[32][FF_LDS];                       // Wo rows of this CTA's column slice
+  bf16 W1[32][FF_LDS];                       // Wq rows of this CTA's column slice
+  bf16 As[FF_BM][FF_LDS];                    // LN(y) rows
+  float Yfull[FF_BM][FF_D];                  // the block's new y, assembled from the eight slices
+};
+
+__global__ void __launch_bounds__(FF_THREADS) attn_out_ln_proj_kernel(const AttnOutProjParams p) {
+  extern __shared__ __align__(128) uint8_t ap_raw[];
+  ApSmem& sm = *reinterpret_cast<ApSmem*>(ap_raw);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int rank = (int)ff_cluster_rank();
+  const int m0 = blockIdx.y * FF_BM;
+  const int g = lane >> 2, c4 = lane & 3, mt = warp & 1, nt = warp >> 1;
+  TRACE_BEGIN();
+  pdl_launch_dependents();
+  ff_cluster_arrive();                                              // phase 1: this CTA's shared memory exists
+  // weights of this CTA's slice: rows [32 rank, +32) of Wo and Wq
+#pragma unroll
+  for (int k = 0; k < 2 * 32 * (FF_D / 8) / FF_THREADS; ++k) {
+    const int idx = tid + k * FF_THREADS, which = idx / (32 * (FF_D / 8)), rem = idx % (32 * (FF_D / 8));
+    const int r = rem / (FF_D / 8), ch = rem % (FF_D / 8);
+    const bf16* src = (which ? p.Wq : p.Wo) + (int64_t)(rank * 32 + r) * FF_D + ch * 8;
+    ff_cp16((uint32_t)__cvta_generic_to_shared(which ? &sm.W1[r][ch * 8] : &sm.W0[r][ch * 8]), src);
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  const int col = rank * 32 + nt * 8 + c4 * 2;                      // this thread's output columns col, col + 1
+  const float bo0 = __ldg(p.bo + col), bo1 = __ldg(p.bo + col + 1);
+  float bq0 = p.bq ? __ldg(p.bq + col) : 0.f, bq1 = p.bq ? __ldg(p.bq + col + 1) : 0.f;
+  float4 gam[2], bet[2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    gam[j] = __ldg(reinterpret_cast<const float4*>(p.gamma + j * 128 + lane * 4));
+    bet[j] = __ldg(reinterpret_cast<const float4*>(p.beta + j * 128 + lane * 4));
+  }
+  pdl_wait();                                                       // att, y and the step counter come from earlier kernels
+#pragma unroll
+  for (int k = 0; k < FF_BM * (FF_D / 8) / FF_THREADS; ++k) {
+    const int idx = tid + k * FF_THREADS, r = idx / (FF_D / 8), ch = idx % (FF_D / 8);
+    const int m = m0 + r < p.M ? m0 + r : 0;
+    ff_cp16((uint32_t)__cvta_generic_to_shared(&sm.A0[r][ch * 8]), p.att + (int64_t)m * p.ld_att + ch * 8);
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  const int r_lo = m0 + mt * 16 + g, r_hi = r_lo + 8;
+  float2 res_lo = make_float2(0.f, 0.f), res_hi = res_lo;
+  if (r_lo < p.M) res_lo = *reinterpret_cast<const float2*>(p.Y + (int64_t)r_lo * FF_D + col);
+  if (r_hi < p.M) res_hi = *reinterpret_cast<const float2*>(p.Y + (int64_t)r_hi * FF_D + col);
+  if (p.rowbias) {
+    const int64_t rb = (int64_t)__ldg(p.rowbias_dyn) * FF_D;
+    bq0 += __ldg(p.rowbias + rb + col);
+    bq1 += __ldg(p.rowbias + rb + col + 1);
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  float acc[4];
+  ap_tile_mma(sm.A0, sm.W0, mt, nt, lane, acc);
+  const float2 y_lo = make_float2(acc[0] + bo0 + res_lo.x, acc[1] + bo1 + res_lo.y);
+  const float2 y_hi = make_float2(acc[2] + bo0 + res_hi.x, acc[3] + bo1 + res_hi.y);
+  if (r_lo < p.M) *reinterpret_cast<float2*>(p.Y + (int64_t)r_lo * FF_D + col) = y_lo;
+  if (r_hi < p.M) *reinterpret_cast<float2*>(p.Y + (int64_t)r_hi * FF_D + col) = y_hi;
+  ff_cluster_wait();                                                // every CTA of the cluster is running
+  {
+    const uint32_t a_lo = (uint32_t)__cvta_generic_to_shared(&sm.Yfull[mt * 16 + g][col]);
+    const uint32_t a_hi = (uint32_t)__cvta_generic_to_shared(&sm.Yfull[mt * 16 + g + 8][col]);
+#pragma unroll
+    for (int dst = 0; dst < 8; ++dst) {
+      ff_st_peer(a_lo, (uint32_t)dst, y_lo);
+      ff_st_peer(a_hi, (uint32_t)dst, y_hi);
+    }
+  }
+  ff_cluster_arrive();
+  ff_cluster_wait();                                                // whole rows of the new y are here
+  {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = warp * 4 + i;
+      float v[8];
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const float4 t = *reinterpret_cast<const float4*>(&sm.Yfull[r][j * 128 + lane * 4]);
+        v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
+      }
+      float s = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s += v[j];
+      const float mean = warp_sum(s) * (1.f / FF_D);
+      float q = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { const float t = v[j] - mean; q = fmaf(t, t, q); }
+      const float rstd = rsqrtf(warp_sum(q) * (1.f / FF_D) + p.eps);
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const float4 ga = gam[j], be = bet[j];
+        __nv_bfloat162 lo = __floats2bfloat162_rn((v[4 * j] - mean) * rstd * ga.x + be.x, (v[4 * j + 1] - mean) * rstd * ga.y + be.y);
+        __nv_bfloat162 hi = __floats2bfloat162_rn((v[4 * j + 2] - mean) * rstd * ga.z + be.z, (v[4 * j + 3] - mean) * rstd * ga.w + be.w);
+        uint2 pk;
+        pk.x = *reinterpret_cast<uint32_t*>(&lo);
+        pk.y = *reinterpret_cast<uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(&sm.As[r][j * 128 + lane * 4]) = pk;
+      }
+    }
+  }
+  __syncthreads();
+  ap_tile_mma(sm.As, sm.W1, mt, nt, lane, acc);
+  if (r_lo < p.M)
+    *reinterpret_cast<__nv_bfloat162*>(p.Q + (int64_t)r_lo * p.ld_q + col) = __floats2bfloat162_rn(acc[0] + bq0, acc[1] + bq1);
+  if (r_hi < p.M)
+    *reinterpret_cast<__nv_bfloat162*>(p.Q + (int64_t)r_hi * p.ld_q + col) = __floats2bfloat162_rn(acc[2] + bq0, acc[3] + bq1);
+  TRACE_END(11, p.Y);
+}
+
 }  // namespace
 
 #ifdef RETR_TRACE
@@ -284,6 +470,34 @@ void ffn_fused_set_trace(unsigned long long* buf) { CUDA_OK(cudaMemcpyToSymbol(t
 
 void ffn_fused_configure() {
   CUDA_OK(cudaFuncSetAttribute(ffn_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FfSmem)));
+  CUDA_OK(cudaFuncSetAttribute(attn_out_ln_proj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ApSmem)));
+}
+
+template <typename P>
+static void launch_cluster8(void (*kernel)(P), const P& p, int M, size_t smem, cudaStream_t s) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(8, (unsigned)cdiv(M, FF_BM), 1);
+  cfg.blockDim = dim3(FF_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  attr[na].id = cudaLaunchAttributeClusterDimension;
+  attr[na].val.clusterDim.x = 8; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+  ++na;
+  if (pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  CUDA_OK(cudaLaunchKernelEx(&cfg, kernel, p));
+  ++g_launches;
+}
+
+void attn_out_ln_proj(const AttnOutProjParams& p, cudaStream_t s) {
+  launch_cluster8(attn_out_ln_proj_kernel, p, p.M, sizeof(ApSmem), s);
 }
 
 bool ffn_fused_supported(int d_model, int d_ff) {
@@ -293,26 +507,7 @@ bool ffn_fused_supported(int d_model, int d_ff) {
 
 void ffn_fused(const FfnFusedParams& p, cudaStream_t s) {
   RETR_CHECK(ffn_fused_supported(FF_D, p.d_ff), "ffn_fused: unsupported shape");
-  const int cl = p.d_ff / FF_D;
-  cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3((unsigned)cl, (unsigned)cdiv(p.M, FF_BM), 1);
-  cfg.blockDim = dim3(FF_THREADS);
-  cfg.dynamicSmemBytes = sizeof(FfSmem);
-  cfg.stream = s;
-  cudaLaunchAttribute attr[2];
-  int na = 0;
-  attr[na].id = cudaLaunchAttributeClusterDimension;
-  attr[na].val.clusterDim.x = (unsigned)cl; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
-  ++na;
-  if (pdl_enabled()) {
-    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[na].val.programmaticStreamSerializationAllowed = 1;
-    ++na;
-  }
-  cfg.attrs = attr;
-  cfg.numAttrs = na;
-  CUDA_OK(cudaLaunchKernelEx(&cfg, ffn_fused_kernel, p));
-  ++g_launches;
+  launch_cluster8(ffn_fused_kernel, p, p.M, sizeof(FfSmem), s);
 }
 
 }  // namespace retr

@@ -10,7 +10,22 @@ struct FfnFusedParams {
   const bf16* W1 = nullptr; const float* b1 = nullptr; // [d_ff, 256], [d_ff]
   const bf16* W2 = nullptr; const float* b2 = nullptr; // [256, d_ff], [256]
   int M = 0, d_ff = 0;
+  // optional stage 0: y <- y + Wo att + bo first (the attention out-projection that precedes the sublayer)
+  const bf16* att = nullptr; int64_t ld_att = 0; const bf16* Wo = nullptr; const float* bo = nullptr;
 };
+
+// y <- y + Wo att + bo ; q = Wq LN(y) + bq + rowbias[*rowbias_dyn]   (d_model = 256; see ffn_fused.cu)
+struct AttnOutProjParams {
+  const bf16* att = nullptr; int64_t ld_att = 0;       // [M, 256] attention output (heads concatenated)
+  const bf16* Wo = nullptr; const float* bo = nullptr; // [256, 256], [256]
+  float* Y = nullptr;                                  // [M, 256] fp32 residual stream, updated in place
+  const float* gamma = nullptr; const float* beta = nullptr; float eps = 1e-5f;
+  const bf16* Wq = nullptr; const float* bq = nullptr; // [256, 256], [256] (may be null)
+  const float* rowbias = nullptr; const int* rowbias_dyn = nullptr;   // [rows, 256] table, row picked on the device
+  bf16* Q = nullptr; int64_t ld_q = 0;                 // [M, 256]
+  int M = 0;
+};
+void attn_out_ln_proj(const AttnOutProjParams& p, cudaStream_t s);
 
 void ffn_fused_configure();                            // opt-in shared memory; call outside stream capture
 bool ffn_fused_supported(int d_model, int d_ff);

@@ -59,12 +59,15 @@ void flash_attention_bf16(const AttnParams& p, int dh, cudaStream_t s);   // att
 template <typename T>
 void decode_attention(const T* q, int64_t ldq, const T* new_kv, int64_t ld_new, T* kcache, T* vcache, int cache_rows,
                       T* out, int64_t ldo, int B, int H, int d, int n_keys, const int* step_dyn,
-                      const uint8_t* key_pad, int64_t ld_pad, cudaStream_t s);
+                      const uint8_t* key_pad, int64_t ld_pad, cudaStream_t s, const int* n_keys_per = nullptr);
 // opt in to the dynamic shared memory the kernel needs (call once, outside stream capture)
 template <typename T> void decode_attention_configure(int max_rows, int dh);
-// rows of [K(d) | V(d)] -> head-major K and V blocks
+// rows of [K(d) | V(d)] -> head-major K and V blocks; with dst_row (key_compaction) only the unpadded keys, densely
 template <typename T>
-void kv_to_head_major(const T* kv, T* kh, T* vh, int B, int rows, int H, int dh, cudaStream_t s);
+void kv_to_head_major(const T* kv, T* kh, T* vh, int B, int rows, int H, int dh, cudaStream_t s,
+                      const int* dst_row = nullptr);
+// dst_row[b*S + j] = rank of key j among sample b's unpadded keys (-1 if padded); n_valid[b] = their number
+void key_compaction(const uint8_t* pad, int B, int S, int* dst_row, int* n_valid, cudaStream_t s);
 // After the vocab GEMM+argmax of step i=*step: the bookkeeping of eval_utils/decode.py:70-79.
 void greedy_update(unsigned long long* argmax_keys, int64_t* caption, int max_len, int B, int eos, int* step,
                    int* done, uint8_t* finished, cudaStream_t s, bool allow_pdl = true);
