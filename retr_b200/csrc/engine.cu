@@ -674,11 +674,10 @@ void EngineT<T>::decode_rows_fused(int r0, int n, int group, int max_len, cudaSt
       dgemm(e.c_q, nullptr, y, e.ln2_g, e.ln2_b, qc, false, n, e.rb_c_q, 0, nullptr, 1, s);
     }
     decode_attention<T>(qc, d, nullptr, 0, ck, cv, S, att, d, n, H, d, S, nullptr, nullptr, 0, s, cross_nvalid_ + r0);
-    if (!ffn_fused_) dgemm(e.c_out, att, nullptr, nullptr, nullptr, y, true, n, nullptr, 0, y, 1, s);
+    dgemm(e.c_out, att, nullptr, nullptr, nullptr, y, true, n, nullptr, 0, y, 1, s);
     if (ffn_fused_) {
       if constexpr (std::is_same<T, bf16>::value) {
         FfnFusedParams fp;
-        fp.att = att; fp.ld_att = d; fp.Wo = e.c_out.w; fp.bo = e.c_out.b;      // cross-attention out-proj rides along
         fp.Y = y; fp.gamma = e.ln3_g; fp.beta = e.ln3_b; fp.W1 = e.ff1.w; fp.b1 = e.ff1.b; fp.W2 = e.ff2.w; fp.b2 = e.ff2.b;
         fp.M = n; fp.d_ff = (int)ff;
         ffn_fused(fp, s);

@@ -7,6 +7,10 @@
 // slices it PUSHES into the shared memory of the CTA that owns those columns (st.shared::cluster, fire and forget).
 // After one cluster barrier every CTA sums its eight slots in a fixed order (deterministic), adds b2 and the residual
 // and writes y in place.  No HBM round trip for h, no atomics, no second launch, no remote-load latency.
+// (Also tried: the cross-attention out-projection as a prologue of this kernel — neutral to 0.4 ms slower — and the NEXT
+// layer's LN + qkv projection as a tail of this kernel — correct, but 2 ms slower per decode: the
+// tail runs on 32 CTAs after two more cluster barriers, while the stand-alone GEMM overlaps its weight fetch with this
+// kernel's end through PDL.  Fusing pays when it removes a dependent round trip, not when it serialises one.)
 // Both GEMMs are the same shape — A[32 x 256] (LN(y) or h_r) times a 64-row weight panel — so one cp.async ring of
 // 64 x 256 panels feeds all eight of them; the first panels are in flight before griddepcontrol.wait (weights do not
 // depend on the previous kernel).
@@ -40,6 +44,11 @@ __device__ __forceinline__ uint32_t ff_cluster_rank() {
 }
 __device__ __forceinline__ void ff_cluster_arrive() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+// arrival that orders nothing: "this CTA is running" / "this CTA is done reading" need no fence, and the release form
+// costs a membar (~1 us at this kernel's scale)
+__device__ __forceinline__ void ff_cluster_arrive_relaxed() {
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void ff_cluster_wait() {
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -101,16 +110,8 @@ __global__ void __launch_bounds__(FF_THREADS) ffn_fused_kernel(const FfnFusedPar
 
   TRACE_BEGIN();
   pdl_launch_dependents();
-  ff_cluster_arrive();                                              // phase 1: "my shared memory exists" (waited on before
+  ff_cluster_arrive_relaxed();                                      // phase 1: "my shared memory exists" (waited on before
                                                                     // the first remote store, five panels from now)
-  if (p.att) {                                                      // stage 0 weights: rows [32 rank, +32) of Wo -> As
-#pragma unroll
-    for (int k = 0; k < 32 * (FF_D / 8) / FF_THREADS; ++k) {
-      const int idx = tid + k * FF_THREADS, r = idx / (FF_D / 8), ch = idx % (FF_D / 8);
-      ff_cp16((uint32_t)__cvta_generic_to_shared(&sm.As[r][ch * 8]), p.Wo + (int64_t)(rank * 32 + r) * FF_D + ch * 8);
-    }
-  }
-  asm volatile("cp.async.commit_group;" ::: "memory");              // (possibly empty) group older than the ring's
 #pragma unroll
   for (int s = 0; s < FF_NST; ++s) {
     load_panel(s, s);
@@ -144,47 +145,13 @@ __global__ void __launch_bounds__(FF_THREADS) ffn_fused_kernel(const FfnFusedPar
   if (trace_on_) tp[tpn++] = trace_now();
 #endif
 
-  // ---- stage 0 (optional): y <- y + Wo att + bo for this block, each CTA one 32-column slice, slices pushed to every
-  // peer (the LayerNorm below needs whole rows).  The assembled block lives in the Ps area until it is consumed.
-  float(*Yfull)[FF_D] = reinterpret_cast<float(*)[FF_D]>(&sm.Ps[0][0][0]);
-  if (p.att) {
-#pragma unroll
-    for (int k = 0; k < FF_BM * (FF_D / 8) / FF_THREADS; ++k) {
-      const int idx = tid + k * FF_THREADS, r = idx / (FF_D / 8), ch = idx % (FF_D / 8);
-      const int m = m0 + r < p.M ? m0 + r : 0;
-      *reinterpret_cast<uint4*>(&sm.Hs[r][ch * 8]) = *reinterpret_cast<const uint4*>(p.att + (int64_t)m * p.ld_att + ch * 8);
-    }
-    const int mt = warp & 1, nt = warp >> 1, col = rank * 32 + nt * 8 + c4 * 2;
-    const int r_lo = m0 + mt * 16 + g, r_hi = r_lo + 8;
-    const float bo0 = __ldg(p.bo + col), bo1 = __ldg(p.bo + col + 1);
-    float2 res_lo = make_float2(0.f, 0.f), res_hi = res_lo;
-    if (r_lo < p.M) res_lo = *reinterpret_cast<const float2*>(p.Y + (int64_t)r_lo * FF_D + col);
-    if (r_hi < p.M) res_hi = *reinterpret_cast<const float2*>(p.Y + (int64_t)r_hi * FF_D + col);
-    asm volatile("cp.async.wait_group %0;" ::"n"(FF_NST) : "memory");   // the Wo slice; the ring may still be in flight
-    __syncthreads();
-    float acc0[4];
-    ap_tile_mma(sm.Hs, sm.As, mt, nt, lane, acc0);
-    const float2 y_lo = make_float2(acc0[0] + bo0 + res_lo.x, acc0[1] + bo1 + res_lo.y);
-    const float2 y_hi = make_float2(acc0[2] + bo0 + res_hi.x, acc0[3] + bo1 + res_hi.y);
-    ff_cluster_wait();                                              // phase 1: every CTA of the cluster is running
-    const uint32_t a_lo = (uint32_t)__cvta_generic_to_shared(&Yfull[mt * 16 + g][col]);
-    const uint32_t a_hi = (uint32_t)__cvta_generic_to_shared(&Yfull[mt * 16 + g + 8][col]);
-#pragma unroll
-    for (int dst = 0; dst < 8; ++dst) {
-      ff_st_peer(a_lo, (uint32_t)dst, y_lo);
-      ff_st_peer(a_hi, (uint32_t)dst, y_hi);
-    }
-    ff_cluster_arrive();
-    ff_cluster_wait();                                              // phase 2: whole rows of the new y are here
-  }
-
   // LayerNorm prologue: warp w normalises rows 4w .. 4w+3 into As (bf16)
   {
     float v[4][8];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int m = m0 + warp * 4 + i;
-      const float* xr = p.att ? &Yfull[warp * 4 + i][0] : p.Y + (int64_t)(m < p.M ? m : 0) * FF_D;
+      const float* xr = p.Y + (int64_t)(m < p.M ? m : 0) * FF_D;
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
         const float4 t = *reinterpret_cast<const float4*>(xr + j * 128 + lane * 4);
@@ -217,19 +184,13 @@ __global__ void __launch_bounds__(FF_THREADS) ffn_fused_kernel(const FfnFusedPar
     }
   }
 
-  float4 resid = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (p.att) {                                                      // the residual of the final sum is this CTA's own slice
-    resid = *reinterpret_cast<const float4*>(&Yfull[tid >> 3][rank * 32 + (tid & 7) * 4]);
-    ff_cluster_arrive();                                            // phase 3: this CTA no longer reads the assembled block
-  }
   uint32_t af[2][8][4];
 #pragma unroll 1
   for (int pi = 0; pi < FF_PANELS; ++pi) {
     const int buf = pi % FF_NST;
     asm volatile("cp.async.wait_group %0;" ::"n"(FF_NST - 1) : "memory");
     __syncthreads();                                                // panel pi landed; As / Hs complete
-    if (pi == 4) ff_cluster_wait();                                 // phase 1 (or 3): peers are running and done with the Ps
-                                                                    // area as "assembled y" — remote partial stores ahead
+    if (pi == 4) ff_cluster_wait();                                 // every CTA of the cluster is running (remote stores ahead)
     if (pi == 0 || pi == 4) {                                       // (re)load this warp's A fragments
       const bf16(*A)[FF_LDS] = pi < 4 ? sm.As : sm.Hs;
 #pragma unroll
@@ -313,7 +274,8 @@ __global__ void __launch_bounds__(FF_THREADS) ffn_fused_kernel(const FfnFusedPar
   // remote stores, visible after the cluster barrier.  One float4 per thread, slots summed in a fixed order.
   const int row = tid >> 3, lc = (tid & 7) * 4, col = rank * 32 + lc;
   const float4 bias2 = __ldg(reinterpret_cast<const float4*>(p.b2 + col));
-  if (!p.att && m0 + row < p.M) resid = *reinterpret_cast<const float4*>(p.Y + (int64_t)(m0 + row) * FF_D + col);
+  float4 resid = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (m0 + row < p.M) resid = *reinterpret_cast<const float4*>(p.Y + (int64_t)(m0 + row) * FF_D + col);
   ff_cluster_arrive();
   ff_cluster_wait();
   {
@@ -367,7 +329,7 @@ __global__ void __launch_bounds__(FF_THREADS) attn_out_ln_proj_kernel(const Attn
   const int g = lane >> 2, c4 = lane & 3, mt = warp & 1, nt = warp >> 1;
   TRACE_BEGIN();
   pdl_launch_dependents();
-  ff_cluster_arrive();                                              // phase 1: this CTA's shared memory exists
+  ff_cluster_arrive_relaxed();                                      // phase 1: this CTA's shared memory exists
   // weights of this CTA's slice: rows [32 rank, +32) of Wo and Wq
 #pragma unroll
   for (int k = 0; k < 2 * 32 * (FF_D / 8) / FF_THREADS; ++k) {
@@ -409,8 +371,6 @@ __global__ void __launch_bounds__(FF_THREADS) attn_out_ln_proj_kernel(const Attn
   ap_tile_mma(sm.A0, sm.W0, mt, nt, lane, acc);
   const float2 y_lo = make_float2(acc[0] + bo0 + res_lo.x, acc[1] + bo1 + res_lo.y);
   const float2 y_hi = make_float2(acc[2] + bo0 + res_hi.x, acc[3] + bo1 + res_hi.y);
-  if (r_lo < p.M) *reinterpret_cast<float2*>(p.Y + (int64_t)r_lo * FF_D + col) = y_lo;
-  if (r_hi < p.M) *reinterpret_cast<float2*>(p.Y + (int64_t)r_hi * FF_D + col) = y_hi;
   ff_cluster_wait();                                                // every CTA of the cluster is running
   {
     const uint32_t a_lo = (uint32_t)__cvta_generic_to_shared(&sm.Yfull[mt * 16 + g][col]);
@@ -423,6 +383,9 @@ __global__ void __launch_bounds__(FF_THREADS) attn_out_ln_proj_kernel(const Attn
   }
   ff_cluster_arrive();
   ff_cluster_wait();                                                // whole rows of the new y are here
+  // (global stores after the barrier: its release would otherwise have to wait for them)
+  if (r_lo < p.M) *reinterpret_cast<float2*>(p.Y + (int64_t)r_lo * FF_D + col) = y_lo;
+  if (r_hi < p.M) *reinterpret_cast<float2*>(p.Y + (int64_t)r_hi * FF_D + col) = y_hi;
   {
 #pragma unroll
     for (int i = 0; i < 4; ++i) {

@@ -10,8 +10,6 @@ struct FfnFusedParams {
   const bf16* W1 = nullptr; const float* b1 = nullptr; // [d_ff, 256], [d_ff]
   const bf16* W2 = nullptr; const float* b2 = nullptr; // [256, d_ff], [256]
   int M = 0, d_ff = 0;
-  // optional stage 0: y <- y + Wo att + bo first (the attention out-projection that precedes the sublayer)
-  const bf16* att = nullptr; int64_t ld_att = 0; const bf16* Wo = nullptr; const float* bo = nullptr;
 };
 
 // y <- y + Wo att + bo ; q = Wq LN(y) + bq + rowbias[*rowbias_dyn]   (d_model = 256; see ffn_fused.cu)
