@@ -34,6 +34,9 @@ KIND = "CaptionGlobalLoc"
 BACKBONE_GFLOP_PER_IMAGE = 19.838
 TOTAL_GFLOP_PER_EXPR = 54.55
 DECODE_MB_PER_EXPR_B256 = 385.0
+# measured (ncu dram__bytes_read.sum + dram__bytes_write.sum over the 106 launches of a 256-image chunk, bf16;
+# profiles/r1_backbone_dram.txt): 21.264 GB per chunk
+BACKBONE_DRAM_BYTES_PER_IMAGE = 21.264e9 / 256
 
 
 def build_model(precision):
@@ -267,6 +270,7 @@ def main():
                                    "CUDA-graph decode (BASELINE.json configs[1])",
                        "batch_per_gpu": B, "decode_steps_executed": int(steps_run[-1]), "sharding": "samples",
                        "l2": "inputs (308 MB/step) exceed L2; no flush",
+                       "cross_kv": "padded keys dropped when the cross K/V caches are built (exact: exp(-inf) = 0)",
                        "weights": "seed-42 build_model init + seeded FrozenBN calibration"},
             "e2e": {"value": e2e, "unit": "expr/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps},
@@ -275,7 +279,10 @@ def main():
             "phases_ms_per_step": {k: v / args.steps for k, v in phases.items()},
             "roofline": {"bound": "tensor", "kernel": "gemm_tcgen05_kernel over the backbone phase (conv launches of "
                          "2B images, incl. stem im2col + maxpool)", "achieved": achieved, "peak": tf_peak,
-                         "unit": "TFLOP/s", "frac": achieved / tf_peak if tf_peak else None, "traffic": None,
+                         "unit": "TFLOP/s", "frac": achieved / tf_peak if tf_peak else None,
+                         "traffic": BACKBONE_DRAM_BYTES_PER_IMAGE * n_img if args.precision == "bf16" else None,
+                         "traffic_note": "DRAM read+write bytes of the backbone phase per step (ncu, "
+                                         "profiles/r1_backbone_dram.txt: 21.26 GB per 256-image chunk), scaled by images",
                          "peak_source": f"{which} bf16 sustained"},
             "roofline_decode": {"bound": "hbm", "achieved": DECODE_MB_PER_EXPR_B256 * B / 1000.0 /
                                 (phases["decode"] / args.steps / 1000.0) if phases["decode"] > 0 else 0.0,
