@@ -129,6 +129,22 @@ int retr_op_attention(int32_t dtype, const void* q, const void* k, const void* v
                       int64_t ldk, int64_t ldv, int64_t ldo, const uint8_t* key_pad,
                       int32_t causal, float* probs, void* stream);
 
+/* ---- fused sublayers of one KV-cached decode step (bf16 operands, d_model 256; parity tests) --------
+ * retr_op_decode_ffn: y <- y + W2 relu(W1 LN(y) + b1) + b2 in place (the pre-norm FeedForward sublayer,
+ *   models/transformer_modules.py:84-97); y fp32 [M,256], W1 bf16 [d_ff,256], W2 bf16 [256,d_ff], d_ff = 2048.
+ * retr_op_decode_out_ln_proj: y <- y + Wo att + bo ; q = Wq LN(y) + bq + rowbias[*row]  (attention out-projection +
+ *   residual, then the next pre-norm projection, models/transformer_modules.py:58-83); att bf16 [M,256],
+ *   Wo/Wq bf16 [256,256], q bf16 [M,256]; bq, rowbias (fp32 [rows,256]) and row (device int) may be NULL together.
+ * retr_op_decode_cross_attention: single-query attention of M samples over head-major K/V caches
+ *   [M][H][cache_rows][dh] that hold n_keys[m] (device int32 [M], or NULL -> cache_rows) valid rows each. */
+int retr_op_decode_ffn(float* y, const float* gamma, const float* beta, float eps, const void* W1, const float* b1,
+                       const void* W2, const float* b2, int32_t M, int32_t d_ff, void* stream);
+int retr_op_decode_out_ln_proj(const void* att, const void* Wo, const float* bo, float* y, const float* gamma,
+                               const float* beta, float eps, const void* Wq, const float* bq, const float* rowbias,
+                               const int32_t* row, void* q, int32_t M, void* stream);
+int retr_op_decode_cross_attention(const void* q, const void* kcache, const void* vcache, int32_t cache_rows, void* out,
+                                   int32_t M, int32_t n_heads, int32_t d_model, const int32_t* n_keys, void* stream);
+
 /* ---- training step (engine.py:52-87 train_one_epoch; optimiser recipe main.py:30-40) ------------- */
 typedef struct retr_trainer retr_trainer;
 

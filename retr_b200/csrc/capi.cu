@@ -1,6 +1,7 @@
 // extern "C" surface declared in include/retr_b200.h.  Every entry point converts C++ exceptions
 // into a non-zero status + retr_last_error(); there is no CPU fallback behind any of them.
 #include "engine.h"
+#include "ffn_fused.h"
 #include "train.h"
 
 namespace retr {
@@ -175,6 +176,43 @@ int retr_op_attention(int32_t dtype, const void* q, const void* k, const void* v
   if (dtype == RETR_FP32) attention<float>(p, static_cast<cudaStream_t>(stream));
   else if (dtype == RETR_BF16) attention<bf16>(p, static_cast<cudaStream_t>(stream));
   else throw Error("unknown dtype");
+  API_END
+}
+
+int retr_op_decode_ffn(float* y, const float* gamma, const float* beta, float eps, const void* W1, const float* b1,
+                       const void* W2, const float* b2, int32_t M, int32_t d_ff, void* stream) {
+  API_BEGIN
+  RETR_CHECK(ffn_fused_supported(256, d_ff), "retr_op_decode_ffn: d_model 256 and d_ff 2048 only");
+  ffn_fused_configure();
+  FfnFusedParams p;
+  p.Y = y; p.gamma = gamma; p.beta = beta; p.eps = eps; p.W1 = static_cast<const bf16*>(W1); p.b1 = b1;
+  p.W2 = static_cast<const bf16*>(W2); p.b2 = b2; p.M = M; p.d_ff = d_ff;
+  ffn_fused(p, static_cast<cudaStream_t>(stream));
+  API_END
+}
+
+int retr_op_decode_out_ln_proj(const void* att, const void* Wo, const float* bo, float* y, const float* gamma,
+                               const float* beta, float eps, const void* Wq, const float* bq, const float* rowbias,
+                               const int32_t* row, void* q, int32_t M, void* stream) {
+  API_BEGIN
+  RETR_CHECK((rowbias == nullptr) == (row == nullptr), "rowbias and row go together");
+  ffn_fused_configure();
+  AttnOutProjParams p;
+  p.att = static_cast<const bf16*>(att); p.ld_att = 256; p.Wo = static_cast<const bf16*>(Wo); p.bo = bo; p.Y = y;
+  p.gamma = gamma; p.beta = beta; p.eps = eps; p.Wq = static_cast<const bf16*>(Wq); p.bq = bq;
+  p.rowbias = rowbias; p.rowbias_dyn = row; p.Q = static_cast<bf16*>(q); p.ld_q = 256; p.M = M;
+  attn_out_ln_proj(p, static_cast<cudaStream_t>(stream));
+  API_END
+}
+
+int retr_op_decode_cross_attention(const void* q, const void* kcache, const void* vcache, int32_t cache_rows, void* out,
+                                   int32_t M, int32_t n_heads, int32_t d_model, const int32_t* n_keys, void* stream) {
+  API_BEGIN
+  decode_attention_configure<bf16>(cache_rows, d_model / n_heads);
+  decode_attention<bf16>(static_cast<const bf16*>(q), d_model, nullptr, 0,
+                         const_cast<bf16*>(static_cast<const bf16*>(kcache)), const_cast<bf16*>(static_cast<const bf16*>(vcache)),
+                         cache_rows, static_cast<bf16*>(out), d_model, M, n_heads, d_model, cache_rows, nullptr, nullptr, 0,
+                         static_cast<cudaStream_t>(stream), n_keys);
   API_END
 }
 

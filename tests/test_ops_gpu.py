@@ -240,3 +240,89 @@ def test_attention(dtype, Lq, Lk, causal, d, H):
     assert (out.float()[valid] - ref[valid]).abs().max().item() < (2e-5 if dtype == FP32 else 2e-2)
     pv = ~torch.isnan(ref_p)
     assert (probs[pv] - ref_p[pv]).abs().max().item() < 2e-5
+
+
+# ---- fused sublayers of the decode step (cluster kernels, csrc/ffn_fused.cu) and the compacted cross-attention ----
+
+def _bf(t):
+    return t.to(torch.bfloat16)
+
+
+@pytest.mark.parametrize("M", [2, 32, 33, 128, 256])
+def test_decode_ffn_fused(M):
+    """y + W2 relu(W1 LN(y) + b1) + b2 (models/transformer_modules.py:84-97) on the operands the kernel sees (bf16
+    weights, bf16 LN output and hidden activations, fp32 accumulation).  Rows beyond a 32-row block (M = 2, 33) cover
+    the tail handling; two launches must be bit-identical (fixed-order cluster reduction)."""
+    native, lib = _lib()
+    torch.manual_seed(M)
+    d, ff = 256, 2048
+    y0 = torch.randn(M, d, device="cuda") * 2
+    g, b = torch.rand(d, device="cuda") + 0.5, torch.randn(d, device="cuda") * 0.1
+    W1, b1 = _bf(torch.randn(ff, d, device="cuda") / 16), torch.randn(ff, device="cuda") * 0.1
+    W2, b2 = _bf(torch.randn(d, ff, device="cuda") / 45), torch.randn(d, device="cuda") * 0.1
+    outs = []
+    for _ in range(2):
+        y = y0.clone()
+        native.check(lib.retr_op_decode_ffn(y.data_ptr(), g.data_ptr(), b.data_ptr(), 1e-5, W1.data_ptr(), b1.data_ptr(),
+                                            W2.data_ptr(), b2.data_ptr(), M, ff, native.stream_ptr()))
+        outs.append(y)
+    assert torch.equal(outs[0], outs[1])
+    a = _bf(F.layer_norm(y0, (d,), g, b, 1e-5)).float()
+    h = _bf(torch.relu(a @ W1.float().t() + b1)).float()
+    ref = y0 + h @ W2.float().t() + b2
+    assert (outs[0] - ref).abs().max().item() < 2e-3 * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("M,with_rowbias", [(2, True), (32, False), (45, True), (128, True)])
+def test_decode_out_ln_proj_fused(M, with_rowbias):
+    """y <- y + Wo att + bo, q = Wq LN(y) + rowbias[*row] (models/transformer_modules.py:58-83, pre-norm)."""
+    native, lib = _lib()
+    torch.manual_seed(100 + M)
+    d = 256
+    att = _bf(torch.randn(M, d, device="cuda"))
+    y0 = torch.randn(M, d, device="cuda") * 2
+    Wo, bo = _bf(torch.randn(d, d, device="cuda") / 16), torch.randn(d, device="cuda") * 0.1
+    Wq = _bf(torch.randn(d, d, device="cuda") / 16)
+    g, b = torch.rand(d, device="cuda") + 0.5, torch.randn(d, device="cuda") * 0.1
+    rb = torch.randn(7, d, device="cuda")
+    row = torch.tensor([5], dtype=torch.int32, device="cuda")
+    y = y0.clone()
+    q = torch.zeros(M, d, device="cuda", dtype=torch.bfloat16)
+    native.check(lib.retr_op_decode_out_ln_proj(att.data_ptr(), Wo.data_ptr(), bo.data_ptr(), y.data_ptr(), g.data_ptr(),
+                                                b.data_ptr(), 1e-5, Wq.data_ptr(), None,
+                                                rb.data_ptr() if with_rowbias else None,
+                                                row.data_ptr() if with_rowbias else None, q.data_ptr(), M,
+                                                native.stream_ptr()))
+    y_ref = y0 + att.float() @ Wo.float().t() + bo
+    assert (y - y_ref).abs().max().item() < 1e-4 * y_ref.abs().max().item()
+    a = _bf(F.layer_norm(y_ref, (d,), g, b, 1e-5)).float()
+    q_ref = a @ Wq.float().t() + (rb[5] if with_rowbias else 0.0)
+    assert (q.float() - q_ref).abs().max().item() < 2e-2 * q_ref.abs().max().item()
+
+
+def test_decode_cross_attention_compacted_equals_masked():
+    """Dropping the padded keys from the cache (key_compaction) is exact up to fp32 summation order: the kernel over
+    n_keys[m] dense rows against a float64 softmax over the unpadded keys of the full cache."""
+    native, lib = _lib()
+    torch.manual_seed(9)
+    M, H, dh, S = 6, 8, 32, 397
+    d = H * dh
+    q = _bf(torch.randn(M, d, device="cuda"))
+    K = _bf(torch.randn(M, H, S, dh, device="cuda"))
+    V = _bf(torch.randn(M, H, S, dh, device="cuda"))
+    pad = torch.rand(M, S, device="cuda") < 0.3
+    pad[0] = False                                   # one sample without padding
+    pad[1, 5:] = True                                # one with five keys
+    n_keys = (~pad).sum(1).to(torch.int32)
+    Kc, Vc = torch.zeros_like(K), torch.zeros_like(V)
+    for m in range(M):
+        idx = (~pad[m]).nonzero().squeeze(1)
+        Kc[m, :, :len(idx)] = K[m, :, idx]
+        Vc[m, :, :len(idx)] = V[m, :, idx]
+    out = torch.zeros(M, d, device="cuda", dtype=torch.bfloat16)
+    native.check(lib.retr_op_decode_cross_attention(q.data_ptr(), Kc.data_ptr(), Vc.data_ptr(), S, out.data_ptr(), M, H, d,
+                                                    n_keys.data_ptr(), native.stream_ptr()))
+    qh = q.double().view(M, H, 1, dh) / math.sqrt(dh)
+    s = (qh @ K.double().transpose(-1, -2)).masked_fill(pad[:, None, None, :], float("-inf"))
+    ref = (s.softmax(-1) @ V.double()).reshape(M, d).float()
+    assert bool(((out.float() - ref).abs() <= ref.abs() * 2 ** -8 + 2e-3).all())
