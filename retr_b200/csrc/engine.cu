@@ -452,6 +452,7 @@ void EngineT<T>::encode(int B, const float* t_img, const uint8_t* t_mask, const 
   CUDA_OK(cudaEventRecord(ev_[0], s));
   for (int set = 0; set < desc.n_images; ++set) {
     const float* img = set == 0 ? t_img : g_img;
+    if (set == 1 && ctx_wait_) CUDA_OK(cudaStreamWaitEvent(s, ctx_ready_, 0));   // generate_host: context copy in flight
     for (int64_t i0 = 0; i0 < B; i0 += chunk_) {
       const int64_t n = std::min<int64_t>(chunk_, B - i0);
       backbone(img + i0 * img_elems, n, feat_ + ((int64_t)set * B + i0) * g2 * cfeat, s);

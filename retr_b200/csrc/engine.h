@@ -52,6 +52,11 @@ class EngineBase {
   float *st_t_img = nullptr, *st_g_img = nullptr, *st_loc = nullptr;
   uint8_t *st_t_mask = nullptr, *st_g_mask = nullptr;
   int64_t* st_ids = nullptr;
+  // generate_host copies the context images on a second stream while the backbone works on the target images;
+  // encode() waits for `ctx_ready_` before the second image set when `ctx_wait_` is set
+  cudaStream_t copy_stream_ = nullptr;
+  cudaEvent_t ctx_ready_ = nullptr, copy_fork_ = nullptr;
+  bool ctx_wait_ = false;
   cudaEvent_t ev_[4] = {nullptr, nullptr, nullptr, nullptr};
   bool finalized_ = false;
   int cur_B_ = 0;         // batch of the last encode

@@ -24,6 +24,9 @@ EngineBase::~EngineBase() {
   for (void* p : owned_) cudaFree(p);
   for (auto& kv : raw_) cudaFree(kv.second.dev);
   for (auto& e : ev_) if (e) cudaEventDestroy(e);
+  if (ctx_ready_) cudaEventDestroy(ctx_ready_);
+  if (copy_fork_) cudaEventDestroy(copy_fork_);
+  if (copy_stream_) cudaStreamDestroy(copy_stream_);
 }
 
 void* EngineBase::dalloc(size_t bytes) {
@@ -72,16 +75,33 @@ void EngineBase::generate_host(int B, const float* t_img, const uint8_t* t_mask,
   // eval_utils/decode.py:62 `samples.to(device)`
   CUDA_OK(cudaMemcpyAsync(st_t_img, t_img, B * 3 * hw * 4, cudaMemcpyHostToDevice, s));
   CUDA_OK(cudaMemcpyAsync(st_t_mask, t_mask, B * hw, cudaMemcpyHostToDevice, s));
-  if (desc.n_images == 2) {
-    RETR_CHECK(g_img && g_mask, "context images required");
-    CUDA_OK(cudaMemcpyAsync(st_g_img, g_img, B * 3 * hw * 4, cudaMemcpyHostToDevice, s));
-    CUDA_OK(cudaMemcpyAsync(st_g_mask, g_mask, B * hw, cudaMemcpyHostToDevice, s));
-  }
   if (desc.n_loc > 0) {
     RETR_CHECK(loc, "location features required");
     CUDA_OK(cudaMemcpyAsync(st_loc, loc, (int64_t)B * desc.n_loc * 4, cudaMemcpyHostToDevice, s));
   }
-  encode(B, st_t_img, st_t_mask, st_g_img, st_g_mask, st_loc, s);
+  if (desc.n_images == 2) {
+    // the context images travel on a second stream, behind the target images on the copy engine, while the backbone
+    // already runs on the target images; encode() waits for them before the second image set
+    RETR_CHECK(g_img && g_mask, "context images required");
+    if (!copy_stream_) {
+      CUDA_OK(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
+      CUDA_OK(cudaEventCreateWithFlags(&ctx_ready_, cudaEventDisableTiming));
+      CUDA_OK(cudaEventCreateWithFlags(&copy_fork_, cudaEventDisableTiming));
+    }
+    CUDA_OK(cudaEventRecord(copy_fork_, s));                 // after the target copies and whatever preceded this call
+    CUDA_OK(cudaStreamWaitEvent(copy_stream_, copy_fork_, 0));
+    CUDA_OK(cudaMemcpyAsync(st_g_img, g_img, B * 3 * hw * 4, cudaMemcpyHostToDevice, copy_stream_));
+    CUDA_OK(cudaMemcpyAsync(st_g_mask, g_mask, B * hw, cudaMemcpyHostToDevice, copy_stream_));
+    CUDA_OK(cudaEventRecord(ctx_ready_, copy_stream_));
+    ctx_wait_ = true;
+  }
+  try {
+    encode(B, st_t_img, st_t_mask, st_g_img, st_g_mask, st_loc, s);
+  } catch (...) {
+    ctx_wait_ = false;
+    throw;
+  }
+  ctx_wait_ = false;
   RETR_CHECK(max_len <= desc.max_pos, "max_len exceeds max_position_embeddings");
   decode_greedy(bos, eos, max_len, st_ids, steps_host, s);
   CUDA_OK(cudaMemcpyAsync(out_ids, st_ids, (int64_t)B * max_len * 8, cudaMemcpyDeviceToHost, s));
