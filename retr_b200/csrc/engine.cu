@@ -699,7 +699,8 @@ void EngineT<T>::decode_rows_fused(int r0, int n, int group, int max_len, cudaSt
   }
   dgemm(mlp_[0], nullptr, y, dec_norm_g_, dec_norm_b_, m1, false, n, nullptr, 1, nullptr, 1, s);
   dgemm(mlp_[1], m1, nullptr, nullptr, nullptr, m2, false, n, nullptr, 1, nullptr, 1, s);
-  GemmParams p = lin(mlp_[2], m2, n, nullptr); p.argmax_out = argmax_keys_ + r0; gemm<T>(p, s);   // logits never reach HBM
+  GemmParams p = lin(mlp_[2], m2, n, nullptr); p.argmax_out = argmax_keys_ + r0; p.pdl = false;
+  gemm<T>(p, s);                                                   // logits never reach HBM
 }
 
 template <typename T>

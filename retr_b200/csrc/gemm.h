@@ -39,6 +39,8 @@ struct GemmParams {
   // Weight-gradient shape (small M x N, very long K): split the contraction over split_k CTAs per output
   // tile (0 = choose from the SM count), fp32 partial tiles in split_ws ([split_k*M, N] floats), summed into C
   // (C += sum when accumulate).  Requires a plain fp32 C with ldc == N and no epilogue operands.
+  bool pdl = true;             // programmatic dependent launch (off where a parked 148-CTA grid would block parallel
+                               // graph branches: the vocabulary head of the decode step)
   int split_k = 1;
   float* split_ws = nullptr;
   int64_t split_ws_floats = 0;

@@ -337,6 +337,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   __syncthreads();
   ptx::tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_holder;
+  // Programmatic dependent launch: the next kernel's CTAs may take this SM as soon as this CTA leaves and run their
+  // set-up (barriers, TMEM allocation, descriptor prefetch) under the tail of this grid; everything that touches
+  // global memory waits for the previous grid here (operands may be its output — activations, refreshed weights).
+  pdl_launch_dependents();
+  pdl_wait();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -566,12 +571,16 @@ CUtensorMap make_tmap_2d(const void* base, int64_t rows, int64_t cols, int64_t l
 
 template <int BN, bool GATHER>
 void launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const CUtensorMap& tmR,
-            KArgs& ka, int grid, cudaStream_t stream) {
+            KArgs& ka, int grid, cudaStream_t stream, bool pdl) {
   ka.stages = Cfg<BN>::stages_for(ka.tma_epi, ka.res_tma, GATHER);
   RETR_CHECK(ka.stages >= (GATHER ? 3 : 2), "not enough shared memory for the pipeline");
   const int smem = Cfg<BN>::fixed_bytes(ka.tma_epi, ka.res_tma, GATHER) + ka.stages * Cfg<BN>::STAGE_BYTES;
-  gemm_tcgen05_kernel<BN, GATHER><<<grid, 384, smem, stream>>>(tmA, tmB, tmC, tmR, ka);
-  LAUNCH_OK();
+  if (pdl) {
+    launch_pdl(gemm_tcgen05_kernel<BN, GATHER>, dim3((unsigned)grid), dim3(384), (size_t)smem, stream, tmA, tmB, tmC, tmR, ka);
+  } else {
+    gemm_tcgen05_kernel<BN, GATHER><<<grid, 384, smem, stream>>>(tmA, tmB, tmC, tmR, ka);
+    LAUNCH_OK();
+  }
 }
 
 }  // namespace
@@ -661,8 +670,8 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
   CUtensorMap tmC = ka.tma_epi ? make_tmap_2d(p.C, p.M, p.N, p.ldc, BM, p.out_fp32) : tmB;
   CUtensorMap tmR = ka.res_tma ? make_tmap_2d(ka.residual, p.M, p.N, ka.ldr, BM, ka.res_fp32 != 0) : tmB;
 #define RETR_LAUNCH(BN_)                                                   \
-  if (gather) launch<BN_, true>(tmA, tmB, tmC, tmR, ka, grid, stream);     \
-  else launch<BN_, false>(tmA, tmB, tmC, tmR, ka, grid, stream)
+  if (gather) launch<BN_, true>(tmA, tmB, tmC, tmR, ka, grid, stream, p.pdl);     \
+  else launch<BN_, false>(tmA, tmB, tmC, tmR, ka, grid, stream, p.pdl)
   switch (bn) {
     case 256: RETR_LAUNCH(256); break;
     case 128: RETR_LAUNCH(128); break;

@@ -1,0 +1,7 @@
+for i in 1 2 3; do
+python bench.py --steps 4 --warmup 3 --no-cpu-baseline 2>/dev/null | python -c "
+import sys,json
+for l in sys.stdin:
+    if l.startswith('{'):
+        d=json.loads(l); print(round(d['value']), round(d['e2e']['value']), d['phases_ms_per_step'])"
+done
