@@ -70,7 +70,10 @@ __device__ __forceinline__ void merge_state(float& m, float& l, float (&acc)[N],
 // each, conflict-free), online softmax per lane group, merged by shuffles and one smem pass.
 // (Persistent variants measured slower inside the decode graph on B200 at B=256 — a CTA-wide ring with one producer
 // warp: 68-74 ms decode vs 62.5; one warp per unit with private rings: 64.5-83 — each needs ~100 KB per SM in flight
-// AND several units' dependent load->compute chains overlapped, which is exactly what 4 resident one-unit CTAs give.)
+// AND several units' dependent load->compute chains overlapped, which is exactly what 4 resident one-unit CTAs give.
+// Also measured and dropped: the eight head-CTAs of a sample as a cluster that finishes the out-projection + residual
+// itself (DSMEM exchange of the 256 partial sums) — removes a launch but costs +6.7 ms per decode: gang scheduling and
+// every CTA held until the slowest head of its sample arrives.)
 template <typename T, int DH>
 __global__ void __launch_bounds__(DA_WARPS * 32)
 decode_attention_kernel(const T* __restrict__ q, int64_t ldq, const T* __restrict__ new_kv, int64_t ld_new,
