@@ -84,7 +84,6 @@ struct FfSmem {
   bf16 Hs[FF_BM][FF_LDS];                    // relu(W1[r] LN(y) + b1[r])
   bf16 Wr[FF_NST][FF_PANEL][FF_LDS];         // weight panel ring
   float Ps[8][FF_BM][FF_D / 8];              // partials of THIS CTA's 32 output columns, one slot per source CTA
-  float red[4][FF_BM][16];                   // K-half exchange between the two warp groups
 };
 
 __global__ void __launch_bounds__(FF_THREADS) ffn_fused_kernel(const FfnFusedParams p) {
@@ -119,10 +118,11 @@ __global__ void __launch_bounds__(FF_THREADS) ffn_fused_kernel(const FfnFusedPar
   }
   // epilogue operands that do not depend on the previous kernel: this thread's bias values of the four W1 panels
   const int g = lane >> 2, c4 = lane & 3;
-  // warp tile: all 32 rows x 16 columns (cg) of the panel output over one half of K (kh); the A fragments of that
-  // K half stay in registers for the four panels of a GEMM, so a panel costs one pass over its own 32 KB and nothing
-  // else — with 16 x 16 tiles re-reading A the loop was bound by shared-memory bandwidth (1.1 us per panel).
-  const int kh = warp >> 2, cg = warp & 3, wc = cg * 16;
+  // warp tile: 16 rows (mt) x 16 columns (cg) of the panel output over all of K.  The A fragments (16 k-steps, 64
+  // registers) stay in registers for the four panels of a GEMM, so a panel costs one pass over its own 32 KB of shared
+  // memory and ONE block barrier — re-reading A per panel was shared-memory-bandwidth bound (1.1 us per panel), and
+  // splitting K over two warp groups needed a second barrier and an exchange buffer per panel.
+  const int mt = warp & 1, cg = warp >> 1, wc = cg * 16;
   float b1r[4][2][2];
 #pragma unroll
   for (int pi = 0; pi < 4; ++pi)
@@ -184,85 +184,64 @@ __global__ void __launch_bounds__(FF_THREADS) ffn_fused_kernel(const FfnFusedPar
     }
   }
 
-  uint32_t af[2][8][4];
+  uint32_t af[16][4];
 #pragma unroll 1
   for (int pi = 0; pi < FF_PANELS; ++pi) {
     const int buf = pi % FF_NST;
-    asm volatile("cp.async.wait_group %0;" ::"n"(FF_NST - 1) : "memory");
-    __syncthreads();                                                // panel pi landed; As / Hs complete
+    asm volatile("cp.async.wait_group %0;" ::"n"(FF_NST - 2) : "memory");
+    __syncthreads();                      // panel pi landed; everyone is done with panel pi-1 (slot free, Hs written)
+    if (pi >= 1 && pi - 1 + FF_NST < FF_PANELS) load_panel(pi - 1 + FF_NST, (pi - 1) % FF_NST);
+    asm volatile("cp.async.commit_group;" ::: "memory");
     if (pi == 4) ff_cluster_wait();                                 // every CTA of the cluster is running (remote stores ahead)
-    if (pi == 0 || pi == 4) {                                       // (re)load this warp's A fragments
+    if (pi == 0 || pi == 4) {                                       // (re)load this warp's A fragments: 16 rows, all of K
       const bf16(*A)[FF_LDS] = pi < 4 ? sm.As : sm.Hs;
 #pragma unroll
-      for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-          ff_ldsm_x4((uint32_t)__cvta_generic_to_shared(&A[mt * 16 + (lane & 15)][kh * 128 + ks * 16 + (lane >> 4) * 8]),
-                     af[mt][ks][0], af[mt][ks][1], af[mt][ks][2], af[mt][ks][3]);
+      for (int ks = 0; ks < 16; ++ks)
+        ff_ldsm_x4((uint32_t)__cvta_generic_to_shared(&A[mt * 16 + (lane & 15)][ks * 16 + (lane >> 4) * 8]),
+                   af[ks][0], af[ks][1], af[ks][2], af[ks][3]);
     }
-    float acc[2][2][4];
+    // two accumulator sets over alternate k-steps: four independent mma chains of length 8
+    float acc[2][4], acc2[2][4];
 #pragma unroll
-    for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-      for (int nt = 0; nt < 2; ++nt) acc[mt][nt][0] = acc[mt][nt][1] = acc[mt][nt][2] = acc[mt][nt][3] = 0.f;
+    for (int nt = 0; nt < 2; ++nt) {
+      acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
+      acc2[nt][0] = acc2[nt][1] = acc2[nt][2] = acc2[nt][3] = 0.f;
+    }
     const uint32_t b_base = (uint32_t)__cvta_generic_to_shared(
-        &sm.Wr[buf][wc + (lane >> 4) * 8 + (lane & 7)][kh * 128 + ((lane >> 3) & 1) * 8]);
+        &sm.Wr[buf][wc + (lane >> 4) * 8 + (lane & 7)][((lane >> 3) & 1) * 8]);
 #pragma unroll
-    for (int ks = 0; ks < 8; ++ks) {
-      uint32_t b0, b1, b2, b3;
+    for (int ks = 0; ks < 16; ks += 2) {
+      uint32_t b0, b1, b2, b3, e0, e1, e2, e3;
       ff_ldsm_x4(b_base + ks * 32, b0, b1, b2, b3);
-      ff_mma(acc[0][0], af[0][ks], b0, b1);
-      ff_mma(acc[0][1], af[0][ks], b2, b3);
-      ff_mma(acc[1][0], af[1][ks], b0, b1);
-      ff_mma(acc[1][1], af[1][ks], b2, b3);
+      ff_ldsm_x4(b_base + (ks + 1) * 32, e0, e1, e2, e3);
+      ff_mma(acc[0], af[ks], b0, b1);
+      ff_mma(acc[1], af[ks], b2, b3);
+      ff_mma(acc2[0], af[ks + 1], e0, e1);
+      ff_mma(acc2[1], af[ks + 1], e2, e3);
     }
-    if (kh == 1) {
 #pragma unroll
-      for (int mt = 0; mt < 2; ++mt)
+    for (int nt = 0; nt < 2; ++nt)
 #pragma unroll
-        for (int nt = 0; nt < 2; ++nt) {
-          *reinterpret_cast<float2*>(&sm.red[cg][mt * 16 + g][nt * 8 + c4 * 2]) = make_float2(acc[mt][nt][0], acc[mt][nt][1]);
-          *reinterpret_cast<float2*>(&sm.red[cg][mt * 16 + g + 8][nt * 8 + c4 * 2]) = make_float2(acc[mt][nt][2], acc[mt][nt][3]);
-        }
-    }
-    __syncthreads();                                                // K halves exchanged; ring slot `buf` is free
-    if (pi + FF_NST < FF_PANELS) load_panel(pi + FF_NST, buf);
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    if (kh == 0) {
+      for (int k = 0; k < 4; ++k) acc[nt][k] += acc2[nt][k];
+    if (pi < 4) {
 #pragma unroll
-      for (int mt = 0; mt < 2; ++mt)
+      for (int nt = 0; nt < 2; ++nt) {
+        const int col = pi * FF_PANEL + wc + nt * 8 + c4 * 2;
+        const float bb0 = pi == 0 ? b1r[0][nt][0] : pi == 1 ? b1r[1][nt][0] : pi == 2 ? b1r[2][nt][0] : b1r[3][nt][0];
+        const float bb1 = pi == 0 ? b1r[0][nt][1] : pi == 1 ? b1r[1][nt][1] : pi == 2 ? b1r[2][nt][1] : b1r[3][nt][1];
+        *reinterpret_cast<__nv_bfloat162*>(&sm.Hs[mt * 16 + g][col]) =
+            __floats2bfloat162_rn(fmaxf(acc[nt][0] + bb0, 0.f), fmaxf(acc[nt][1] + bb1, 0.f));
+        *reinterpret_cast<__nv_bfloat162*>(&sm.Hs[mt * 16 + g + 8][col]) =
+            __floats2bfloat162_rn(fmaxf(acc[nt][2] + bb0, 0.f), fmaxf(acc[nt][3] + bb1, 0.f));
+      }
+    } else {
 #pragma unroll
-        for (int nt = 0; nt < 2; ++nt) {
-          const float2 lo = *reinterpret_cast<const float2*>(&sm.red[cg][mt * 16 + g][nt * 8 + c4 * 2]);
-          const float2 hi = *reinterpret_cast<const float2*>(&sm.red[cg][mt * 16 + g + 8][nt * 8 + c4 * 2]);
-          acc[mt][nt][0] += lo.x; acc[mt][nt][1] += lo.y; acc[mt][nt][2] += hi.x; acc[mt][nt][3] += hi.y;
-        }
-      if (pi < 4) {
-#pragma unroll
-        for (int nt = 0; nt < 2; ++nt) {
-          const int col = pi * FF_PANEL + wc + nt * 8 + c4 * 2;
-          const float bb0 = pi == 0 ? b1r[0][nt][0] : pi == 1 ? b1r[1][nt][0] : pi == 2 ? b1r[2][nt][0] : b1r[3][nt][0];
-          const float bb1 = pi == 0 ? b1r[0][nt][1] : pi == 1 ? b1r[1][nt][1] : pi == 2 ? b1r[2][nt][1] : b1r[3][nt][1];
-#pragma unroll
-          for (int mt = 0; mt < 2; ++mt) {
-            *reinterpret_cast<__nv_bfloat162*>(&sm.Hs[mt * 16 + g][col]) =
-                __floats2bfloat162_rn(fmaxf(acc[mt][nt][0] + bb0, 0.f), fmaxf(acc[mt][nt][1] + bb1, 0.f));
-            *reinterpret_cast<__nv_bfloat162*>(&sm.Hs[mt * 16 + g + 8][col]) =
-                __floats2bfloat162_rn(fmaxf(acc[mt][nt][2] + bb0, 0.f), fmaxf(acc[mt][nt][3] + bb1, 0.f));
-          }
-        }
-      } else {
-#pragma unroll
-        for (int nt = 0; nt < 2; ++nt) {
-          const int col = (pi - 4) * FF_PANEL + wc + nt * 8 + c4 * 2;  // output column; owner CTA = col / 32
-          const uint32_t owner = (uint32_t)(col >> 5);
-          const int lc = col & 31;
-#pragma unroll
-          for (int mt = 0; mt < 2; ++mt) {
-            ff_st_peer((uint32_t)__cvta_generic_to_shared(&sm.Ps[rank][mt * 16 + g][lc]), owner, make_float2(acc[mt][nt][0], acc[mt][nt][1]));
-            ff_st_peer((uint32_t)__cvta_generic_to_shared(&sm.Ps[rank][mt * 16 + g + 8][lc]), owner, make_float2(acc[mt][nt][2], acc[mt][nt][3]));
-          }
-        }
+      for (int nt = 0; nt < 2; ++nt) {
+        const int col = (pi - 4) * FF_PANEL + wc + nt * 8 + c4 * 2;  // output column; owner CTA = col / 32
+        const uint32_t owner = (uint32_t)(col >> 5);
+        const int lc = col & 31;
+        ff_st_peer((uint32_t)__cvta_generic_to_shared(&sm.Ps[rank][mt * 16 + g][lc]), owner, make_float2(acc[nt][0], acc[nt][1]));
+        ff_st_peer((uint32_t)__cvta_generic_to_shared(&sm.Ps[rank][mt * 16 + g + 8][lc]), owner, make_float2(acc[nt][2], acc[nt][3]));
       }
     }
 #ifdef RETR_TRACE
