@@ -36,6 +36,13 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
+// one MUFU.EX2 (exp2f adds a denormal-range rescale the softmax does not need: tiny probabilities flush to zero)
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 template <int DH>
 __global__ void __launch_bounds__(128) flash_attention_kernel(const AttnParams p) {
   constexpr int LDS = DH + 8;                       // padded row (elements): conflict-free ldmatrix
@@ -115,15 +122,19 @@ __global__ void __launch_bounds__(128) flash_attention_kernel(const AttnParams p
         mma_16816(s[2 * np + 1], qa[ks], b2, b3);
       }
     }
-    // masks + online softmax (base-2)
+    // masks + online softmax (base-2).  The 64 padding bytes of the tile become two ballot words once per warp; the
+    // per-score test is then a bit of a register (the kernel is issue-bound: one LDS.U8 + ISETP per score was 15 % of
+    // its instructions), and a tile without padding or causal cut skips the masking altogether.
     const int kbase = t * FK;
+    const unsigned dead_lo = __ballot_sync(0xffffffffu, Ms[buf][lane] != 0) >> (c4 * 2);
+    const unsigned dead_hi = __ballot_sync(0xffffffffu, Ms[buf][32 + lane] != 0) >> (c4 * 2);
     float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt) {
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
         const int kl = nt * 8 + c4 * 2 + e;
-        const bool dead = Ms[buf][kl];
+        const bool dead = ((nt < 4 ? dead_lo >> (nt * 8 + e) : dead_hi >> ((nt - 4) * 8 + e)) & 1u) != 0;
         const int j = kbase + kl;
         const bool d0 = dead || (p.causal && j > qrow0), d1 = dead || (p.causal && j > qrow0 + 8);
         s[nt][e] = d0 ? -INFINITY : s[nt][e] * sl2;
@@ -136,13 +147,13 @@ __global__ void __launch_bounds__(128) flash_attention_kernel(const AttnParams p
     mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
     const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
     const float mu0 = mn0 == -INFINITY ? 0.f : mn0, mu1 = mn1 == -INFINITY ? 0.f : mn1;
-    const float cr0 = exp2f(m0 - mu0), cr1 = exp2f(m1 - mu1);
+    const float cr0 = fast_exp2(m0 - mu0), cr1 = fast_exp2(m1 - mu1);
     m0 = mn0; m1 = mn1;
     float rs0 = 0.f, rs1 = 0.f;
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt) {
-      s[nt][0] = exp2f(s[nt][0] - mu0); s[nt][1] = exp2f(s[nt][1] - mu0);
-      s[nt][2] = exp2f(s[nt][2] - mu1); s[nt][3] = exp2f(s[nt][3] - mu1);
+      s[nt][0] = fast_exp2(s[nt][0] - mu0); s[nt][1] = fast_exp2(s[nt][1] - mu0);
+      s[nt][2] = fast_exp2(s[nt][2] - mu1); s[nt][3] = fast_exp2(s[nt][3] - mu1);
       rs0 += s[nt][0] + s[nt][1];
       rs1 += s[nt][2] + s[nt][3];
     }
