@@ -43,7 +43,7 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
-template <int DH>
+template <int DH, bool CAUSAL>
 __global__ void __launch_bounds__(128) flash_attention_kernel(const AttnParams p) {
   constexpr int LDS = DH + 8;                       // padded row (elements): conflict-free ldmatrix
   constexpr int KS = DH / 16;                       // k-steps of Q.K^T
@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(128) flash_attention_kernel(const AttnParams p
   const bf16* qg = static_cast<const bf16*>(p.q) + (int64_t)b * p.Lq * p.ldq + h * DH;
   const bf16* kg = static_cast<const bf16*>(p.k) + (int64_t)b * p.Lk * p.ldk + h * DH;
   const bf16* vg = static_cast<const bf16*>(p.v) + (int64_t)b * p.Lk * p.ldv + h * DH;
-  const int k_end = p.causal ? min(p.Lk, q0 + FQ) : p.Lk;
+  const int k_end = CAUSAL ? min(p.Lk, q0 + FQ) : p.Lk;
   const int n_tiles = (k_end + FK - 1) / FK;
 
   auto load_kv = [&](int t, int buf) {
@@ -136,9 +136,10 @@ __global__ void __launch_bounds__(128) flash_attention_kernel(const AttnParams p
         const int kl = nt * 8 + c4 * 2 + e;
         const bool dead = ((nt < 4 ? dead_lo >> (nt * 8 + e) : dead_hi >> ((nt - 4) * 8 + e)) & 1u) != 0;
         const int j = kbase + kl;
-        const bool d0 = dead || (p.causal && j > qrow0), d1 = dead || (p.causal && j > qrow0 + 8);
-        s[nt][e] = d0 ? -INFINITY : s[nt][e] * sl2;
-        s[nt][2 + e] = d1 ? -INFINITY : s[nt][2 + e] * sl2;
+        const bool d0 = dead || (CAUSAL && j > qrow0), d1 = dead || (CAUSAL && j > qrow0 + 8);
+        // scores stay unscaled; scale * log2(e) > 0 is folded into the exponent's FFMA below
+        s[nt][e] = d0 ? -INFINITY : s[nt][e];
+        s[nt][2 + e] = d1 ? -INFINITY : s[nt][2 + e];
         mx0 = fmaxf(mx0, s[nt][e]);
         mx1 = fmaxf(mx1, s[nt][2 + e]);
       }
@@ -147,13 +148,14 @@ __global__ void __launch_bounds__(128) flash_attention_kernel(const AttnParams p
     mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
     const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
     const float mu0 = mn0 == -INFINITY ? 0.f : mn0, mu1 = mn1 == -INFINITY ? 0.f : mn1;
-    const float cr0 = fast_exp2(m0 - mu0), cr1 = fast_exp2(m1 - mu1);
+    const float cr0 = fast_exp2((m0 - mu0) * sl2), cr1 = fast_exp2((m1 - mu1) * sl2);
+    const float ms0 = -mu0 * sl2, ms1 = -mu1 * sl2;
     m0 = mn0; m1 = mn1;
     float rs0 = 0.f, rs1 = 0.f;
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt) {
-      s[nt][0] = fast_exp2(s[nt][0] - mu0); s[nt][1] = fast_exp2(s[nt][1] - mu0);
-      s[nt][2] = fast_exp2(s[nt][2] - mu1); s[nt][3] = fast_exp2(s[nt][3] - mu1);
+      s[nt][0] = fast_exp2(fmaf(s[nt][0], sl2, ms0)); s[nt][1] = fast_exp2(fmaf(s[nt][1], sl2, ms0));
+      s[nt][2] = fast_exp2(fmaf(s[nt][2], sl2, ms1)); s[nt][3] = fast_exp2(fmaf(s[nt][3], sl2, ms1));
       rs0 += s[nt][0] + s[nt][1];
       rs1 += s[nt][2] + s[nt][3];
     }
@@ -199,8 +201,13 @@ __global__ void __launch_bounds__(128) flash_attention_kernel(const AttnParams p
 void flash_attention_bf16(const AttnParams& p, int dh, cudaStream_t s) {
   RETR_CHECK(p.ldq % 8 == 0 && p.ldk % 8 == 0 && p.ldv % 8 == 0 && p.ldo % 2 == 0, "attention pitches must be 16-byte multiples");
   dim3 grid((unsigned)cdiv(p.Lq, FQ), (unsigned)p.H, (unsigned)p.B);
-  if (dh == 32) flash_attention_kernel<32><<<grid, 128, 0, s>>>(p);
-  else flash_attention_kernel<64><<<grid, 128, 0, s>>>(p);
+  if (dh == 32) {
+    if (p.causal) flash_attention_kernel<32, true><<<grid, 128, 0, s>>>(p);
+    else flash_attention_kernel<32, false><<<grid, 128, 0, s>>>(p);
+  } else {
+    if (p.causal) flash_attention_kernel<64, true><<<grid, 128, 0, s>>>(p);
+    else flash_attention_kernel<64, false><<<grid, 128, 0, s>>>(p);
+  }
   LAUNCH_OK();
 }
 
