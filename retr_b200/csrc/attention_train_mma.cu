@@ -39,6 +39,12 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 __device__ __forceinline__ uint32_t sptr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+// one MUFU.EX2 (exp2f adds a denormal-range rescale softmax does not need: tiny probabilities flush to zero)
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 
 // rows [r0, r0+64) of a [*, ld] bf16 matrix (head slice of DH columns) -> smem tile [64][DH+8]; rows >= r_end zero
 template <int DH>
@@ -145,13 +151,16 @@ __global__ void __launch_bounds__(128) flash_train_fwd_kernel(const AttnTrainPar
     float s[8][4];
     mma_a_tileT<DH>(s, qa, Ks[buf], lane);
     const int kbase = t * TK;
+    // padding bytes of the tile as two ballot words (one LDS.U8 per score otherwise; the kernels are issue-bound)
+    const unsigned dead_lo = __ballot_sync(0xffffffffu, Ms[buf][lane] != 0) >> (c4 * 2);
+    const unsigned dead_hi = __ballot_sync(0xffffffffu, Ms[buf][32 + lane] != 0) >> (c4 * 2);
     float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt)
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
         const int kl = nt * 8 + c4 * 2 + e;
-        const bool dead = Ms[buf][kl];
+        const bool dead = ((nt < 4 ? dead_lo >> (nt * 8 + e) : dead_hi >> ((nt - 4) * 8 + e)) & 1u) != 0;
         const int j = kbase + kl;
         const bool d0 = dead || (p.causal && j > qrow0), d1 = dead || (p.causal && j > qrow0 + 8);
         s[nt][e] = d0 ? -INFINITY : s[nt][e] * sl2;
@@ -163,13 +172,13 @@ __global__ void __launch_bounds__(128) flash_train_fwd_kernel(const AttnTrainPar
     mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
     const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
     const float mu0 = mn0 == -INFINITY ? 0.f : mn0, mu1 = mn1 == -INFINITY ? 0.f : mn1;
-    const float cr0 = exp2f(m0 - mu0), cr1 = exp2f(m1 - mu1);
+    const float cr0 = fast_exp2(m0 - mu0), cr1 = fast_exp2(m1 - mu1);
     m0 = mn0; m1 = mn1;
     float rs0 = 0.f, rs1 = 0.f;
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt) {
-      s[nt][0] = exp2f(s[nt][0] - mu0); s[nt][1] = exp2f(s[nt][1] - mu0);
-      s[nt][2] = exp2f(s[nt][2] - mu1); s[nt][3] = exp2f(s[nt][3] - mu1);
+      s[nt][0] = fast_exp2(s[nt][0] - mu0); s[nt][1] = fast_exp2(s[nt][1] - mu0);
+      s[nt][2] = fast_exp2(s[nt][2] - mu1); s[nt][3] = fast_exp2(s[nt][3] - mu1);
       rs0 += s[nt][0] + s[nt][1];
       rs1 += s[nt][2] + s[nt][3];
     }
@@ -294,8 +303,8 @@ __global__ void __launch_bounds__(128) flash_train_bwd_dq_kernel(const AttnBwdPa
         const bool dead = Ms[buf][kl];
         const int j = kbase + kl;
         const bool d0 = dead || (p.causal && j > qrow0), d1 = dead || (p.causal && j > qrow0 + 8);
-        const float p0 = d0 ? 0.f : exp2f(s[nt][e] * sl2 - lse0);
-        const float p1 = d1 ? 0.f : exp2f(s[nt][2 + e] * sl2 - lse1);
+        const float p0 = d0 ? 0.f : fast_exp2(fmaf(s[nt][e], sl2, -lse0));
+        const float p1 = d1 ? 0.f : fast_exp2(fmaf(s[nt][2 + e], sl2, -lse1));
         s[nt][e] = p0 * (dp[nt][e] * ks0[e] - delta0);
         s[nt][2 + e] = p1 * (dp[nt][2 + e] * ks1[e] - delta1);
       }
@@ -392,8 +401,8 @@ __global__ void __launch_bounds__(128) flash_train_bwd_kv_kernel(const AttnBwdPa
         const int i = qbase + ql;
         const float lse = Ls[buf][ql], dl = Ds[buf][ql];
         const bool d0 = dead0 || (p.causal && krow0 > i), d1 = dead1 || (p.causal && krow0 + 8 > i);
-        const float p0 = d0 ? 0.f : exp2f(st[nt][e] * sl2 - lse);
-        const float p1 = d1 ? 0.f : exp2f(st[nt][2 + e] * sl2 - lse);
+        const float p0 = d0 ? 0.f : fast_exp2(fmaf(st[nt][e], sl2, -lse));
+        const float p1 = d1 ? 0.f : fast_exp2(fmaf(st[nt][2 + e], sl2, -lse));
         const float m0 = ms0[e], m1 = ms1[e];
         const float g0 = dpt[nt][e] * m0, g1 = dpt[nt][2 + e] * m1;
         st[nt][e] = p0 * m0;                              // (P o mask)^T  -> dV
