@@ -90,6 +90,16 @@ int retr_generate_host(retr_ctx* ctx, int32_t batch, const float* t_img_host,
                        int32_t eos, int32_t max_len, int64_t* out_ids_host,
                        int32_t* steps_run_host, void* stream);
 
+/* replaces: the one-batch-at-a-time `samples.to(device)` of the evaluation loop (engine.py:138-146,
+ * eval_utils/decode.py:62) with a double-buffered transfer: queues the H2D copies of the NEXT batch on
+ * the context's copy stream and returns at once.  The next retr_generate_host call given the same
+ * batch and host pointers consumes the staged copy (no second transfer, one backbone pass); any other
+ * call simply copies as before.  The host buffers must stay alive and unchanged until that
+ * retr_generate_host returns.  Call it between two retr_generate_host calls, never concurrently. */
+int retr_prefetch_host(retr_ctx* ctx, int32_t batch, const float* t_img_host,
+                       const uint8_t* t_mask_host, const float* g_img_host,
+                       const uint8_t* g_mask_host, const float* loc_host);
+
 /* ---- introspection (tests, bench) ------------------------------------------------------ */
 int     retr_encoder_tokens(const retr_ctx* ctx);           /* S */
 /* Copies of intermediate state as fp32: "memory" [B,S,d], "mask" (uint8 [B,S]),

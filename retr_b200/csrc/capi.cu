@@ -123,6 +123,14 @@ int retr_generate_host(retr_ctx* ctx, int32_t batch, const float* t_img_host, co
   API_END
 }
 
+int retr_prefetch_host(retr_ctx* ctx, int32_t batch, const float* t_img_host, const uint8_t* t_mask_host,
+                       const float* g_img_host, const uint8_t* g_mask_host, const float* loc_host) {
+  API_BEGIN
+  RETR_CHECK(ctx && t_img_host && t_mask_host, "null argument");
+  ctx->eng->prefetch_host(batch, t_img_host, t_mask_host, g_img_host, g_mask_host, loc_host);
+  API_END
+}
+
 int retr_encoder_tokens(const retr_ctx* ctx) { return ctx ? ctx->eng->S : -1; }
 
 int retr_read_state(retr_ctx* ctx, const char* what, void* dst, int64_t dst_bytes, void* stream) {

@@ -34,6 +34,10 @@ class EngineBase {
   void generate_host(int B, const float* t_img, const uint8_t* t_mask, const float* g_img, const uint8_t* g_mask,
                      const float* loc, int bos, int eos, int max_len, int64_t* out_ids, int* steps_host,
                      cudaStream_t s);
+  // Queue the host->device copies of the NEXT batch on the copy stream (second staging set); the next generate_host
+  // call with the same host pointers and batch consumes them instead of copying.
+  void prefetch_host(int B, const float* t_img, const uint8_t* t_mask, const float* g_img, const uint8_t* g_mask,
+                     const float* loc);
 
   retr_model_desc desc;
   int S = 0;              // encoder tokens per sample
@@ -48,10 +52,21 @@ class EngineBase {
   const RawWeight& raw(const std::string& name) const;
   std::map<std::string, RawWeight> raw_;
   std::vector<void*> owned_;
-  // host->device staging for generate_host
-  float *st_t_img = nullptr, *st_g_img = nullptr, *st_loc = nullptr;
-  uint8_t *st_t_mask = nullptr, *st_g_mask = nullptr;
+  // host->device staging for generate_host / prefetch_host: two sets, so a batch queued by prefetch_host can wait in
+  // one while the batch before it is decoded out of the other
+  struct Staging {
+    float *t_img = nullptr, *g_img = nullptr, *loc = nullptr;
+    uint8_t *t_mask = nullptr, *g_mask = nullptr;
+    // what prefetch_host staged here and nobody consumed yet
+    bool pending = false;
+    int B = 0;
+    const void *h_t_img = nullptr, *h_g_img = nullptr, *h_loc = nullptr;
+    cudaEvent_t ready = nullptr;
+  } st_[2];
+  int st_next_ = 0;        // set the next prefetch goes to
   int64_t* st_ids = nullptr;
+  void ensure_staging(int set);
+  void ensure_copy_stream();
   // generate_host copies the context images on a second stream while the backbone works on the target images;
   // encode() waits for `ctx_ready_` before the second image set when `ctx_wait_` is set
   cudaStream_t copy_stream_ = nullptr;

@@ -26,6 +26,7 @@ EngineBase::~EngineBase() {
   for (auto& e : ev_) if (e) cudaEventDestroy(e);
   if (ctx_ready_) cudaEventDestroy(ctx_ready_);
   if (copy_fork_) cudaEventDestroy(copy_fork_);
+  for (auto& st : st_) if (st.ready) cudaEventDestroy(st.ready);
   if (copy_stream_) cudaStreamDestroy(copy_stream_);
 }
 
@@ -56,53 +57,116 @@ void EngineBase::load_weight(const std::string& name, const float* data, const i
   raw_[name] = w;
 }
 
+void EngineBase::ensure_staging(int set) {
+  Staging& st = st_[set];
+  if (st.t_img) return;
+  const int64_t hw = (int64_t)desc.image_size * desc.image_size;
+  const int64_t mb = desc.max_batch;
+  st.t_img = static_cast<float*>(dalloc(mb * 3 * hw * 4));
+  st.t_mask = static_cast<uint8_t*>(dalloc(mb * hw));
+  if (desc.n_images == 2) {
+    st.g_img = static_cast<float*>(dalloc(mb * 3 * hw * 4));
+    st.g_mask = static_cast<uint8_t*>(dalloc(mb * hw));
+  }
+  if (desc.n_loc > 0) st.loc = static_cast<float*>(dalloc(mb * desc.n_loc * 4));
+  CUDA_OK(cudaEventCreateWithFlags(&st.ready, cudaEventDisableTiming));
+  if (!st_ids) st_ids = static_cast<int64_t*>(dalloc(mb * desc.max_pos * 8));
+}
+
+void EngineBase::ensure_copy_stream() {
+  if (copy_stream_) return;
+  CUDA_OK(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
+  CUDA_OK(cudaEventCreateWithFlags(&ctx_ready_, cudaEventDisableTiming));
+  CUDA_OK(cudaEventCreateWithFlags(&copy_fork_, cudaEventDisableTiming));
+}
+
+// The DataLoader-side overlap an eval loop gets from pinned memory + non_blocking copies (engine.py:138-146 moves one
+// batch at a time): the next batch crosses PCIe on the copy stream while the current one is being decoded.  The caller
+// keeps the host buffers alive and unchanged until the generate_host call that consumes them returns.
+void EngineBase::prefetch_host(int B, const float* t_img, const uint8_t* t_mask, const float* g_img,
+                               const uint8_t* g_mask, const float* loc) {
+  RETR_CHECK(B > 0 && B <= desc.max_batch, "batch exceeds max_batch");
+  RETR_CHECK(t_img && t_mask, "target images required");
+  const int64_t hw = (int64_t)desc.image_size * desc.image_size;
+  // generate_host synchronises its stream before returning, so no kernel still reads either set here; a set whose
+  // prefetch was never consumed is simply overwritten (copy-stream order keeps that safe)
+  const int set = st_next_;
+  st_next_ ^= 1;
+  ensure_staging(set);
+  ensure_copy_stream();
+  Staging& st = st_[set];
+  st.pending = false;
+  CUDA_OK(cudaMemcpyAsync(st.t_img, t_img, B * 3 * hw * 4, cudaMemcpyHostToDevice, copy_stream_));
+  CUDA_OK(cudaMemcpyAsync(st.t_mask, t_mask, B * hw, cudaMemcpyHostToDevice, copy_stream_));
+  if (desc.n_loc > 0) {
+    RETR_CHECK(loc, "location features required");
+    CUDA_OK(cudaMemcpyAsync(st.loc, loc, (int64_t)B * desc.n_loc * 4, cudaMemcpyHostToDevice, copy_stream_));
+  }
+  if (desc.n_images == 2) {
+    RETR_CHECK(g_img && g_mask, "context images required");
+    CUDA_OK(cudaMemcpyAsync(st.g_img, g_img, B * 3 * hw * 4, cudaMemcpyHostToDevice, copy_stream_));
+    CUDA_OK(cudaMemcpyAsync(st.g_mask, g_mask, B * hw, cudaMemcpyHostToDevice, copy_stream_));
+  }
+  CUDA_OK(cudaEventRecord(st.ready, copy_stream_));
+  st.pending = true;
+  st.B = B;
+  st.h_t_img = t_img;
+  st.h_g_img = g_img;
+  st.h_loc = loc;
+}
+
 void EngineBase::generate_host(int B, const float* t_img, const uint8_t* t_mask, const float* g_img,
                                const uint8_t* g_mask, const float* loc, int bos, int eos, int max_len,
                                int64_t* out_ids, int* steps_host, cudaStream_t s) {
   RETR_CHECK(B > 0 && B <= desc.max_batch, "batch exceeds max_batch");
-  const int64_t hw = (int64_t)desc.image_size * desc.image_size;
-  if (!st_t_img) {
-    const int64_t mb = desc.max_batch;
-    st_t_img = static_cast<float*>(dalloc(mb * 3 * hw * 4));
-    st_t_mask = static_cast<uint8_t*>(dalloc(mb * hw));
-    if (desc.n_images == 2) {
-      st_g_img = static_cast<float*>(dalloc(mb * 3 * hw * 4));
-      st_g_mask = static_cast<uint8_t*>(dalloc(mb * hw));
-    }
-    if (desc.n_loc > 0) st_loc = static_cast<float*>(dalloc(mb * desc.n_loc * 4));
-    st_ids = static_cast<int64_t*>(dalloc(mb * desc.max_pos * 8));
-  }
-  // eval_utils/decode.py:62 `samples.to(device)`
-  CUDA_OK(cudaMemcpyAsync(st_t_img, t_img, B * 3 * hw * 4, cudaMemcpyHostToDevice, s));
-  CUDA_OK(cudaMemcpyAsync(st_t_mask, t_mask, B * hw, cudaMemcpyHostToDevice, s));
-  if (desc.n_loc > 0) {
-    RETR_CHECK(loc, "location features required");
-    CUDA_OK(cudaMemcpyAsync(st_loc, loc, (int64_t)B * desc.n_loc * 4, cudaMemcpyHostToDevice, s));
-  }
-  if (desc.n_images == 2) {
-    // the context images travel on a second stream, behind the target images on the copy engine, while the backbone
-    // already runs on the target images; encode() waits for them before the second image set
-    RETR_CHECK(g_img && g_mask, "context images required");
-    if (!copy_stream_) {
-      CUDA_OK(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
-      CUDA_OK(cudaEventCreateWithFlags(&ctx_ready_, cudaEventDisableTiming));
-      CUDA_OK(cudaEventCreateWithFlags(&copy_fork_, cudaEventDisableTiming));
-    }
-    CUDA_OK(cudaEventRecord(copy_fork_, s));                 // after the target copies and whatever preceded this call
-    CUDA_OK(cudaStreamWaitEvent(copy_stream_, copy_fork_, 0));
-    CUDA_OK(cudaMemcpyAsync(st_g_img, g_img, B * 3 * hw * 4, cudaMemcpyHostToDevice, copy_stream_));
-    CUDA_OK(cudaMemcpyAsync(st_g_mask, g_mask, B * hw, cudaMemcpyHostToDevice, copy_stream_));
-    CUDA_OK(cudaEventRecord(ctx_ready_, copy_stream_));
-    ctx_wait_ = true;
-  }
-  try {
-    encode(B, st_t_img, st_t_mask, st_g_img, st_g_mask, st_loc, s);
-  } catch (...) {
-    ctx_wait_ = false;
-    throw;
-  }
-  ctx_wait_ = false;
   RETR_CHECK(max_len <= desc.max_pos, "max_len exceeds max_position_embeddings");
+  const int64_t hw = (int64_t)desc.image_size * desc.image_size;
+  int hit = -1;
+  for (int i = 0; i < 2; ++i)
+    if (st_[i].pending && st_[i].B == B && st_[i].h_t_img == t_img && st_[i].h_g_img == g_img && st_[i].h_loc == loc)
+      hit = i;
+  if (hit >= 0) {
+    // this batch was staged by prefetch_host: wait for its copy, then one backbone pass over both image sets
+    Staging& st = st_[hit];
+    st.pending = false;
+    CUDA_OK(cudaStreamWaitEvent(s, st.ready, 0));
+    encode(B, st.t_img, st.t_mask, st.g_img, st.g_mask, st.loc, s);
+  } else {
+    // a set no prefetched batch is waiting in (the older prefetch loses its slot if both are taken)
+    const int set = !st_[0].pending ? 0 : (!st_[1].pending ? 1 : st_next_);
+    ensure_staging(set);
+    Staging& st = st_[set];
+    if (st.pending) {                                        // its copy may still be in flight on the copy stream
+      st.pending = false;
+      CUDA_OK(cudaStreamWaitEvent(s, st.ready, 0));
+    }
+    // eval_utils/decode.py:62 `samples.to(device)`
+    CUDA_OK(cudaMemcpyAsync(st.t_img, t_img, B * 3 * hw * 4, cudaMemcpyHostToDevice, s));
+    CUDA_OK(cudaMemcpyAsync(st.t_mask, t_mask, B * hw, cudaMemcpyHostToDevice, s));
+    if (desc.n_loc > 0) {
+      RETR_CHECK(loc, "location features required");
+      CUDA_OK(cudaMemcpyAsync(st.loc, loc, (int64_t)B * desc.n_loc * 4, cudaMemcpyHostToDevice, s));
+    }
+    if (desc.n_images == 2) {
+      // the context images travel on a second stream, behind the target images on the copy engine, while the backbone
+      // already runs on the target images; encode() waits for them before the second image set
+      RETR_CHECK(g_img && g_mask, "context images required");
+      ensure_copy_stream();
+      CUDA_OK(cudaEventRecord(copy_fork_, s));               // after the target copies and whatever preceded this call
+      CUDA_OK(cudaStreamWaitEvent(copy_stream_, copy_fork_, 0));
+      CUDA_OK(cudaMemcpyAsync(st.g_img, g_img, B * 3 * hw * 4, cudaMemcpyHostToDevice, copy_stream_));
+      CUDA_OK(cudaMemcpyAsync(st.g_mask, g_mask, B * hw, cudaMemcpyHostToDevice, copy_stream_));
+      CUDA_OK(cudaEventRecord(ctx_ready_, copy_stream_));
+      ctx_wait_ = true;
+    }
+    try {
+      encode(B, st.t_img, st.t_mask, st.g_img, st.g_mask, st.loc, s);
+    } catch (...) {
+      ctx_wait_ = false;
+      throw;
+    }
+    ctx_wait_ = false;
+  }
   decode_greedy(bos, eos, max_len, st_ids, steps_host, s);
   CUDA_OK(cudaMemcpyAsync(out_ids, st_ids, (int64_t)B * max_len * 8, cudaMemcpyDeviceToHost, s));
   CUDA_OK(cudaStreamSynchronize(s));

@@ -50,6 +50,49 @@ def greedy(samples, model, max_len=20, device="auto", bos_token=1, eos_token=2):
     return _literal_greedy(samples, model, max_len, device, bos_token, eos_token)
 
 
+def greedy_stream(batches, model, max_len=20, bos_token=1, eos_token=2):
+    """``greedy`` over an ITERABLE of host sample tuples (what a DataLoader yields after ``pack_encoder_inputs``),
+    double-buffered: while batch i is being encoded and decoded, the images of batch i+1 already cross PCIe on the
+    engine's copy stream (``retr_prefetch_host``), which the reference's one-batch-at-a-time ``samples.to(device)``
+    (eval_utils/decode.py:62 inside engine.py:138-146) cannot do.  Yields one ``[B, max_len]`` int64 HOST tensor per
+    batch, equal to ``greedy(batch, model, ...).cpu()``."""
+    if not isinstance(model, _CaptionBase):
+        raise RuntimeError("greedy_stream needs a retr_b200 caption model (use greedy for a foreign callable)")
+
+    def stage(samples):
+        t, g, loc = model._split_samples(samples)
+        host = [t.tensors, t.mask.to(torch.uint8), None if g is None else g.tensors,
+                None if g is None else g.mask.to(torch.uint8), loc]
+        out = []
+        for x in host:
+            if x is not None:
+                x = x.float() if x.dtype not in (torch.uint8, torch.float32) else x
+                x = x.contiguous()
+                x = x if x.is_pinned() else x.pin_memory()
+            out.append(x)
+        return out
+
+    it = iter(batches)
+    try:
+        cur = stage(next(it))
+    except StopIteration:
+        return
+    eng = model.engine(cur[0].shape[0])
+    eng.prefetch_host(*cur)
+    while cur is not None:
+        try:
+            nxt = stage(next(it))
+        except StopIteration:
+            nxt = None
+        if nxt is not None:
+            if nxt[0].shape[0] > eng.max_batch:
+                raise RuntimeError("greedy_stream: a later batch is larger than the first; set model.max_batch")
+            eng.prefetch_host(*nxt)          # second staging set; crosses PCIe while `cur` is decoded
+        ids, _ = eng.generate_host(*cur, bos_token, eos_token, max_len)
+        yield ids
+        cur = nxt
+
+
 def prune_cap_ids(idx_seqs, clean=True, pad_token=0, bos_token=1, eos_token=2):
     """Cut each row after its first EOS; ``clean`` drops every pad/bos/eos id.
     reference eval_utils/decode.py:84-101."""

@@ -152,6 +152,19 @@ class Engine:
         self.batch = B
         return out, steps.value
 
+    def prefetch_host(self, t_img, t_mask, g_img, g_mask, loc):
+        """Queue the H2D copies of the NEXT batch (pinned host tensors) while the current one decodes; the
+        following generate_host call with these same tensors consumes the staged copy."""
+        B = t_img.shape[0]
+        for t in (t_img, t_mask, g_img, g_mask, loc):
+            if t is not None and (t.device.type != "cpu" or not t.is_contiguous()):
+                raise ValueError("prefetch_host takes contiguous host tensors")
+        with torch.cuda.device(self.device):
+            native.check(self.lib.retr_prefetch_host(
+                self.handle, B, native.ptr(t_img), native.ptr(t_mask), native.ptr(g_img), native.ptr(g_mask),
+                native.ptr(loc)))
+        self._keep_pf = (t_img, t_mask, g_img, g_mask, loc)
+
     def read_state(self, what):
         B, S, d = self.batch, self.S, self.d_model
         if what == "mask":

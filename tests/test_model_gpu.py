@@ -242,6 +242,45 @@ def test_generate_host_matches_device_path():
     assert eng.kernel_launches() > 0
 
 
+@pytest.mark.parametrize("kind", ["CaptionGlobalLoc", "CaptionLoc"])
+def test_greedy_stream_prefetch_equals_per_batch_greedy(kind):
+    """retr_prefetch_host double-buffers the H2D copies across batches; ids must equal greedy() batch by batch,
+    including a ragged last batch, a prefetch nobody consumes, and a plain generate_host in between."""
+    model, sd, cfg = gpu_model(kind, "bf16", calibrated=True)
+    model.max_batch = 3
+    batches, want = [], []
+    for shard, b in ((2, 3), (5, 3), (7, 2)):
+        _, enc_in = synthetic_samples(kind, b, shard=shard, train=False)
+        batches.append(samples_of(kind, enc_in, "cpu"))
+        with torch.no_grad():
+            want.append(decode.greedy(batches[-1], model, max_len=128, device="cuda", bos_token=101,
+                                      eos_token=102).cpu())
+    assert not torch.equal(want[0], want[1])
+    got = [ids.clone() for ids in decode.greedy_stream(batches, model, max_len=128, bos_token=101, eos_token=102)]
+    assert len(got) == 3
+    for g, w in zip(got, want):
+        assert torch.equal(g, w)
+    # a staged batch that is never consumed must not leak into a later, different call
+    eng = model.engine(3)
+
+    def pinned(samples):
+        t, g, loc = model._split_samples(samples)
+        xs = [t.tensors, t.mask.to(torch.uint8), None if g is None else g.tensors,
+              None if g is None else g.mask.to(torch.uint8), loc]
+        return [None if x is None else x.contiguous().pin_memory() for x in xs]
+    p0, p1 = pinned(batches[0]), pinned(batches[1])
+    eng.prefetch_host(*p0)
+    out, _ = eng.generate_host(*p1, 101, 102, 128)           # not the prefetched one: plain copy path
+    assert torch.equal(out, want[1])
+    out, _ = eng.generate_host(*p0, 101, 102, 128)           # still pending: consumed now
+    assert torch.equal(out, want[0])
+    eng.prefetch_host(*p0)
+    eng.prefetch_host(*p1)
+    eng.prefetch_host(*p0)                                   # overwrites the older slot
+    out, _ = eng.generate_host(*p1, 101, 102, 128)
+    assert torch.equal(out, want[1])
+
+
 def test_scaled_variant_d512_heads64():
     """BASELINE.json configs[4] geometry in miniature: hidden_dim 512 (head dim 64), a different Bottleneck
     ResNet, fewer layers so the CPU oracle stays fast — exercises the dh=64 attention kernels, the K=512
