@@ -115,11 +115,32 @@ def eval_model(model, data_loader, tokenizer, config, metrics_to_omit=(), print_
     bos_id = tokenizer.convert_tokens_to_ids(tokenizer.cls_token)
     eos_id = tokenizer.convert_tokens_to_ids(tokenizer.sep_token)
     use_global, use_loc = _flags(data_loader)
-    with torch.no_grad():
+    from collections import deque
+
+    from .eval_utils.decode import greedy_stream, idx2sents, prune_cap_ids
+    from .models.caption import _CaptionBase
+    max_len = config.max_position_embeddings
+    pending_ann = deque()
+
+    def packed():
         for ann_ids, *encoder_input, _caps, _cap_masks in data_loader:
-            samples = pack_encoder_inputs(encoder_input, use_global, use_loc)
-            hyps = greedy_decoding(samples, model, tokenizer, max_len=config.max_position_embeddings, clean=True,
-                                   pad_token=pad_id, bos_token=bos_id, eos_token=eos_id, device="auto")
+            pending_ann.append(ann_ids)
+            yield pack_encoder_inputs(encoder_input, use_global, use_loc)
+
+    def decoded():
+        if isinstance(model, _CaptionBase) and next(model.parameters()).device.type == "cuda":
+            # native model: the next batch's images cross PCIe while this one is decoded (retr_prefetch_host)
+            for ids in greedy_stream(packed(), model, max_len=max_len, bos_token=bos_id, eos_token=eos_id):
+                yield idx2sents(prune_cap_ids(ids.numpy().tolist(), clean=True, pad_token=pad_id, bos_token=bos_id,
+                                              eos_token=eos_id), tokenizer)
+        else:
+            for samples in packed():
+                yield greedy_decoding(samples, model, tokenizer, max_len=max_len, clean=True, pad_token=pad_id,
+                                      bos_token=bos_id, eos_token=eos_id, device="auto")
+
+    with torch.no_grad():
+        for hyps in decoded():
+            ann_ids = pending_ann.popleft()
             hypotheses += hyps
             ann_list = ann_ids.tolist() if hasattr(ann_ids, "tolist") else list(ann_ids)
             ids_hyps = [{"ann_id": i, "expression": h} for i, h in zip(ann_list, hyps)]

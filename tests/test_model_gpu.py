@@ -281,6 +281,34 @@ def test_greedy_stream_prefetch_equals_per_batch_greedy(kind):
     assert torch.equal(out, want[1])
 
 
+def test_eval_model_native_streams_batches_and_matches_greedy_decoding():
+    """engine.eval_model with a native model goes through greedy_stream; hypotheses must equal per-batch
+    greedy_decoding and stay aligned with their ann_ids (engine.py:138-158)."""
+    from types import SimpleNamespace
+
+    from retr_b200 import engine
+    from test_abi_and_host import _StubTok
+    kind = "CaptionGlobalLoc"
+    model, sd, cfg = gpu_model(kind, "bf16", calibrated=True)
+    model.max_batch = 3
+    tok = _StubTok()
+    batches, want = [], []
+    for k, (shard, b) in enumerate(((2, 3), (5, 2))):
+        _, enc_in = synthetic_samples(kind, b, shard=shard, train=False)
+        ann = torch.arange(b) + 10 * k
+        batches.append((ann, *enc_in, None, None))
+        with torch.no_grad():
+            want += decode.greedy_decoding(samples_of(kind, enc_in, "cpu"), model, tok, max_len=128, clean=True,
+                                           pad_token=0, bos_token=101, eos_token=102, device="cuda")
+
+    class Loader(list):
+        dataset = SimpleNamespace(annot=[(i, 0, "w5") for i in (0, 1, 2, 10, 11)], return_global_context=True,
+                                  return_location_features=True)
+    _, ids_hyps = engine.eval_model(model, Loader(batches), tok, SimpleNamespace(max_position_embeddings=128))
+    assert [h["ann_id"] for h in ids_hyps] == [0, 1, 2, 10, 11]
+    assert [h["expression"] for h in ids_hyps] == want
+
+
 def test_scaled_variant_d512_heads64():
     """BASELINE.json configs[4] geometry in miniature: hidden_dim 512 (head dim 64), a different Bottleneck
     ResNet, fewer layers so the CPU oracle stays fast — exercises the dh=64 attention kernels, the K=512
