@@ -100,6 +100,21 @@ int retr_prefetch_host(retr_ctx* ctx, int32_t batch, const float* t_img_host,
                        const uint8_t* t_mask_host, const float* g_img_host,
                        const uint8_t* g_mask_host, const float* loc_host);
 
+/* Two contexts in flight (eval_utils.decode.greedy_stream with contexts=2): the reference's eval loop
+ * (engine.py:138-146) handles one batch at a time; here the NEXT batch's copies, backbone and encoder
+ * (tensor-core bound) run on one context while the CURRENT batch's decode loop (latency / HBM bound) runs
+ * on another, each on its own stream.  retr_encode_host is retr_generate_host up to and including the
+ * encoder and returns at once; retr_decode_host runs the greedy loop of the batch last encoded on this
+ * context (eval_utils/decode.py:64-81) and returns when the ids are in out_ids_host.
+ * retr_set_encode_cta_cap bounds the persistent GEMM grids of the encode phase to `ctas` SMs (0 = all)
+ * so the decode kernels of the other context always find free SMs. */
+int retr_encode_host(retr_ctx* ctx, int32_t batch, const float* t_img_host, const uint8_t* t_mask_host,
+                     const float* g_img_host, const uint8_t* g_mask_host, const float* loc_host,
+                     void* stream);
+int retr_decode_host(retr_ctx* ctx, int32_t bos, int32_t eos, int32_t max_len, int64_t* out_ids_host,
+                     int32_t* steps_run_host, void* stream);
+int retr_set_encode_cta_cap(retr_ctx* ctx, int32_t ctas);
+
 /* ---- introspection (tests, bench) ------------------------------------------------------ */
 int     retr_encoder_tokens(const retr_ctx* ctx);           /* S */
 /* Copies of intermediate state as fp32: "memory" [B,S,d], "mask" (uint8 [B,S]),

@@ -131,6 +131,30 @@ int retr_prefetch_host(retr_ctx* ctx, int32_t batch, const float* t_img_host, co
   API_END
 }
 
+int retr_encode_host(retr_ctx* ctx, int32_t batch, const float* t_img_host, const uint8_t* t_mask_host,
+                     const float* g_img_host, const uint8_t* g_mask_host, const float* loc_host, void* stream) {
+  API_BEGIN
+  RETR_CHECK(ctx && t_img_host && t_mask_host, "null argument");
+  ctx->eng->encode_host(batch, t_img_host, t_mask_host, g_img_host, g_mask_host, loc_host,
+                        static_cast<cudaStream_t>(stream), false);
+  API_END
+}
+
+int retr_decode_host(retr_ctx* ctx, int32_t bos, int32_t eos, int32_t max_len, int64_t* out_ids_host,
+                     int32_t* steps_run_host, void* stream) {
+  API_BEGIN
+  RETR_CHECK(ctx && out_ids_host, "null argument");
+  ctx->eng->decode_host(bos, eos, max_len, out_ids_host, steps_run_host, static_cast<cudaStream_t>(stream));
+  API_END
+}
+
+int retr_set_encode_cta_cap(retr_ctx* ctx, int32_t ctas) {
+  API_BEGIN
+  RETR_CHECK(ctx && ctas >= 0, "bad argument");
+  ctx->eng->encode_cta_cap = ctas;
+  API_END
+}
+
 int retr_encoder_tokens(const retr_ctx* ctx) { return ctx ? ctx->eng->S : -1; }
 
 int retr_read_state(retr_ctx* ctx, const char* what, void* dst, int64_t dst_bytes, void* stream) {

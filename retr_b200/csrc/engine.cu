@@ -27,6 +27,16 @@ void ffn_fused_set_trace(unsigned long long* buf);
 #endif
 namespace {
 
+// The decode step is captured on high-priority streams (kernel nodes keep the priority of the stream they were
+// captured on): when a second context's encode phase shares the GPU, the short decode kernels are placed ahead of the
+// queued CTAs of its convolutions.  RETR_DECODE_PRIORITY=0 turns it off.
+static int decode_priority() {
+  int least = 0, greatest = 0;
+  CUDA_OK(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+  const char* e = getenv("RETR_DECODE_PRIORITY");
+  return (e && atoi(e) == 0) ? least : greatest;
+}
+
 template <typename T> void gemm(const GemmParams& p, cudaStream_t s);
 template <> void gemm<float>(const GemmParams& p, cudaStream_t s) { gemm_fp32(p, s); }
 template <> void gemm<bf16>(const GemmParams& p, cudaStream_t s) { gemm_bf16(p, s); }
@@ -369,7 +379,7 @@ void EngineT<T>::alloc_buffers() {
   CUDA_OK(cudaMemset(splitk_tickets_, 0, (size_t)groups_ * 1024 * 4));
   for (int g = 1; g < groups_; ++g) {
     cudaStream_t st; cudaEvent_t ev;
-    CUDA_OK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    CUDA_OK(cudaStreamCreateWithPriority(&st, cudaStreamNonBlocking, decode_priority()));
     CUDA_OK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     gstreams_.push_back(st); gjoin_.push_back(ev);
   }
@@ -453,6 +463,7 @@ void EngineT<T>::encode(int B, const float* t_img, const uint8_t* t_mask, const 
   const long long l0 = g_launches;
   const int d = desc.d_model, g2 = grid_hw * grid_hw, Hi = desc.image_size;
   const int64_t cfeat = blocks_.back().c3.cout, img_elems = 3LL * Hi * Hi;
+  struct CapGuard { explicit CapGuard(int c) { gemm_set_cta_cap(c); } ~CapGuard() { gemm_set_cta_cap(0); } } cap_guard(encode_cta_cap);
   CUDA_OK(cudaEventRecord(ev_[0], s));
   // Per-launch ramp and tail cost ~18 us x 104 convs per pass, so both image sets go through the backbone in ONE pass
   // when they are already on the device (measured 22.5 -> 20.7 ms at B = 256); generate_host keeps two passes so the
@@ -753,7 +764,7 @@ void EngineT<T>::decode_greedy(int bos, int eos, int max_len, int64_t* out_ids, 
       const long long c0 = g_launches;
       // capture on a private stream: the caller's stream may be the legacy default stream,
       // which cannot be captured; nothing executes during capture, so ordering is unaffected
-      if (!capture_stream_) CUDA_OK(cudaStreamCreateWithFlags(&capture_stream_, cudaStreamNonBlocking));
+      if (!capture_stream_) CUDA_OK(cudaStreamCreateWithPriority(&capture_stream_, cudaStreamNonBlocking, decode_priority()));
       CUDA_OK(cudaStreamBeginCapture(capture_stream_, cudaStreamCaptureModeThreadLocal));
       try {
         decode_step(B, eos, max_len, capture_stream_);

@@ -34,6 +34,11 @@ class EngineBase {
   void generate_host(int B, const float* t_img, const uint8_t* t_mask, const float* g_img, const uint8_t* g_mask,
                      const float* loc, int bos, int eos, int max_len, int64_t* out_ids, int* steps_host,
                      cudaStream_t s);
+  // The two halves of generate_host, for callers that keep TWO contexts in flight: encode_host is asynchronous
+  // (copies + backbone + encoder queued on `s`), decode_host blocks until the ids are in `out_ids`.
+  void encode_host(int B, const float* t_img, const uint8_t* t_mask, const float* g_img, const uint8_t* g_mask,
+                   const float* loc, cudaStream_t s, bool split_context_copy);
+  void decode_host(int bos, int eos, int max_len, int64_t* out_ids, int* steps_host, cudaStream_t s);
   // Queue the host->device copies of the NEXT batch on the copy stream (second staging set); the next generate_host
   // call with the same host pointers and batch consumes them instead of copying.
   void prefetch_host(int B, const float* t_img, const uint8_t* t_mask, const float* g_img, const uint8_t* g_mask,
@@ -46,6 +51,9 @@ class EngineBase {
   long long launches = 0;
   float phase_ms[3] = {0, 0, 0};
   float* att_enc_capture = nullptr;
+  // > 0: persistent GEMM grids of encode() use at most this many CTAs (SMs), leaving the rest to the decode loop
+  // of another context running at the same time (retr_set_encode_cta_cap)
+  int encode_cta_cap = 0;
 
  protected:
   void* dalloc(size_t bytes);

@@ -115,11 +115,13 @@ void EngineBase::prefetch_host(int B, const float* t_img, const uint8_t* t_mask,
   st.h_loc = loc;
 }
 
-void EngineBase::generate_host(int B, const float* t_img, const uint8_t* t_mask, const float* g_img,
-                               const uint8_t* g_mask, const float* loc, int bos, int eos, int max_len,
-                               int64_t* out_ids, int* steps_host, cudaStream_t s) {
+// Host buffers -> device staging -> encode(), all asynchronous on `s`.  `split_context_copy`: the context images travel
+// on the copy stream behind the target images while the backbone already runs on the target images (two backbone
+// passes; the serial generate_host path).  Without it everything is copied on `s` and both image sets go through the
+// backbone in one pass (the pipelined path: the copies overlap ANOTHER context's decode loop instead).
+void EngineBase::encode_host(int B, const float* t_img, const uint8_t* t_mask, const float* g_img,
+                             const uint8_t* g_mask, const float* loc, cudaStream_t s, bool split_context_copy) {
   RETR_CHECK(B > 0 && B <= desc.max_batch, "batch exceeds max_batch");
-  RETR_CHECK(max_len <= desc.max_pos, "max_len exceeds max_position_embeddings");
   const int64_t hw = (int64_t)desc.image_size * desc.image_size;
   int hit = -1;
   for (int i = 0; i < 2; ++i)
@@ -131,26 +133,26 @@ void EngineBase::generate_host(int B, const float* t_img, const uint8_t* t_mask,
     st.pending = false;
     CUDA_OK(cudaStreamWaitEvent(s, st.ready, 0));
     encode(B, st.t_img, st.t_mask, st.g_img, st.g_mask, st.loc, s);
-  } else {
-    // a set no prefetched batch is waiting in (the older prefetch loses its slot if both are taken)
-    const int set = !st_[0].pending ? 0 : (!st_[1].pending ? 1 : st_next_);
-    ensure_staging(set);
-    Staging& st = st_[set];
-    if (st.pending) {                                        // its copy may still be in flight on the copy stream
-      st.pending = false;
-      CUDA_OK(cudaStreamWaitEvent(s, st.ready, 0));
-    }
-    // eval_utils/decode.py:62 `samples.to(device)`
-    CUDA_OK(cudaMemcpyAsync(st.t_img, t_img, B * 3 * hw * 4, cudaMemcpyHostToDevice, s));
-    CUDA_OK(cudaMemcpyAsync(st.t_mask, t_mask, B * hw, cudaMemcpyHostToDevice, s));
-    if (desc.n_loc > 0) {
-      RETR_CHECK(loc, "location features required");
-      CUDA_OK(cudaMemcpyAsync(st.loc, loc, (int64_t)B * desc.n_loc * 4, cudaMemcpyHostToDevice, s));
-    }
-    if (desc.n_images == 2) {
-      // the context images travel on a second stream, behind the target images on the copy engine, while the backbone
-      // already runs on the target images; encode() waits for them before the second image set
-      RETR_CHECK(g_img && g_mask, "context images required");
+    return;
+  }
+  // a set no prefetched batch is waiting in (the older prefetch loses its slot if both are taken)
+  const int set = !st_[0].pending ? 0 : (!st_[1].pending ? 1 : st_next_);
+  ensure_staging(set);
+  Staging& st = st_[set];
+  if (st.pending) {                                        // its copy may still be in flight on the copy stream
+    st.pending = false;
+    CUDA_OK(cudaStreamWaitEvent(s, st.ready, 0));
+  }
+  // eval_utils/decode.py:62 `samples.to(device)`
+  CUDA_OK(cudaMemcpyAsync(st.t_img, t_img, B * 3 * hw * 4, cudaMemcpyHostToDevice, s));
+  CUDA_OK(cudaMemcpyAsync(st.t_mask, t_mask, B * hw, cudaMemcpyHostToDevice, s));
+  if (desc.n_loc > 0) {
+    RETR_CHECK(loc, "location features required");
+    CUDA_OK(cudaMemcpyAsync(st.loc, loc, (int64_t)B * desc.n_loc * 4, cudaMemcpyHostToDevice, s));
+  }
+  if (desc.n_images == 2) {
+    RETR_CHECK(g_img && g_mask, "context images required");
+    if (split_context_copy) {
       ensure_copy_stream();
       CUDA_OK(cudaEventRecord(copy_fork_, s));               // after the target copies and whatever preceded this call
       CUDA_OK(cudaStreamWaitEvent(copy_stream_, copy_fork_, 0));
@@ -158,18 +160,36 @@ void EngineBase::generate_host(int B, const float* t_img, const uint8_t* t_mask,
       CUDA_OK(cudaMemcpyAsync(st.g_mask, g_mask, B * hw, cudaMemcpyHostToDevice, copy_stream_));
       CUDA_OK(cudaEventRecord(ctx_ready_, copy_stream_));
       ctx_wait_ = true;
+    } else {
+      CUDA_OK(cudaMemcpyAsync(st.g_img, g_img, B * 3 * hw * 4, cudaMemcpyHostToDevice, s));
+      CUDA_OK(cudaMemcpyAsync(st.g_mask, g_mask, B * hw, cudaMemcpyHostToDevice, s));
     }
-    try {
-      encode(B, st.t_img, st.t_mask, st.g_img, st.g_mask, st.loc, s);
-    } catch (...) {
-      ctx_wait_ = false;
-      throw;
-    }
-    ctx_wait_ = false;
   }
+  try {
+    encode(B, st.t_img, st.t_mask, st.g_img, st.g_mask, st.loc, s);
+  } catch (...) {
+    ctx_wait_ = false;
+    throw;
+  }
+  ctx_wait_ = false;
+}
+
+// Greedy loop over the batch of the last encode / encode_host, ids back to the host buffer; returns when they are there.
+void EngineBase::decode_host(int bos, int eos, int max_len, int64_t* out_ids, int* steps_host, cudaStream_t s) {
+  RETR_CHECK(max_len <= desc.max_pos, "max_len exceeds max_position_embeddings");
+  RETR_CHECK(cur_B_ > 0, "decode_host: nothing encoded");
+  ensure_staging(0);
   decode_greedy(bos, eos, max_len, st_ids, steps_host, s);
-  CUDA_OK(cudaMemcpyAsync(out_ids, st_ids, (int64_t)B * max_len * 8, cudaMemcpyDeviceToHost, s));
+  CUDA_OK(cudaMemcpyAsync(out_ids, st_ids, (int64_t)cur_B_ * max_len * 8, cudaMemcpyDeviceToHost, s));
   CUDA_OK(cudaStreamSynchronize(s));
+}
+
+void EngineBase::generate_host(int B, const float* t_img, const uint8_t* t_mask, const float* g_img,
+                               const uint8_t* g_mask, const float* loc, int bos, int eos, int max_len,
+                               int64_t* out_ids, int* steps_host, cudaStream_t s) {
+  RETR_CHECK(max_len <= desc.max_pos, "max_len exceeds max_position_embeddings");
+  encode_host(B, t_img, t_mask, g_img, g_mask, loc, s, true);
+  decode_host(bos, eos, max_len, out_ids, steps_host, s);
 }
 
 }  // namespace retr

@@ -50,5 +50,7 @@ struct GemmParams {
 void gemm_fp32(const GemmParams& p, cudaStream_t stream);   // gemm_simt.cu  (A, W fp32)
 void gemm_bf16(const GemmParams& p, cudaStream_t stream);   // gemm_sm100.cu (A, W bf16, tcgen05)
 int  sm_count();
+// Per-thread cap on the persistent grid of gemm_bf16 (0 = one CTA per SM); set around a phase that shares the GPU.
+void gemm_set_cta_cap(int ctas);
 
 }  // namespace retr

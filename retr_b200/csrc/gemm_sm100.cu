@@ -283,7 +283,12 @@ __device__ __forceinline__ void epilogue_chunk_staged(const KArgs& a, uint32_t (
   }
 }
 
-template <int BN, bool GATHER>
+// AMODE: how the A tile reaches shared memory.  0: plain matrix, tiled TMA.  1: implicit-GEMM convolution, rows gathered
+// by cp.async (one thread per tile row; fallback, RETR_CONV_GATHER=1).  2: implicit-GEMM convolution, TMA im2col mode:
+// one bulk-tensor instruction per k-block loads 128 consecutive output pixels x 64 channels of one filter tap, zero-
+// filling the padding, straight into the 128B-swizzled layout — no gather threads, so the convolution keeps the plain
+// variant's two epilogue warp groups.
+template <int BN, int AMODE>
 __global__ void __launch_bounds__(384, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmR,
@@ -292,6 +297,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   // epilogue warp groups: a plain GEMM has two (warps 4-7 and 8-11) that take alternate 128-byte column
   // sub-tiles of the accumulator — tiles with K <= 1024 are epilogue-bound with one; the convolution variant
   // keeps one and uses warps 8-11 for the im2col gather (its K >= 576 tiles are main-loop bound).
+  constexpr bool GATHER = AMODE == 1;
+  constexpr bool IM2COL = AMODE == 2;
   constexpr int EG = GATHER ? 1 : 2;
   const int STAGES = a.stages;
   extern __shared__ uint8_t smem_raw[];
@@ -350,12 +357,28 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const TileCoord tc = tile_coord(a, tile);
         const int m_blk = tc.m_blk, n_blk = tc.n_blk;
+        int iw0 = 0, ih0 = 0, img0 = 0;
+        if (IM2COL) {
+          const int64_t m0 = (int64_t)m_blk * BM;
+          const int64_t t = m0 / a.OW;
+          iw0 = (int)(m0 - t * a.OW) * a.stride - a.pad;
+          ih0 = (int)(t % a.OH) * a.stride - a.pad;
+          img0 = (int)(t / a.OH);
+        }
         for (int kb = tc.kb0; kb < tc.kb1; ++kb) {
           ptx::mbar_wait(&empty[s], ph ^ 1);
           uint8_t* As = smem + s * C::STAGE_BYTES;
           uint8_t* Bs = As + A_TILE_BYTES;
           ptx::mbar_arrive_expect_tx(&full[s], C::B_TILE_BYTES + (GATHER ? 0 : A_TILE_BYTES));
-          if (!GATHER) ptx::tma_load_2d(As, &tmA, &full[s], kb * BK, m_blk * BM);
+          if (IM2COL) {
+            // k-block kb = (filter tap, 64-channel block); the tile's first output pixel fixes the base input pixel
+            const int tap = kb / a.cblocks, cb = kb - tap * a.cblocks;
+            const int fr = tap / a.kw, fs = tap - fr * a.kw;
+            ptx::tma_load_im2col_4d(As, &tmA, &full[s], cb * BK, iw0, ih0, img0, (uint16_t)(fs * a.dil),
+                                    (uint16_t)(fr * a.dil));
+          } else if (!GATHER) {
+            ptx::tma_load_2d(As, &tmA, &full[s], kb * BK, m_blk * BM);
+          }
           ptx::tma_load_2d(Bs, &tmB, &full[s], kb * BK, n_blk * BN);
           if (++s == (uint32_t)STAGES) { s = 0; ph ^= 1; }
         }
@@ -550,6 +573,18 @@ PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
   return fn;
 }
 
+PFN_cuTensorMapEncodeIm2col_v12000 get_encode_im2col_fn() {
+  static PFN_cuTensorMapEncodeIm2col_v12000 fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    CUDA_OK(cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &qres));
+    RETR_CHECK(p != nullptr && qres == cudaDriverEntryPointSuccess, "cuTensorMapEncodeIm2col not available");
+    fn = reinterpret_cast<PFN_cuTensorMapEncodeIm2col_v12000>(p);
+  }
+  return fn;
+}
+
 // 2-D tensor [rows, cols] with row pitch ld (elements); box {box_cols, box_rows} with 128-byte inner
 // extent, 128B swizzle.
 CUtensorMap make_tmap_2d(const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows, bool fp32 = false) {
@@ -569,16 +604,37 @@ CUtensorMap make_tmap_2d(const void* base, int64_t rows, int64_t cols, int64_t l
   return m;
 }
 
-template <int BN, bool GATHER>
+// NHWC activation [n, H, W, C] as an im2col tensor map (the A operand of a convolution): the bounding box of base
+// pixels starts at -pad and ends (k-1)*dil - pad short of the far edge, traversed with the convolution stride, so
+// "128 pixels from base pixel (iw0, ih0, img)" are 128 consecutive output pixels in (img, oh, ow) order; the filter tap
+// is the per-instruction offset.  Same corner rule as CUTLASS's fprop (conv/collective/detail.hpp).
+CUtensorMap make_tmap_im2col(const void* base, int64_t n, const ConvView& c) {
+  CUtensorMap m;
+  cuuint64_t dims[4] = {(cuuint64_t)c.C, (cuuint64_t)c.W, (cuuint64_t)c.H, (cuuint64_t)n};
+  cuuint64_t strides[3] = {(cuuint64_t)c.C * 2, (cuuint64_t)c.W * c.C * 2, (cuuint64_t)c.H * c.W * c.C * 2};
+  const int lo = -c.pad, hi_h = c.pad - (c.kh - 1) * c.dil, hi_w = c.pad - (c.kw - 1) * c.dil;
+  int lower[2] = {lo, lo}, upper[2] = {hi_w, hi_h};
+  cuuint32_t estr[4] = {1, (cuuint32_t)c.stride, (cuuint32_t)c.stride, 1};
+  RETR_CHECK((reinterpret_cast<uintptr_t>(base) & 15) == 0, "im2col operand must be 16-byte aligned");
+  CUresult r = get_encode_im2col_fn()(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides,
+                                      lower, upper, (cuuint32_t)BK, (cuuint32_t)BM, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  RETR_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeIm2col failed (" + std::to_string((int)r) + ")");
+  return m;
+}
+
+template <int BN, int AMODE>
 void launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const CUtensorMap& tmR,
             KArgs& ka, int grid, cudaStream_t stream, bool pdl) {
+  constexpr bool GATHER = AMODE == 1;
   ka.stages = Cfg<BN>::stages_for(ka.tma_epi, ka.res_tma, GATHER);
   RETR_CHECK(ka.stages >= (GATHER ? 3 : 2), "not enough shared memory for the pipeline");
   const int smem = Cfg<BN>::fixed_bytes(ka.tma_epi, ka.res_tma, GATHER) + ka.stages * Cfg<BN>::STAGE_BYTES;
   if (pdl) {
-    launch_pdl(gemm_tcgen05_kernel<BN, GATHER>, dim3((unsigned)grid), dim3(384), (size_t)smem, stream, tmA, tmB, tmC, tmR, ka);
+    launch_pdl(gemm_tcgen05_kernel<BN, AMODE>, dim3((unsigned)grid), dim3(384), (size_t)smem, stream, tmA, tmB, tmC, tmR, ka);
   } else {
-    gemm_tcgen05_kernel<BN, GATHER><<<grid, 384, smem, stream>>>(tmA, tmB, tmC, tmR, ka);
+    gemm_tcgen05_kernel<BN, AMODE><<<grid, 384, smem, stream>>>(tmA, tmB, tmC, tmR, ka);
     LAUNCH_OK();
   }
 }
@@ -586,12 +642,14 @@ void launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& t
 }  // namespace
 
 template <int BN> static void prepare_bn() {
-  CUDA_OK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-  CUDA_OK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  CUDA_OK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  CUDA_OK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  CUDA_OK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
 }
 void gemm_bf16_prepare() {
   prepare_bn<32>(); prepare_bn<64>(); prepare_bn<128>(); prepare_bn<256>();
   get_encode_fn();
+  get_encode_im2col_fn();
 }
 
 int sm_count() {
@@ -603,6 +661,9 @@ int sm_count() {
   }
   return n;
 }
+
+static thread_local int g_cta_cap = 0;
+void gemm_set_cta_cap(int ctas) { g_cta_cap = ctas > 0 ? ctas : 0; }
 
 void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
   static bool prepared = false;
@@ -664,14 +725,24 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
   ka.res_tma = ka.tma_epi && ka.residual;
   ka.m_tiles = (int)cdiv(p.M, BM);
   ka.n_tiles = (int)cdiv(p.N, bn);
-  const int grid = (int)std::min<int64_t>((int64_t)ka.m_tiles * ka.n_tiles * splits, sms);
+  const int grid = (int)std::min<int64_t>((int64_t)ka.m_tiles * ka.n_tiles * splits, g_cta_cap > 0 ? std::min(g_cta_cap, sms) : sms);
   CUtensorMap tmB = make_tmap_2d(p.W, p.N, p.K, p.K, bn);
-  CUtensorMap tmA = gather ? tmB : make_tmap_2d(p.A, p.M, p.K, p.lda, BM);
+  // both spatial corners must fit the descriptor's signed bytes; anything else keeps the cp.async gather
+  static const bool force_gather = getenv("RETR_CONV_GATHER") != nullptr && atoi(getenv("RETR_CONV_GATHER")) != 0;
+  const bool im2col = gather && !force_gather && p.conv.pad <= 127 && (p.conv.kh - 1) * p.conv.dil - p.conv.pad <= 128 &&
+                      p.conv.stride <= 8 && p.conv.kh == p.conv.kw;
+  CUtensorMap tmA = im2col   ? make_tmap_im2col(p.A, p.M / ((int64_t)p.conv.OH * p.conv.OW), p.conv)
+                    : gather ? tmB
+                             : make_tmap_2d(p.A, p.M, p.K, p.lda, BM);
   CUtensorMap tmC = ka.tma_epi ? make_tmap_2d(p.C, p.M, p.N, p.ldc, BM, p.out_fp32) : tmB;
   CUtensorMap tmR = ka.res_tma ? make_tmap_2d(ka.residual, p.M, p.N, ka.ldr, BM, ka.res_fp32 != 0) : tmB;
+  // a capped grid shares the GPU with another context: an early-launched dependent grid would park its CTAs on
+  // exactly the SMs the cap leaves free, so programmatic dependent launch is off then
+  const bool pdl = p.pdl && g_cta_cap == 0;
 #define RETR_LAUNCH(BN_)                                                   \
-  if (gather) launch<BN_, true>(tmA, tmB, tmC, tmR, ka, grid, stream, p.pdl);     \
-  else launch<BN_, false>(tmA, tmB, tmC, tmR, ka, grid, stream, p.pdl)
+  if (im2col) launch<BN_, 2>(tmA, tmB, tmC, tmR, ka, grid, stream, pdl);          \
+  else if (gather) launch<BN_, 1>(tmA, tmB, tmC, tmR, ka, grid, stream, pdl);     \
+  else launch<BN_, 0>(tmA, tmB, tmC, tmR, ka, grid, stream, pdl)
   switch (bn) {
     case 256: RETR_LAUNCH(256); break;
     case 128: RETR_LAUNCH(128); break;

@@ -70,6 +70,7 @@ class _CaptionBase(nn.Module):
         self.transformer = transformer
         self.mlp = MLP(hidden_dim, 512, vocab_size, 3)
         self._engine = None
+        self._pipeline = []               # extra contexts of greedy_stream(contexts=2), each with its own stream
         self._trainer = None
         self.dropout_p = 0.1              # config.dropout (configuration_template.py:48)
         self.pad_token_id = 0
@@ -99,6 +100,28 @@ class _CaptionBase(nn.Module):
             self._engine = Engine(self, device, self.precision, max_batch=max_batch)
         return self._engine
 
+    def pipeline_engines(self, batch, n=2):
+        """``n`` native contexts of this model, each with its own stream, for keeping ``n`` batches in flight
+        (eval_utils.decode.greedy_stream): the encode phase of one overlaps the decode loop of another.  Weights are
+        uploaded per context (0.5 GB each)."""
+        from ..runtime import Engine
+        device = next(self.parameters()).device
+        if device.type != "cuda":
+            raise RuntimeError("retr_b200 runs only on a CUDA device (B200, sm_100a); there is no CPU path.")
+        keep = []
+        for eng in self._pipeline:
+            if (eng.device == device and eng.precision == self.precision and eng.max_batch >= batch
+                    and eng.weights_version == Engine.version_of(self)):
+                keep.append(eng)
+            else:
+                eng.close()
+        self._pipeline = keep
+        while len(self._pipeline) < n:
+            eng = Engine(self, device, self.precision, max_batch=max(batch, self.max_batch))
+            eng.stream = torch.cuda.Stream(device=device)
+            self._pipeline.append(eng)
+        return self._pipeline[:n]
+
     def trainer(self, batch=1):
         """The native trainer bound (by pointer) to this model's parameters; rebuilt when a parameter
         tensor was replaced, a FrozenBatchNorm2d buffer was rewritten, or a larger batch arrives."""
@@ -124,6 +147,9 @@ class _CaptionBase(nn.Module):
         if self._engine is not None:       # parameters moved: pointers held by the context are stale
             self._engine.close()
             self._engine = None
+        for eng in self._pipeline:
+            eng.close()
+        self._pipeline = []
         if self._trainer is not None:
             self._trainer.close()
             self._trainer = None

@@ -51,6 +51,9 @@ SIGNATURES = {
     "retr_generate_host": (C.c_int, [C.c_void_p, C.c_int32] + [C.c_void_p] * 5 + [C.c_int32] * 3 +
                            [C.c_void_p, C.POINTER(C.c_int32), C.c_void_p]),
     "retr_prefetch_host": (C.c_int, [C.c_void_p, C.c_int32] + [C.c_void_p] * 5),
+    "retr_encode_host": (C.c_int, [C.c_void_p, C.c_int32] + [C.c_void_p] * 5 + [C.c_void_p]),
+    "retr_decode_host": (C.c_int, [C.c_void_p] + [C.c_int32] * 3 + [C.c_void_p, C.POINTER(C.c_int32), C.c_void_p]),
+    "retr_set_encode_cta_cap": (C.c_int, [C.c_void_p, C.c_int32]),
     "retr_encoder_tokens": (C.c_int, [C.c_void_p]),
     "retr_read_state": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "retr_kernel_launches": (C.c_int64, [C.c_void_p]),

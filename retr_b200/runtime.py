@@ -61,6 +61,7 @@ class Engine:
         self.S = self.lib.retr_encoder_tokens(self.handle)
         self.weights_version = self.version_of(model)
         self.batch = 0
+        self.stream = None
 
     # ---- weights --------------------------------------------------------------------------
     @staticmethod
@@ -90,6 +91,9 @@ class Engine:
 
     # ---- hot path ---------------------------------------------------------------------------
     def _stream(self):
+        # a context used next to another one (greedy_stream with contexts=2) owns a stream; otherwise torch's current
+        if self.stream is not None:
+            return self.stream.cuda_stream
         return native.stream_ptr(self.device)
 
     def encode(self, t_img, t_mask, g_img=None, g_mask=None, loc=None, att_enc=None):
@@ -151,6 +155,32 @@ class Engine:
                 native.ptr(loc), bos, eos, max_len, native.ptr(out), C.byref(steps), self._stream()))
         self.batch = B
         return out, steps.value
+
+    def encode_host(self, t_img, t_mask, g_img, g_mask, loc):
+        """Asynchronous first half of generate_host (copies + backbone + encoder queued on this context's stream)."""
+        B = t_img.shape[0]
+        for t in (t_img, t_mask, g_img, g_mask, loc):
+            if t is not None and (t.device.type != "cpu" or not t.is_contiguous()):
+                raise ValueError("encode_host takes contiguous host tensors")
+        with torch.cuda.device(self.device):
+            native.check(self.lib.retr_encode_host(
+                self.handle, B, native.ptr(t_img), native.ptr(t_mask), native.ptr(g_img), native.ptr(g_mask),
+                native.ptr(loc), self._stream()))
+        self._keep_eh = (t_img, t_mask, g_img, g_mask, loc)
+        self.batch = B
+
+    def decode_host(self, bos, eos, max_len, out=None):
+        """Second half: greedy loop of the batch last encoded here; returns with the ids in `out` (host)."""
+        if out is None:
+            out = torch.empty(self.batch, max_len, dtype=torch.int64).pin_memory()
+        steps = C.c_int32(0)
+        with torch.cuda.device(self.device):
+            native.check(self.lib.retr_decode_host(self.handle, bos, eos, max_len, native.ptr(out), C.byref(steps),
+                                                   self._stream()))
+        return out, steps.value
+
+    def set_encode_cta_cap(self, ctas):
+        native.check(self.lib.retr_set_encode_cta_cap(self.handle, int(ctas)))
 
     def prefetch_host(self, t_img, t_mask, g_img, g_mask, loc):
         """Queue the H2D copies of the NEXT batch (pinned host tensors) while the current one decodes; the

@@ -260,6 +260,14 @@ def test_greedy_stream_prefetch_equals_per_batch_greedy(kind):
     assert len(got) == 3
     for g, w in zip(got, want):
         assert torch.equal(g, w)
+    # two contexts in flight (retr_encode_host / retr_decode_host), with and without a capped encode grid
+    for cap in (None, 100):
+        got = [ids.clone() for ids in decode.greedy_stream(batches, model, max_len=128, bos_token=101, eos_token=102,
+                                                           contexts=2, encode_cta_cap=cap)]
+        assert len(got) == 3
+        for g, w in zip(got, want):
+            assert torch.equal(g, w)
+    assert len(model._pipeline) == 2 and model._pipeline[0].stream is not model._pipeline[1].stream
     # a staged batch that is never consumed must not leak into a later, different call
     eng = model.engine(3)
 

@@ -147,7 +147,8 @@ def test_gemm_vocab_argmax_and_ragged_n(dtype):
 
 CONVS = [  # (Cin, Cout, k, stride, pad, dil, H)
     (64, 64, 3, 1, 1, 1, 56), (128, 128, 3, 2, 1, 1, 56), (256, 512, 1, 2, 0, 1, 56),
-    (512, 512, 3, 1, 2, 2, 14), (256, 256, 3, 1, 1, 1, 14), (64, 256, 1, 1, 0, 1, 20)]
+    (512, 512, 3, 1, 2, 2, 14), (256, 256, 3, 1, 1, 1, 14), (64, 256, 1, 1, 0, 1, 20),
+    (128, 128, 3, 2, 1, 1, 15), (64, 64, 3, 1, 1, 1, 9)]    # odd sides: rows that wrap mid-tile, strided tail
 
 
 @pytest.mark.parametrize("dtype", [FP32, BF16])
