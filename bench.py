@@ -34,9 +34,9 @@ KIND = "CaptionGlobalLoc"
 BACKBONE_GFLOP_PER_IMAGE = 19.838
 TOTAL_GFLOP_PER_EXPR = 54.55
 DECODE_MB_PER_EXPR_B256 = 385.0
-# measured (ncu dram__bytes_read.sum + dram__bytes_write.sum over the 106 launches of a 256-image chunk, bf16;
-# profiles/r1_backbone_dram.txt): 21.264 GB per chunk
-BACKBONE_DRAM_BYTES_PER_IMAGE = 21.264e9 / 256
+# measured (ncu dram__bytes_read.sum + dram__bytes_write.sum over the 108 launches of the 512-image backbone pass, bf16,
+# TMA-im2col build; profiles/r1_backbone_v2_dram.txt): 45.955 GB per pass
+BACKBONE_DRAM_BYTES_PER_IMAGE = 45.955e9 / 512
 
 
 def build_model(precision):
@@ -307,7 +307,7 @@ def main():
                          "unit": "TFLOP/s", "frac": achieved / tf_peak if tf_peak else None,
                          "traffic": BACKBONE_DRAM_BYTES_PER_IMAGE * n_img if args.precision == "bf16" else None,
                          "traffic_note": "DRAM read+write bytes of the backbone phase per step (ncu, "
-                                         "profiles/r1_backbone_dram.txt: 21.26 GB per 256-image chunk), scaled by images",
+                                         "profiles/r1_backbone_v2_dram.txt: 45.96 GB per 512-image pass), scaled by images",
                          "peak_source": f"{which} bf16 sustained"},
             "roofline_decode": {"bound": "hbm", "achieved": DECODE_MB_PER_EXPR_B256 * B / 1000.0 /
                                 (phases["decode"] / args.steps / 1000.0) if phases["decode"] > 0 else 0.0,

@@ -139,6 +139,10 @@ typedef struct retr_gemm_args {
   int32_t kh, kw, stride, pad, dil, H, W_in, C_in, OH, OW;
   /* fused argmax over N (vocab head): packed (value,index) keys, uint64 [M]; C may be NULL */
   unsigned long long* argmax_out;
+  /* mn_major != 0 (bf16 only): C[M,N] = A^T . W with A given as [K, M] (row pitch lda) and W as [K, N] (row pitch
+   * ldb) — the weight-gradient contraction over tokens / pixels, operands read in place.  With a conv view, W is the
+   * NHWC layer input, N = kh*kw*C_in and K = images*OH*OW (dW of the convolution as [C_out, (kh,kw,C_in)]). */
+  int32_t mn_major; int64_t ldb;
 } retr_gemm_args;
 int retr_op_gemm(int32_t dtype, const retr_gemm_args* args, void* stream);
 

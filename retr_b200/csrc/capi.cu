@@ -184,6 +184,8 @@ int retr_op_gemm(int32_t dtype, const retr_gemm_args* a, void* stream) {
   p.conv.kh = a->kh; p.conv.kw = a->kw; p.conv.stride = a->stride; p.conv.pad = a->pad; p.conv.dil = a->dil;
   p.conv.H = a->H; p.conv.W = a->W_in; p.conv.C = a->C_in; p.conv.OH = a->OH; p.conv.OW = a->OW;
   p.argmax_out = a->argmax_out;
+  p.mn_major = a->mn_major != 0; p.ldb = a->ldb;
+  RETR_CHECK(!p.mn_major || dtype == RETR_BF16, "mn_major GEMM is bf16 only");
   if (dtype == RETR_FP32) gemm_fp32(p, static_cast<cudaStream_t>(stream));
   else if (dtype == RETR_BF16) gemm_bf16(p, static_cast<cudaStream_t>(stream));
   else throw Error("unknown dtype");

@@ -45,6 +45,12 @@ struct GemmParams {
   float* split_ws = nullptr;
   int64_t split_ws_floats = 0;
   bool accumulate = false;
+  // Both operands MN-major (bf16 / tcgen05 only): C[M,N] = A^T . B with A given as [K, M] (row pitch lda) and W as
+  // [K, N] (row pitch ldb) — the weight-gradient contraction dW = dY^T . X over tokens/pixels, read in place, no
+  // transposed copies.  With a conv view, W is the NHWC layer input and B its im2col [pixels, kh*kw*C] (TMA im2col),
+  // K = images*OH*OW.
+  bool mn_major = false;
+  int64_t ldb = 0;
 };
 
 void gemm_fp32(const GemmParams& p, cudaStream_t stream);   // gemm_simt.cu  (A, W fp32)

@@ -299,6 +299,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   // keeps one and uses warps 8-11 for the im2col gather (its K >= 576 tiles are main-loop bound).
   constexpr bool GATHER = AMODE == 1;
   constexpr bool IM2COL = AMODE == 2;
+  constexpr bool TN = AMODE >= 3;          // both operands MN-major: C[M,N] = A[K,M]^T . B[K,N]   (weight gradients)
+  constexpr bool TN_CONV = AMODE == 4;     // ... with B = im2col(NHWC input), loaded by TMA im2col, 64 pixels per k-block
   constexpr int EG = GATHER ? 1 : 2;
   const int STAGES = a.stages;
   extern __shared__ uint8_t smem_raw[];
@@ -370,7 +372,33 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           uint8_t* As = smem + s * C::STAGE_BYTES;
           uint8_t* Bs = As + A_TILE_BYTES;
           ptx::mbar_arrive_expect_tx(&full[s], C::B_TILE_BYTES + (GATHER ? 0 : A_TILE_BYTES));
-          if (IM2COL) {
+          if (TN) {
+            // MN-major tiles arrive as [64 rows of K] x [64 elements of M or N] boxes of 8 KB
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j)
+              ptx::tma_load_2d(As + j * 8192, &tmA, &full[s], m_blk * BM + j * 64, kb * BK);
+            int tw = 0, th = 0, tn = 0;
+            if (TN_CONV) {                          // first output pixel of this k-block -> base input pixel
+              const int64_t m0 = (int64_t)kb * BK;
+              const int64_t t = m0 / a.OW;
+              tw = (int)(m0 - t * a.OW) * a.stride - a.pad;
+              th = (int)(t % a.OH) * a.stride - a.pad;
+              tn = (int)(t / a.OH);
+            }
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j) {
+              int n = n_blk * BN + j * 64;
+              if (TN_CONV) {
+                if (n >= a.N) n = 0;                // columns past N are never stored; keep the coordinates legal
+                const int tap = n / a.Cin, c = n - tap * a.Cin;
+                const int fr = tap / a.kw, fs = tap - fr * a.kw;
+                ptx::tma_load_im2col_4d(Bs + j * 8192, &tmB, &full[s], c, tw, th, tn, (uint16_t)(fs * a.dil),
+                                        (uint16_t)(fr * a.dil));
+              } else {
+                ptx::tma_load_2d(Bs + j * 8192, &tmB, &full[s], n, kb * BK);
+              }
+            }
+          } else if (IM2COL) {
             // k-block kb = (filter tap, 64-channel block); the tile's first output pixel fixes the base input pixel
             const int tap = kb / a.cblocks, cb = kb - tap * a.cblocks;
             const int fr = tap / a.kw, fs = tap - fr * a.kw;
@@ -379,7 +407,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           } else if (!GATHER) {
             ptx::tma_load_2d(As, &tmA, &full[s], kb * BK, m_blk * BM);
           }
-          ptx::tma_load_2d(Bs, &tmB, &full[s], kb * BK, n_blk * BN);
+          if (!TN) ptx::tma_load_2d(Bs, &tmB, &full[s], kb * BK, n_blk * BN);
           if (++s == (uint32_t)STAGES) { s = 0; ph ^= 1; }
         }
       }
@@ -387,7 +415,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   } else if (warp == 1) {
     if (lane == 0) {
       // ===== MMA issuer =====
-      constexpr uint32_t idesc = ptx::idesc_bf16_f32(BM, BN);
+      constexpr uint32_t idesc = TN ? ptx::idesc_bf16_f32_mn(BM, BN) : ptx::idesc_bf16_f32(BM, BN);
       uint32_t s = 0, ph = 0, tcount = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
         const uint32_t as = tcount & 1, aph = (tcount >> 1) & 1;
@@ -402,8 +430,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const uint32_t b_addr = a_addr + A_TILE_BYTES;
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
-            ptx::mma_bf16_ss(d_tmem, ptx::smem_desc_sw128(a_addr + k * 32),
-                             ptx::smem_desc_sw128(b_addr + k * 32), idesc, ((kb - tc.kb0) | k) != 0);
+            if (TN)       // 16 rows of K = two 8-row groups = 2048 B inside every 64-element box
+              ptx::mma_bf16_ss(d_tmem, ptx::smem_desc_mn_sw128(a_addr + k * 2048, 8192),
+                               ptx::smem_desc_mn_sw128(b_addr + k * 2048, 8192), idesc, ((kb - tc.kb0) | k) != 0);
+            else
+              ptx::mma_bf16_ss(d_tmem, ptx::smem_desc_sw128(a_addr + k * 32),
+                               ptx::smem_desc_sw128(b_addr + k * 32), idesc, ((kb - tc.kb0) | k) != 0);
           }
           ptx::mma_commit(&empty[s]);      // frees the smem slot when these MMAs retire
           if (++s == (uint32_t)STAGES) { s = 0; ph ^= 1; }
@@ -608,7 +640,7 @@ CUtensorMap make_tmap_2d(const void* base, int64_t rows, int64_t cols, int64_t l
 // pixels starts at -pad and ends (k-1)*dil - pad short of the far edge, traversed with the convolution stride, so
 // "128 pixels from base pixel (iw0, ih0, img)" are 128 consecutive output pixels in (img, oh, ow) order; the filter tap
 // is the per-instruction offset.  Same corner rule as CUTLASS's fprop (conv/collective/detail.hpp).
-CUtensorMap make_tmap_im2col(const void* base, int64_t n, const ConvView& c) {
+CUtensorMap make_tmap_im2col(const void* base, int64_t n, const ConvView& c, int pixels = BM) {
   CUtensorMap m;
   cuuint64_t dims[4] = {(cuuint64_t)c.C, (cuuint64_t)c.W, (cuuint64_t)c.H, (cuuint64_t)n};
   cuuint64_t strides[3] = {(cuuint64_t)c.C * 2, (cuuint64_t)c.W * c.C * 2, (cuuint64_t)c.H * c.W * c.C * 2};
@@ -617,7 +649,7 @@ CUtensorMap make_tmap_im2col(const void* base, int64_t n, const ConvView& c) {
   cuuint32_t estr[4] = {1, (cuuint32_t)c.stride, (cuuint32_t)c.stride, 1};
   RETR_CHECK((reinterpret_cast<uintptr_t>(base) & 15) == 0, "im2col operand must be 16-byte aligned");
   CUresult r = get_encode_im2col_fn()(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides,
-                                      lower, upper, (cuuint32_t)BK, (cuuint32_t)BM, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                      lower, upper, (cuuint32_t)BK, (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                       CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   RETR_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeIm2col failed (" + std::to_string((int)r) + ")");
@@ -645,6 +677,10 @@ template <int BN> static void prepare_bn() {
   CUDA_OK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
   CUDA_OK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
   CUDA_OK(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  if (BN >= 64) {
+    CUDA_OK(cudaFuncSetAttribute(gemm_tcgen05_kernel<(BN < 64 ? 64 : BN), 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    CUDA_OK(cudaFuncSetAttribute(gemm_tcgen05_kernel<(BN < 64 ? 64 : BN), 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  }
 }
 void gemm_bf16_prepare() {
   prepare_bn<32>(); prepare_bn<64>(); prepare_bn<128>(); prepare_bn<256>();
@@ -669,8 +705,13 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
   static bool prepared = false;
   if (!prepared) { gemm_bf16_prepare(); prepared = true; }
   RETR_CHECK(p.M > 0 && p.N > 0 && p.K > 0, "empty GEMM");
-  RETR_CHECK(p.K % 8 == 0, "K must be a multiple of 8 (16-byte rows)");
+  const bool tn = p.mn_major;
+  RETR_CHECK(tn || p.K % 8 == 0, "K must be a multiple of 8 (16-byte rows)");
   const bool gather = p.conv.kh > 0;
+  if (tn) {
+    RETR_CHECK(p.lda % 8 == 0 && (gather || p.ldb % 8 == 0), "MN-major operands need 16-byte row pitches");
+    RETR_CHECK(!gather || p.N == p.conv.kh * p.conv.kw * p.conv.C, "MN-major conv: N must be kh*kw*C_in");
+  }
   KArgs ka{};
   ka.M = p.M; ka.N = p.N; ka.K = p.K;
   ka.num_kb = (int)cdiv(p.K, BK);
@@ -688,8 +729,8 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
   if (gather) {
     const ConvView& c = p.conv;
     RETR_CHECK(c.C % BK == 0, "implicit-GEMM conv needs C_in % 64 == 0");
-    RETR_CHECK(p.K == c.kh * c.kw * c.C, "conv K mismatch");
-    RETR_CHECK(p.M % ((int64_t)c.OH * c.OW) == 0, "conv M must be images*OH*OW");
+    RETR_CHECK(tn || p.K == c.kh * c.kw * c.C, "conv K mismatch");
+    RETR_CHECK((tn ? (int64_t)p.K : p.M) % ((int64_t)c.OH * c.OW) == 0, "conv pixel count must be images*OH*OW");
     ka.kh = c.kh; ka.kw = c.kw; ka.stride = c.stride; ka.pad = c.pad; ka.dil = c.dil;
     ka.H = c.H; ka.W = c.W; ka.Cin = c.C; ka.OH = c.OH; ka.OW = c.OW; ka.cblocks = c.C / BK;
   }
@@ -701,7 +742,7 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
     RETR_CHECK(p.out_fp32 && p.C && p.ldc == p.N && !p.scale && !p.bias && !p.rowbias && !p.residual && !p.relu &&
                    !p.argmax_out && !p.c_group,
                "split-K GEMM takes a plain fp32 C and no epilogue operands");
-    while (bn > 32 && bn / 2 >= p.N) bn /= 2;
+    while (bn > (tn ? 64 : 32) && bn / 2 >= p.N) bn /= 2;
     const int64_t tiles = cdiv(p.M, BM) * cdiv(p.N, bn);
     splits = p.split_k > 1 ? p.split_k : (int)std::max<int64_t>(1, (2 * sms) / tiles);
     splits = std::min(splits, std::max(1, ka.num_kb / 4));
@@ -709,7 +750,7 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
     else splits = 1;
     splits = std::max(splits, 1);
   } else {
-    while (bn > 32 && (bn / 2 >= p.N || cdiv(p.M, BM) * cdiv(p.N, bn) < sms)) bn /= 2;
+    while (bn > (tn ? 64 : 32) && (bn / 2 >= p.N || cdiv(p.M, BM) * cdiv(p.N, bn) < sms)) bn /= 2;
   }
   ka.kb_per_split = (int)cdiv(ka.num_kb, splits);
   splits = (int)cdiv(ka.num_kb, ka.kb_per_split);          // no empty split
@@ -726,12 +767,16 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
   ka.m_tiles = (int)cdiv(p.M, BM);
   ka.n_tiles = (int)cdiv(p.N, bn);
   const int grid = (int)std::min<int64_t>((int64_t)ka.m_tiles * ka.n_tiles * splits, g_cta_cap > 0 ? std::min(g_cta_cap, sms) : sms);
-  CUtensorMap tmB = make_tmap_2d(p.W, p.N, p.K, p.K, bn);
+  const int64_t n_img = gather ? (tn ? (int64_t)p.K : p.M) / ((int64_t)p.conv.OH * p.conv.OW) : 0;
+  CUtensorMap tmB = !tn      ? make_tmap_2d(p.W, p.N, p.K, p.K, bn)
+                    : gather ? make_tmap_im2col(p.W, n_img, p.conv, BK)
+                             : make_tmap_2d(p.W, p.K, p.N, p.ldb, BK);
   // both spatial corners must fit the descriptor's signed bytes; anything else keeps the cp.async gather
   static const bool force_gather = getenv("RETR_CONV_GATHER") != nullptr && atoi(getenv("RETR_CONV_GATHER")) != 0;
-  const bool im2col = gather && !force_gather && p.conv.pad <= 127 && (p.conv.kh - 1) * p.conv.dil - p.conv.pad <= 128 &&
+  const bool im2col = !tn && gather && !force_gather && p.conv.pad <= 127 && (p.conv.kh - 1) * p.conv.dil - p.conv.pad <= 128 &&
                       p.conv.stride <= 8 && p.conv.kh == p.conv.kw;
-  CUtensorMap tmA = im2col   ? make_tmap_im2col(p.A, p.M / ((int64_t)p.conv.OH * p.conv.OW), p.conv)
+  CUtensorMap tmA = tn       ? make_tmap_2d(p.A, p.K, p.M, p.lda, BK)
+                    : im2col ? make_tmap_im2col(p.A, n_img, p.conv)
                     : gather ? tmB
                              : make_tmap_2d(p.A, p.M, p.K, p.lda, BM);
   CUtensorMap tmC = ka.tma_epi ? make_tmap_2d(p.C, p.M, p.N, p.ldc, BM, p.out_fp32) : tmB;
@@ -740,7 +785,9 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
   // exactly the SMs the cap leaves free, so programmatic dependent launch is off then
   const bool pdl = p.pdl && g_cta_cap == 0;
 #define RETR_LAUNCH(BN_)                                                   \
-  if (im2col) launch<BN_, 2>(tmA, tmB, tmC, tmR, ka, grid, stream, pdl);          \
+  if (tn && gather) launch<(BN_ < 64 ? 64 : BN_), 4>(tmA, tmB, tmC, tmR, ka, grid, stream, pdl);   \
+  else if (tn) launch<(BN_ < 64 ? 64 : BN_), 3>(tmA, tmB, tmC, tmR, ka, grid, stream, pdl);        \
+  else if (im2col) launch<BN_, 2>(tmA, tmB, tmC, tmR, ka, grid, stream, pdl);          \
   else if (gather) launch<BN_, 1>(tmA, tmB, tmC, tmR, ka, grid, stream, pdl);     \
   else launch<BN_, 0>(tmA, tmB, tmC, tmR, ka, grid, stream, pdl)
   switch (bn) {

@@ -192,6 +192,25 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t smem_addr) {
   d |= (uint64_t)2 << 61;                            // SWIZZLE_128B
   return d;
 }
+// MN-major operand (the M or N index is the contiguous one, K strides by rows), 128B swizzle: atoms of 64 elements
+// (128 B) along MN x 8 rows along K.  A tile is laid out as TMA delivers [64-row x 64-element] boxes: the 8-row groups
+// of one box follow each other (stride byte offset 1024), the next 64 elements along MN are the next box
+// (leading byte offset = box bytes).  Canonical form ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte units
+// (cute/atom/mma_traits_sm100.hpp, make_umma_desc<Major::MN>).
+__device__ __forceinline__ uint64_t smem_desc_mn_sw128(uint32_t smem_addr, uint32_t box_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)((box_bytes >> 4) & 0x3FFFu) << 16;  // leading byte offset: next 64 elements along MN
+  d |= (uint64_t)(1024 >> 4) << 32;                  // stride byte offset: next 8 rows along K
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// kind::f16 instruction descriptor: bf16 x bf16 -> fp32, both operands MN-major (bits 15 / 16)
+__host__ __device__ constexpr uint32_t idesc_bf16_f32_mn(int m, int n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(n >> 3) << 17) |
+         ((uint32_t)(m >> 4) << 24);
+}
 // kind::f16 instruction descriptor: bf16 x bf16 -> fp32, both operands K-major
 __host__ __device__ constexpr uint32_t idesc_bf16_f32(int m, int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);

@@ -679,10 +679,26 @@ void TrainerT<T>::forward(int B, const float* t_img, const uint8_t* t_mask, cons
   forward_impl(B, t_img, t_mask, g_img, g_mask, loc, ids, id_mask, logits_out, false, dropout_p, seed, s);
 }
 
+// RETR_WGRAD_TN=0: weight gradients through transposed copies + the K-major GEMM (the first implementation)
+static bool wgrad_in_place() {
+  static const bool on = !(getenv("RETR_WGRAD_TN") && atoi(getenv("RETR_WGRAD_TN")) == 0);
+  return on;
+}
+
 // ---- backward helpers ---------------------------------------------------------------------------------------------
 template <typename T>
 void TrainerT<T>::wgrad(const T* dy, int64_t ld_dy, int n_out, const T* x, int64_t ld_x, int k_in, int64_t M, float* gw,
                         bool accumulate, cudaStream_t s) {
+  if (std::is_same<T, bf16>::value && wgrad_in_place() && ld_dy % 8 == 0 && ld_x % 8 == 0 &&
+      reinterpret_cast<uintptr_t>(dy) % 16 == 0 && reinterpret_cast<uintptr_t>(x) % 16 == 0) {
+    // dW = dY^T . X with both operands read in place as MN-major tcgen05 tiles (no transposed copies)
+    GemmParams p;
+    p.mn_major = true;
+    p.A = dy; p.lda = ld_dy; p.W = x; p.ldb = ld_x; p.M = n_out; p.N = k_in; p.K = (int)M; p.C = gw; p.ldc = k_in;
+    p.out_fp32 = true; p.split_k = 0; p.split_ws = ws_; p.split_ws_floats = ws_floats_; p.accumulate = accumulate;
+    gemmT<T>(p, s);
+    return;
+  }
   const int64_t Mp = rup(M, 16);
   RETR_CHECK((int64_t)n_out * Mp <= tA_cap_ && (int64_t)k_in * Mp <= tB_cap_, "wgrad scratch too small");
   transpose_pad<T, T>(dy, ld_dy, tA_, Mp, M, n_out, s);
@@ -717,7 +733,22 @@ void TrainerT<T>::conv_bwd(const TConv<T>& c, const T* g, const T* x, int64_t ni
   const int64_t Mo = nimg * OH * OH, Mp = rup(Mo, 16);
   const int kk = c.k * c.k * c.cin;
   const bool plain = c.k == 1 && c.stride == 1;
-  if (c.gw) {
+  const bool in_place = std::is_same<T, bf16>::value && wgrad_in_place() && c.cout % 8 == 0 && c.cin % 64 == 0 &&
+                        c.pad <= 127 && c.stride <= 8;
+  if (c.gw && in_place) {
+    // dW[C_out, (kh,kw,C_in)] = dY^T . im2col(X): dY and the NHWC input read in place (TMA im2col as the B operand)
+    GemmParams p;
+    p.mn_major = true;
+    p.A = g; p.lda = c.cout; p.W = x; p.ldb = c.cin; p.M = c.cout; p.N = kk; p.K = (int)Mo; p.ldc = kk; p.out_fp32 = true;
+    p.C = c.k == 1 ? c.gw : dwk_;
+    if (!plain) {
+      p.conv.kh = p.conv.kw = c.k; p.conv.stride = c.stride; p.conv.pad = c.pad; p.conv.dil = c.dil;
+      p.conv.H = H; p.conv.W = H; p.conv.C = c.cin; p.conv.OH = OH; p.conv.OW = OH;
+    }
+    p.split_k = 0; p.split_ws = ws_; p.split_ws_floats = ws_floats_;
+    gemmT<T>(p, s);
+    if (c.k != 1) filter_grad_unpack(dwk_, c.gw, c.cout, c.cin, c.k, c.k, kk, s);
+  } else if (c.gw) {
     RETR_CHECK((int64_t)c.cout * Mp <= tA_cap_ && (int64_t)kk * Mp <= tB_cap_, "conv wgrad scratch too small");
     transpose_pad<T, T>(g, c.cout, tA_, Mp, Mo, c.cout, s);
     if (plain) transpose_pad<T, T>(x, c.cin, tB_, Mp, Mo, c.cin, s);

@@ -32,7 +32,8 @@ class GemmArgs(C.Structure):
                 ("kh", C.c_int32), ("kw", C.c_int32), ("stride", C.c_int32), ("pad", C.c_int32),
                 ("dil", C.c_int32), ("H", C.c_int32), ("W_in", C.c_int32), ("C_in", C.c_int32),
                 ("OH", C.c_int32), ("OW", C.c_int32),
-                ("argmax_out", C.c_void_p)]
+                ("argmax_out", C.c_void_p),
+                ("mn_major", C.c_int32), ("ldb", C.c_int64)]
 
 
 # name -> (restype, argtypes); every symbol include/retr_b200.h declares

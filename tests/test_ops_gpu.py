@@ -18,7 +18,7 @@ def _lib():
 
 
 def run_gemm(dtype, A, W, *, M, N, K, lda=None, ldc=None, scale=None, bias=None, rowbias=None, period=1,
-             residual=None, relu=0, out_fp32=False, conv=None, argmax=False, want_c=True, out=None):
+             residual=None, relu=0, out_fp32=False, conv=None, argmax=False, want_c=True, out=None, mn_major=0, ldb=0):
     native, lib = _lib()
     dev = A.device
     out_dtype = torch.float32 if (out_fp32 or dtype == FP32) else torch.bfloat16
@@ -39,6 +39,7 @@ def run_gemm(dtype, A, W, *, M, N, K, lda=None, ldc=None, scale=None, bias=None,
         for k, v in conv.items():
             setattr(a, k, v)
     a.argmax_out = keys.data_ptr() if argmax else None
+    a.mn_major, a.ldb = mn_major, ldb
     native.check(lib.retr_op_gemm(dtype, C.byref(a), native.stream_ptr(dev)))
     torch.cuda.synchronize()
     idx = None
@@ -178,6 +179,42 @@ def test_conv_implicit_gemm(dtype, out_fp32, cin, cout, k, stride, pad, dil, H):
         assert (got - ref).abs().max().item() < 2e-4
     else:       # bf16 result: one rounding of the fp32 value (staged TMA-store epilogue, bf16 residual by TMA)
         assert bool(((got.float() - ref).abs() <= ref.abs() * 2 ** -8 + 2e-4).all())
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 256, 4096), (200, 576, 1000), (64, 64, 128), (1000, 520, 300), (128, 2304, 25088)])
+def test_gemm_mn_major(M, N, K):
+    """C = A^T B with A [K,M] and B [K,N] read in place (MN-major tcgen05 operands): the weight-gradient contraction
+    of engine.py:76 loss.backward() for a Linear, without transposed copies.  Ragged M, N and K."""
+    torch.manual_seed(M + N + K)
+    dev = "cuda"
+    At = torch.randn(K, M, device=dev).bfloat16()
+    Bm = torch.randn(K, N, device=dev).bfloat16()
+    ref = (At.double().t() @ Bm.double()).float()
+    got, _ = run_gemm(BF16, At, Bm, M=M, N=N, K=K, lda=M, out_fp32=True, mn_major=1, ldb=N)
+    assert (got - ref).abs().max().item() <= 2e-5 * ref.abs().max().item() * max(1.0, math.sqrt(K) / 8)
+
+
+@pytest.mark.parametrize("cin,cout,k,stride,pad,dil,H", [(64, 64, 3, 1, 1, 1, 14), (128, 128, 3, 2, 1, 1, 15),
+                                                         (64, 128, 3, 1, 2, 2, 14), (64, 256, 1, 2, 0, 1, 20),
+                                                         (256, 64, 3, 1, 1, 1, 9)])
+def test_conv_wgrad_mn_major(cin, cout, k, stride, pad, dil, H):
+    """dW[C_out, (kh,kw,C_in)] = dY^T . im2col(X) with dY [pixels, C_out] and the NHWC input read in place (TMA im2col
+    as the MN-major B operand) vs the autograd weight gradient of F.conv2d."""
+    torch.manual_seed(cin + cout + k + stride + H)
+    dev = "cuda"
+    n = 3
+    x = torch.randn(n, cin, H, H, device=dev).bfloat16()
+    w = torch.zeros(cout, cin, k, k, device=dev, dtype=torch.double, requires_grad=True)
+    y = F.conv2d(x.double(), w, stride=stride, padding=pad, dilation=dil)
+    OH = y.shape[-1]
+    dy = torch.randn(n, OH, OH, cout, device=dev).bfloat16()
+    y.backward(dy.double().permute(0, 3, 1, 2))
+    ref = w.grad.permute(0, 2, 3, 1).reshape(cout, k * k * cin).float()
+    A = x.permute(0, 2, 3, 1).contiguous()
+    conv = dict(kh=k, kw=k, stride=stride, pad=pad, dil=dil, H=H, W_in=H, C_in=cin, OH=OH, OW=OH)
+    got, _ = run_gemm(BF16, dy.reshape(-1, cout), A, M=cout, N=k * k * cin, K=n * OH * OH, lda=cout, out_fp32=True,
+                      conv=conv, mn_major=1)
+    assert (got - ref).abs().max().item() <= 1e-4 * ref.abs().max().item()
 
 
 @pytest.mark.parametrize("out_bf16", [0, 1])
