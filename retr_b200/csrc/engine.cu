@@ -146,6 +146,7 @@ class EngineT final : public EngineBase {
   int *cross_dst_ = nullptr, *cross_nvalid_ = nullptr;   // cross caches hold only the unpadded keys (decode_ops.cu)
   uint8_t *tok_mask_ = nullptr, *finished_ = nullptr;
   int64_t* caption_ = nullptr;
+  int cross_prefetch_ = 0;      // RETR_CROSS_PREFETCH: measured slower (decode 46.7 -> 47.8 ms; 48.5 with the wrap-around), off
   int *step_ = nullptr, *done_ = nullptr;
   int* done_host_ = nullptr;                         // pinned [2]: done, step
   unsigned long long* argmax_keys_ = nullptr;
@@ -369,6 +370,7 @@ void EngineT<T>::alloc_buffers() {
   argmax_keys_ = static_cast<unsigned long long*>(dalloc(Md * 8));
   CUDA_OK(cudaMemset(argmax_keys_, 0, Md * 8));
   CUDA_OK(cudaMallocHost(&done_host_, 16));
+  if (const char* e = getenv("RETR_CROSS_PREFETCH")) cross_prefetch_ = atoi(e);
   if (const char* e = getenv("RETR_DECODE_GROUPS")) groups_ = std::min(16, std::max(1, atoi(e)));
   ffn_fused_ = std::is_same<T, bf16>::value && ffn_fused_supported((int)d, (int)desc.d_ff) &&
                !(getenv("RETR_FFN_FUSED") && atoi(getenv("RETR_FFN_FUSED")) == 0);
@@ -701,6 +703,13 @@ void EngineT<T>::decode_rows_fused(int r0, int n, int group, int max_len, cudaSt
         FfnFusedParams fp;
         fp.Y = y; fp.gamma = e.ln3_g; fp.beta = e.ln3_b; fp.W1 = e.ff1.w; fp.b1 = e.ff1.b; fp.W2 = e.ff2.w; fp.b2 = e.ff2.b;
         fp.M = n; fp.d_ff = (int)ff;
+        // optional: the next layer's cross K/V -> L2 while HBM is idle (=2: also layer 0's for the next step).  Measured
+        // SLOWER at B=256 (75 MB per layer next to ~50 MB of weights re-read every step: the prefetch evicts them)
+        const int nl = l + 1 < desc.dec_layers ? l + 1 : (cross_prefetch_ >= 2 ? 0 : -1);
+        if (cross_prefetch_ && H == 8 && nl >= 0) {
+          fp.pf_k = ck_[nl] + (int64_t)r0 * S * d; fp.pf_v = cv_[nl] + (int64_t)r0 * S * d;
+          fp.pf_nvalid = cross_nvalid_ + r0; fp.pf_rows = S; fp.pf_dh = d / H;
+        }
         ffn_fused(fp, s);
       }
     } else {

@@ -116,6 +116,15 @@ __global__ void __launch_bounds__(FF_THREADS) ffn_fused_kernel(const FfnFusedPar
     load_panel(s, s);
     asm volatile("cp.async.commit_group;" ::: "memory");
   }
+  if (p.pf_k && tid < 2 * FF_BM) {
+    // CTA `rank` of the cluster takes head `rank` of its 32 samples: one K and one V block each
+    const int b = m0 + (tid >> 1);
+    if (b < p.M) {
+      const uint32_t bytes = (uint32_t)(p.pf_nvalid ? p.pf_nvalid[b] : p.pf_rows) * p.pf_dh * 2u;
+      const bf16* blk = ((tid & 1) ? p.pf_v : p.pf_k) + ((int64_t)b * 8 + rank) * p.pf_rows * p.pf_dh;
+      if (bytes) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(blk), "r"(bytes) : "memory");
+    }
+  }
   // epilogue operands that do not depend on the previous kernel: this thread's bias values of the four W1 panels
   const int g = lane >> 2, c4 = lane & 3;
   // warp tile: 16 rows (mt) x 16 columns (cg) of the panel output over all of K.  The A fragments (16 k-steps, 64

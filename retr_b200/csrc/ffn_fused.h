@@ -10,6 +10,11 @@ struct FfnFusedParams {
   const bf16* W1 = nullptr; const float* b1 = nullptr; // [d_ff, 256], [d_ff]
   const bf16* W2 = nullptr; const float* b2 = nullptr; // [256, d_ff], [256]
   int M = 0, d_ff = 0;
+  // Optional L2 prefetch issued at kernel entry: the head-major cross-attention K/V blocks ([M][8][pf_rows][pf_dh] bf16,
+  // pf_nvalid[m] valid rows each) of the NEXT decoder layer for this kernel's rows.  HBM is idle during the FFN /
+  // projection phase of a decode step; the next cross-attention then reads L2 instead of DRAM.
+  const bf16* pf_k = nullptr; const bf16* pf_v = nullptr; const int* pf_nvalid = nullptr;
+  int pf_rows = 0, pf_dh = 0;
 };
 
 // y <- y + Wo att + bo ; q = Wq LN(y) + bq + rowbias[*rowbias_dyn]   (d_model = 256; see ffn_fused.cu)
