@@ -52,6 +52,7 @@ template <typename T> struct TConv {
   int cin = 0, cout = 0, k = 1, stride = 1, pad = 0, dil = 1, kpad = 0;
   T* wk = nullptr;        // [cout, kpad]
   T* wkt = nullptr;       // [kpad, cout]
+  T* wkd = nullptr;       // [cin, k*k*cout], taps flipped: filter of the input-gradient convolution (stride-1 k>1, bf16)
   float *scale = nullptr, *shift = nullptr;
 };
 template <typename T> struct TBlock {
@@ -276,6 +277,9 @@ TConv<T> TrainerT<T>::conv(const std::string& wname, const std::string& bn, int 
   c.kpad = (int)rup((int64_t)c.k * c.k * c.cin, 16);
   c.wk = alloc<T>((int64_t)c.cout * c.kpad);
   if (trainable) c.wkt = alloc<T>((int64_t)c.kpad * c.cout);
+  if (trainable && std::is_same<T, bf16>::value && c.k > 1 && c.stride == 1 && c.cout % 64 == 0 && c.cin % 8 == 0 &&
+      c.dil * (c.k - 1) - c.pad >= 0 && !(getenv("RETR_DGRAD_IMPLICIT") && atoi(getenv("RETR_DGRAD_IMPLICIT")) == 0))
+    c.wkd = alloc<T>((int64_t)c.cin * c.k * c.k * c.cout);
   // FrozenBatchNorm2d (models/backbone.py:41-51): buffers, never trained -> folded once
   const int n = c.cout;
   std::vector<float> bw(n), bb(n), rm(n), rv(n), sc(n), sh(n);
@@ -466,6 +470,7 @@ template <typename T>
 void TrainerT<T>::refresh(const TConv<T>& c, cudaStream_t s) {
   repack_filter<T>(c.w, c.wk, c.cout, c.cin, c.k, c.k, c.kpad, s);
   if (c.wkt) transpose_pad<T, T>(c.wk, c.kpad, c.wkt, c.cout, c.cout, c.kpad, s);
+  if (c.wkd) repack_filter_dgrad<T>(c.w, c.wkd, c.cout, c.cin, c.k, c.k, s);
 }
 template <typename T>
 void TrainerT<T>::refresh_all(cudaStream_t s) {
@@ -760,7 +765,17 @@ void TrainerT<T>::conv_bwd(const TConv<T>& c, const T* g, const T* x, int64_t ni
     gemmT<T>(p, s);
     if (c.k != 1) filter_grad_unpack(dwk_, c.gw, c.cout, c.cin, c.k, c.k, kk, s);
   }
-  if (need_dx) {
+  if (need_dx && c.wkd) {
+    // input gradient of a stride-1 k x k convolution = convolution of dY with the flipped, transposed filter (TMA
+    // im2col over dY, pad' = dil*(k-1) - pad); the other branch's gradient rides in as the epilogue residual.  No
+    // [pixels, k*k*C_in] column matrix, no col2im.
+    GemmParams p;
+    p.A = g; p.lda = c.cout; p.W = c.wkd; p.C = dx; p.M = nimg * H * H; p.N = c.cin; p.K = c.k * c.k * c.cout; p.ldc = c.cin;
+    p.conv.kh = p.conv.kw = c.k; p.conv.stride = 1; p.conv.pad = c.dil * (c.k - 1) - c.pad; p.conv.dil = c.dil;
+    p.conv.H = OH; p.conv.W = OH; p.conv.C = c.cout; p.conv.OH = H; p.conv.OW = H;
+    if (dx_add) { p.residual = dx_add; p.ldr = c.cin; p.res_fp32 = false; }
+    gemmT<T>(p, s);
+  } else if (need_dx) {
     GemmParams p;
     p.A = g; p.lda = c.cout; p.W = c.wkt; p.M = Mo; p.N = kk; p.K = c.cout; p.ldc = kk;
     if (plain) {

@@ -790,6 +790,23 @@ void col2im(const T* dcol, T* dx, int64_t nimg, int H, int W, int C, int k, int 
 template void col2im<float>(const float*, float*, int64_t, int, int, int, int, int, int, int, int, int, const float*, cudaStream_t);
 template void col2im<bf16>(const bf16*, bf16*, int64_t, int, int, int, int, int, int, int, int, int, const bf16*, cudaStream_t);
 
+template <typename T>
+__global__ void repack_filter_dgrad_kernel(const float* __restrict__ w, T* __restrict__ out, int O, int I, int kh, int kw) {
+  const int64_t kk = (int64_t)kh * kw * O, total = (int64_t)I * kk;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(idx / kk), k = (int)(idx % kk);
+    const int tap = k / O, o = k % O, r = kh - 1 - tap / kw, s = kw - 1 - tap % kw;
+    out[idx] = from_f<T>(w[(((int64_t)o * I + c) * kh + r) * kw + s]);
+  }
+}
+template <typename T>
+void repack_filter_dgrad(const float* oihw, T* out, int O, int I, int kh, int kw, cudaStream_t s) {
+  repack_filter_dgrad_kernel<T><<<ew_blocks((int64_t)O * I * kh * kw), EW_THREADS, 0, s>>>(oihw, out, O, I, kh, kw);
+  LAUNCH_OK();
+}
+template void repack_filter_dgrad<float>(const float*, float*, int, int, int, int, cudaStream_t);
+template void repack_filter_dgrad<bf16>(const float*, bf16*, int, int, int, int, cudaStream_t);
+
 void filter_grad_unpack(const float* dwk, float* dw, int O, int C, int kh, int kw, int kpad, cudaStream_t s) {
   filter_grad_unpack_kernel<<<ew_blocks((int64_t)O * C * kh * kw), EW_THREADS, 0, s>>>(dwk, dw, O, C, kh, kw, kpad);
   LAUNCH_OK();

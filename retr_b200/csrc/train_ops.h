@@ -26,6 +26,10 @@ void im2col_T(const T* x, T* colT, int64_t ldm, int64_t nimg, int H, int W, int 
 template <typename T>
 void col2im(const T* dcol, T* dx, int64_t nimg, int H, int W, int C, int k, int stride, int pad, int dil, int OH, int OW,
             const T* add, cudaStream_t s);
+// Filter of the input-gradient convolution (stride 1): out[c, ((kh-1-r)*kw + (kw-1-s))*O + o] = w[o, c, r, s]
+// (OIHW fp32 master -> [C_in, (kh,kw,C_out)] with the taps flipped), so dx = conv(dy, out) with pad' = dil*(k-1) - pad.
+template <typename T>
+void repack_filter_dgrad(const float* oihw, T* out, int O, int I, int kh, int kw, cudaStream_t s);
 // dW[o, c, r, s] = dWk[o, (r*kw+s)*C + c]      (fp32; kpad = row pitch of dWk)
 void filter_grad_unpack(const float* dwk, float* dw, int O, int C, int kh, int kw, int kpad, cudaStream_t s);
 // sum of partial C tiles written by a split-K GEMM: out[i] (+)= sum_s part[s*n + i]
