@@ -185,10 +185,16 @@ __global__ void __launch_bounds__(128) flash_train_fwd_kernel(const AttnTrainPar
     l0 = l0 * cr0 + rs0; l1 = l1 * cr1 + rs1;          // the normaliser is that of the un-dropped softmax
     if (p.drop.p > 0.f) {
 #pragma unroll
-      for (int nt = 0; nt < 8; ++nt) {
-        const uint32_t j = (uint32_t)(kbase + nt * 8 + c4 * 2);
-        const float2 k0 = drop_scale_cols2(p.drop, (uint64_t)prow0, j), k1 = drop_scale_cols2(p.drop, (uint64_t)prow1, j);
-        s[nt][0] *= k0.x; s[nt][1] *= k0.y; s[nt][2] *= k1.x; s[nt][3] *= k1.y;
+      for (int gq = 0; gq < 2; ++gq) {                    // one evaluation per row and 32-key group: four 8-key tiles
+        const uint32_t j = (uint32_t)(kbase + gq * 32 + c4 * 2);
+        const uint4 r0 = drop_block_row8(p.drop, (uint64_t)prow0, j), r1 = drop_block_row8(p.drop, (uint64_t)prow1, j);
+        const uint32_t w0[4] = {r0.x, r0.y, r0.z, r0.w}, w1[4] = {r1.x, r1.y, r1.z, r1.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int nt = gq * 4 + q;
+          const float2 k0 = drop_keep_pair(p.drop, w0[q]), k1 = drop_keep_pair(p.drop, w1[q]);
+          s[nt][0] *= k0.x; s[nt][1] *= k0.y; s[nt][2] *= k1.x; s[nt][3] *= k1.y;
+        }
       }
     }
 #pragma unroll
@@ -292,10 +298,20 @@ __global__ void __launch_bounds__(128) flash_train_bwd_dq_kernel(const AttnBwdPa
     mma_a_tileT<DH>(s, qa, Ks[buf], lane);
     mma_a_tileT<DH>(dp, da, Vs[buf], lane);
     const int kbase = t * TK;
+    uint32_t dw0[8], dw1[8];                              // dropout words of this thread's two rows, one per 8-key tile
+    if (p.drop.p > 0.f) {
+#pragma unroll
+      for (int gq = 0; gq < 2; ++gq) {
+        const uint32_t jq = (uint32_t)(kbase + gq * 32 + c4 * 2);
+        const uint4 r0 = drop_block_row8(p.drop, (uint64_t)prow0, jq), r1 = drop_block_row8(p.drop, (uint64_t)prow1, jq);
+        dw0[gq * 4] = r0.x; dw0[gq * 4 + 1] = r0.y; dw0[gq * 4 + 2] = r0.z; dw0[gq * 4 + 3] = r0.w;
+        dw1[gq * 4] = r1.x; dw1[gq * 4 + 1] = r1.y; dw1[gq * 4 + 2] = r1.z; dw1[gq * 4 + 3] = r1.w;
+      }
+    }
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt) {
-      const uint32_t jb = (uint32_t)(kbase + nt * 8 + c4 * 2);
-      const float2 ka = drop_scale_cols2(p.drop, (uint64_t)prow0, jb), kb = drop_scale_cols2(p.drop, (uint64_t)prow1, jb);
+      float2 ka = make_float2(1.f, 1.f), kb = make_float2(1.f, 1.f);
+      if (p.drop.p > 0.f) { ka = drop_keep_pair(p.drop, dw0[nt]); kb = drop_keep_pair(p.drop, dw1[nt]); }
       const float ks0[2] = {ka.x, ka.y}, ks1[2] = {kb.x, kb.y};
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
@@ -383,17 +399,21 @@ __global__ void __launch_bounds__(128) flash_train_bwd_kv_kernel(const AttnBwdPa
     const int qbase = t * TK;
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt) {
-      // queries i (even) and i + 1 of this thread: one Philox evaluation per key row.  (bh*Lq + i) keeps the parity
-      // of i only when bh*Lq is even, so the pair is split into two single lookups otherwise.
+      // queries i and i + 1 of this thread, keys krow0 and krow0 + 8 (same 32-key group, same column pair): lane g and
+      // its neighbour g ^ 1 (lane ^ 4) need the same two evaluations, so each computes ONE row and they swap the two
+      // words that hold keys krow0.. and krow0 + 8..
       const int64_t prow_e = bh * p.Lq + qbase + nt * 8 + c4 * 2;
-      float ms0[2], ms1[2];
-      if (prow_e & 1) {
-        ms0[0] = drop_scale_rc(p.drop, (uint64_t)prow_e, (uint32_t)krow0); ms0[1] = drop_scale_rc(p.drop, (uint64_t)prow_e + 1, (uint32_t)krow0);
-        ms1[0] = drop_scale_rc(p.drop, (uint64_t)prow_e, (uint32_t)(krow0 + 8)); ms1[1] = drop_scale_rc(p.drop, (uint64_t)prow_e + 1, (uint32_t)(krow0 + 8));
-      } else {
-        const float2 a0 = drop_scale_rows2(p.drop, (uint64_t)prow_e, (uint32_t)krow0);
-        const float2 a1 = drop_scale_rows2(p.drop, (uint64_t)prow_e, (uint32_t)(krow0 + 8));
-        ms0[0] = a0.x; ms0[1] = a0.y; ms1[0] = a1.x; ms1[1] = a1.y;
+      float ms0[2] = {1.f, 1.f}, ms1[2] = {1.f, 1.f};
+      if (p.drop.p > 0.f) {
+        const uint32_t mine = (uint32_t)g & 1u, t0 = ((uint32_t)krow0 >> 3) & 3u;
+        const uint4 blk = drop_block_row8(p.drop, (uint64_t)(prow_e + mine), (uint32_t)krow0);
+        const uint32_t wa = drop_word(blk, t0), wb = drop_word(blk, t0 + 1);
+        const uint32_t oa = __shfl_xor_sync(0xffffffffu, wa, 4), ob = __shfl_xor_sync(0xffffffffu, wb, 4);
+        const uint32_t half = (uint32_t)krow0 & 1u;
+        const float ma = drop_keep_half(p.drop, wa, half), mb = drop_keep_half(p.drop, wb, half);
+        const float xa = drop_keep_half(p.drop, oa, half), xb = drop_keep_half(p.drop, ob, half);
+        ms0[0] = mine ? xa : ma; ms0[1] = mine ? ma : xa;
+        ms1[0] = mine ? xb : mb; ms1[1] = mine ? mb : xb;
       }
 #pragma unroll
       for (int e = 0; e < 2; ++e) {

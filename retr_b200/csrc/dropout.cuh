@@ -27,34 +27,34 @@ __device__ __forceinline__ float drop_scale(const DropCfg& dc, uint64_t idx) {
   return ((float)w * 2.3283064365386963e-10f >= dc.p) ? 1.f / (1.f - dc.p) : 0.f;
 }
 
-// Attention probabilities are indexed (row = (b*H + h)*Lq + i, key j).  One Philox evaluation covers a 2 x 2 patch
-// (rows row&~1..|1, keys j&~1..|1; word = 2*(row&1) + (j&1)), so the two adjacent keys a thread owns in an MMA
-// accumulator fragment of the forward / dQ kernels, and the two adjacent queries it owns in the transposed
-// dK/dV kernel, each come from ONE evaluation.
-__device__ __forceinline__ uint4 drop_block_rc(const DropCfg& dc, uint64_t row, uint32_t col) {
+// Attention probabilities are indexed (row = (b*H + h)*Lq + i, key j).  One Philox evaluation yields EIGHT 16-bit
+// decisions: row `row`, the eight keys {32*G + 8*t + 2*c + e : t = 0..3, e = 0..1} — the keys one thread of an MMA
+// accumulator fragment owns across four consecutive 8-key tiles (its column pair c).  Field (t, e) = half e of word t;
+// an element is kept iff its field >= round(p * 65536), and kept elements are scaled by the exact reciprocal of that
+// keep probability.  (The first version spent one evaluation per 2 x 2 patch of which a thread used half: the Philox
+// rounds were two thirds of the ALU work of the three training attention kernels — 20 ms of a 77 ms step.)
+__device__ __forceinline__ uint4 drop_block_row8(const DropCfg& dc, uint64_t row, uint32_t col) {
   return philox4(make_uint2((uint32_t)dc.seed, (uint32_t)(dc.seed >> 32)),
-                 make_uint4(col >> 1, (uint32_t)(row >> 1), dc.site ^ 0x80000000u, (uint32_t)(row >> 33)));
+                 make_uint4(((col >> 5) << 2) | ((col >> 1) & 3u), (uint32_t)row, dc.site ^ 0x80000000u,
+                            (uint32_t)(row >> 32)));
 }
-__device__ __forceinline__ float drop_keep(const DropCfg& dc, uint32_t w) {
-  return ((float)w * 2.3283064365386963e-10f >= dc.p) ? 1.f / (1.f - dc.p) : 0.f;
+__device__ __forceinline__ uint32_t drop_thr16(const DropCfg& dc) { return (uint32_t)(dc.p * 65536.f + 0.5f); }
+__device__ __forceinline__ uint32_t drop_word(const uint4& r, uint32_t t) {
+  return t == 0 ? r.x : (t == 1 ? r.y : (t == 2 ? r.z : r.w));
+}
+// both halves of one word: (row, col) and (row, col + 1), col even
+__device__ __forceinline__ float2 drop_keep_pair(const DropCfg& dc, uint32_t w) {
+  const uint32_t thr = drop_thr16(dc);
+  const float sc = 65536.f / (65536.f - (float)thr);
+  return make_float2((w & 0xFFFFu) >= thr ? sc : 0.f, (w >> 16) >= thr ? sc : 0.f);
+}
+__device__ __forceinline__ float drop_keep_half(const DropCfg& dc, uint32_t w, uint32_t e) {
+  const float2 k = drop_keep_pair(dc, w);
+  return e ? k.y : k.x;
 }
 __device__ __forceinline__ float drop_scale_rc(const DropCfg& dc, uint64_t row, uint32_t col) {
   if (dc.p <= 0.f) return 1.f;
-  const uint4 r = drop_block_rc(dc, row, col);
-  const uint32_t sel = (((uint32_t)row & 1u) << 1) | (col & 1u);
-  return drop_keep(dc, sel == 0 ? r.x : (sel == 1 ? r.y : (sel == 2 ? r.z : r.w)));
-}
-// (row, col) and (row, col + 1), col even
-__device__ __forceinline__ float2 drop_scale_cols2(const DropCfg& dc, uint64_t row, uint32_t col) {
-  if (dc.p <= 0.f) return make_float2(1.f, 1.f);
-  const uint4 r = drop_block_rc(dc, row, col);
-  return (row & 1u) ? make_float2(drop_keep(dc, r.z), drop_keep(dc, r.w)) : make_float2(drop_keep(dc, r.x), drop_keep(dc, r.y));
-}
-// (row, col) and (row + 1, col), row even
-__device__ __forceinline__ float2 drop_scale_rows2(const DropCfg& dc, uint64_t row, uint32_t col) {
-  if (dc.p <= 0.f) return make_float2(1.f, 1.f);
-  const uint4 r = drop_block_rc(dc, row, col);
-  return (col & 1u) ? make_float2(drop_keep(dc, r.y), drop_keep(dc, r.w)) : make_float2(drop_keep(dc, r.x), drop_keep(dc, r.z));
+  return drop_keep_half(dc, drop_word(drop_block_row8(dc, row, col), (col >> 3) & 3u), col & 1u);
 }
 
 }  // namespace retr
