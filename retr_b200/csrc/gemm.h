@@ -27,7 +27,8 @@ struct GemmParams {
   const void* residual = nullptr;
   int64_t ldr = 0;
   bool res_fp32 = false;
-  int relu = 0;                 // 0 none, 1 before residual, 2 after residual
+  int relu = 0;                 // 0 none, 1 before residual, 2 after residual, 3: ReLU BACKWARD — `residual` is the
+                                // forward activation, the result is kept where it was > 0 (bf16 / tcgen05 only)
   bool out_fp32 = false;
   ConvView conv;
   unsigned long long* argmax_out = nullptr;

@@ -250,7 +250,23 @@ __device__ __forceinline__ void epilogue_chunk_staged(const KArgs& a, uint32_t (
 #pragma unroll
     for (int c = 0; c < NCH; ++c) {
       const uint4 t = *reinterpret_cast<const uint4*>(rrow + (((uint32_t)(chunk16 + c) ^ swz) << 4));
-      if (sizeof(OutT) == 4) {
+      if (a.relu == 3) {
+        // ReLU backward: the "residual" tile is the forward activation; keep the gradient where it was positive
+        if (sizeof(OutT) == 4) {
+          if (!(__uint_as_float(t.x) > 0.f)) v[4 * c] = 0.f;
+          if (!(__uint_as_float(t.y) > 0.f)) v[4 * c + 1] = 0.f;
+          if (!(__uint_as_float(t.z) > 0.f)) v[4 * c + 2] = 0.f;
+          if (!(__uint_as_float(t.w) > 0.f)) v[4 * c + 3] = 0.f;
+        } else {
+          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&t);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float2 f = __bfloat1622float2(h[q]);
+            if (!(f.x > 0.f)) v[8 * c + 2 * q] = 0.f;
+            if (!(f.y > 0.f)) v[8 * c + 2 * q + 1] = 0.f;
+          }
+        }
+      } else if (sizeof(OutT) == 4) {
         v[4 * c] += __uint_as_float(t.x); v[4 * c + 1] += __uint_as_float(t.y);
         v[4 * c + 2] += __uint_as_float(t.z); v[4 * c + 3] += __uint_as_float(t.w);
       } else {
@@ -738,11 +754,12 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
   const int sms = sm_count();
   int bn = 256;
   int splits = 1;
+  const int bn_min = (tn || p.relu == 3) ? 64 : 32;      // MN-major boxes / the staged bf16 epilogue need 64 columns
   if (p.split_k != 1) {
     RETR_CHECK(p.out_fp32 && p.C && p.ldc == p.N && !p.scale && !p.bias && !p.rowbias && !p.residual && !p.relu &&
                    !p.argmax_out && !p.c_group,
                "split-K GEMM takes a plain fp32 C and no epilogue operands");
-    while (bn > (tn ? 64 : 32) && bn / 2 >= p.N) bn /= 2;
+    while (bn > bn_min && bn / 2 >= p.N) bn /= 2;
     const int64_t tiles = cdiv(p.M, BM) * cdiv(p.N, bn);
     splits = p.split_k > 1 ? p.split_k : (int)std::max<int64_t>(1, (2 * sms) / tiles);
     splits = std::min(splits, std::max(1, ka.num_kb / 4));
@@ -750,7 +767,7 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
     else splits = 1;
     splits = std::max(splits, 1);
   } else {
-    while (bn > (tn ? 64 : 32) && (bn / 2 >= p.N || cdiv(p.M, BM) * cdiv(p.N, bn) < sms)) bn /= 2;
+    while (bn > bn_min && (bn / 2 >= p.N || cdiv(p.M, BM) * cdiv(p.N, bn) < sms)) bn /= 2;
   }
   ka.kb_per_split = (int)cdiv(ka.num_kb, splits);
   splits = (int)cdiv(ka.num_kb, ka.kb_per_split);          // no empty split
@@ -764,6 +781,7 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
   ka.tma_epi = !force_direct && splits == 1 && ka.vecC && !p.argmax_out && !p.c_group && (p.out_fp32 || bn >= 64) &&
                (!ka.residual || (ka.vecR && ka.res_fp32 == p.out_fp32));
   ka.res_tma = ka.tma_epi && ka.residual;
+  RETR_CHECK(p.relu != 3 || ka.res_tma, "relu == 3 (mask by the residual operand) needs the staged TMA epilogue");
   ka.m_tiles = (int)cdiv(p.M, BM);
   ka.n_tiles = (int)cdiv(p.N, bn);
   const int grid = (int)std::min<int64_t>((int64_t)ka.m_tiles * ka.n_tiles * splits, g_cta_cap > 0 ? std::min(g_cta_cap, sms) : sms);

@@ -182,8 +182,10 @@ class TrainerT final : public TrainerBase {
              bool accumulate, cudaStream_t s);
   void lin_bwd(const TLin<T>& l, const T* dy, int64_t ld_dy, const T* x, int64_t ld_x, int64_t M, void* dx, bool dx_fp32,
                float* bias_grad, cudaStream_t s);
-  void conv_bwd(const TConv<T>& c, const T* g, const T* x, int64_t nimg, int H, int OH, T* dx, const T* dx_add,
-                bool need_dx, cudaStream_t s);
+  // returns true when the ReLU/FrozenBN backward of the layer BELOW (dx <- dx * (relu_out > 0) * relu_scale[c]) was
+  // folded into the input-gradient GEMM's epilogue; otherwise the caller runs relu_bn_bwd on dx
+  bool conv_bwd(const TConv<T>& c, const T* g, const T* x, int64_t nimg, int H, int OH, T* dx, const T* dx_add,
+                bool need_dx, cudaStream_t s, const T* relu_out = nullptr, const float* relu_scale = nullptr);
   void attn_fwd(const T* q, int64_t ldq, const T* k, const T* v, int64_t ldkv, T* out, T* probs, float* lse, int Lq,
                 int Lk, const uint8_t* pad, int causal, unsigned site, cudaStream_t s);
   void attn_bwd(const T* q, int64_t ldq, const T* k, const T* v, int64_t ldkv, const T* probs, const float* lse,
@@ -733,8 +735,11 @@ void TrainerT<T>::lin_bwd(const TLin<T>& l, const T* dy, int64_t ld_dy, const T*
 
 // g = dL/d(conv output) with the FrozenBN scale already applied, [nimg*OH*OH, cout]; x = conv input NHWC
 template <typename T>
-void TrainerT<T>::conv_bwd(const TConv<T>& c, const T* g, const T* x, int64_t nimg, int H, int OH, T* dx, const T* dx_add,
-                           bool need_dx, cudaStream_t s) {
+bool TrainerT<T>::conv_bwd(const TConv<T>& c, const T* g, const T* x, int64_t nimg, int H, int OH, T* dx, const T* dx_add,
+                           bool need_dx, cudaStream_t s, const T* relu_out, const float* relu_scale) {
+  static const bool fuse_env = getenv("RETR_FUSE_RELU_BWD") && atoi(getenv("RETR_FUSE_RELU_BWD")) != 0;   // off until verified
+  const bool can_mask = fuse_env && std::is_same<T, bf16>::value && relu_out && !dx_add && c.cin % 64 == 0;
+  bool fused = false;
   const int64_t Mo = nimg * OH * OH, Mp = rup(Mo, 16);
   const int kk = c.k * c.k * c.cin;
   const bool plain = c.k == 1 && c.stride == 1;
@@ -774,6 +779,7 @@ void TrainerT<T>::conv_bwd(const TConv<T>& c, const T* g, const T* x, int64_t ni
     p.conv.kh = p.conv.kw = c.k; p.conv.stride = 1; p.conv.pad = c.dil * (c.k - 1) - c.pad; p.conv.dil = c.dil;
     p.conv.H = OH; p.conv.W = OH; p.conv.C = c.cout; p.conv.OH = H; p.conv.OW = H;
     if (dx_add) { p.residual = dx_add; p.ldr = c.cin; p.res_fp32 = false; }
+    if (can_mask) { p.scale = relu_scale; p.residual = relu_out; p.ldr = c.cin; p.res_fp32 = false; p.relu = 3; fused = true; }
     gemmT<T>(p, s);
   } else if (need_dx) {
     GemmParams p;
@@ -781,6 +787,7 @@ void TrainerT<T>::conv_bwd(const TConv<T>& c, const T* g, const T* x, int64_t ni
     if (plain) {
       p.C = dx;
       if (dx_add) { p.residual = dx_add; p.ldr = kk; p.res_fp32 = std::is_same<T, float>::value; }
+      if (can_mask) { p.scale = relu_scale; p.residual = relu_out; p.ldr = kk; p.res_fp32 = false; p.relu = 3; fused = true; }
       gemmT<T>(p, s);
     } else {
       p.C = dcol_;
@@ -788,6 +795,7 @@ void TrainerT<T>::conv_bwd(const TConv<T>& c, const T* g, const T* x, int64_t ni
       col2im<T>(dcol_, dx, nimg, H, H, c.cin, c.k, c.stride, c.pad, c.dil, OH, OH, dx_add, s);
     }
   }
+  return fused;
 }
 
 // ---- backward -------------------------------------------------------------------------------------------------------
@@ -921,10 +929,10 @@ void TrainerT<T>::backward_impl(cudaStream_t s) {
       const int64_t Mo = NI * b.Hout * b.Hout, Mi = NI * b.Hin * b.Hin;
       T *g3s = bb_[2], *g3 = bb_[3], *t2 = bb_[4], *t1 = bb_[5], *gid = bb_[6];
       relu_bn_bwd<T>(dy, b.y, b.c3.scale, g3s, g3, Mo, b.c3.cout, s);
-      conv_bwd(b.c3, g3s, b.o2, NI, b.Hout, b.Hout, t2, nullptr, true, s);
-      relu_bn_bwd<T>(t2, b.o2, b.c2.scale, t2, nullptr, Mo, b.c2.cout, s);
-      conv_bwd(b.c2, t2, b.o1, NI, b.Hin, b.Hout, t1, nullptr, true, s);
-      relu_bn_bwd<T>(t1, b.o1, b.c1.scale, t1, nullptr, Mi, b.c1.cout, s);
+      if (!conv_bwd(b.c3, g3s, b.o2, NI, b.Hout, b.Hout, t2, nullptr, true, s, b.o2, b.c2.scale))
+        relu_bn_bwd<T>(t2, b.o2, b.c2.scale, t2, nullptr, Mo, b.c2.cout, s);
+      if (!conv_bwd(b.c2, t2, b.o1, NI, b.Hin, b.Hout, t1, nullptr, true, s, b.o1, b.c1.scale))
+        relu_bn_bwd<T>(t1, b.o1, b.c1.scale, t1, nullptr, Mi, b.c1.cout, s);
       const T* idgrad = g3;
       if (b.has_ds) {
         relu_bn_bwd<T>(g3, nullptr, b.ds.scale, g3s, nullptr, Mo, b.ds.cout, s);

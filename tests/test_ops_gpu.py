@@ -181,6 +181,22 @@ def test_conv_implicit_gemm(dtype, out_fp32, cin, cout, k, stride, pad, dil, H):
         assert bool(((got.float() - ref).abs() <= ref.abs() * 2 ** -8 + 2e-4).all())
 
 
+@pytest.mark.parametrize("M,N,K", [(300, 128, 512), (1000, 64, 256), (256, 512, 2048)])
+def test_gemm_relu_backward_epilogue(M, N, K):
+    """relu == 3: the residual operand is the forward activation, the (scaled) result is kept where it was > 0 — the
+    ReLU + FrozenBN backward (dx * (out > 0) * scale[c]) folded into the input-gradient GEMM."""
+    torch.manual_seed(M + N + K)
+    dev = "cuda"
+    A = torch.randn(M, K, device=dev).bfloat16()
+    W = (torch.randn(N, K, device=dev) / math.sqrt(K)).bfloat16()
+    act = torch.randn(M, N, device=dev).relu().bfloat16()           # about half zeros, like a ReLU output
+    scale = torch.rand(N, device=dev) + 0.5
+    ref = (A.float() @ W.float().t()) * scale * (act.float() > 0)
+    got, _ = run_gemm(BF16, A, W, M=M, N=N, K=K, scale=scale, residual=act, relu=3)
+    assert bool(((got.float() - ref).abs() <= ref.abs() * 2 ** -8 + 2e-4).all())
+    assert bool((got.float()[act.float() <= 0] == 0).all())
+
+
 @pytest.mark.parametrize("M,N,K", [(256, 256, 4096), (200, 576, 1000), (64, 64, 128), (1000, 520, 300), (128, 2304, 25088)])
 def test_gemm_mn_major(M, N, K):
     """C = A^T B with A [K,M] and B [K,N] read in place (MN-major tcgen05 operands): the weight-gradient contraction
