@@ -194,3 +194,49 @@ def test_eval_model_shell_collects_hypotheses_and_references():
     assert seen["hyp"] == ["w7 w9", "w8", "w7 w9", "w8"]
     assert seen["ref"] == [["w5 w6", "w8", "w1", "w5 w6"], ["w5", "w8 w8", "w2", "w5"]]   # transposed (engine.py:180)
     assert engine.eval_model(model, Loader(batches), tok, SimpleNamespace(max_position_embeddings=8))[0] == {}
+
+
+def test_greedy_stream_two_contexts_call_order(monkeypatch):
+    """Host logic of greedy_stream(contexts=2): the NEXT batch is encoded (asynchronously) on the other context before
+    the current one is decoded; outputs come back in batch order; a ragged last batch is fine.  Scripted contexts, no
+    device."""
+    from retr_b200.eval_utils import decode
+    from retr_b200.models.utils import NestedTensor
+    m, _, _ = build_product_model("CaptionGlobalLoc")
+    log = []
+
+    class FakeEngine:
+        def __init__(self, name):
+            self.name, self.max_batch, self.cur, self.cap = name, 4, None, None
+
+        def set_encode_cta_cap(self, cap):
+            self.cap = cap
+
+        def encode_host(self, t_img, t_mask, g_img, g_mask, loc):
+            assert t_mask.dtype == torch.uint8 and t_img.is_contiguous()
+            self.cur = int(loc[0, 0])
+            log.append((self.name, "encode", self.cur))
+
+        def decode_host(self, bos, eos, max_len):
+            log.append((self.name, "decode", self.cur))
+            return torch.full((1, max_len), self.cur, dtype=torch.int64), max_len - 1
+
+    engs = [FakeEngine("a"), FakeEngine("b")]
+    monkeypatch.setattr(m, "pipeline_engines", lambda batch, n=2: engs)
+
+    def unpinned(model, samples):                      # pin_memory needs a CUDA runtime; the order logic does not
+        t, g, loc = model._split_samples(samples)
+        return [t.tensors, t.mask.to(torch.uint8), g.tensors, g.mask.to(torch.uint8), loc]
+    monkeypatch.setattr(decode, "_stage_host", unpinned)
+
+    def batch(tag, b):
+        img, mask = torch.zeros(b, 3, 8, 8), torch.zeros(b, 8, 8, dtype=torch.bool)
+        return (NestedTensor(img, mask), NestedTensor(img, mask), torch.full((b, 5), float(tag)))
+    outs = list(decode.greedy_stream([batch(0, 2), batch(1, 2), batch(2, 1)], m, max_len=6, bos_token=101, eos_token=102,
+                                     contexts=2, encode_cta_cap=100))
+    assert [int(o[0, 0]) for o in outs] == [0, 1, 2]
+    assert log == [("a", "encode", 0), ("b", "encode", 1), ("a", "decode", 0), ("a", "encode", 2), ("b", "decode", 1),
+                   ("a", "decode", 2)]
+    assert engs[0].cap == 100 and engs[1].cap == 100
+    with pytest.raises(RuntimeError):                  # a later batch larger than the contexts were sized for
+        list(decode.greedy_stream([batch(0, 2), batch(1, 5)], m, max_len=6, contexts=2))
