@@ -2,6 +2,7 @@
 """Headline benchmark: referring expressions/sec, greedy decode, max_len 128 (BASELINE.json).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--impl native|reference]
+                    [--workload default|scaled] [--no-train-leg] [--no-parity-leg] [--no-cpu-baseline]
 
 One "step" = one greedy decode of a batch of B synthetic RefCOCO-shaped samples through the hot
 path (backbone x2 -> concat encoder -> 127 KV-cached decode steps).  N>1 is launched with torchrun,
@@ -10,11 +11,17 @@ weak scaling), timing is CUDA events bracketed by barrier + synchronize, max ove
 
 Keys of the JSON line (see the round brief): value = device-resident throughput; e2e = the same
 through the host-buffer C-ABI call (H2D of the samples and D2H of the ids inside the timed region);
-roofline = the dominant kernel (tcgen05 implicit-GEMM over the backbone phase); cpu_baseline = the
-reference algorithm (oracle port: full model recompute per token, eval_utils/decode.py:68-79) on
-the host cores for a bounded sample.
+roofline = the dominant kernel (tcgen05 implicit-GEMM over the backbone phase) + the decode phase against
+HBM + the combined two-phase figure; parity = strict / teacher-forced agreement of the benchmarked
+precision against the fp32 mode on a sub-batch; train_step = the data-parallel training step
+(BASELINE.json configs[3]) at the same N, the path's one real collective; cpu_baseline = the
+reference's own greedy loop (oracle/_ref when present, else the oracle port) on the host cores for a
+bounded sample.
 """
 import argparse
+import contextlib
+import hashlib
+import io
 import json
 import os
 import subprocess
@@ -30,22 +37,24 @@ sys.path.insert(0, ROOT)
 METRIC = "referring expressions/sec (greedy, max_len 128)"
 BOS, EOS, MAX_LEN = 101, 102, 128
 KIND = "CaptionGlobalLoc"
-# algorithmic FLOPs per expression, default config
-BACKBONE_GFLOP_PER_IMAGE = 19.838
-TOTAL_GFLOP_PER_EXPR = 54.55
-DECODE_MB_PER_EXPR_B256 = 385.0
-# measured (ncu dram__bytes_read.sum + dram__bytes_write.sum over the 108 launches of the 512-image backbone pass, bf16,
-# TMA-im2col build; profiles/r1_backbone_v2_dram.txt): 45.955 GB per pass
-BACKBONE_DRAM_BYTES_PER_IMAGE = 45.955e9 / 512
+# algorithmic work per expression.  encode = backbone x2 + input_proj + encoder + cross K/V (tensor
+# bound); decode = cross-KV + self-KV + decoder/head weights streamed per step (HBM bound; weights term = 127 W / B).
+WORKLOADS = {
+    "default": dict(cfg=dict(), batch=256, name="ResNet-101 d256 6+6", backbone_gflop_img=19.838,
+                    encode_gflop=47.92, total_gflop=54.55, kv_mb=309.8 + 49.9, weights_mb=50.9,
+                    ref="BASELINE.json configs[1]"),
+    "scaled": dict(cfg=dict(backbone="ResNet152", hidden_dim=512), batch=64, name="ResNet-152 d512 6+6",
+                   backbone_gflop_img=27.262, encode_gflop=54.524 + 0.822 + 16.923 + 2.498, total_gflop=85.18,
+                   kv_mb=619.5 + 99.9, weights_mb=82.6, ref="BASELINE.json configs[4]: 512 samples over 8 GPUs = 64/GPU"),
+}
 
 
-def build_model(precision):
+def build_model(precision, workload="default"):
     from retr_b200 import synthetic
     from retr_b200.configuration import Config
     from retr_b200.models import caption
-    cfg = Config(use_global_features=True, use_location_features=True)
+    cfg = Config(use_global_features=True, use_location_features=True, **WORKLOADS[workload]["cfg"])
     torch.manual_seed(cfg.seed)
-    import contextlib, io
     with contextlib.redirect_stdout(io.StringIO()):
         model, _ = caption.build_model(cfg)
     # documented seeded transform so FrozenBN is not the identity (see synthetic.calibrate_frozen_bn)
@@ -98,24 +107,99 @@ def measured_peaks():
     return 1400.0, 6650.0, "fallback"
 
 
-def cpu_reference_throughput(batch, steps):
-    """The reference algorithm on the host cores: literal greedy (full forward per token) for a
-    bounded number of steps; per-step cost is constant (always 128 positions, both ResNet passes),
-    so expr/s = batch / (127 * seconds_per_step)."""
-    from oracle import retr_oracle as O
-    from retr_b200 import synthetic
-    model, cfg = build_model("fp32")
-    sd = model.state_dict()
-    data = synthetic.make_batch(batch, shard=0)
-    enc = (data["t_img"], data["t_mask"], data["g_img"], data["g_mask"], data["loc"])
-    cores = torch.get_num_threads()
-    with torch.no_grad():
-        O.greedy(sd, cfg, *enc, max_len=MAX_LEN, bos_token=BOS, eos_token=EOS, literal=True, max_steps=1)  # warm-up
-        t0 = time.perf_counter()
-        _, ran = O.greedy(sd, cfg, *enc, max_len=MAX_LEN, bos_token=BOS, eos_token=EOS, literal=True, max_steps=steps)
-        dt = time.perf_counter() - t0
-    per_step = dt / ran
-    return batch / (per_step * (MAX_LEN - 1)), cores, per_step, ran
+def backbone_traffic_bytes_per_image():
+    """DRAM read+write bytes per image of the backbone pass from the committed ncu table — only while the kernels
+    it was measured on are the kernels in the tree (the table records a hash of the GEMM + schedule sources)."""
+    p = os.path.join(ROOT, "profiles", "backbone_dram_traffic.json")
+    if not os.path.exists(p):
+        return None, "no committed ncu table"
+    t = json.load(open(p))
+    h = hashlib.sha256()
+    for f in t.get("sources", []):
+        with open(os.path.join(ROOT, f), "rb") as fh:
+            h.update(fh.read())
+    if h.hexdigest()[:16] != t.get("sources_sha16"):
+        return None, f"stale: {t.get('from')} was measured on other kernel sources"
+    return float(t["dram_bytes_per_image"]), t.get("from")
+
+
+# ---- the reference's CPU path --------------------------------------------------------------------------------
+def host_threads():
+    """torchrun exports OMP_NUM_THREADS=1; the CPU arm must still use every core this process may run on."""
+    n = int(os.environ.get("RETR_CPU_THREADS", "0")) or len(os.sched_getaffinity(0))
+    torch.set_num_threads(n)
+    return torch.get_num_threads()
+
+
+class _EosAfter:
+    """Bounds the reference's own greedy loop: after `n` full forwards the logits make every row emit EOS, so
+    eval_utils/decode.py:73-76 returns through its own early exit."""
+
+    def __init__(self, model, n, eos):
+        self.model, self.n, self.eos, self.calls = model, n, eos, 0
+
+    def __call__(self, *a, **k):
+        out = self.model(*a, **k)
+        self.calls += 1
+        if self.calls >= self.n:
+            out = out.clone()
+            out[:, :, self.eos] = float("inf")
+        return out
+
+
+class CpuReference:
+    """The reference algorithm (full model recompute per token, eval_utils/decode.py:68-79) on the host cores.
+    kind "reference": the UNMODIFIED modules from oracle/_ref (models.caption.build_model + eval_utils.decode.greedy);
+    kind "port": oracle/retr_oracle.py when oracle/_ref was not built."""
+
+    def __init__(self, batch=8):
+        from retr_b200 import synthetic
+        self.batch, self.cores = batch, host_threads()
+        self.data = synthetic.make_batch(batch, shard=0)
+        model, self.cfg = build_model("fp32")
+        self.sd = {k: v.clone() for k, v in model.state_dict().items()}
+        self.ref = None
+        try:
+            from oracle import make_ref
+            self.ref = make_ref.load()
+        except Exception:
+            self.ref = None
+        if self.ref is not None:
+            cfg = self.ref["Config"]()
+            cfg.use_global_features = cfg.use_location_features = True
+            torch.manual_seed(cfg.seed)
+            with contextlib.redirect_stdout(io.StringIO()):
+                self.model, _ = self.ref["caption"].build_model(cfg)
+            self.model.load_state_dict(self.sd)
+            self.model.eval()
+            NT = self.ref["utils"].NestedTensor
+            d = self.data
+            self.samples = (NT(d["t_img"], d["t_mask"]), NT(d["g_img"], d["g_mask"]), d["loc"])
+        self.kind = "reference" if self.ref is not None else "port"
+
+    def run(self, steps):
+        """-> (expr/s extrapolated to 127 steps, seconds per full-forward step, steps run)"""
+        with torch.no_grad():
+            t0 = time.perf_counter()
+            if self.ref is not None:
+                bounded = _EosAfter(self.model, steps, EOS)
+                self.ref["decode"].greedy(self.samples, bounded, max_len=MAX_LEN, device="cpu", bos_token=BOS,
+                                          eos_token=EOS)
+                ran = bounded.calls
+            else:
+                from oracle import retr_oracle as O
+                d = self.data
+                _, ran = O.greedy(self.sd, self.cfg, d["t_img"], d["t_mask"], d["g_img"], d["g_mask"], d["loc"],
+                                  max_len=MAX_LEN, bos_token=BOS, eos_token=EOS, literal=True, max_steps=steps)
+            dt = time.perf_counter() - t0
+        per_step = dt / ran
+        return self.batch / (per_step * (MAX_LEN - 1)), per_step, ran
+
+    def describe(self, per_step, ran):
+        what = ("unmodified reference modules (oracle/_ref: models.caption + eval_utils.decode.greedy, torch.no_grad)"
+                if self.ref is not None else "oracle port of the reference loop (oracle/_ref absent)")
+        return (f"{what}, batch {self.batch}, full forward per token, {ran} timed steps at {per_step:.2f} s/step on "
+                f"{self.cores} threads, extrapolated x127")
 
 
 def reference_eager_on_gpu(batch, steps, dev):
@@ -143,23 +227,107 @@ def run_reference(args, rank):
     if rank != 0:
         return
     batch = 8                                   # BASELINE.json configs[0]: 8 samples on the CPU
-    vals = []
+    ref = CpuReference(batch)                   # model built ONCE
+    ref.run(1)                                  # page-in / allocator warm-up, not a bench step
+    vals, per = [], []
     for _ in range(args.warmup + args.steps):
-        v, cores, per_step, ran = cpu_reference_throughput(batch, 2)
-        vals.append(v)
-    vals = vals[args.warmup:]
+        v, per_step, ran = ref.run(2)
+        vals.append(v); per.append(per_step)
+    vals, per = vals[args.warmup:], per[args.warmup:]
     value = sum(vals) / len(vals)
-    sample = (f"oracle port of the reference loop, batch {batch}, {ran} timed full-forward steps per bench step, "
-              f"{per_step:.2f} s/step, extrapolated x127 steps")
+    sample = ref.describe(sum(per) / len(per), 2) + " (per bench step)"
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": "expr/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * batch / value,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "CaptionGlobalLoc ResNet-101 d256 6+6, greedy max_len 128, CPU full recompute per token",
-                   "batch": batch},
-        "cpu_baseline": {"value": value, "unit": "expr/s", "cores": cores, "kind": "port", "sample": sample},
+        "config": {"workload": "CaptionGlobalLoc ResNet-101 d256 6+6, greedy max_len 128, CPU full recompute per token "
+                               "(BASELINE.json configs[0])", "batch": batch},
+        "cpu_baseline": {"value": value, "unit": "expr/s", "cores": ref.cores, "kind": ref.kind, "sample": sample},
         "e2e": {"value": value, "unit": "expr/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
+
+
+# ---- extra legs of the native arm -----------------------------------------------------------------------------
+def parity_leg(model16, dev, n=64, shard=900):
+    """Strict sequence-exact % and teacher-forced per-step agreement of the benchmarked precision against the
+    fp32 mode (pinned to the oracle by tests/test_model_gpu.py) on `n` fresh samples.  Outside every timed region."""
+    from retr_b200 import synthetic
+    from retr_b200.eval_utils import decode
+    m32, _ = build_model("fp32")
+    m32.max_batch = n
+    m32 = m32.to(dev)
+    data = synthetic.make_batch(n, shard=shard)
+    s = tuple(x.to(dev) for x in synthetic.pack(data))
+    with torch.no_grad():
+        ref = decode.greedy(s, m32, max_len=MAX_LEN, device=dev, bos_token=BOS, eos_token=EOS)
+        ids = decode.greedy(s, model16, max_len=MAX_LEN, device=dev, bos_token=BOS, eos_token=EOS)
+        cm = torch.zeros(n, MAX_LEN, dtype=torch.bool, device=dev)
+        l32 = m32(*s, ref, cm)[:, :MAX_LEN - 1]
+        l16 = model16(*s, ref, cm)[:, :MAX_LEN - 1]
+        agree = l16.argmax(-1) == l32.argmax(-1)
+        top2 = l32.topk(2, -1).values
+        margin = top2[..., 0] - top2[..., 1]
+        err = (l16 - l32).abs().max().item()
+        out = {"against": "native fp32 mode (== oracle, tests/test_model_gpu.py)", "sequences": n,
+               "strict_exact_pct": 100.0 * float((ids == ref).all(1).float().mean()),
+               "teacher_forced_step_pct": 100.0 * float(agree.float().mean()),
+               "teacher_forced_sequence_pct": 100.0 * float(agree.all(1).float().mean()),
+               "margin_aware_step_pct": 100.0 * float((agree | (margin <= 2 * err)).float().mean()),
+               "max_logit_err_rel": err / l32.abs().max().item(),
+               "fp32_top2_margin_median_rel": float(margin.median()) / l32.abs().max().item(),
+               "fp32_top2_margin_min_per_sequence_median_rel":
+                   float(margin.min(1).values.median()) / l32.abs().max().item()}
+    del m32
+    torch.cuda.empty_cache()
+    return out
+
+
+def train_leg(dev, rank, world, precision, steps=5, warmup=3, batch=128):
+    """BASELINE.json configs[3]: teacher-forced training step, batch 128/GPU, data parallel — forward (dropout 0.1),
+    fused CE, backward with the bucketed NCCL all-reduce overlapped, clip + AdamW.  Device time, max over ranks."""
+    import torch.distributed as dist
+    from retr_b200 import engine as E
+    from retr_b200 import synthetic
+    model, cfg = build_model(precision)
+    model.max_train_batch = batch
+    model = model.to(dev).train()
+    torch.manual_seed(cfg.seed + rank)
+    data = synthetic.make_batch(batch, shard=rank, train=True)
+    samples = tuple(s.to(dev) for s in synthetic.pack(data))
+    caps, masks = data["caps"].to(dev), data["cap_masks"].to(dev)
+
+    def step():
+        return E.train_step_native(model, samples, caps, masks, max_norm=cfg.clip_max_norm, lr=cfg.lr,
+                                   lr_backbone=cfg.lr_backbone, weight_decay=cfg.weight_decay)
+
+    losses = [step()[0] for _ in range(warmup)]
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        losses.append(step()[0])
+    e1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms) / steps
+    tr = model.trainer(batch)
+    tf_peak = measured_peaks()[0]
+    tf = batch / (ms / 1000.0) * 3 * 54.65 / 1000.0
+    out = {"metric": "training samples/sec (fwd + CE + bwd + gradient all-reduce + clip + AdamW)",
+           "value": batch * world / (ms / 1000.0), "unit": "samples/s", "ms_per_step": ms, "batch_per_gpu": batch,
+           "parallelism": f"dp{world}", "dropout": float(model.dropout_p), "steps": steps, "warmup": warmup,
+           "allreduce": tr.allreduce_info() if hasattr(tr, "allreduce_info") else None,
+           "tflops_per_gpu": tf, "frac_of_bf16_peak": tf / tf_peak,
+           "loss_first_last": [float(losses[0]), float(losses[-1])]}
+    del model
+    torch.cuda.empty_cache()
+    return out
 
 
 def main():
@@ -167,10 +335,13 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--batch", type=int, default=256, help="samples per GPU per step")
+    ap.add_argument("--batch", type=int, default=0, help="samples per GPU per step (default: the workload's)")
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--workload", default="default", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-train-leg", action="store_true")
+    ap.add_argument("--no-parity-leg", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -186,8 +357,9 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
-    B = args.batch
-    model, cfg = build_model(args.precision)
+    wl = WORKLOADS[args.workload]
+    B = args.batch or wl["batch"]
+    model, cfg = build_model(args.precision, args.workload)
     model.max_batch = B
     model = model.to(dev)
     # every rank decodes its own shard of samples (seeded by shard id)
@@ -277,19 +449,31 @@ def main():
     value = total / (ms / 1000.0)
     e2e = total / (ms_e2e / 1000.0)
 
+    train = None
+    if not args.no_train_leg and args.workload == "default":
+        try:
+            train = train_leg(dev, rank, world, args.precision)
+        except Exception as e:              # a reported extra, never a reason to lose the bench line
+            train = {"unavailable": f"{type(e).__name__}: {str(e)[:300]}"}
+
     if rank == 0:
         tf_peak, hbm_peak, which = measured_peaks()
-        bb_ms = phases["backbone"] / args.steps
+        ph = {k: v / args.steps for k, v in phases.items()}
+        bb_ms = ph["backbone"]
         n_img = 2 * B
-        achieved = BACKBONE_GFLOP_PER_IMAGE * n_img / (bb_ms / 1000.0) / 1000.0 if bb_ms > 0 else 0.0
+        achieved = wl["backbone_gflop_img"] * n_img / (bb_ms / 1000.0) / 1000.0 if bb_ms > 0 else 0.0
+        traffic_img, traffic_src = backbone_traffic_bytes_per_image() if args.workload == "default" else (None, "n/a")
+        decode_mb = wl["kv_mb"] + wl["weights_mb"] * (MAX_LEN - 1) / B
+        dec_gbs = decode_mb * B / 1000.0 / (ph["decode"] / 1000.0) if ph["decode"] > 0 else 0.0
+        ideal_ms = (wl["encode_gflop"] * B / (tf_peak * 1000.0) + decode_mb * B / (hbm_peak * 1000.0)) * 1000.0
         line = {
             "metric": METRIC, "value": value, "unit": "expr/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
-            "config": {"workload": f"{KIND} ResNet-101 d256 6+6, greedy max_len 128, batch {B}/GPU, KV-cached "
-                                   "CUDA-graph decode (BASELINE.json configs[1])",
+            "config": {"workload": f"{KIND} {wl['name']}, greedy max_len 128, batch {B}/GPU, KV-cached "
+                                   f"CUDA-graph decode ({wl['ref']})",
                        "batch_per_gpu": B, "decode_steps_executed": int(steps_run[-1]), "sharding": "samples",
-                       "l2": "inputs (308 MB/step) exceed L2; no flush",
+                       "l2": f"inputs ({h2d / 1e6:.0f} MB/step) exceed L2; no flush",
                        "cross_kv": "padded keys dropped when the cross K/V caches are built (exact: exp(-inf) = 0)",
                        "weights": "seed-42 build_model init + seeded FrozenBN calibration"},
             "e2e": {"value": e2e, "unit": "expr/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -301,24 +485,35 @@ def main():
                                 "with the current decode; reported beside, not instead of, the serial value"}},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "phases_ms_per_step": {k: v / args.steps for k, v in phases.items()},
+            "phases_ms_per_step": ph,
             "roofline": {"bound": "tensor", "kernel": "gemm_tcgen05_kernel over the backbone phase (conv launches of "
-                         "2B images, incl. stem im2col + maxpool)", "achieved": achieved, "peak": tf_peak,
+                         "2B images, incl. stem + maxpool)", "achieved": achieved, "peak": tf_peak,
                          "unit": "TFLOP/s", "frac": achieved / tf_peak if tf_peak else None,
-                         "traffic": BACKBONE_DRAM_BYTES_PER_IMAGE * n_img if args.precision == "bf16" else None,
-                         "traffic_note": "DRAM read+write bytes of the backbone phase per step (ncu, "
-                                         "profiles/r1_backbone_v2_dram.txt: 45.96 GB per 512-image pass), scaled by images",
+                         "traffic": traffic_img * n_img if traffic_img and args.precision == "bf16" else None,
+                         "traffic_note": f"DRAM read+write bytes of the backbone phase per step, ncu: {traffic_src}",
                          "peak_source": f"{which} bf16 sustained"},
-            "roofline_decode": {"bound": "hbm", "achieved": DECODE_MB_PER_EXPR_B256 * B / 1000.0 /
-                                (phases["decode"] / args.steps / 1000.0) if phases["decode"] > 0 else 0.0,
-                                "peak": hbm_peak, "unit": "GB/s"},
+            "roofline_decode": {"bound": "hbm", "achieved": dec_gbs, "peak": hbm_peak, "unit": "GB/s",
+                                "frac": dec_gbs / hbm_peak,
+                                "bytes_note": f"algorithmic {decode_mb:.0f} MB/expression: all {127} steps x (cross K/V "
+                                              "of every key + self K/V) + decoder/head weights once per step per batch"},
+            "roofline_combined": {"ideal_ms": ideal_ms, "measured_ms": ms / args.steps,
+                                  "frac": ideal_ms / (ms / args.steps),
+                                  "note": "SURVEY §8d: encode FLOPs / sustained bf16 peak + decode bytes / HBM peak, "
+                                          "phases serialised, over the measured step"},
         }
-        line["roofline_decode"]["frac"] = line["roofline_decode"]["achieved"] / hbm_peak
-        if not args.no_cpu_baseline and world == 1:
-            v, cores, per_step, ran = cpu_reference_throughput(8, 6)
-            line["cpu_baseline"] = {"value": v, "unit": "expr/s", "cores": cores, "kind": "port",
-                                    "sample": f"oracle port of the reference loop (full forward per token), batch 8, "
-                                              f"{ran} timed steps at {per_step:.2f} s/step, extrapolated x127"}
+        if train is not None:
+            line["train_step"] = train
+        if not args.no_parity_leg and world == 1 and args.workload == "default" and args.precision != "fp32":
+            try:
+                line["parity"] = parity_leg(model, dev)
+            except Exception as e:
+                line["parity"] = {"unavailable": f"{type(e).__name__}: {str(e)[:300]}"}
+        if not args.no_cpu_baseline and world == 1 and args.workload == "default":
+            ref = CpuReference(8)
+            ref.run(1)
+            v, per_step, ran = ref.run(6)
+            line["cpu_baseline"] = {"value": v, "unit": "expr/s", "cores": ref.cores, "kind": ref.kind,
+                                    "sample": ref.describe(per_step, ran)}
             try:
                 v2, ps2, ran2 = reference_eager_on_gpu(64, 4, dev)
                 line["reference_algorithm_eager_b200"] = {

@@ -79,6 +79,11 @@ class _CaptionBase(nn.Module):
         self.backbone_stride = 16
         self.layer_norm_eps = 1e-12
         self.pre_norm = True
+        # reference models/caption.py:141 un-masks random positions of an all-masked context row (models/utils.py:60-89)
+        # in BOTH modes; finding such a row costs one host sync per forward, so it can be switched off for inputs
+        # known to be sane (real and synthetic RefCOCO samples never have an all-masked context)
+        self.check_all_masked_context = True
+        self.max_train_batch = 0          # capacity of the first native trainer (grows only before the first step)
 
     # ---- native runtime ------------------------------------------------------------------
     def engine(self, batch=1):
@@ -135,8 +140,15 @@ class _CaptionBase(nn.Module):
         stale = (tr is None or tr.device != device or tr.precision != self.precision or tr.max_batch < batch
                  or tr.signature != Trainer.signature_of(self))
         if stale:
-            max_batch = max(batch, tr.max_batch if tr is not None else 0)
+            max_batch = max(batch, self.max_train_batch, tr.max_batch if tr is not None else 0)
             if tr is not None:
+                if tr.step_count > 0 and tr.signature == Trainer.signature_of(self) and tr.device == device \
+                        and tr.precision == self.precision:
+                    # only the batch grew: the AdamW moments and step count live in the old native arena
+                    raise RuntimeError(
+                        f"batch {batch} exceeds the native trainer's capacity {tr.max_batch} after {tr.step_count} "
+                        "optimiser steps; rebuilding would reset the AdamW state. Set model.max_train_batch to the "
+                        "largest batch before the first training step.")
                 tr.close()
             self._trainer = Trainer(self, device, self.precision, max_batch=max_batch,
                                     pad_token_id=self.pad_token_id)
@@ -144,6 +156,7 @@ class _CaptionBase(nn.Module):
 
     def _apply(self, fn, *a, **kw):
         out = super()._apply(fn, *a, **kw)
+        self.__dict__.pop("_version_tensors", None)
         if self._engine is not None:       # parameters moved: pointers held by the context are stale
             self._engine.close()
             self._engine = None
@@ -160,8 +173,20 @@ class _CaptionBase(nn.Module):
         g_img = g_mask = None
         if g_samples is not None:
             g_samples = self._nested(g_samples)
-            g_img, g_mask = g_samples.tensors, g_samples.mask
+            g_img, g_mask = g_samples.tensors, self._context_mask(g_samples.mask)
         return (t_samples.tensors, t_samples.mask, g_img, g_mask, loc, target_exp, target_exp_mask)
+
+    def _context_mask(self, g_mask):
+        """models/caption.py:141 ``ensure_unmasked_values`` on the 14x14 context mask, expressed on the full-size
+        mask the native side subsamples (models/backbone.py:75 picks pixel (16i,16j))."""
+        if not self.check_all_masked_context:
+            return g_mask
+        st = self.backbone_stride
+        m14 = g_mask[:, ::st, ::st]
+        if bool(m14.reshape(m14.shape[0], -1).all(dim=1).any()):
+            m14 = utils.ensure_unmasked_values(m14.clone())
+            g_mask = m14.repeat_interleave(st, 1).repeat_interleave(st, 2)
+        return g_mask
 
     @staticmethod
     def _nested(samples):
@@ -177,14 +202,7 @@ class _CaptionBase(nn.Module):
         g_img = g_mask = None
         if g_samples is not None:
             g_samples = self._nested(g_samples)
-            # all-masked context rows get random positions un-masked (models/utils.py:60-89);
-            # real and synthetic inputs never hit it, so it is checked, not reproduced
-            g_img, g_mask = g_samples.tensors, g_samples.mask
-            st = self.backbone_stride
-            m14 = g_mask[:, ::st, ::st]           # the nearest-interpolated mask (models/backbone.py:75)
-            if bool(m14.reshape(B, -1).all(dim=1).any()):
-                m14 = utils.ensure_unmasked_values(m14.clone())
-                g_mask = m14.repeat_interleave(st, 1).repeat_interleave(st, 2)
+            g_img, g_mask = g_samples.tensors, self._context_mask(g_samples.mask)
         eng.encode(t_samples.tensors, t_samples.mask, g_img, g_mask, loc, att_enc)
         return eng
 

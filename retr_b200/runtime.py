@@ -5,6 +5,7 @@ the library under the reference's key names, and exposes encode / teacher-forced
 greedy decode.  Tensors are only ever passed down as raw device pointers.
 """
 import ctypes as C
+import weakref
 
 import torch
 
@@ -40,6 +41,18 @@ def model_desc(model, device, precision, max_batch, image_size=224):
     return d
 
 
+def check_loc(desc, loc, B):
+    """The native side reads ``B * n_loc`` contiguous floats; a differently shaped tensor would be mis-read
+    silently where the reference's ``loc_proj`` Linear raises a shape error (models/caption.py:60,108,126-128)."""
+    if desc.loc_in_dim == 0:
+        return
+    if loc is None:
+        raise ValueError("this model class takes location features")
+    if tuple(loc.shape) != (B, desc.n_loc):
+        raise RuntimeError(f"location features must be [{B},{desc.n_loc}] for this model, got {tuple(loc.shape)} "
+                           "(CaptionGlobalLoc: set model.n_loc_feats before the first call to change the count)")
+
+
 class Engine:
     def __init__(self, model, device, precision="bf16", max_batch=8, image_size=224):
         device = torch.device(device)
@@ -66,7 +79,14 @@ class Engine:
     # ---- weights --------------------------------------------------------------------------
     @staticmethod
     def version_of(model):
-        return sum(t._version for t in model.state_dict(keep_vars=True).values())
+        """Changes when any parameter/buffer was written through torch (``_version``) or by the native optimiser
+        (``model._weights_epoch``, bumped by Trainer.clip_adamw: it updates the masters through raw pointers, which
+        torch's version counters never see).  The tensor list is cached on the model (rebuilt when it moves)."""
+        tensors = model.__dict__.get("_version_tensors")
+        if tensors is None:
+            tensors = list(model.state_dict(keep_vars=True).values())
+            model.__dict__["_version_tensors"] = tensors
+        return sum(t._version for t in tensors), model.__dict__.get("_weights_epoch", 0)
 
     def _load(self, model):
         for name, t in model.state_dict().items():
@@ -102,6 +122,7 @@ class Engine:
             raise RuntimeError(f"batch {B} exceeds the context's max_batch {self.max_batch}")
         if tuple(t_img.shape[1:]) != (3, self.image_size, self.image_size):
             raise ValueError(f"images must be [B,3,{self.image_size},{self.image_size}], got {tuple(t_img.shape)}")
+        check_loc(self.desc, loc, B)
         keep = [_as(t_img, torch.float32, self.device), _as(t_mask, torch.uint8, self.device)]
         keep += [None if g_img is None else _as(g_img, torch.float32, self.device),
                  None if g_mask is None else _as(g_mask, torch.uint8, self.device),
@@ -146,6 +167,7 @@ class Engine:
         for t in (t_img, t_mask, g_img, g_mask, loc):
             if t is not None and (t.device.type != "cpu" or not t.is_contiguous()):
                 raise ValueError("generate_host takes contiguous host tensors")
+        check_loc(self.desc, loc, B)
         if out is None:
             out = torch.empty(B, max_len, dtype=torch.int64).pin_memory()
         steps = C.c_int32(0)
@@ -162,6 +184,7 @@ class Engine:
         for t in (t_img, t_mask, g_img, g_mask, loc):
             if t is not None and (t.device.type != "cpu" or not t.is_contiguous()):
                 raise ValueError("encode_host takes contiguous host tensors")
+        check_loc(self.desc, loc, B)
         with torch.cuda.device(self.device):
             native.check(self.lib.retr_encode_host(
                 self.handle, B, native.ptr(t_img), native.ptr(t_mask), native.ptr(g_img), native.ptr(g_mask),
@@ -189,6 +212,7 @@ class Engine:
         for t in (t_img, t_mask, g_img, g_mask, loc):
             if t is not None and (t.device.type != "cpu" or not t.is_contiguous()):
                 raise ValueError("prefetch_host takes contiguous host tensors")
+        check_loc(self.desc, loc, B)
         with torch.cuda.device(self.device):
             native.check(self.lib.retr_prefetch_host(
                 self.handle, B, native.ptr(t_img), native.ptr(t_mask), native.ptr(g_img), native.ptr(g_mask),
@@ -272,6 +296,7 @@ class Trainer:
             native.check(self.lib.retr_train_finalize(self.handle))
         self.signature = self.signature_of(model)
         self.batch, self.step_count = 0, 0
+        self._model = weakref.ref(model)
         self._loss = torch.zeros(1, dtype=torch.float32, device=device)
         self._sumsq = torch.zeros(1, dtype=torch.float32, device=device)
 
@@ -299,6 +324,7 @@ class Trainer:
         if tuple(ids.shape) != (B, self.T):
             raise RuntimeError(f"The size of tensor a ({ids.shape[1]}) must match the size of tensor b ({self.T}) "
                                "(caption length must equal max_position_embeddings)")
+        check_loc(self.desc, loc, B)
         keep = [_as(t_img, torch.float32, self.device), _as(t_mask, torch.uint8, self.device),
                 None if g_img is None else _as(g_img, torch.float32, self.device),
                 None if g_mask is None else _as(g_mask, torch.uint8, self.device),
@@ -339,6 +365,9 @@ class Trainer:
     def clip_adamw(self, max_norm, lr, lr_backbone, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-4):
         """clip_grad_norm_ + AdamW in native kernels; returns the pre-clip gradient norm (0-d device tensor)."""
         self.step_count += 1
+        model = self._model()
+        if model is not None:       # the masters change under torch's feet: inference contexts must reload
+            model.__dict__["_weights_epoch"] = model.__dict__.get("_weights_epoch", 0) + 1
         with torch.cuda.device(self.device):
             native.check(self.lib.retr_train_clip_adamw(self.handle, float(max_norm), float(lr), float(lr_backbone),
                                                         float(betas[0]), float(betas[1]), float(eps), float(weight_decay),

@@ -240,3 +240,22 @@ def test_greedy_stream_two_contexts_call_order(monkeypatch):
     assert engs[0].cap == 100 and engs[1].cap == 100
     with pytest.raises(RuntimeError):                  # a later batch larger than the contexts were sized for
         list(decode.greedy_stream([batch(0, 2), batch(1, 5)], m, max_len=6, contexts=2))
+
+
+def test_check_loc_shapes():
+    """a [B,7] loc into CaptionGlobalLoc (5 tokens) or a [B,5] loc into CaptionLoc must raise, as the
+    reference's loc_proj Linear would, instead of being read as B*n contiguous floats."""
+    from retr_b200 import native
+    from retr_b200.runtime import check_loc
+    d = native.ModelDesc()
+    d.loc_in_dim, d.n_loc = 1, 5
+    check_loc(d, torch.zeros(3, 5), 3)
+    with pytest.raises(RuntimeError):
+        check_loc(d, torch.zeros(3, 7), 3)
+    with pytest.raises(ValueError):
+        check_loc(d, None, 3)
+    d.loc_in_dim, d.n_loc = 7, 7
+    with pytest.raises(RuntimeError):
+        check_loc(d, torch.zeros(3, 5), 3)
+    d.loc_in_dim = 0
+    check_loc(d, None, 3)

@@ -345,3 +345,111 @@ def test_scaled_variant_d512_heads64():
         assert (logits - ref).abs().max().item() <= tol_rel * ref.abs().max().item(), precision
         if precision == "fp32":
             assert torch.equal(ids[:, :13], ref_ids[:, :13])
+
+
+# ---- parity at the MEASURED configuration (bench.py runs B = 256) ---------------------------------------------
+BENCH_B = 256
+BENCH_ROWS = [0, 127, 128, 255]
+
+
+def _bench_batch(shard=21):
+    kind = "CaptionGlobalLoc"
+    data, enc_in = synthetic_samples(kind, BENCH_B, shard=shard, train=False)
+    return kind, data, enc_in
+
+
+def test_b256_fp32_rows_match_oracle():
+    """Samples are independent, so rows {0,127,128,255} of a B=256 decode must equal the oracle run on those four
+    samples alone: exercises the backbone chunking, key compaction with per-sample n_valid, and the row blocking of
+    the decode step at the batch the benchmark uses."""
+    kind, data, enc_in = _bench_batch()
+    model, sd, cfg = gpu_model(kind, "fp32", calibrated=True)
+    model.max_batch = BENCH_B
+    with torch.no_grad():
+        ids = decode.greedy(samples_of(kind, enc_in, "cpu"), model, max_len=128, device="cuda", bos_token=101,
+                            eos_token=102).cpu()
+        sub = tuple(None if t is None else t[BENCH_ROWS] for t in enc_in)
+        ref, _ = O.greedy(sd, cfg, *sub, max_len=128, bos_token=101, eos_token=102, literal=False)
+    assert ids.shape == (BENCH_B, 128)
+    assert torch.equal(ids[BENCH_ROWS], ref)
+
+
+def sequence_parity(ids, ref_ids, tf_logits=None, ref_tf_logits=None):
+    """strict % of identical sequences; teacher-forced per-step argmax agreement (no cascade) when logits are given"""
+    out = {"sequences": int(ids.shape[0]),
+           "strict_exact_pct": 100.0 * float((ids == ref_ids).all(1).float().mean()),
+           "first_divergence_median": None}
+    div = (ids != ref_ids).float().argmax(1)[(ids != ref_ids).any(1)]
+    if div.numel():
+        out["first_divergence_median"] = float(div.float().median())
+    if tf_logits is not None:
+        out["teacher_forced_step_pct"] = 100.0 * float(
+            (tf_logits[:, :127].argmax(-1) == ref_tf_logits[:, :127].argmax(-1)).float().mean())
+    return out
+
+
+def test_b256_bf16_sequence_parity_statistics():
+    """The benchmarked precision at the benchmarked batch against the fp32 mode (itself pinned to the oracle by the
+    test above): strict sequence-exact %, and teacher-forced per-step agreement on 64 of the rows.  With random-init
+    weights the top-2 logit margins are 4e-6 .. 5e-2 (oracle/margin_study.py: rounding the operands of ANY one stage
+    to bf16 flips a token in half of the 127-step sequences), so the strict figure is reported, and what is asserted
+    is the per-step agreement and that every first divergence sits at a near-tie of the fp32 logits."""
+    kind, data, enc_in = _bench_batch()
+    m32, sd, cfg = gpu_model(kind, "fp32", calibrated=True)
+    m16, _, _ = gpu_model(kind, "bf16", calibrated=True)
+    m32.max_batch = m16.max_batch = BENCH_B
+    n_tf = 64
+    with torch.no_grad():
+        s = samples_of(kind, enc_in, "cpu")
+        ref = decode.greedy(s, m32, max_len=128, device="cuda", bos_token=101, eos_token=102)
+        ids = decode.greedy(s, m16, max_len=128, device="cuda", bos_token=101, eos_token=102)
+        sub = samples_of(kind, tuple(None if t is None else t[:n_tf] for t in enc_in))
+        cm = torch.zeros(n_tf, 128, dtype=torch.bool, device="cuda")
+        l32 = m32(*sub, ref[:n_tf], cm)
+        l16 = m16(*sub, ref[:n_tf], cm)
+    stats = sequence_parity(ids.cpu(), ref.cpu(), l16.cpu(), l32.cpu())
+    print("bf16 vs fp32 at B=256:", stats)
+    assert stats["teacher_forced_step_pct"] >= 97.0
+    # every teacher-forced disagreement is a near-tie of the fp32 logits (margin below the bf16 logit tolerance)
+    scale = l32.abs().max().item()
+    err = (l16 - l32).abs().max().item()
+    assert err <= BF16_LOGIT_TOL * scale
+    top2 = l32[:, :127].topk(2, -1).values
+    margin = top2[..., 0] - top2[..., 1]
+    bad = l16[:, :127].argmax(-1) != l32[:, :127].argmax(-1)
+    assert bool((margin[bad] <= 2 * err).all())
+
+
+def test_eval_after_native_train_step_sees_new_weights():
+    """train_step_native updates the masters through raw pointers; an inference context created BEFORE
+    the step must not keep decoding with the old weights."""
+    from retr_b200 import engine as E
+    kind = "CaptionGlobalLoc"
+    model, sd, cfg = gpu_model(kind, "bf16", calibrated=True)
+    data, enc_in = synthetic_samples(kind, 2, shard=4)
+    s = samples_of(kind, enc_in)
+    caps, cm = data["caps"].cuda(), data["cap_masks"].cuda()
+    with torch.no_grad():
+        before = model(*s, caps[:, :-1], cm[:, :-1]).clone()
+    model.train()
+    for _ in range(3):
+        E.train_step_native(model, s, caps, cm, max_norm=0.1, lr=1e-2, lr_backbone=1e-3)
+    model.eval()
+    with torch.no_grad():
+        after = model(*s, caps[:, :-1], cm[:, :-1]).clone()
+        model._engine.close()
+        model._engine = None
+        fresh = model(*s, caps[:, :-1], cm[:, :-1])
+    assert (after - before).abs().max().item() > 1e-3          # the update is visible ...
+    assert torch.equal(after, fresh)                            # ... and is exactly what a new context computes
+
+
+def test_location_feature_shape_is_checked():
+    kind = "CaptionGlobalLoc"
+    model, sd, cfg = gpu_model(kind, "bf16", calibrated=True)
+    data, enc_in = synthetic_samples(kind, 2, shard=4)
+    t, g, loc = samples_of(kind, enc_in)
+    caps, cm = data["caps"].cuda(), data["cap_masks"].cuda()
+    bad = torch.cat([loc, loc[:, :2]], 1)                       # [B,7] into a 5-token model
+    with pytest.raises(RuntimeError, match="location features"):
+        model(t, g, bad, caps[:, :-1], cm[:, :-1])
