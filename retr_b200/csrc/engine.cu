@@ -13,6 +13,7 @@
 // (q=k=LN(x)+pos, q=LN(y)+query_pos, k=memory+pos) is folded into a per-position bias table,
 // W(x+p)+b = Wx + (Wp+b), computed once in fp32 at weight-load time (rowbias epilogue).
 #include "engine.h"
+#include "decode_stack.h"
 #include "ffn_fused.h"
 #include "small_gemm.h"
 
@@ -165,6 +166,12 @@ class EngineT final : public EngineBase {
   cudaEvent_t gfork_ = nullptr;
   int cur_G_ = 1;                                    // row groups of the step being captured
   bool ffn_fused_ = false;                           // FFN sublayer of the decode step as one cluster kernel (ffn_fused.cu)
+  // the whole decoder stack of a decode step as ONE cluster kernel (decode_stack.cu): its own chunked, swizzled caches
+  bool stack_decode_ = false;
+  int cross_chunks_ = 0, self_chunks_ = 0;
+  std::vector<bf16*> ckv2_, skv2_;
+  DecStackParams stack_params_;
+  void build_stack_params();
   size_t splitk_group_stride_ = 0;                   // floats of split-K scratch per group
 };
 
@@ -389,8 +396,51 @@ void EngineT<T>::alloc_buffers() {
   fast_decode_ = std::is_same<T, bf16>::value && getenv("RETR_NO_FAST_DECODE") == nullptr && (d == 256 || d == 512) &&
                  ff % 256 == 0;
   if (fast_decode_) small_gemm_configure();
+  stack_decode_ = fast_decode_ && !(getenv("RETR_DECODE_STACK") && atoi(getenv("RETR_DECODE_STACK")) == 0) &&
+                  decode_stack_supported((int)d, desc.n_heads, (int)ff, desc.dec_layers, mlp_[0].out, (int)Tn) &&
+                  mlp_[1].out == mlp_[0].out && mlp_[2].in == mlp_[1].out;
+  if (stack_decode_) {
+    cross_chunks_ = (int)cdiv(S, DS_CHUNK_KEYS);
+    self_chunks_ = (int)Tn / DS_CHUNK_KEYS;
+    for (int l = 0; l < desc.dec_layers; ++l) {
+      // zero-filled once: rows past a sample's valid keys are multiplied by p = 0 and must stay finite
+      const size_t cb = (size_t)B * desc.n_heads * cross_chunks_ * DS_CHUNK_ELEMS * 2;
+      const size_t sb = (size_t)B * desc.n_heads * self_chunks_ * DS_CHUNK_ELEMS * 2;
+      ckv2_.push_back(static_cast<bf16*>(dalloc(cb)));
+      skv2_.push_back(static_cast<bf16*>(dalloc(sb)));
+      CUDA_OK(cudaMemset(ckv2_.back(), 0, cb));
+      CUDA_OK(cudaMemset(skv2_.back(), 0, sb));
+    }
+    decode_stack_configure();
+    build_stack_params();
+  }
   if (getenv("RETR_NO_CARVEOUT_HINT") == nullptr) ops_prefer_max_shared();
   decode_attention_configure<T>(std::max<int>(S, (int)Tn), (int)(d / desc.n_heads));
+}
+
+template <> void EngineT<float>::build_stack_params() {}
+template <> void EngineT<bf16>::build_stack_params() {
+  DecStackParams& p = stack_params_;
+  p = DecStackParams{};
+  p.n_layers = desc.dec_layers;
+  for (int l = 0; l < desc.dec_layers; ++l) {
+    const DecLayer<bf16>& e = dec_[l];
+    DecStackLayer& L = p.L[l];
+    L.ln1_g = e.ln1_g; L.ln1_b = e.ln1_b; L.ln2_g = e.ln2_g; L.ln2_b = e.ln2_b; L.ln3_g = e.ln3_g; L.ln3_b = e.ln3_b;
+    L.w_sqkv = e.s_qkv.w; L.rb_sqkv = e.rb_s_qkv;
+    L.w_so = e.s_out.w; L.b_so = e.s_out.b;
+    L.w_cq = e.c_q.w; L.rb_cq = e.rb_c_q;
+    L.w_co = e.c_out.w; L.b_co = e.c_out.b;
+    L.w_ff1 = e.ff1.w; L.b_ff1 = e.ff1.b; L.w_ff2 = e.ff2.w; L.b_ff2 = e.ff2.b;
+    L.self_kv = skv2_[l]; L.cross_kv = ckv2_[l];
+  }
+  p.caption = caption_;
+  p.e_word = e_word_; p.e_pos = e_pos_; p.emb_g = emb_g_; p.emb_b = emb_b_; p.emb_eps = desc.embed_ln_eps;
+  p.fin_g = dec_norm_g_; p.fin_b = dec_norm_b_;
+  p.w_m0 = mlp_[0].w; p.b_m0 = mlp_[0].b; p.w_m1 = mlp_[1].w; p.b_m1 = mlp_[1].b;
+  p.m2_out = m2_;
+  p.step = step_; p.n_valid = cross_nvalid_;
+  p.self_chunks = self_chunks_; p.cross_chunks = cross_chunks_; p.d_ff = desc.d_ff;
 }
 
 // ---- backbone --------------------------------------------------------------------------------------
@@ -529,6 +579,9 @@ void EngineT<T>::encode(int B, const float* t_img, const uint8_t* t_mask, const 
     p.rowbias = dec_[l].rb_c_kv; p.rowbias_period = S;
     gemm<T>(p, s);
     if (l == 0) key_compaction(tok_mask_, B, S, cross_dst_, cross_nvalid_, s);
+    if constexpr (std::is_same<T, bf16>::value) {
+      if (stack_decode_) { kv_to_chunked(ckv_[l], ckv2_[l], B, S, cross_chunks_, cross_dst_, s); continue; }
+    }
     kv_to_head_major<T>(ckv_[l], ck_[l], cv_[l], B, S, desc.n_heads, d / desc.n_heads, s, cross_dst_);
   }
   CUDA_OK(cudaEventRecord(ev_[2], s));
@@ -725,6 +778,21 @@ void EngineT<T>::decode_rows_fused(int r0, int n, int group, int max_len, cudaSt
 
 template <typename T>
 void EngineT<T>::decode_step_fused(int B, int eos, int max_len, cudaStream_t s) {
+  if constexpr (std::is_same<T, bf16>::value) {
+    if (stack_decode_) {
+      // three launches per step: the decoder stack + first two head layers (one cluster kernel), the vocabulary
+      // GEMM with the argmax in its epilogue (tcgen05), the token bookkeeping
+      cur_G_ = 1;
+      DecStackParams p = stack_params_;
+      p.B = B; p.max_len = max_len;
+      decode_stack(p, s);
+      GemmParams gp = lin(mlp_[2], m2_, B, nullptr);
+      gp.argmax_out = argmax_keys_;
+      gemm<T>(gp, s);                                                  // logits never reach HBM
+      greedy_update(argmax_keys_, caption_, max_len, B, eos, step_, done_, finished_, s, true);
+      return;
+    }
+  }
   // rows per group: a multiple of the small-GEMM row granularity, at least group_rows_min_
   int rows = (int)cdiv(B, groups_);
   rows = (int)cdiv(std::max(rows, group_rows_min_), 32) * 32;

@@ -453,3 +453,39 @@ def test_location_feature_shape_is_checked():
     bad = torch.cat([loc, loc[:, :2]], 1)                       # [B,7] into a 5-token model
     with pytest.raises(RuntimeError, match="location features"):
         model(t, g, bad, caps[:, :-1], cm[:, :-1])
+
+
+@pytest.mark.parametrize("B", [5, 19])
+def test_decode_stack_kernel_consistent_with_teacher_forced(B, monkeypatch):
+    """The one-kernel decoder stack (csrc/decode_stack.cu: clusters of 8 CTAs x 16 samples, chunked swizzled K/V
+    caches, tensor-core single-query attention) against two independent computations of the same function:
+    (a) the full-sequence bf16 kernels fed the ids it produced — the token chosen at step i must be the teacher-forced
+        argmax at position i unless that position is a near-tie;
+    (b) the launch-chain decode path of round 1 (RETR_DECODE_STACK=0).
+    B = 5 leaves 11 of a cluster's 16 rows empty; B = 19 adds a second, ragged cluster."""
+    kind = "CaptionGlobalLoc"
+    model, sd, cfg = gpu_model(kind, "bf16", calibrated=True)
+    model.max_batch = B
+    _, enc_in = synthetic_samples(kind, B, shard=31, train=False)
+    s = samples_of(kind, enc_in)
+    with torch.no_grad():
+        ids = decode.greedy(s, model, max_len=128, device="cuda", bos_token=101, eos_token=102)
+        cm = torch.zeros(B, 128, dtype=torch.bool, device="cuda")
+        tf = model(*s, ids, cm)[:, :127]
+    assert int(ids.min()) >= 0 and int(ids.max()) < cfg.vocab_size
+    top2 = tf.topk(2, -1)
+    agree = top2.indices[..., 0] == ids[:, 1:]
+    margin = (top2.values[..., 0] - top2.values[..., 1]) / tf.abs().max()
+    print(f"stack decode vs teacher-forced (B={B}): agreement {agree.float().mean().item():.4f}, "
+          f"largest margin at a disagreement {margin[~agree].max().item() if (~agree).any() else 0:.2e}")
+    assert agree.float().mean().item() >= 0.98
+    assert bool((margin[~agree] < 1e-2).all())
+    monkeypatch.setenv("RETR_DECODE_STACK", "0")
+    old, _, _ = gpu_model(kind, "bf16", calibrated=True)
+    old.max_batch = B
+    with torch.no_grad():
+        ids_old = decode.greedy(s, old, max_len=128, device="cuda", bos_token=101, eos_token=102)
+    same = (ids_old == ids).all(1).float().mean().item()
+    first = (ids_old != ids).float().argmax(1)[(ids_old != ids).any(1)]
+    print(f"  vs launch-chain path: {same * 100:.0f}% sequences identical; first divergences at {first.tolist()}")
+    assert bool((ids_old[:, :4] == ids[:, :4]).all())
