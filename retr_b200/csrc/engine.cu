@@ -31,6 +31,11 @@ namespace {
 // The decode step is captured on high-priority streams (kernel nodes keep the priority of the stream they were
 // captured on): when a second context's encode phase shares the GPU, the short decode kernels are placed ahead of the
 // queued CTAs of its convolutions.  RETR_DECODE_PRIORITY=0 turns it off.
+// The one-kernel decode step (decode_stack.cu).  RETR_DECODE_STACK=0/1 overrides the default.
+static bool stack_decode_wanted() {
+  const char* e = getenv("RETR_DECODE_STACK");
+  return e ? atoi(e) != 0 : false;   // off until it beats the launch chain (measured 69.7 vs 46.8 ms at B = 256: two waves)
+}
 static int decode_priority() {
   int least = 0, greatest = 0;
   CUDA_OK(cudaDeviceGetStreamPriorityRange(&least, &greatest));
@@ -396,7 +401,7 @@ void EngineT<T>::alloc_buffers() {
   fast_decode_ = std::is_same<T, bf16>::value && getenv("RETR_NO_FAST_DECODE") == nullptr && (d == 256 || d == 512) &&
                  ff % 256 == 0;
   if (fast_decode_) small_gemm_configure();
-  stack_decode_ = fast_decode_ && !(getenv("RETR_DECODE_STACK") && atoi(getenv("RETR_DECODE_STACK")) == 0) &&
+  stack_decode_ = fast_decode_ && stack_decode_wanted() &&
                   decode_stack_supported((int)d, desc.n_heads, (int)ff, desc.dec_layers, mlp_[0].out, (int)Tn) &&
                   mlp_[1].out == mlp_[0].out && mlp_[2].in == mlp_[1].out;
   if (stack_decode_) {

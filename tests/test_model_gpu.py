@@ -464,6 +464,7 @@ def test_decode_stack_kernel_consistent_with_teacher_forced(B, monkeypatch):
     (b) the launch-chain decode path of round 1 (RETR_DECODE_STACK=0).
     B = 5 leaves 11 of a cluster's 16 rows empty; B = 19 adds a second, ragged cluster."""
     kind = "CaptionGlobalLoc"
+    monkeypatch.setenv("RETR_DECODE_STACK", "1")
     model, sd, cfg = gpu_model(kind, "bf16", calibrated=True)
     model.max_batch = B
     _, enc_in = synthetic_samples(kind, B, shard=31, train=False)
