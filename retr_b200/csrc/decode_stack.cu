@@ -7,23 +7,30 @@
 // 128-long prefix (eval_utils/decode.py:68-79).
 //
 // Why one kernel: as a chain of launches a decode step was ~41 dependent kernels of 5-25 us for ~70 us of HBM time
-// (profiles/r1_decode_timeline.txt).  Samples are independent through the whole stack, so a thread-block CLUSTER of 8
-// CTAs takes 16 samples through all six layers with no grid-wide synchronisation at all — only cluster barriers:
-//   * CTA r of the cluster is head r of every attention and column slice r of every projection: the q/k/v projection
-//     gives CTA r exactly the q, k, v of head r, so attention needs no exchange before it;
-//   * every CTA keeps a full fp32 replica of the 16 residual rows in shared memory (LayerNorm needs whole rows); after
-//     each sublayer the eight 32-column slices are pushed to every peer through distributed shared memory;
-//   * the FFN splits the hidden dimension: CTA r computes relu(W1[256r:256r+256] LN(y)) and its partial product with
-//     W2[:, 256r:256r+256], pushes 32-column slices of the partial to the owning CTA, which sums them in a fixed order;
-//   * GEMMs are M = 16 (one m16n8k16 row block): weights stream global(L2) -> registers as B fragments with 16-byte
-//     loads (each weight byte is used exactly once per CTA, so staging it in shared memory buys nothing); the k index
-//     is permuted identically for A and B so that a thread's 16 bytes are 8 consecutive k;
+// (profiles/r1_decode_timeline.txt).  Samples are independent through the whole stack, so a thread-block CLUSTER of 4
+// CTAs takes 8 samples through all six layers with no grid-wide synchronisation at all — only cluster barriers:
+//   * CTA r of the cluster owns heads 2r, 2r+1 of every attention and column slice [64r, 64r+64) of every projection:
+//     the q/k/v projection gives CTA r exactly the q, k, v of its heads, so attention needs no exchange before it;
+//   * every CTA keeps a full fp32 replica of the 8 residual rows in shared memory (LayerNorm needs whole rows); after
+//     each sublayer the four 64-column slices are pushed to every peer through distributed shared memory;
+//   * the FFN splits the hidden dimension: CTA r computes relu(W1[512r:512r+512] LN(y)) and its partial product with
+//     W2[:, 512r:512r+512], pushes 64-column slices of the partial to the owning CTA, which sums them in a fixed order;
+//   * GEMMs are one m16n8k16 row block (rows 8-15 are zero registers): weights stream global(L2) -> registers as
+//     B fragments with 16-byte loads, double-buffered two n-tiles at a time (each weight byte is used exactly once
+//     per CTA, so staging it in shared memory buys nothing); the k index is permuted identically for A and B so that
+//     a thread's 16 bytes are 8 consecutive k; the loads of a GEMM are issued BEFORE the cluster barrier / LayerNorm
+//     that precedes it;
 //   * attention: K/V caches are stored in 4 KB chunks [K 32 keys x 32 | V 32 keys x 32] (bf16, 16-byte units XOR-
-//     swizzled by the key index, written that way by the cache builders), each warp owns two samples and a private
-//     5-slot ring of chunks filled by cp.async.bulk (one elected lane, completion on an mbarrier); the ring runs
-//     AHEAD across sublayers and layers (the next cross-attention's chunks arrive while the projections run).
-//     Scores and P.V run on the tensor cores (q as row 0 of the A operand; ldmatrix / ldmatrix.trans on the swizzled
-//     chunk), online softmax per 16 keys: math starts on the first chunk instead of waiting for a whole K block.
+//     swizzled by the key index, written that way by the cache builders).  Warp w owns sample w and walks its two
+//     heads in lock-step (two independent dependency chains), fed by a private 5-slot ring of chunks filled by
+//     cp.async.bulk (one elected lane, completion on an mbarrier); the ring runs AHEAD across sublayers and layers
+//     (the next cross-attention's chunks arrive while the projections run).  Scores and P.V run on the tensor cores
+//     (q as row 0 of the A operand; ldmatrix / ldmatrix.trans on the swizzled chunk), online softmax per chunk:
+//     math starts on the first chunk instead of waiting for a whole K block.
+// Sizing: 8 samples x 4 CTAs because thread-block clusters of 8 with this much shared memory reach only 15
+// co-resident clusters on a B200 (cudaOccupancyMaxActiveClusters), one short of the 16 that 256 samples need — the
+// first version (16 samples per 8-CTA cluster) ran the benchmark batch in TWO waves, 500 us per step.  Clusters of 4
+// pack the GPCs better: the batch runs as ONE wave of 32 clusters on 128 SMs.
 #include "decode_stack.h"
 
 #include "sm100_ptx.cuh"
@@ -31,23 +38,34 @@
 namespace retr {
 namespace {
 
-constexpr int D = 256, DH = 32, NH = 8, R = DS_ROWS, THREADS = 256, NWARP = 8;
+constexpr int D = 256, DH = 32, NH = 8, CL = 4, HPC = NH / CL, R = DS_ROWS, THREADS = 256, NWARP = 8;
+constexpr int SL = D / CL;                   // 64: columns of a projection owned by one CTA
 constexpr int LDA = D + 32;                  // bf16 per A row in shared memory: 576 B, rows 16 banks apart
+constexpr int FS = 512, LDH = FS + 32;       // FFN hidden slice per CTA
 constexpr int MH = 512, LDM1 = MH + 32;      // MLP head hidden width
 constexpr int SLOTS = 5, SLOT_BYTES = DS_CHUNK_ELEMS * 2;
 constexpr float LOG2E = 1.4426950408889634f;
+static_assert(R == NWARP, "one sample per warp");
+
+// -DDS_PROFILE: thread 0 of cluster 0 / CTA 0 accumulates SM cycles per phase and prints them at step 60
+#ifdef DS_PROFILE
+#define DS_T(i) do { if (prof_on) { const long long now_ = clock64(); prof[i] += now_ - prof_last; prof_last = now_; } } while (0)
+#else
+#define DS_T(i) do { } while (0)
+#endif
 
 struct Smem {
-  uint8_t ring[NWARP][SLOTS][SLOT_BYTES];    // per-warp K/V chunk rings
+  uint8_t ring[NWARP][SLOTS][SLOT_BYTES];    // per-warp K/V chunk rings (160 KB)
   float Y[R][D];                             // residual stream rows (full replica in every CTA of the cluster)
-  float Ps[NH][R][32];                       // FFN partials of this CTA's 32 output columns, one slot per source CTA
+  float Ps[CL][R][SL];                       // FFN partials of this CTA's 64 output columns, one slot per source CTA
   bf16 Abuf[R][LDA];                         // LayerNorm output (A operand)
   bf16 Att[R][LDA];                          // attention output, heads gathered from the peers
-  bf16 Hs[R][LDA];                           // FFN hidden slice; Att+Hs are reused as M1[R][LDM1] by the head
-  bf16 Qs[R][DH], Kn[R][DH], Vn[R][DH];      // this head's (scaled) query and the step's new key / value rows
+  bf16 Hs[R][LDH];                           // FFN hidden slice; reused as M1[R][LDM1] by the head
+  bf16 Qs[R][SL], Kn[R][SL], Vn[R][SL];      // this CTA's heads: (scaled) query and the step's new key / value rows
   uint64_t bars[NWARP][SLOTS];
 };
-static_assert(sizeof(bf16) * R * LDM1 <= 2 * sizeof(bf16) * R * LDA, "M1 must fit in Att+Hs");
+static_assert(LDM1 <= LDH, "M1 must fit in Hs");
+static_assert(sizeof(Smem) <= 227 * 1024, "shared memory budget");
 
 // ---- small PTX wrappers ------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t cluster_rank() {
@@ -58,7 +76,6 @@ __device__ __forceinline__ uint32_t cluster_rank() {
 __device__ __forceinline__ void cluster_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
 __device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
 __device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
-__device__ __forceinline__ void cluster_sync() { cluster_arrive(); cluster_wait(); }
 __device__ __forceinline__ uint32_t map_peer(uint32_t local_addr, uint32_t rank) {
   uint32_t remote;
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(rank));
@@ -94,88 +111,94 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<const uint32_t*>(&v);
 }
 
-// ---- M = 16 GEMM pieces --------------------------------------------------------------------------------------------
-// A fragments of the 16 rows over 256 consecutive k (8 blocks of 32).  Within a block thread (g, c) owns the 8
-// consecutive k [8c, 8c+8) of rows g and g+8: k-step 0 uses elements {0,1 | 2,3}, k-step 1 {4,5 | 6,7} — the same
-// assignment as the 16-byte weight loads below, so the products pair up correctly (a dot product does not care in
-// which order k is visited).
+// ---- GEMM pieces: 8 real rows (rows 8-15 of the m16 block are zero registers) -------------------------------------
+// A fragments of row g over 256 consecutive k (8 blocks of 32).  Within a block thread (g, c) owns the 8 consecutive
+// k [8c, 8c+8): k-step 0 uses elements {0,1 | 2,3}, k-step 1 {4,5 | 6,7} — the same assignment as the 16-byte weight
+// loads, so the products pair up correctly (a dot product does not care in which order k is visited).
 struct AFrag {
-  uint4 x[8], y[8];
+  uint4 x[8];
 };
 __device__ __forceinline__ void load_a(AFrag& a, const bf16* A, int lda, int lane) {
   const int g = lane >> 2, c = lane & 3;
 #pragma unroll
-  for (int kb = 0; kb < 8; ++kb) {
-    a.x[kb] = *reinterpret_cast<const uint4*>(A + (size_t)g * lda + kb * 32 + 8 * c);
-    a.y[kb] = *reinterpret_cast<const uint4*>(A + (size_t)(g + 8) * lda + kb * 32 + 8 * c);
-  }
+  for (int kb = 0; kb < 8; ++kb) a.x[kb] = *reinterpret_cast<const uint4*>(A + (size_t)g * lda + kb * 32 + 8 * c);
 }
-// acc[j] (+)= A[16 x 256] . W_j[8 x 256]^T for NT n-tiles; wrow[j] = &W[(n0_j + g) * ldw + k0 + 8c]
-template <int NT>
-__device__ __forceinline__ void mma_tiles(const AFrag& a, const bf16* const (&wrow)[NT], float (&acc)[NT][4]) {
+// B fragments of NT n-tiles over 256 k: wrow[j] = &W[(n0_j + g) * ldw + k0 + 8c]
+template <int NT> struct WFrag {
   uint4 w[NT][8];
+};
+template <int NT> __device__ __forceinline__ void load_w(WFrag<NT>& f, const bf16* const (&wrow)[NT]) {
 #pragma unroll
   for (int j = 0; j < NT; ++j)
 #pragma unroll
-    for (int kb = 0; kb < 8; ++kb) w[j][kb] = ldg_stream(wrow[j] + kb * 32);
+    for (int kb = 0; kb < 8; ++kb) f.w[j][kb] = ldg_stream(wrow[j] + kb * 32);
+}
+// acc[j] += A . W_j^T; k outer / tiles inner so the NT accumulator chains interleave; with one tile the even and odd
+// k blocks go to two accumulators
+template <int NT> __device__ __forceinline__ void mma_w(const AFrag& a, const WFrag<NT>& f, float (&acc)[NT][4]) {
+  if constexpr (NT == 1) {
+    float alt[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-  for (int j = 0; j < NT; ++j)
+    for (int kb = 0; kb < 8; kb += 2) {
+      mma16816(acc[0], a.x[kb].x, 0u, a.x[kb].y, 0u, f.w[0][kb].x, f.w[0][kb].y);
+      mma16816(alt, a.x[kb + 1].x, 0u, a.x[kb + 1].y, 0u, f.w[0][kb + 1].x, f.w[0][kb + 1].y);
+      mma16816(acc[0], a.x[kb].z, 0u, a.x[kb].w, 0u, f.w[0][kb].z, f.w[0][kb].w);
+      mma16816(alt, a.x[kb + 1].z, 0u, a.x[kb + 1].w, 0u, f.w[0][kb + 1].z, f.w[0][kb + 1].w);
+    }
+    acc[0][0] += alt[0]; acc[0][1] += alt[1];
+  } else {
 #pragma unroll
     for (int kb = 0; kb < 8; ++kb) {
-      mma16816(acc[j], a.x[kb].x, a.y[kb].x, a.x[kb].y, a.y[kb].y, w[j][kb].x, w[j][kb].y);
-      mma16816(acc[j], a.x[kb].z, a.y[kb].z, a.x[kb].w, a.y[kb].w, w[j][kb].z, w[j][kb].w);
+#pragma unroll
+      for (int j = 0; j < NT; ++j) mma16816(acc[j], a.x[kb].x, 0u, a.x[kb].y, 0u, f.w[j][kb].x, f.w[j][kb].y);
+#pragma unroll
+      for (int j = 0; j < NT; ++j) mma16816(acc[j], a.x[kb].z, 0u, a.x[kb].w, 0u, f.w[j][kb].z, f.w[j][kb].w);
     }
+  }
 }
 template <int NT> __device__ __forceinline__ void zero_acc(float (&acc)[NT][4]) {
 #pragma unroll
   for (int j = 0; j < NT; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
 }
 
-// LayerNorm of the 16 replica rows -> bf16 A operand; warp w takes rows 2w, 2w+1
-__device__ __forceinline__ void layernorm_rows(const float (*Y)[D], bf16 (*A)[LDA], const float* __restrict__ gamma,
-                                               const float* __restrict__ beta, float eps, int warp, int lane) {
-  float4 ga[2], be[2];
+// LayerNorm of replica row `warp` -> bf16 A operand
+__device__ __forceinline__ void layernorm_row(const float (*Y)[D], bf16 (*A)[LDA], const float* __restrict__ gamma,
+                                              const float* __restrict__ beta, float eps, int warp, int lane) {
+  float v[8];
 #pragma unroll
   for (int j = 0; j < 2; ++j) {
-    ga[j] = __ldg(reinterpret_cast<const float4*>(gamma + j * 128 + lane * 4));
-    be[j] = __ldg(reinterpret_cast<const float4*>(beta + j * 128 + lane * 4));
+    const float4 t = *reinterpret_cast<const float4*>(&Y[warp][j * 128 + lane * 4]);
+    v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
   }
+  float s = 0.f;
 #pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const int r = warp * 2 + i;
-    float v[8];
+  for (int j = 0; j < 8; ++j) s += v[j];
+  const float mean = warp_sum(s) * (1.f / D);
+  float q = 0.f;
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      const float4 t = *reinterpret_cast<const float4*>(&Y[r][j * 128 + lane * 4]);
-      v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
-    }
-    float s = 0.f;
+  for (int j = 0; j < 8; ++j) { const float t = v[j] - mean; q = fmaf(t, t, q); }
+  const float rstd = rsqrtf(warp_sum(q) * (1.f / D) + eps);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) s += v[j];
-    const float mean = warp_sum(s) * (1.f / D);
-    float q = 0.f;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { const float t = v[j] - mean; q = fmaf(t, t, q); }
-    const float rstd = rsqrtf(warp_sum(q) * (1.f / D) + eps);
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      uint2 pk;
-      pk.x = pack_bf16((v[4 * j] - mean) * rstd * ga[j].x + be[j].x, (v[4 * j + 1] - mean) * rstd * ga[j].y + be[j].y);
-      pk.y = pack_bf16((v[4 * j + 2] - mean) * rstd * ga[j].z + be[j].z, (v[4 * j + 3] - mean) * rstd * ga[j].w + be[j].w);
-      *reinterpret_cast<uint2*>(&A[r][j * 128 + lane * 4]) = pk;
-    }
+  for (int j = 0; j < 2; ++j) {
+    const float4 ga = __ldg(reinterpret_cast<const float4*>(gamma + j * 128 + lane * 4));
+    const float4 be = __ldg(reinterpret_cast<const float4*>(beta + j * 128 + lane * 4));
+    uint2 pk;
+    pk.x = pack_bf16((v[4 * j] - mean) * rstd * ga.x + be.x, (v[4 * j + 1] - mean) * rstd * ga.y + be.y);
+    pk.y = pack_bf16((v[4 * j + 2] - mean) * rstd * ga.z + be.z, (v[4 * j + 3] - mean) * rstd * ga.w + be.w);
+    *reinterpret_cast<uint2*>(&A[warp][j * 128 + lane * 4]) = pk;
   }
 }
 
 // ---- per-warp K/V chunk stream ---------------------------------------------------------------------------------------
 // The chunks a warp will consume during the whole kernel form one fixed sequence:
-//   for layer: [self chunks of its sample 0, of its sample 1, cross chunks of sample 0, of sample 1]
-// The issue cursor runs SLOTS chunks ahead of the consume cursor, across sublayer and layer boundaries.
+//   for layer: [self chunk 0 of head A, of head B, self chunk 1 of A, of B, ..., cross chunk 0 of A, of B, ...]
+// (both heads of a sample have the same number of keys).  The issue cursor runs SLOTS chunks ahead of the consume
+// cursor, across sublayer and layer boundaries.
 struct Stream {
   int issued, consumed;
-  int il, iph, isi, ic;                      // issue cursor: layer, phase (0 self / 1 cross), sample 0/1, chunk
-  int n_self, n_cross0, n_cross1;            // chunks per (phase, sample)
-  int b0, b1;                                // the warp's two samples (clamped to B-1)
+  int il, iph, ic, ih;                       // issue cursor: layer, phase (0 self / 1 cross), chunk, head 0/1
+  int n_self, n_cross;                       // chunks per head in each phase
+  int b;                                     // the warp's sample (clamped to B-1)
   uint32_t ring, bars;                       // shared-memory addresses of this warp's ring and barriers
 };
 __device__ __forceinline__ void stream_issue(const DecStackParams& p, Stream& st, int rank, int lane, uint64_t policy) {
@@ -183,10 +206,10 @@ __device__ __forceinline__ void stream_issue(const DecStackParams& p, Stream& st
   const int slot = st.issued % SLOTS;
   if (lane == 0) {
     const DecStackLayer& L = p.L[st.il];
-    const int b = st.isi ? st.b1 : st.b0;
+    const int head = rank * HPC + st.ih;
     const bf16* src = st.iph == 0
-        ? L.self_kv + ((size_t)(b * NH + rank) * p.self_chunks + st.ic) * DS_CHUNK_ELEMS
-        : L.cross_kv + ((size_t)(b * NH + rank) * p.cross_chunks + st.ic) * DS_CHUNK_ELEMS;
+        ? L.self_kv + ((size_t)(st.b * NH + head) * p.self_chunks + st.ic) * DS_CHUNK_ELEMS
+        : L.cross_kv + ((size_t)(st.b * NH + head) * p.cross_chunks + st.ic) * DS_CHUNK_ELEMS;
     const uint32_t bar = st.bars + slot * 8, dst = st.ring + slot * SLOT_BYTES;
     ptx::fence_proxy_async_smem();           // the slot was last touched through the generic proxy
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(SLOT_BYTES) : "memory");
@@ -199,17 +222,16 @@ __device__ __forceinline__ void stream_issue(const DecStackParams& p, Stream& st
     }
   }
   ++st.issued;
-  const int n = st.iph == 0 ? st.n_self : (st.isi ? st.n_cross1 : st.n_cross0);
-  if (++st.ic == n) {
-    st.ic = 0;
-    if (++st.isi == 2) {
-      st.isi = 0;
+  if (++st.ih == HPC) {
+    st.ih = 0;
+    if (++st.ic == (st.iph == 0 ? st.n_self : st.n_cross)) {
+      st.ic = 0;
       if (++st.iph == 2) { st.iph = 0; ++st.il; }
     }
   }
 }
-__device__ __forceinline__ void stream_wait(const Stream& st) {
-  const uint32_t bar = st.bars + (st.consumed % SLOTS) * 8, parity = (st.consumed / SLOTS) & 1;
+__device__ __forceinline__ void stream_wait(const Stream& st, int idx) {
+  const uint32_t bar = st.bars + (idx % SLOTS) * 8, parity = (idx / SLOTS) & 1;
   uint32_t ok = 0;
   while (!ok) {
     asm volatile(
@@ -220,125 +242,152 @@ __device__ __forceinline__ void stream_wait(const Stream& st) {
   }
 }
 
-// Single-query attention of one (sample, head) over `n_keys` cached keys arriving through the warp's ring.
-// q (pre-scaled by log2(e)/sqrt(dh)) is row 0 of the m16 A operand; K chunks give the B fragments of q.K^T through
-// ldmatrix, V chunks those of P.V through ldmatrix.trans; only the quad g == 0 (lanes 0-3) carries real rows.
-// patch_key >= 0: that key's K/V rows (this step's, not yet in the cache copy) are written into the chunk first.
-// The normalised output (32 values) is pushed to column slice `rank` of row `row` of every peer's Att buffer.
-__device__ __forceinline__ void attend(const DecStackParams& p, Smem& sm, Stream& st, int rank, int warp, int lane,
-                                       int row, int n_keys, int patch_key, uint64_t policy) {
-  const int g = lane >> 2, c = lane & 3;
-  uint32_t qa[2][2];                                         // k-step x {a0 (dims 2c..), a2 (dims 2c+8..)}; rows 8-15: 0
+// Per-head running state of the single-query attention (row 0 of the m16 block; only quad g == 0 carries real data)
+struct HeadState {
+  uint32_t qa[2][2];                         // q fragments: k-step x {dims 2c.., dims 2c+8..}
+  float m, l, o[4][4];
+};
+// One 32-key chunk of one head: scores for all 32 keys (4 n-tiles), one online-softmax update, P.V over both 16-key
+// groups.  Keys >= kmax are masked; their V rows are finite (caches are zero-initialised), so p = 0 removes them.
+__device__ __forceinline__ void attend_chunk(HeadState& h, uint32_t base, int kmax, int lane) {
+  const int c = lane & 3;
+  float s[4][4];
+  zero_acc<4>(s);
 #pragma unroll
-  for (int ks = 0; ks < 2; ++ks) {
-    qa[ks][0] = g == 0 ? *reinterpret_cast<const uint32_t*>(&sm.Qs[row][ks * 16 + 2 * c]) : 0u;
-    qa[ks][1] = g == 0 ? *reinterpret_cast<const uint32_t*>(&sm.Qs[row][ks * 16 + 8 + 2 * c]) : 0u;
+  for (int j = 0; j < 4; ++j) {                              // 8 keys each
+    const int key = j * 8 + (lane & 7), unit = lane >> 3;
+    uint32_t k0, k1, k2, k3;
+    ldsm_x4(base + key * 64 + ((unit ^ ((key >> 1) & 3)) << 4), k0, k1, k2, k3);
+    mma16816(s[j], h.qa[0][0], 0u, h.qa[0][1], 0u, k0, k1);
+    mma16816(s[j], h.qa[1][0], 0u, h.qa[1][1], 0u, k2, k3);
   }
-  float m = -INFINITY, l = 0.f, o[4][4];
-  zero_acc<4>(o);
+  float mx = -INFINITY;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    if (j * 8 + 2 * c >= kmax) s[j][0] = -INFINITY;
+    if (j * 8 + 2 * c + 1 >= kmax) s[j][1] = -INFINITY;
+    mx = fmaxf(mx, fmaxf(s[j][0], s[j][1]));
+  }
+  mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+  mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+  const float m_new = fmaxf(h.m, mx);                        // finite: key 0 of the chunk is valid
+  const float corr = exp2f(h.m - m_new);
+  float ps = 0.f;
+  uint32_t pa[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float p0 = exp2f(s[j][0] - m_new), p1 = exp2f(s[j][1] - m_new);
+    ps += p0 + p1;
+    pa[j] = pack_bf16(p0, p1);
+  }
+  h.l = fmaf(h.l, corr, ps);
+  h.m = m_new;
+#pragma unroll
+  for (int nt = 0; nt < 4; ++nt) { h.o[nt][0] *= corr; h.o[nt][1] *= corr; }
+#pragma unroll
+  for (int kg = 0; kg < 2; ++kg)
+#pragma unroll
+    for (int dp = 0; dp < 2; ++dp) {                         // 16 output dims each
+      const int key = kg * 16 + ((lane >> 3) & 1) * 8 + (lane & 7), unit = 2 * dp + (lane >> 4);
+      uint32_t v0, v1, v2, v3;
+      ldsm_x4_trans(base + 2048 + key * 64 + ((unit ^ ((key >> 1) & 3)) << 4), v0, v1, v2, v3);
+      mma16816(h.o[2 * dp], pa[2 * kg], 0u, pa[2 * kg + 1], 0u, v0, v1);
+      mma16816(h.o[2 * dp + 1], pa[2 * kg], 0u, pa[2 * kg + 1], 0u, v2, v3);
+    }
+}
+
+// Single-query attention of sample `warp` for the CTA's two heads over `n_keys` cached keys arriving through the warp's
+// ring (chunk c of head A in one slot, of head B in the next).  q (pre-scaled by log2(e)/sqrt(dh)) is row 0 of the
+// m16 A operand.  patch_key >= 0: that key's K/V rows (this step's, not yet in the cache copy) are written into the
+// chunks first.  The normalised outputs (2 x 32 values) are pushed to columns [64 rank, +64) of row `warp` of every
+// peer's Att buffer.
+__device__ __forceinline__ void attend2(const DecStackParams& p, Smem& sm, Stream& st, int rank, int warp, int lane,
+                                        int n_keys, int patch_key, uint64_t policy) {
+  const int g = lane >> 2, c = lane & 3;
+  HeadState h[HPC];
+#pragma unroll
+  for (int hd = 0; hd < HPC; ++hd) {
+#pragma unroll
+    for (int ks = 0; ks < 2; ++ks) {
+      h[hd].qa[ks][0] = g == 0 ? *reinterpret_cast<const uint32_t*>(&sm.Qs[warp][hd * DH + ks * 16 + 2 * c]) : 0u;
+      h[hd].qa[ks][1] = g == 0 ? *reinterpret_cast<const uint32_t*>(&sm.Qs[warp][hd * DH + ks * 16 + 8 + 2 * c]) : 0u;
+    }
+    h[hd].m = -INFINITY; h[hd].l = 0.f;
+    zero_acc<4>(h[hd].o);
+  }
   const int n_chunks = (n_keys + DS_CHUNK_KEYS - 1) / DS_CHUNK_KEYS;
   for (int ch = 0; ch < n_chunks; ++ch) {
-    const uint32_t base = st.ring + (st.consumed % SLOTS) * SLOT_BYTES;
-    stream_wait(st);
+    const int kmax = min(DS_CHUNK_KEYS, n_keys - ch * DS_CHUNK_KEYS);
+#pragma unroll
+    for (int hd = 0; hd < HPC; ++hd) stream_wait(st, st.consumed + hd);
     if (patch_key >= 0 && (patch_key >> 5) == ch) {
-      if (lane < 8) {
-        const int u = lane & 3, isv = lane >> 2, kr = patch_key & 31;
-        const uint4 v = *reinterpret_cast<const uint4*>(isv ? &sm.Vn[row][u * 8] : &sm.Kn[row][u * 8]);
-        const uint32_t dst = base + isv * 2048 + kr * 64 + ((u ^ ((kr >> 1) & 3)) << 4);
+      if (lane < 16) {
+        const int u = lane & 3, isv = (lane >> 2) & 1, hd = lane >> 3, kr = patch_key & 31;
+        const uint4 v = *reinterpret_cast<const uint4*>(isv ? &sm.Vn[warp][hd * DH + u * 8] : &sm.Kn[warp][hd * DH + u * 8]);
+        const uint32_t dst = st.ring + ((st.consumed + hd) % SLOTS) * SLOT_BYTES + isv * 2048 + kr * 64 +
+                             ((u ^ ((kr >> 1) & 3)) << 4);
         asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
       }
       __syncwarp();
     }
-    const int kmax = min(DS_CHUNK_KEYS, n_keys - ch * DS_CHUNK_KEYS);
 #pragma unroll
-    for (int kg = 0; kg < 2; ++kg) {
-      if (kg * 16 < kmax) {
-        float s[2][4];
-        zero_acc<2>(s);
+    for (int hd = 0; hd < HPC; ++hd)
+      attend_chunk(h[hd], st.ring + ((st.consumed + hd) % SLOTS) * SLOT_BYTES, kmax, lane);
+    __syncwarp();                                            // every lane is done reading the two slots
+    st.consumed += HPC;
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {                        // 8 keys each
-          const int key = kg * 16 + j * 8 + (lane & 7), unit = lane >> 3;
-          uint32_t k0, k1, k2, k3;
-          ldsm_x4(base + key * 64 + ((unit ^ ((key >> 1) & 3)) << 4), k0, k1, k2, k3);
-          mma16816(s[j], qa[0][0], 0u, qa[0][1], 0u, k0, k1);
-          mma16816(s[j], qa[1][0], 0u, qa[1][1], 0u, k2, k3);
-        }
-        const int key0 = kg * 16 + 2 * c;                    // chunk-local key of s[0][0]; s[1][*] are 8 further
-        if (key0 >= kmax) s[0][0] = -INFINITY;
-        if (key0 + 1 >= kmax) s[0][1] = -INFINITY;
-        if (key0 + 8 >= kmax) s[1][0] = -INFINITY;
-        if (key0 + 9 >= kmax) s[1][1] = -INFINITY;
-        float mx = fmaxf(fmaxf(s[0][0], s[0][1]), fmaxf(s[1][0], s[1][1]));
-        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
-        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
-        const float m_new = fmaxf(m, mx);                    // finite: the group holds at least one valid key
-        const float corr = exp2f(m - m_new);
-        const float p00 = exp2f(s[0][0] - m_new), p01 = exp2f(s[0][1] - m_new);
-        const float p10 = exp2f(s[1][0] - m_new), p11 = exp2f(s[1][1] - m_new);
-        l = fmaf(l, corr, (p00 + p01) + (p10 + p11));
-        m = m_new;
-#pragma unroll
-        for (int nt = 0; nt < 4; ++nt) { o[nt][0] *= corr; o[nt][1] *= corr; }
-        const uint32_t pa0 = pack_bf16(p00, p01), pa2 = pack_bf16(p10, p11);
-#pragma unroll
-        for (int dp = 0; dp < 2; ++dp) {                     // 16 output dims each
-          const int key = kg * 16 + ((lane >> 3) & 1) * 8 + (lane & 7), unit = 2 * dp + (lane >> 4);
-          uint32_t v0, v1, v2, v3;
-          ldsm_x4_trans(base + 2048 + key * 64 + ((unit ^ ((key >> 1) & 3)) << 4), v0, v1, v2, v3);
-          mma16816(o[2 * dp], pa0, 0u, pa2, 0u, v0, v1);
-          mma16816(o[2 * dp + 1], pa0, 0u, pa2, 0u, v2, v3);
-        }
-      }
-    }
-    __syncwarp();                                            // every lane is done reading the slot
-    ++st.consumed;
-    stream_issue(p, st, rank, lane, policy);
+    for (int hd = 0; hd < HPC; ++hd) stream_issue(p, st, rank, lane, policy);
   }
-  l += __shfl_xor_sync(0xffffffffu, l, 1);
-  l += __shfl_xor_sync(0xffffffffu, l, 2);
-  const float inv = 1.f / l;
-  uint32_t w[4];
+  // lanes 0-3 hold the outputs: word (hd, nt) of quad lane c = dims hd*32 + 8 nt + 2c, +1, i.e. word index
+  // 16 hd + 4 nt + c of the 32-word row slice.  Lane i sends the four words {(i & 7) + 8k} to peer i >> 3.
+  uint32_t w[HPC][4];
 #pragma unroll
-  for (int nt = 0; nt < 4; ++nt) w[nt] = pack_bf16(o[nt][0] * inv, o[nt][1] * inv);   // dims 8nt + 2c, +1 (lanes 0-3)
-  // lane i sends quad-lane (i & 3)'s four words to peer i >> 2
-  const int src = lane & 3, peer = lane >> 2;
-  const uint32_t dst = map_peer(ptx::smem_u32(&sm.Att[row][rank * DH + 2 * src]), (uint32_t)peer);
+  for (int hd = 0; hd < HPC; ++hd) {
+    float l = h[hd].l;
+    l += __shfl_xor_sync(0xffffffffu, l, 1);
+    l += __shfl_xor_sync(0xffffffffu, l, 2);
+    const float inv = 1.f / l;
 #pragma unroll
-  for (int nt = 0; nt < 4; ++nt) st_peer_b32(dst + nt * 16, __shfl_sync(0xffffffffu, w[nt], src));
+    for (int nt = 0; nt < 4; ++nt) w[hd][nt] = pack_bf16(h[hd].o[nt][0] * inv, h[hd].o[nt][1] * inv);
+  }
+  const int src = lane & 3, peer = lane >> 3, odd = (lane >> 2) & 1;
+  const uint32_t dst = map_peer(ptx::smem_u32(&sm.Att[warp][rank * SL]), (uint32_t)peer) + (lane & 7) * 4;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {          // word (lane & 7) + 8k = 16 (k >> 1) + 4 (2 (k & 1) + odd) + src
+    const uint32_t va = __shfl_sync(0xffffffffu, w[k >> 1][2 * (k & 1)], src);
+    const uint32_t vb = __shfl_sync(0xffffffffu, w[k >> 1][2 * (k & 1) + 1], src);
+    st_peer_b32(dst + k * 32, odd ? vb : va);
+  }
 }
 
-// y slice [16 x 32] of this CTA = A . W[32 rank .. +32]^T + bias + residual, pushed to every peer's Y (warps 0-3)
-__device__ __forceinline__ void proj_residual_push(Smem& sm, const bf16 (*A)[LDA], const bf16* __restrict__ W,
+// y slice [8 x 64] of this CTA = A . W[64 rank .. +64]^T + bias + residual (one n-tile per warp, weights already in
+// registers), pushed to every peer's Y
+__device__ __forceinline__ void proj_residual_push(Smem& sm, const bf16 (*A)[LDA], const WFrag<1>& wf,
                                                    const float* __restrict__ bias, int rank, int warp, int lane) {
-  if (warp < 4) {
-    const int g = lane >> 2, c = lane & 3;
-    AFrag a;
-    load_a(a, &A[0][0], LDA, lane);
-    const bf16* wrow[1] = {W + (size_t)(rank * 32 + warp * 8 + g) * D + 8 * c};
-    float acc[1][4];
-    zero_acc<1>(acc);
-    mma_tiles<1>(a, wrow, acc);
-    const int col = rank * 32 + warp * 8 + 2 * c;
-    const float b0 = __ldg(bias + col), b1 = __ldg(bias + col + 1);
-    const float2 lo = make_float2(acc[0][0] + b0 + sm.Y[g][col], acc[0][1] + b1 + sm.Y[g][col + 1]);
-    const float2 hi = make_float2(acc[0][2] + b0 + sm.Y[g + 8][col], acc[0][3] + b1 + sm.Y[g + 8][col + 1]);
-    const uint32_t a_lo = ptx::smem_u32(&sm.Y[g][col]), a_hi = ptx::smem_u32(&sm.Y[g + 8][col]);
+  const int g = lane >> 2, c = lane & 3, col = rank * SL + warp * 8 + 2 * c;
+  const float b0 = __ldg(bias + col), b1 = __ldg(bias + col + 1);
+  AFrag a;
+  load_a(a, &A[0][0], LDA, lane);
+  float acc[1][4];
+  zero_acc<1>(acc);
+  mma_w<1>(a, wf, acc);
+  const float2 v = make_float2(acc[0][0] + b0 + sm.Y[g][col], acc[0][1] + b1 + sm.Y[g][col + 1]);
+  const uint32_t addr = ptx::smem_u32(&sm.Y[g][col]);
 #pragma unroll
-    for (int dst = 0; dst < NH; ++dst) {
-      st_peer_f2(map_peer(a_lo, (uint32_t)dst), lo);
-      st_peer_f2(map_peer(a_hi, (uint32_t)dst), hi);
-    }
-  }
+  for (int dst = 0; dst < CL; ++dst) st_peer_f2(map_peer(addr, (uint32_t)dst), v);
 }
 
-__global__ void __cluster_dims__(NH, 1, 1) __launch_bounds__(THREADS, 1)
+__global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(THREADS, 1)
 decode_stack_kernel(const __grid_constant__ DecStackParams p) {
   extern __shared__ __align__(128) uint8_t ds_raw[];
   Smem& sm = *reinterpret_cast<Smem*>(ds_raw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, c = lane & 3;
   const int rank = (int)cluster_rank();
   const int m0 = blockIdx.y * R;
-
+#ifdef DS_PROFILE
+  const bool prof_on = tid == 0 && blockIdx.y == 0 && rank == 0;
+  long long prof[20] = {0}, prof_last = clock64();
+#endif
   pdl_launch_dependents();
   cluster_arrive_relaxed();                                  // "my shared memory exists" (waited on before the first push)
   if (tid < NWARP * SLOTS) ptx::mbar_init(&sm.bars[0][0] + tid, 1);
@@ -350,26 +399,23 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
   pdl_wait();                                                // ids, step counter and the self caches come from earlier kernels
 
   const int t = *p.step;
+  const bool row_ok = m0 + g < p.B;                          // this thread's GEMM output row is a real sample
   Stream st;
   st.issued = st.consumed = 0;
-  st.il = st.iph = st.isi = st.ic = 0;
+  st.il = st.iph = st.ic = st.ih = 0;
+  st.b = min(m0 + warp, p.B - 1);
+  const int nv = max(1, __ldg(p.n_valid + st.b));
   st.n_self = t / DS_CHUNK_KEYS + 1;
-  st.b0 = min(m0 + 2 * warp, p.B - 1);
-  st.b1 = min(m0 + 2 * warp + 1, p.B - 1);
-  const int nv0 = max(1, __ldg(p.n_valid + st.b0)), nv1 = max(1, __ldg(p.n_valid + st.b1));
-  st.n_cross0 = (nv0 + DS_CHUNK_KEYS - 1) / DS_CHUNK_KEYS;
-  st.n_cross1 = (nv1 + DS_CHUNK_KEYS - 1) / DS_CHUNK_KEYS;
+  st.n_cross = (nv + DS_CHUNK_KEYS - 1) / DS_CHUNK_KEYS;
   st.ring = ptx::smem_u32(&sm.ring[warp][0][0]);
   st.bars = ptx::smem_u32(&sm.bars[warp][0]);
   const uint64_t policy = ptx::policy_evict_first();
 #pragma unroll 1
   for (int i = 0; i < SLOTS; ++i) stream_issue(p, st, rank, lane, policy);
 
-  // ---- DecoderEmbeddings: y = LN_eps(E_word[id] + E_pos[t]) (models/transformer_modules.py:113-129) ----
-#pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const int r = warp * 2 + i, b = min(m0 + r, p.B - 1);
-    const int64_t id = p.caption[(int64_t)b * p.max_len + t];
+  // ---- DecoderEmbeddings: y = LN_eps(E_word[id] + E_pos[t]) (models/transformer_modules.py:113-129); warp w = row w ----
+  {
+    const int64_t id = p.caption[(int64_t)st.b * p.max_len + t];
     float v[8];
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
@@ -389,197 +435,253 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
     for (int j = 0; j < 2; ++j) {
       const float4 ga = __ldg(reinterpret_cast<const float4*>(p.emb_g + j * 128 + lane * 4));
       const float4 be = __ldg(reinterpret_cast<const float4*>(p.emb_b + j * 128 + lane * 4));
-      *reinterpret_cast<float4*>(&sm.Y[r][j * 128 + lane * 4]) =
+      *reinterpret_cast<float4*>(&sm.Y[warp][j * 128 + lane * 4]) =
           make_float4((v[4 * j] - mean) * rstd * ga.x + be.x, (v[4 * j + 1] - mean) * rstd * ga.y + be.y,
                       (v[4 * j + 2] - mean) * rstd * ga.z + be.z, (v[4 * j + 3] - mean) * rstd * ga.w + be.w);
     }
   }
   __syncthreads();
   cluster_wait();                                            // every CTA of the cluster is running
+  DS_T(0);
 
   const float qscale = rsqrtf((float)DH) * LOG2E;
+  const int scol = warp * 8 + 2 * c;                         // this thread's column pair within the CTA's 64-column slice
 #pragma unroll 1
   for (int l = 0; l < p.n_layers; ++l) {
     const DecStackLayer& L = p.L[l];
     // ---- self-attention sublayer (models/transformer_modules.py:22-46) ----
-    layernorm_rows(sm.Y, sm.Abuf, L.ln1_g, L.ln1_b, 1e-5f, warp, lane);
-    __syncthreads();
     {
-      // q, k, v of head `rank`: 12 n-tiles (4 each), warp w takes tile w and, for w < 4, tile w + 8
+      // q, k, v columns [64 rank + 8 warp, +8) of each: three n-tiles per warp
+      WFrag<3> wf;
+      const bf16* wrow[3];
+      float rb[3][2];
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        wrow[j] = L.w_sqkv + (size_t)(j * D + rank * SL + warp * 8 + g) * D + 8 * c;
+        const float* r = L.rb_sqkv + (size_t)t * 3 * D + j * D + rank * SL + scol;
+        rb[j][0] = __ldg(r); rb[j][1] = __ldg(r + 1);
+      }
+      load_w<3>(wf, wrow);
+      layernorm_row(sm.Y, sm.Abuf, L.ln1_g, L.ln1_b, 1e-5f, warp, lane);
+      __syncthreads();
       AFrag a;
       load_a(a, &sm.Abuf[0][0], LDA, lane);
-      const int ntiles = warp < 4 ? 2 : 1;
-      float acc[2][4];
-      zero_acc<2>(acc);
-      auto wrow_of = [&](int nt) {
-        return L.w_sqkv + (size_t)((nt >> 2) * D + rank * DH + (nt & 3) * 8 + g) * D + 8 * c;
-      };
-      if (ntiles == 2) {
-        const bf16* wrow[2] = {wrow_of(warp), wrow_of(warp + 8)};
-        mma_tiles<2>(a, wrow, acc);
-      } else {
-        const bf16* wrow[1] = {wrow_of(warp)};
-        float acc1[1][4];
-        zero_acc<1>(acc1);
-        mma_tiles<1>(a, wrow, acc1);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) acc[0][k] = acc1[0][k];
-      }
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        if (j >= ntiles) break;
-        const int nt = warp + 8 * j, which = nt >> 2, col = (nt & 3) * 8 + 2 * c;       // col within the head
-        const float* rb = L.rb_sqkv + (size_t)t * 3 * D + which * D + rank * DH + col;
-        const float r0 = __ldg(rb), r1 = __ldg(rb + 1);
-        float v00 = acc[j][0] + r0, v01 = acc[j][1] + r1, v10 = acc[j][2] + r0, v11 = acc[j][3] + r1;
-        if (which == 0) {
-          *reinterpret_cast<uint32_t*>(&sm.Qs[g][col]) = pack_bf16(v00 * qscale, v01 * qscale);
-          *reinterpret_cast<uint32_t*>(&sm.Qs[g + 8][col]) = pack_bf16(v10 * qscale, v11 * qscale);
-        } else {
-          bf16(*dst)[DH] = which == 1 ? sm.Kn : sm.Vn;
-          const uint32_t lo = pack_bf16(v00, v01), hi = pack_bf16(v10, v11);
-          *reinterpret_cast<uint32_t*>(&dst[g][col]) = lo;
-          *reinterpret_cast<uint32_t*>(&dst[g + 8][col]) = hi;
-          // append to the cache for the steps to come (chunk t/32, row t%32, swizzled 16-byte units)
-          const int kr = t & 31, unit = (nt & 3) ^ ((kr >> 1) & 3);
-          const size_t off = (size_t)(t >> 5) * DS_CHUNK_ELEMS + (which == 2 ? 1024 : 0) + kr * 32 + unit * 8 + 2 * c;
-          if (m0 + g < p.B)
-            *reinterpret_cast<uint32_t*>(L.self_kv + (size_t)((m0 + g) * NH + rank) * p.self_chunks * DS_CHUNK_ELEMS + off) = lo;
-          if (m0 + g + 8 < p.B)
-            *reinterpret_cast<uint32_t*>(L.self_kv + (size_t)((m0 + g + 8) * NH + rank) * p.self_chunks * DS_CHUNK_ELEMS + off) = hi;
-        }
+      float acc[3][4];
+      zero_acc<3>(acc);
+      mma_w<3>(a, wf, acc);
+      *reinterpret_cast<uint32_t*>(&sm.Qs[g][scol]) = pack_bf16((acc[0][0] + rb[0][0]) * qscale, (acc[0][1] + rb[0][1]) * qscale);
+      const uint32_t kk = pack_bf16(acc[1][0] + rb[1][0], acc[1][1] + rb[1][1]);
+      const uint32_t vv = pack_bf16(acc[2][0] + rb[2][0], acc[2][1] + rb[2][1]);
+      *reinterpret_cast<uint32_t*>(&sm.Kn[g][scol]) = kk;
+      *reinterpret_cast<uint32_t*>(&sm.Vn[g][scol]) = vv;
+      if (row_ok) {
+        // append to the cache for the steps to come (chunk t/32, row t%32, swizzled 16-byte units)
+        const int kr = t & 31, head = rank * HPC + (warp >> 2), unit = (warp & 3) ^ ((kr >> 1) & 3);
+        bf16* dst = L.self_kv + ((size_t)((m0 + g) * NH + head) * p.self_chunks + (t >> 5)) * DS_CHUNK_ELEMS + kr * 32 +
+                    unit * 8 + 2 * c;
+        *reinterpret_cast<uint32_t*>(dst) = kk;
+        *reinterpret_cast<uint32_t*>(dst + 1024) = vv;
       }
     }
     __syncthreads();
-    attend(p, sm, st, rank, warp, lane, 2 * warp, t + 1, t, policy);
-    attend(p, sm, st, rank, warp, lane, 2 * warp + 1, t + 1, t, policy);
-    cluster_sync();                                          // #1: Att rows complete in every CTA
-    proj_residual_push(sm, sm.Att, L.w_so, L.b_so, rank, warp, lane);
-    cluster_sync();                                          // #2: new residual rows complete
+    DS_T(1);
+    WFrag<1> wo;
+    {
+      const bf16* wrow[1] = {L.w_so + (size_t)(rank * SL + warp * 8 + g) * D + 8 * c};
+      load_w<1>(wo, wrow);                                   // lands while the attention runs
+    }
+    attend2(p, sm, st, rank, warp, lane, t + 1, t, policy);
+    DS_T(2);
+    cluster_arrive();
+    cluster_wait();                                          // #1: Att rows complete in every CTA
+    DS_T(3);
+    proj_residual_push(sm, sm.Att, wo, L.b_so, rank, warp, lane);
+    DS_T(4);
+    cluster_arrive();
+    float rq[2];
+    {
+      const bf16* wrow[1] = {L.w_cq + (size_t)(rank * SL + warp * 8 + g) * D + 8 * c};
+      load_w<1>(wo, wrow);
+      const float* r = L.rb_cq + (size_t)t * D + rank * SL + scol;
+      rq[0] = __ldg(r); rq[1] = __ldg(r + 1);
+    }
+    cluster_wait();                                          // #2: new residual rows complete
+    DS_T(5);
 
     // ---- cross-attention sublayer (models/transformer_modules.py:49-74) ----
-    layernorm_rows(sm.Y, sm.Abuf, L.ln2_g, L.ln2_b, 1e-5f, warp, lane);
+    layernorm_row(sm.Y, sm.Abuf, L.ln2_g, L.ln2_b, 1e-5f, warp, lane);
     __syncthreads();
-    if (warp < 4) {
+    {
       AFrag a;
       load_a(a, &sm.Abuf[0][0], LDA, lane);
-      const bf16* wrow[1] = {L.w_cq + (size_t)(rank * DH + warp * 8 + g) * D + 8 * c};
       float acc[1][4];
       zero_acc<1>(acc);
-      mma_tiles<1>(a, wrow, acc);
-      const int col = warp * 8 + 2 * c;
-      const float* rb = L.rb_cq + (size_t)t * D + rank * DH + col;
-      const float r0 = __ldg(rb), r1 = __ldg(rb + 1);
-      *reinterpret_cast<uint32_t*>(&sm.Qs[g][col]) = pack_bf16((acc[0][0] + r0) * qscale, (acc[0][1] + r1) * qscale);
-      *reinterpret_cast<uint32_t*>(&sm.Qs[g + 8][col]) = pack_bf16((acc[0][2] + r0) * qscale, (acc[0][3] + r1) * qscale);
+      mma_w<1>(a, wo, acc);
+      *reinterpret_cast<uint32_t*>(&sm.Qs[g][scol]) = pack_bf16((acc[0][0] + rq[0]) * qscale, (acc[0][1] + rq[1]) * qscale);
+      const bf16* wrow[1] = {L.w_co + (size_t)(rank * SL + warp * 8 + g) * D + 8 * c};
+      load_w<1>(wo, wrow);
     }
     __syncthreads();
-    attend(p, sm, st, rank, warp, lane, 2 * warp, nv0, -1, policy);
-    attend(p, sm, st, rank, warp, lane, 2 * warp + 1, nv1, -1, policy);
-    cluster_sync();                                          // #3
-    proj_residual_push(sm, sm.Att, L.w_co, L.b_co, rank, warp, lane);
-    cluster_sync();                                          // #4
-
-    // ---- feed-forward sublayer (models/transformer_modules.py:77-97), hidden slice [256 rank, +256) ----
-    layernorm_rows(sm.Y, sm.Abuf, L.ln3_g, L.ln3_b, 1e-5f, warp, lane);
+    DS_T(6);
+    attend2(p, sm, st, rank, warp, lane, nv, -1, policy);
+    DS_T(7);
+    cluster_arrive();
+    cluster_wait();                                          // #3
+    DS_T(8);
+    proj_residual_push(sm, sm.Att, wo, L.b_co, rank, warp, lane);
+    DS_T(9);
+    cluster_arrive();
+    // ---- feed-forward sublayer (models/transformer_modules.py:77-97), hidden slice [512 rank, +512) ----
+    // FF1: 64 n-tiles, 8 per warp, two at a time through two register buffers (the next pair loads while this one
+    // multiplies); FF2: K = 512 in two halves, 4 n-tiles per warp, same ping-pong.
+    WFrag<2> wa, wb;
+    auto ff1_rows = [&](int bt, const bf16* (&wrow)[2]) {
+#pragma unroll
+      for (int j = 0; j < 2; ++j) wrow[j] = L.w_ff1 + (size_t)(rank * FS + (warp * 8 + bt * 2 + j) * 8 + g) * D + 8 * c;
+    };
+    auto ff2_rows = [&](int kh, int bt, const bf16* (&wrow)[2]) {
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+        wrow[j] = L.w_ff2 + (size_t)((warp * 4 + bt * 2 + j) * 8 + g) * p.d_ff + rank * FS + kh * D + 8 * c;
+    };
+    {
+      const bf16* wrow[2];
+      ff1_rows(0, wrow);
+      load_w<2>(wa, wrow);
+    }
+    cluster_wait();                                          // #4
+    DS_T(10);
+    layernorm_row(sm.Y, sm.Abuf, L.ln3_g, L.ln3_b, 1e-5f, warp, lane);
     __syncthreads();
     {
       AFrag a;
       load_a(a, &sm.Abuf[0][0], LDA, lane);
-      const bf16* wrow[4];
+      auto ff1_epilogue = [&](int bt, const float (&acc)[2][4]) {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) wrow[j] = L.w_ff1 + (size_t)(rank * D + (warp * 4 + j) * 8 + g) * D + 8 * c;
-      float acc[4][4];
-      zero_acc<4>(acc);
-      mma_tiles<4>(a, wrow, acc);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int col = (warp * 4 + j) * 8 + 2 * c;
-        const float b0 = __ldg(L.b_ff1 + rank * D + col), b1 = __ldg(L.b_ff1 + rank * D + col + 1);
-        *reinterpret_cast<uint32_t*>(&sm.Hs[g][col]) = pack_bf16(fmaxf(acc[j][0] + b0, 0.f), fmaxf(acc[j][1] + b1, 0.f));
-        *reinterpret_cast<uint32_t*>(&sm.Hs[g + 8][col]) = pack_bf16(fmaxf(acc[j][2] + b0, 0.f), fmaxf(acc[j][3] + b1, 0.f));
-      }
+        for (int j = 0; j < 2; ++j) {
+          const int col = (warp * 8 + bt * 2 + j) * 8 + 2 * c;
+          const float b0 = __ldg(L.b_ff1 + rank * FS + col), b1 = __ldg(L.b_ff1 + rank * FS + col + 1);
+          *reinterpret_cast<uint32_t*>(&sm.Hs[g][col]) = pack_bf16(fmaxf(acc[j][0] + b0, 0.f), fmaxf(acc[j][1] + b1, 0.f));
+        }
+      };
+      const bf16* wrow[2];
+      float acc[2][4];
+      ff1_rows(1, wrow); load_w<2>(wb, wrow);
+      zero_acc<2>(acc); mma_w<2>(a, wa, acc); ff1_epilogue(0, acc);
+      ff1_rows(2, wrow); load_w<2>(wa, wrow);
+      zero_acc<2>(acc); mma_w<2>(a, wb, acc); ff1_epilogue(1, acc);
+      ff1_rows(3, wrow); load_w<2>(wb, wrow);
+      zero_acc<2>(acc); mma_w<2>(a, wa, acc); ff1_epilogue(2, acc);
+      ff2_rows(0, 0, wrow); load_w<2>(wa, wrow);
+      zero_acc<2>(acc); mma_w<2>(a, wb, acc); ff1_epilogue(3, acc);
     }
     __syncthreads();
+    DS_T(11);
     {
       AFrag a;
-      load_a(a, &sm.Hs[0][0], LDA, lane);
-      const bf16* wrow[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) wrow[j] = L.w_ff2 + (size_t)((warp * 4 + j) * 8 + g) * p.d_ff + rank * D + 8 * c;
-      float acc[4][4];
-      zero_acc<4>(acc);
-      mma_tiles<4>(a, wrow, acc);
-      // output columns [32 warp, +32) belong to CTA `warp`: its slot `rank`
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const uint32_t a_lo = map_peer(ptx::smem_u32(&sm.Ps[rank][g][j * 8 + 2 * c]), (uint32_t)warp);
-        const uint32_t a_hi = map_peer(ptx::smem_u32(&sm.Ps[rank][g + 8][j * 8 + 2 * c]), (uint32_t)warp);
-        st_peer_f2(a_lo, make_float2(acc[j][0], acc[j][1]));
-        st_peer_f2(a_hi, make_float2(acc[j][2], acc[j][3]));
-      }
+      const bf16* wrow[2];
+      float acc0[2][4], acc1[2][4];
+      zero_acc<2>(acc0); zero_acc<2>(acc1);
+      load_a(a, &sm.Hs[0][0], LDH, lane);
+      ff2_rows(0, 1, wrow); load_w<2>(wb, wrow);
+      mma_w<2>(a, wa, acc0);
+      ff2_rows(1, 0, wrow); load_w<2>(wa, wrow);
+      mma_w<2>(a, wb, acc1);
+      load_a(a, &sm.Hs[0][D], LDH, lane);
+      ff2_rows(1, 1, wrow); load_w<2>(wb, wrow);
+      mma_w<2>(a, wa, acc0);
+      mma_w<2>(a, wb, acc1);
+      // output columns [32 warp, +32) belong to CTA warp >> 1: its slot `rank`
+      const uint32_t base = map_peer(ptx::smem_u32(&sm.Ps[rank][g][(warp & 1) * 32 + 2 * c]), (uint32_t)(warp >> 1));
+      st_peer_f2(base, make_float2(acc0[0][0], acc0[0][1]));
+      st_peer_f2(base + 32, make_float2(acc0[1][0], acc0[1][1]));
+      st_peer_f2(base + 64, make_float2(acc1[0][0], acc1[0][1]));
+      st_peer_f2(base + 96, make_float2(acc1[1][0], acc1[1][1]));
     }
-    cluster_sync();                                          // #5: the eight partial slots of my columns are here
+    DS_T(12);
+    cluster_arrive();
+    const int rc2 = lane * 2, rcol = rank * SL + rc2;        // reduction: warp = row, lane = column pair of my slice
+    float2 s = make_float2(__ldg(L.b_ff2 + rcol) + sm.Y[warp][rcol], __ldg(L.b_ff2 + rcol + 1) + sm.Y[warp][rcol + 1]);
+    cluster_wait();                                          // #5: the four partial slots of my columns are here
+    DS_T(13);
     {
-      const int row = tid >> 4, c2 = (tid & 15) * 2, col = rank * 32 + c2;
-      float2 s = make_float2(__ldg(L.b_ff2 + col) + sm.Y[row][col], __ldg(L.b_ff2 + col + 1) + sm.Y[row][col + 1]);
-      float2 part = *reinterpret_cast<const float2*>(&sm.Ps[0][row][c2]);
+      float2 part = *reinterpret_cast<const float2*>(&sm.Ps[0][warp][rc2]);
 #pragma unroll
-      for (int src = 1; src < NH; ++src) {
-        const float2 v = *reinterpret_cast<const float2*>(&sm.Ps[src][row][c2]);
+      for (int src = 1; src < CL; ++src) {
+        const float2 v = *reinterpret_cast<const float2*>(&sm.Ps[src][warp][rc2]);
         part.x += v.x; part.y += v.y;
       }
       s.x += part.x; s.y += part.y;
-      const uint32_t a = ptx::smem_u32(&sm.Y[row][col]);
+      const uint32_t a = ptx::smem_u32(&sm.Y[warp][rcol]);
 #pragma unroll
-      for (int dst = 0; dst < NH; ++dst) st_peer_f2(map_peer(a, (uint32_t)dst), s);
+      for (int dst = 0; dst < CL; ++dst) st_peer_f2(map_peer(a, (uint32_t)dst), s);
     }
-    cluster_sync();                                          // #6
+    DS_T(14);
+    cluster_arrive();
+    cluster_wait();                                          // #6
+    DS_T(15);
   }
 
   // ---- final LayerNorm + MLP head layers 0 and 1 (models/ConcatTransformer.py:146-147, models/caption.py:161-174) ----
-  layernorm_rows(sm.Y, sm.Abuf, p.fin_g, p.fin_b, 1e-5f, warp, lane);
-  __syncthreads();
-  bf16(*M1)[LDM1] = reinterpret_cast<bf16(*)[LDM1]>(&sm.Att[0][0]);
+  bf16(*M1)[LDH] = sm.Hs;
   {
-    // hidden columns [64 rank, +64): one n-tile per warp, pushed to every peer (layer 1 needs whole rows)
+    // hidden columns [128 rank, +128): two n-tiles per warp, pushed to every peer (layer 1 needs whole rows)
+    WFrag<2> wf;
+    const int n0 = rank * (MH / CL) + warp * 16;
+    const bf16* wrow[2] = {p.w_m0 + (size_t)(n0 + g) * D + 8 * c, p.w_m0 + (size_t)(n0 + 8 + g) * D + 8 * c};
+    load_w<2>(wf, wrow);
+    layernorm_row(sm.Y, sm.Abuf, p.fin_g, p.fin_b, 1e-5f, warp, lane);
+    __syncthreads();
     AFrag a;
     load_a(a, &sm.Abuf[0][0], LDA, lane);
-    const int n0 = rank * 64 + warp * 8;
-    const bf16* wrow[1] = {p.w_m0 + (size_t)(n0 + g) * D + 8 * c};
-    float acc[1][4];
-    zero_acc<1>(acc);
-    mma_tiles<1>(a, wrow, acc);
-    const float b0 = __ldg(p.b_m0 + n0 + 2 * c), b1 = __ldg(p.b_m0 + n0 + 2 * c + 1);
-    const uint32_t lo = pack_bf16(fmaxf(acc[0][0] + b0, 0.f), fmaxf(acc[0][1] + b1, 0.f));
-    const uint32_t hi = pack_bf16(fmaxf(acc[0][2] + b0, 0.f), fmaxf(acc[0][3] + b1, 0.f));
-    const uint32_t a_lo = ptx::smem_u32(&M1[g][n0 + 2 * c]), a_hi = ptx::smem_u32(&M1[g + 8][n0 + 2 * c]);
+    float acc[2][4];
+    zero_acc<2>(acc);
+    mma_w<2>(a, wf, acc);
 #pragma unroll
-    for (int dst = 0; dst < NH; ++dst) {
-      st_peer_b32(map_peer(a_lo, (uint32_t)dst), lo);
-      st_peer_b32(map_peer(a_hi, (uint32_t)dst), hi);
+    for (int j = 0; j < 2; ++j) {
+      const int col = n0 + j * 8 + 2 * c;
+      const float b0 = __ldg(p.b_m0 + col), b1 = __ldg(p.b_m0 + col + 1);
+      const uint32_t v = pack_bf16(fmaxf(acc[j][0] + b0, 0.f), fmaxf(acc[j][1] + b1, 0.f));
+      const uint32_t addr = ptx::smem_u32(&M1[g][col]);
+#pragma unroll
+      for (int dst = 0; dst < CL; ++dst) st_peer_b32(map_peer(addr, (uint32_t)dst), v);
     }
   }
-  cluster_sync();                                            // last remote stores of the kernel are behind this barrier
   {
-    const int n0 = rank * 64 + warp * 8;
-    float acc[1][4];
-    zero_acc<1>(acc);
-#pragma unroll 1
-    for (int kh = 0; kh < MH / D; ++kh) {
-      AFrag a;
-      load_a(a, &M1[0][kh * D], LDM1, lane);
-      const bf16* wrow[1] = {p.w_m1 + (size_t)(n0 + g) * MH + kh * D + 8 * c};
-      mma_tiles<1>(a, wrow, acc);
+    WFrag<2> wf0, wf1;
+    const int n0 = rank * (MH / CL) + warp * 16;
+    const bf16* wrow0[2] = {p.w_m1 + (size_t)(n0 + g) * MH + 8 * c, p.w_m1 + (size_t)(n0 + 8 + g) * MH + 8 * c};
+    const bf16* wrow1[2] = {wrow0[0] + D, wrow0[1] + D};
+    cluster_arrive();
+    load_w<2>(wf0, wrow0);
+    load_w<2>(wf1, wrow1);
+    cluster_wait();                                          // last remote stores of the kernel are behind this barrier
+    float acc[2][4];
+    zero_acc<2>(acc);
+    AFrag a;
+    load_a(a, &M1[0][0], LDH, lane);
+    mma_w<2>(a, wf0, acc);
+    load_a(a, &M1[0][D], LDH, lane);
+    mma_w<2>(a, wf1, acc);
+    if (row_ok) {
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int col = n0 + j * 8 + 2 * c;
+        const float b0 = __ldg(p.b_m1 + col), b1 = __ldg(p.b_m1 + col + 1);
+        *reinterpret_cast<uint32_t*>(p.m2_out + (size_t)(m0 + g) * MH + col) =
+            pack_bf16(fmaxf(acc[j][0] + b0, 0.f), fmaxf(acc[j][1] + b1, 0.f));
+      }
     }
-    const float b0 = __ldg(p.b_m1 + n0 + 2 * c), b1 = __ldg(p.b_m1 + n0 + 2 * c + 1);
-    if (m0 + g < p.B)
-      *reinterpret_cast<uint32_t*>(p.m2_out + (size_t)(m0 + g) * MH + n0 + 2 * c) =
-          pack_bf16(fmaxf(acc[0][0] + b0, 0.f), fmaxf(acc[0][1] + b1, 0.f));
-    if (m0 + g + 8 < p.B)
-      *reinterpret_cast<uint32_t*>(p.m2_out + (size_t)(m0 + g + 8) * MH + n0 + 2 * c) =
-          pack_bf16(fmaxf(acc[0][2] + b0, 0.f), fmaxf(acc[0][3] + b1, 0.f));
   }
+#ifdef DS_PROFILE
+  DS_T(16);
+  if (prof_on && t == 60) {
+    printf("DS_PROFILE t=60 cycles: prologue %lld | ln1+qkv %lld self %lld bar1 %lld out %lld bar2 %lld | ln2+q %lld cross %lld bar3 "
+           "%lld cout %lld bar4 %lld | ln3+ff1 %lld ff2 %lld bar5 %lld reduce %lld bar6 %lld | head %lld\n",
+           prof[0], prof[1], prof[2], prof[3], prof[4], prof[5], prof[6], prof[7], prof[8], prof[9], prof[10], prof[11],
+           prof[12], prof[13], prof[14], prof[15], prof[16]);
+  }
+#endif
 }
 
 // rows of [K(256) | V(256)] -> [B][8][chunks][K 32x32 | V 32x32] with the 16-byte units of a key row XOR-swizzled by
@@ -607,17 +709,27 @@ __global__ void kv_to_chunked_kernel(const bf16* __restrict__ kv, bf16* __restri
 }  // namespace
 
 bool decode_stack_supported(int d_model, int n_heads, int d_ff, int n_layers, int mlp_hidden, int max_pos) {
-  return d_model == D && n_heads == NH && d_ff == NH * D && n_layers >= 1 && n_layers <= DS_MAX_LAYERS &&
+  return d_model == D && n_heads == NH && d_ff == CL * FS && n_layers >= 1 && n_layers <= DS_MAX_LAYERS &&
          mlp_hidden == MH && max_pos % DS_CHUNK_KEYS == 0;
 }
 
 void decode_stack_configure() {
   CUDA_OK(cudaFuncSetAttribute(decode_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
+  if (getenv("RETR_VERBOSE")) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(CL, 64, 1);
+    cfg.blockDim = dim3(THREADS);
+    cfg.dynamicSmemBytes = sizeof(Smem);
+    int n = -1;
+    cudaError_t e = cudaOccupancyMaxActiveClusters(&n, decode_stack_kernel, &cfg);
+    fprintf(stderr, "[retr] decode_stack_kernel: %zu B shared memory per CTA, max co-resident clusters of %d: %d (%s)\n",
+            sizeof(Smem), CL, n, cudaGetErrorString(e));
+  }
 }
 
 void decode_stack(const DecStackParams& p, cudaStream_t s) {
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(NH, (unsigned)cdiv(p.B, R), 1);
+  cfg.gridDim = dim3(CL, (unsigned)cdiv(p.B, R), 1);
   cfg.blockDim = dim3(THREADS);
   cfg.dynamicSmemBytes = sizeof(Smem);
   cfg.stream = s;

@@ -6,7 +6,7 @@
 namespace retr {
 
 constexpr int DS_MAX_LAYERS = 8;
-constexpr int DS_ROWS = 16;          // samples per cluster
+constexpr int DS_ROWS = 8;           // samples per cluster (one per warp)
 constexpr int DS_CHUNK_KEYS = 32;    // keys per K/V cache chunk
 constexpr int DS_CHUNK_ELEMS = 2 * DS_CHUNK_KEYS * 32;   // [K 32x32 | V 32x32] bf16 = 4 KB
 

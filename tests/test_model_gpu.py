@@ -457,12 +457,12 @@ def test_location_feature_shape_is_checked():
 
 @pytest.mark.parametrize("B", [5, 19])
 def test_decode_stack_kernel_consistent_with_teacher_forced(B, monkeypatch):
-    """The one-kernel decoder stack (csrc/decode_stack.cu: clusters of 8 CTAs x 16 samples, chunked swizzled K/V
+    """The one-kernel decoder stack (csrc/decode_stack.cu: clusters of 4 CTAs x 8 samples, chunked swizzled K/V
     caches, tensor-core single-query attention) against two independent computations of the same function:
     (a) the full-sequence bf16 kernels fed the ids it produced — the token chosen at step i must be the teacher-forced
         argmax at position i unless that position is a near-tie;
     (b) the launch-chain decode path of round 1 (RETR_DECODE_STACK=0).
-    B = 5 leaves 11 of a cluster's 16 rows empty; B = 19 adds a second, ragged cluster."""
+    B = 5 leaves 3 of a cluster's 8 rows empty; B = 19 is two full clusters and a ragged third."""
     kind = "CaptionGlobalLoc"
     monkeypatch.setenv("RETR_DECODE_STACK", "1")
     model, sd, cfg = gpu_model(kind, "bf16", calibrated=True)
