@@ -174,6 +174,21 @@ int retr_op_decode_out_ln_proj(const void* att, const void* Wo, const float* bo,
 int retr_op_decode_cross_attention(const void* q, const void* kcache, const void* vcache, int32_t cache_rows, void* out,
                                    int32_t M, int32_t n_heads, int32_t d_model, const int32_t* n_keys, void* stream);
 
+/* ---- allocation-free operator ---------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * C[M,N] (fp32, row pitch N) = A[M,K] . W[N,K]^T + bias[N] (bias may be NULL); A, W bf16 row-major, device memory.
+ * The decode step's small-M GEMM (csrc/small_gemm.cu) with a deterministic split-K over `split_k` CTAs per output
+ * tile, whose partial tiles and tile tickets live in file-scope static __device__ arrays instead of an arena:
+ * the call path performs no cudaMalloc / cudaFree / allocating library call.
+ * Limits (a clear error otherwise): split_k * M * N <= 1 048 576 floats (4 MiB of static scratch, held by every
+ * GPU that loads the library until exit); ceil(M/64) * ceil(N/32) <= 4096 tiles; N % 8 == 0; K % 256 == 0;
+ * split_k divides K/256 (K/512 when K == 512); M <= 2048.
+ * All calls on a device SHARE the static arrays, which keep the previous call's contents: tickets are cleared on
+ * `stream` before each launch; calls that overlap on the GPU (different streams without a dependency) race. */
+int retr_op_small_gemm_noalloc(const void* A, const void* W, const float* bias, float* C, int32_t M, int32_t N,
+                               int32_t K, int32_t split_k, void* stream);
+
 /* ---- training step (engine.py:52-87 train_one_epoch; optimiser recipe main.py:30-40) ------------- */
 typedef struct retr_trainer retr_trainer;
 

@@ -1,6 +1,7 @@
 // extern "C" surface declared in include/retr_b200.h.  Every entry point converts C++ exceptions
 // into a non-zero status + retr_last_error(); there is no CPU fallback behind any of them.
 #include "engine.h"
+#include "small_gemm.h"
 #include "ffn_fused.h"
 #include "train.h"
 
@@ -189,6 +190,14 @@ int retr_op_gemm(int32_t dtype, const retr_gemm_args* a, void* stream) {
   if (dtype == RETR_FP32) gemm_fp32(p, static_cast<cudaStream_t>(stream));
   else if (dtype == RETR_BF16) gemm_bf16(p, static_cast<cudaStream_t>(stream));
   else throw Error("unknown dtype");
+  API_END
+}
+
+int retr_op_small_gemm_noalloc(const void* A, const void* W, const float* bias, float* C, int32_t M, int32_t N, int32_t K,
+                               int32_t split_k, void* stream) {
+  API_BEGIN
+  small_gemm_splitk_static(static_cast<const bf16*>(A), static_cast<const bf16*>(W), bias, C, M, N, K, split_k,
+                           static_cast<cudaStream_t>(stream));
   API_END
 }
 

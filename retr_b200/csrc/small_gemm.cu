@@ -10,6 +10,9 @@
 // The encoder-sized GEMMs use the tcgen05 kernel (gemm_sm100.cu); this one only serves M <= a few hundred.
 #include "small_gemm.h"
 
+#include <mutex>
+#include <string>
+
 namespace retr {
 namespace {
 RETR_TRACE_DECL
@@ -252,6 +255,67 @@ bool small_gemm_supported(int M, int N, int K, bool ln) {
   if (N % 8 != 0 || M > 2048) return false;
   if (ln) return K == 256 || K == 512;
   return K % 256 == 0;
+}
+
+// ---- split-K small GEMM on STATIC scratch (no allocation anywhere on the call path) ---------------------------------
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it): the
+// partial tiles and the tile tickets of the deterministic split-K live in file-scope __device__ arrays that every GPU
+// loading the library holds until exit (4 MiB + 16 KiB).  The array NAMES are host-side stand-ins in host code, not
+// device addresses: the device address is fetched once per device, with that device current, by
+// cudaGetSymbolAddress.  Every call shares the arrays and they keep the previous call's contents: the tickets are
+// cleared on the stream before each launch (the partial tiles are fully overwritten before they are read); two calls
+// that overlap on the GPU (different streams, no dependency) race on them.
+constexpr int64_t NA_MAX_SCRATCH_FLOATS = 1 << 20;          // split_k * M * N <= 1 Mi floats (4 MiB)
+constexpr int NA_MAX_TILES = 4096;                           // ceil(M/64) * ceil(N/32) <= 4096
+static __device__ __align__(256) float na_scratch[NA_MAX_SCRATCH_FLOATS];
+static __device__ __align__(256) unsigned na_tickets[NA_MAX_TILES];
+
+namespace {
+struct NaDevice {
+  float* scratch = nullptr;
+  unsigned* tickets = nullptr;
+};
+NaDevice na_dev[64];
+std::mutex na_mutex;
+}  // namespace
+
+void small_gemm_splitk_static(const bf16* A, const bf16* W, const float* bias, float* C, int M, int N, int K,
+                              int split_k, cudaStream_t s) {
+  RETR_CHECK(A && W && C, "null operand");
+  RETR_CHECK(M >= 1 && N >= 1 && K >= 1 && split_k >= 1, "sizes must be positive");
+  RETR_CHECK(small_gemm_supported(M, N, K, false), "no-alloc small GEMM: needs N % 8 == 0, K % 256 == 0, M <= 2048");
+  const int kc = K == 512 ? 512 : 256;
+  RETR_CHECK((K / kc) % split_k == 0, "no-alloc small GEMM: split_k must divide K / 256");
+  const int64_t need = (int64_t)split_k * M * N;
+  const int64_t tiles = cdiv(M, SM_BM) * cdiv(N, SM_BN);
+  RETR_CHECK(need <= NA_MAX_SCRATCH_FLOATS,
+             "no-alloc small GEMM: split_k * M * N = " + std::to_string(need) + " floats exceeds the static scratch of " +
+                 std::to_string(NA_MAX_SCRATCH_FLOATS) + " floats (4 MiB); use fewer splits or the allocating path");
+  RETR_CHECK(tiles <= NA_MAX_TILES, "no-alloc small GEMM: more than " + std::to_string(NA_MAX_TILES) + " output tiles");
+  int dev = -1;
+  CUDA_OK(cudaGetDevice(&dev));
+  RETR_CHECK(dev >= 0 && dev < 64, "device ordinal out of range");
+  NaDevice nd;
+  {
+    std::lock_guard<std::mutex> lock(na_mutex);
+    if (!na_dev[dev].scratch) {                              // once per device, with that device current
+      float* sp = nullptr;
+      unsigned* tp = nullptr;
+      CUDA_OK(cudaGetSymbolAddress(reinterpret_cast<void**>(&sp), na_scratch));
+      CUDA_OK(cudaGetSymbolAddress(reinterpret_cast<void**>(&tp), na_tickets));
+      small_gemm_configure();                                // opt-in shared memory: an attribute, not an allocation
+      na_dev[dev].tickets = tp;
+      na_dev[dev].scratch = sp;
+    }
+    nd = na_dev[dev];
+  }
+  // the tickets must start at zero; a previous call that was aborted mid-kernel could have left some behind
+  CUDA_OK(cudaMemsetAsync(nd.tickets, 0, (size_t)tiles * sizeof(unsigned), s));
+  SmallGemmParams p;
+  p.A = A; p.lda = K; p.W = W; p.C = C; p.ldc = N; p.out_fp32 = 1;
+  p.M = M; p.N = N; p.K = K; p.bias = bias;
+  p.split_k = split_k; p.scratch = nd.scratch; p.tickets = nd.tickets;
+  small_gemm(p, s);
 }
 
 void small_gemm(const SmallGemmParams& p_in, cudaStream_t s) {

@@ -21,5 +21,9 @@ struct SmallGemmParams {
 void small_gemm_configure();                           // opt-in shared memory; call outside stream capture
 bool small_gemm_supported(int M, int N, int K, bool ln);
 void small_gemm(const SmallGemmParams& p, cudaStream_t s);
+// C[M,N] (fp32) = A[M,K] . W[N,K]^T + bias, deterministic split-K on file-scope static device scratch: allocates
+// nothing (see small_gemm.cu); split_k * M * N <= 1 Mi floats.
+void small_gemm_splitk_static(const bf16* A, const bf16* W, const float* bias, float* C, int M, int N, int K,
+                              int split_k, cudaStream_t s);
 
 }  // namespace retr
