@@ -123,15 +123,22 @@ __device__ __forceinline__ void load_a(AFrag& a, const bf16* A, int lda, int lan
 #pragma unroll
   for (int kb = 0; kb < 8; ++kb) a.x[kb] = *reinterpret_cast<const uint4*>(A + (size_t)g * lda + kb * 32 + 8 * c);
 }
-// B fragments of NT n-tiles over 256 k: wrow[j] = &W[(n0_j + g) * ldw + k0 + 8c]
+// B fragments of NT n-tiles over 256 k.  The weights are stored in FRAGMENT ORDER (repack_frag_kernel, at weight
+// load): for every 8-row tile and every 32-wide k block the 32 lanes' 16-byte pieces are contiguous, so one warp-wide
+// load reads four whole 128-byte lines (the row-major layout touched eight lines per load and used half of each):
+//   Wf[((n / 8) * (K / 32) + k / 32) * 256 + ((n % 8) * 4 + (k % 32) / 8) * 8 + k % 8] = W[n][k]
+// wrow[j] = frag_ptr(Wf, tile_j, K / 32, first k block, lane)
 template <int NT> struct WFrag {
   uint4 w[NT][8];
 };
+__device__ __forceinline__ const bf16* frag_ptr(const bf16* Wf, int tile, int kblocks, int kb0, int lane) {
+  return Wf + ((size_t)tile * kblocks + kb0) * 256 + lane * 8;
+}
 template <int NT> __device__ __forceinline__ void load_w(WFrag<NT>& f, const bf16* const (&wrow)[NT]) {
 #pragma unroll
   for (int j = 0; j < NT; ++j)
 #pragma unroll
-    for (int kb = 0; kb < 8; ++kb) f.w[j][kb] = ldg_stream(wrow[j] + kb * 32);
+    for (int kb = 0; kb < 8; ++kb) f.w[j][kb] = ldg_stream(wrow[j] + kb * 256);
 }
 // acc[j] += A . W_j^T; k outer / tiles inner so the NT accumulator chains interleave; with one tile the even and odd
 // k blocks go to two accumulators
@@ -301,9 +308,17 @@ __device__ __forceinline__ void attend_chunk(HeadState& h, uint32_t base, int km
 // m16 A operand.  patch_key >= 0: that key's K/V rows (this step's, not yet in the cache copy) are written into the
 // chunks first.  The normalised outputs (2 x 32 values) are pushed to columns [64 rank, +64) of row `warp` of every
 // peer's Att buffer.
+#ifdef DS_PROFILE
+#define DS_A(i) do { if (apr) { const long long now_ = clock64(); apr[i] += now_ - alast; alast = now_; } } while (0)
+#else
+#define DS_A(i) do { } while (0)
+#endif
 __device__ __forceinline__ void attend2(const DecStackParams& p, Smem& sm, Stream& st, int rank, int warp, int lane,
-                                        int n_keys, int patch_key, uint64_t policy) {
+                                        int n_keys, int patch_key, uint64_t policy, long long* apr = nullptr) {
   const int g = lane >> 2, c = lane & 3;
+#ifdef DS_PROFILE
+  long long alast = clock64();
+#endif
   HeadState h[HPC];
 #pragma unroll
   for (int hd = 0; hd < HPC; ++hd) {
@@ -320,6 +335,7 @@ __device__ __forceinline__ void attend2(const DecStackParams& p, Smem& sm, Strea
     const int kmax = min(DS_CHUNK_KEYS, n_keys - ch * DS_CHUNK_KEYS);
 #pragma unroll
     for (int hd = 0; hd < HPC; ++hd) stream_wait(st, st.consumed + hd);
+    DS_A(0);
     if (patch_key >= 0 && (patch_key >> 5) == ch) {
       if (lane < 16) {
         const int u = lane & 3, isv = (lane >> 2) & 1, hd = lane >> 3, kr = patch_key & 31;
@@ -334,9 +350,12 @@ __device__ __forceinline__ void attend2(const DecStackParams& p, Smem& sm, Strea
     for (int hd = 0; hd < HPC; ++hd)
       attend_chunk(h[hd], st.ring + ((st.consumed + hd) % SLOTS) * SLOT_BYTES, kmax, lane);
     __syncwarp();                                            // every lane is done reading the two slots
+    DS_A(1);
     st.consumed += HPC;
 #pragma unroll
     for (int hd = 0; hd < HPC; ++hd) stream_issue(p, st, rank, lane, policy);
+    __syncwarp();
+    DS_A(2);
   }
   // lanes 0-3 hold the outputs: word (hd, nt) of quad lane c = dims hd*32 + 8 nt + 2c, +1, i.e. word index
   // 16 hd + 4 nt + c of the 32-word row slice.  Lane i sends the four words {(i & 7) + 8k} to peer i >> 3.
@@ -358,6 +377,7 @@ __device__ __forceinline__ void attend2(const DecStackParams& p, Smem& sm, Strea
     const uint32_t vb = __shfl_sync(0xffffffffu, w[k >> 1][2 * (k & 1) + 1], src);
     st_peer_b32(dst + k * 32, odd ? vb : va);
   }
+  DS_A(3);
 }
 
 // y slice [8 x 64] of this CTA = A . W[64 rank .. +64]^T + bias + residual (one n-tile per warp, weights already in
@@ -386,7 +406,10 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
   const int m0 = blockIdx.y * R;
 #ifdef DS_PROFILE
   const bool prof_on = tid == 0 && blockIdx.y == 0 && rank == 0;
-  long long prof[20] = {0}, prof_last = clock64();
+  long long prof[20] = {0}, prof_last = clock64(), aprof[8] = {0};
+#define DS_APR(i) , (prof_on ? aprof + i : nullptr)
+#else
+#define DS_APR(i)
 #endif
   pdl_launch_dependents();
   cluster_arrive_relaxed();                                  // "my shared memory exists" (waited on before the first push)
@@ -457,7 +480,7 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
       float rb[3][2];
 #pragma unroll
       for (int j = 0; j < 3; ++j) {
-        wrow[j] = L.w_sqkv + (size_t)(j * D + rank * SL + warp * 8 + g) * D + 8 * c;
+        wrow[j] = frag_ptr(L.w_sqkv, j * (D / 8) + rank * (SL / 8) + warp, D / 32, 0, lane);
         const float* r = L.rb_sqkv + (size_t)t * 3 * D + j * D + rank * SL + scol;
         rb[j][0] = __ldg(r); rb[j][1] = __ldg(r + 1);
       }
@@ -487,10 +510,10 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
     DS_T(1);
     WFrag<1> wo;
     {
-      const bf16* wrow[1] = {L.w_so + (size_t)(rank * SL + warp * 8 + g) * D + 8 * c};
+      const bf16* wrow[1] = {frag_ptr(L.w_so, rank * (SL / 8) + warp, D / 32, 0, lane)};
       load_w<1>(wo, wrow);                                   // lands while the attention runs
     }
-    attend2(p, sm, st, rank, warp, lane, t + 1, t, policy);
+    attend2(p, sm, st, rank, warp, lane, t + 1, t, policy DS_APR(0));
     DS_T(2);
     cluster_arrive();
     cluster_wait();                                          // #1: Att rows complete in every CTA
@@ -500,7 +523,7 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
     cluster_arrive();
     float rq[2];
     {
-      const bf16* wrow[1] = {L.w_cq + (size_t)(rank * SL + warp * 8 + g) * D + 8 * c};
+      const bf16* wrow[1] = {frag_ptr(L.w_cq, rank * (SL / 8) + warp, D / 32, 0, lane)};
       load_w<1>(wo, wrow);
       const float* r = L.rb_cq + (size_t)t * D + rank * SL + scol;
       rq[0] = __ldg(r); rq[1] = __ldg(r + 1);
@@ -518,12 +541,12 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
       zero_acc<1>(acc);
       mma_w<1>(a, wo, acc);
       *reinterpret_cast<uint32_t*>(&sm.Qs[g][scol]) = pack_bf16((acc[0][0] + rq[0]) * qscale, (acc[0][1] + rq[1]) * qscale);
-      const bf16* wrow[1] = {L.w_co + (size_t)(rank * SL + warp * 8 + g) * D + 8 * c};
+      const bf16* wrow[1] = {frag_ptr(L.w_co, rank * (SL / 8) + warp, D / 32, 0, lane)};
       load_w<1>(wo, wrow);
     }
     __syncthreads();
     DS_T(6);
-    attend2(p, sm, st, rank, warp, lane, nv, -1, policy);
+    attend2(p, sm, st, rank, warp, lane, nv, -1, policy DS_APR(4));
     DS_T(7);
     cluster_arrive();
     cluster_wait();                                          // #3
@@ -537,12 +560,12 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
     WFrag<2> wa, wb;
     auto ff1_rows = [&](int bt, const bf16* (&wrow)[2]) {
 #pragma unroll
-      for (int j = 0; j < 2; ++j) wrow[j] = L.w_ff1 + (size_t)(rank * FS + (warp * 8 + bt * 2 + j) * 8 + g) * D + 8 * c;
+      for (int j = 0; j < 2; ++j) wrow[j] = frag_ptr(L.w_ff1, rank * (FS / 8) + warp * 8 + bt * 2 + j, D / 32, 0, lane);
     };
     auto ff2_rows = [&](int kh, int bt, const bf16* (&wrow)[2]) {
 #pragma unroll
       for (int j = 0; j < 2; ++j)
-        wrow[j] = L.w_ff2 + (size_t)((warp * 4 + bt * 2 + j) * 8 + g) * p.d_ff + rank * FS + kh * D + 8 * c;
+        wrow[j] = frag_ptr(L.w_ff2, warp * 4 + bt * 2 + j, p.d_ff / 32, (rank * FS + kh * D) / 32, lane);
     };
     {
       const bf16* wrow[2];
@@ -628,7 +651,7 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
     // hidden columns [128 rank, +128): two n-tiles per warp, pushed to every peer (layer 1 needs whole rows)
     WFrag<2> wf;
     const int n0 = rank * (MH / CL) + warp * 16;
-    const bf16* wrow[2] = {p.w_m0 + (size_t)(n0 + g) * D + 8 * c, p.w_m0 + (size_t)(n0 + 8 + g) * D + 8 * c};
+    const bf16* wrow[2] = {frag_ptr(p.w_m0, n0 / 8, D / 32, 0, lane), frag_ptr(p.w_m0, n0 / 8 + 1, D / 32, 0, lane)};
     load_w<2>(wf, wrow);
     layernorm_row(sm.Y, sm.Abuf, p.fin_g, p.fin_b, 1e-5f, warp, lane);
     __syncthreads();
@@ -650,8 +673,8 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
   {
     WFrag<2> wf0, wf1;
     const int n0 = rank * (MH / CL) + warp * 16;
-    const bf16* wrow0[2] = {p.w_m1 + (size_t)(n0 + g) * MH + 8 * c, p.w_m1 + (size_t)(n0 + 8 + g) * MH + 8 * c};
-    const bf16* wrow1[2] = {wrow0[0] + D, wrow0[1] + D};
+    const bf16* wrow0[2] = {frag_ptr(p.w_m1, n0 / 8, MH / 32, 0, lane), frag_ptr(p.w_m1, n0 / 8 + 1, MH / 32, 0, lane)};
+    const bf16* wrow1[2] = {frag_ptr(p.w_m1, n0 / 8, MH / 32, D / 32, lane), frag_ptr(p.w_m1, n0 / 8 + 1, MH / 32, D / 32, lane)};
     cluster_arrive();
     load_w<2>(wf0, wrow0);
     load_w<2>(wf1, wrow1);
@@ -680,6 +703,9 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
            "%lld cout %lld bar4 %lld | ln3+ff1 %lld ff2 %lld bar5 %lld reduce %lld bar6 %lld | head %lld\n",
            prof[0], prof[1], prof[2], prof[3], prof[4], prof[5], prof[6], prof[7], prof[8], prof[9], prof[10], prof[11],
            prof[12], prof[13], prof[14], prof[15], prof[16]);
+    printf("   attention detail: self wait %lld math %lld issue %lld tail %lld | cross wait %lld math %lld issue %lld tail %lld"
+           " (self chunks/head %d, cross chunks/head %d)\n", aprof[0], aprof[1], aprof[2], aprof[3], aprof[4], aprof[5],
+           aprof[6], aprof[7], st.n_self, st.n_cross);
   }
 #endif
 }
@@ -706,7 +732,25 @@ __global__ void kv_to_chunked_kernel(const bf16* __restrict__ kv, bf16* __restri
   *reinterpret_cast<uint4*>(dst) = val;
 }
 
+// row-major W[N][K] -> fragment order (see load_w); one thread per 16-byte piece
+__global__ void repack_frag_kernel(const bf16* __restrict__ W, bf16* __restrict__ out, int N, int K) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)N * K / 8) return;
+  const int lane = (int)(idx & 31);
+  const int64_t blk = idx >> 5;                              // (tile, k block)
+  const int kblocks = K / 32, kb = (int)(blk % kblocks), tile = (int)(blk / kblocks);
+  const int n = tile * 8 + (lane >> 2), k = kb * 32 + (lane & 3) * 8;
+  *reinterpret_cast<uint4*>(out + idx * 8) = *reinterpret_cast<const uint4*>(W + (size_t)n * K + k);
+}
+
 }  // namespace
+
+void repack_frag(const bf16* W, bf16* out, int N, int K, cudaStream_t s) {
+  RETR_CHECK(N % 8 == 0 && K % 32 == 0, "repack_frag: N % 8, K % 32");
+  const int64_t n = (int64_t)N * K / 8;
+  repack_frag_kernel<<<(unsigned)cdiv(n, 256), 256, 0, s>>>(W, out, N, K);
+  LAUNCH_OK();
+}
 
 bool decode_stack_supported(int d_model, int n_heads, int d_ff, int n_layers, int mlp_hidden, int max_pos) {
   return d_model == D && n_heads == NH && d_ff == CL * FS && n_layers >= 1 && n_layers <= DS_MAX_LAYERS &&

@@ -12,6 +12,7 @@ constexpr int DS_CHUNK_ELEMS = 2 * DS_CHUNK_KEYS * 32;   // [K 32x32 | V 32x32] 
 
 struct DecStackLayer {
   const float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *ln3_g, *ln3_b;
+  // every bf16 weight below is in FRAGMENT ORDER (repack_frag), not row-major
   const bf16* w_sqkv; const float* rb_sqkv;      // [3d, d]; [T, 3d] position + bias table (row = step)
   const bf16* w_so; const float* b_so;           // [d, d]
   const bf16* w_cq; const float* rb_cq;          // [d, d]; [T, d]
@@ -39,6 +40,9 @@ struct DecStackParams {
 bool decode_stack_supported(int d_model, int n_heads, int d_ff, int n_layers, int mlp_hidden, int max_pos);
 void decode_stack_configure();                   // opt-in shared memory; call outside stream capture
 void decode_stack(const DecStackParams& p, cudaStream_t s);
+
+// row-major bf16 W[N][K] -> the fragment order the stack kernel streams (decode_stack.cu: load_w)
+void repack_frag(const bf16* W, bf16* out, int N, int K, cudaStream_t s);
 
 // encoder-side cache build: rows of [K(d) | V(d)] (d = 256, 8 heads) -> chunked, swizzled, compacted cross cache
 void kv_to_chunked(const bf16* kv, bf16* out, int B, int rows, int chunks, const int* dst_row, cudaStream_t s);

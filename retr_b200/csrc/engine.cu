@@ -428,21 +428,26 @@ template <> void EngineT<bf16>::build_stack_params() {
   DecStackParams& p = stack_params_;
   p = DecStackParams{};
   p.n_layers = desc.dec_layers;
+  auto frag = [&](const Linear<bf16>& l) {                   // private fragment-ordered copy of a weight matrix
+    bf16* out = static_cast<bf16*>(dalloc((size_t)l.out * l.in * 2));
+    repack_frag(l.w, out, l.out, l.in, 0);
+    return out;
+  };
   for (int l = 0; l < desc.dec_layers; ++l) {
     const DecLayer<bf16>& e = dec_[l];
     DecStackLayer& L = p.L[l];
     L.ln1_g = e.ln1_g; L.ln1_b = e.ln1_b; L.ln2_g = e.ln2_g; L.ln2_b = e.ln2_b; L.ln3_g = e.ln3_g; L.ln3_b = e.ln3_b;
-    L.w_sqkv = e.s_qkv.w; L.rb_sqkv = e.rb_s_qkv;
-    L.w_so = e.s_out.w; L.b_so = e.s_out.b;
-    L.w_cq = e.c_q.w; L.rb_cq = e.rb_c_q;
-    L.w_co = e.c_out.w; L.b_co = e.c_out.b;
-    L.w_ff1 = e.ff1.w; L.b_ff1 = e.ff1.b; L.w_ff2 = e.ff2.w; L.b_ff2 = e.ff2.b;
+    L.w_sqkv = frag(e.s_qkv); L.rb_sqkv = e.rb_s_qkv;
+    L.w_so = frag(e.s_out); L.b_so = e.s_out.b;
+    L.w_cq = frag(e.c_q); L.rb_cq = e.rb_c_q;
+    L.w_co = frag(e.c_out); L.b_co = e.c_out.b;
+    L.w_ff1 = frag(e.ff1); L.b_ff1 = e.ff1.b; L.w_ff2 = frag(e.ff2); L.b_ff2 = e.ff2.b;
     L.self_kv = skv2_[l]; L.cross_kv = ckv2_[l];
   }
   p.caption = caption_;
   p.e_word = e_word_; p.e_pos = e_pos_; p.emb_g = emb_g_; p.emb_b = emb_b_; p.emb_eps = desc.embed_ln_eps;
   p.fin_g = dec_norm_g_; p.fin_b = dec_norm_b_;
-  p.w_m0 = mlp_[0].w; p.b_m0 = mlp_[0].b; p.w_m1 = mlp_[1].w; p.b_m1 = mlp_[1].b;
+  p.w_m0 = frag(mlp_[0]); p.b_m0 = mlp_[0].b; p.w_m1 = frag(mlp_[1]); p.b_m1 = mlp_[1].b;
   p.m2_out = m2_;
   p.step = step_; p.n_valid = cross_nvalid_;
   p.self_chunks = self_chunks_; p.cross_chunks = cross_chunks_; p.d_ff = desc.d_ff;
