@@ -22,7 +22,7 @@
 //     that precedes it;
 //   * attention: K/V caches are stored in 4 KB chunks [K 32 keys x 32 | V 32 keys x 32] (bf16, 16-byte units XOR-
 //     swizzled by the key index, written that way by the cache builders).  Warp w owns sample w and walks its two
-//     heads in lock-step (two independent dependency chains), fed by a private 5-slot ring of chunks filled by
+//     heads in lock-step (two independent dependency chains), fed by a private 3-slot ring of 8 KB two-head blocks filled by
 //     cp.async.bulk (one elected lane, completion on an mbarrier); the ring runs AHEAD across sublayers and layers
 //     (the next cross-attention's chunks arrive while the projections run).  Scores and P.V run on the tensor cores
 //     (q as row 0 of the A operand; ldmatrix / ldmatrix.trans on the swizzled chunk), online softmax per chunk:
@@ -43,7 +43,7 @@ constexpr int SL = D / CL;                   // 64: columns of a projection owne
 constexpr int LDA = D + 32;                  // bf16 per A row in shared memory: 576 B, rows 16 banks apart
 constexpr int FS = 512, LDH = FS + 32;       // FFN hidden slice per CTA
 constexpr int MH = 512, LDM1 = MH + 32;      // MLP head hidden width
-constexpr int SLOTS = 5, SLOT_BYTES = DS_CHUNK_ELEMS * 2;
+constexpr int SLOTS = 3, SLOT_BYTES = HPC * DS_CHUNK_ELEMS * 2;   // a slot = one 32-key chunk of BOTH heads (8 KB)
 constexpr float LOG2E = 1.4426950408889634f;
 static_assert(R == NWARP, "one sample per warp");
 
@@ -55,13 +55,17 @@ static_assert(R == NWARP, "one sample per warp");
 #endif
 
 struct Smem {
-  uint8_t ring[NWARP][SLOTS][SLOT_BYTES];    // per-warp K/V chunk rings (160 KB)
+  uint8_t ring[NWARP][SLOTS][SLOT_BYTES];    // per-warp K/V chunk rings (192 KB)
   float Y[R][D];                             // residual stream rows (full replica in every CTA of the cluster)
-  float Ps[CL][R][SL];                       // FFN partials of this CTA's 64 output columns, one slot per source CTA
+  union {                                    // live in disjoint phases, separated by cluster barriers #4 / #6:
+    float Ps[CL][R][SL];                     //   FFN partials of this CTA's 64 output columns, one slot per source CTA
+    struct {                                 //   this CTA's heads: (scaled) query and the step's new key / value rows
+      bf16 Qs[R][SL], Kn[R][SL], Vn[R][SL];
+    };
+  };
   bf16 Abuf[R][LDA];                         // LayerNorm output (A operand)
   bf16 Att[R][LDA];                          // attention output, heads gathered from the peers
   bf16 Hs[R][LDH];                           // FFN hidden slice; reused as M1[R][LDM1] by the head
-  bf16 Qs[R][SL], Kn[R][SL], Vn[R][SL];      // this CTA's heads: (scaled) query and the step's new key / value rows
   uint64_t bars[NWARP][SLOTS];
 };
 static_assert(LDM1 <= LDH, "M1 must fit in Hs");
@@ -197,28 +201,30 @@ __device__ __forceinline__ void layernorm_row(const float (*Y)[D], bf16 (*A)[LDA
 }
 
 // ---- per-warp K/V chunk stream ---------------------------------------------------------------------------------------
-// The chunks a warp will consume during the whole kernel form one fixed sequence:
-//   for layer: [self chunk 0 of head A, of head B, self chunk 1 of A, of B, ..., cross chunk 0 of A, of B, ...]
-// (both heads of a sample have the same number of keys).  The issue cursor runs SLOTS chunks ahead of the consume
-// cursor, across sublayer and layer boundaries.
+// The caches hold, per (sample, CTA rank), 8 KB blocks [head A: K 32x32 | V 32x32][head B: K | V] per 32 keys, so one
+// bulk copy brings a chunk of BOTH heads of the CTA.  The blocks a warp will consume during the whole kernel form one
+// fixed sequence: for layer: [self block 0, 1, ..., cross block 0, 1, ...].  The issue cursor runs SLOTS blocks ahead
+// of the consume cursor, across sublayer and layer boundaries.  Issuing costs the consumer ~250 cycles per copy (it
+// was 460 with a proxy fence per copy and two copies per iteration), so there is one copy per iteration and the
+// fence is kept only where the slot was WRITTEN through the generic proxy (the self-attention patch).
 struct Stream {
   int issued, consumed;
-  int il, iph, ic, ih;                       // issue cursor: layer, phase (0 self / 1 cross), chunk, head 0/1
-  int n_self, n_cross;                       // chunks per head in each phase
+  int il, iph, ic;                           // issue cursor: layer, phase (0 self / 1 cross), block
+  int n_self, n_cross;                       // blocks in each phase
   int b;                                     // the warp's sample (clamped to B-1)
   uint32_t ring, bars;                       // shared-memory addresses of this warp's ring and barriers
 };
-__device__ __forceinline__ void stream_issue(const DecStackParams& p, Stream& st, int rank, int lane, uint64_t policy) {
+__device__ __forceinline__ void stream_issue(const DecStackParams& p, Stream& st, int rank, int lane, uint64_t policy,
+                                             bool fence) {
   if (st.il >= p.n_layers) return;
   const int slot = st.issued % SLOTS;
   if (lane == 0) {
     const DecStackLayer& L = p.L[st.il];
-    const int head = rank * HPC + st.ih;
     const bf16* src = st.iph == 0
-        ? L.self_kv + ((size_t)(st.b * NH + head) * p.self_chunks + st.ic) * DS_CHUNK_ELEMS
-        : L.cross_kv + ((size_t)(st.b * NH + head) * p.cross_chunks + st.ic) * DS_CHUNK_ELEMS;
+        ? L.self_kv + ((size_t)(st.b * CL + rank) * p.self_chunks + st.ic) * (HPC * DS_CHUNK_ELEMS)
+        : L.cross_kv + ((size_t)(st.b * CL + rank) * p.cross_chunks + st.ic) * (HPC * DS_CHUNK_ELEMS);
     const uint32_t bar = st.bars + slot * 8, dst = st.ring + slot * SLOT_BYTES;
-    ptx::fence_proxy_async_smem();           // the slot was last touched through the generic proxy
+    if (fence) ptx::fence_proxy_async_smem();
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(SLOT_BYTES) : "memory");
     if (st.iph == 0) {
       asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -229,13 +235,29 @@ __device__ __forceinline__ void stream_issue(const DecStackParams& p, Stream& st
     }
   }
   ++st.issued;
-  if (++st.ih == HPC) {
-    st.ih = 0;
-    if (++st.ic == (st.iph == 0 ? st.n_self : st.n_cross)) {
-      st.ic = 0;
-      if (++st.iph == 2) { st.iph = 0; ++st.il; }
+  if (++st.ic == (st.iph == 0 ? st.n_self : st.n_cross)) {
+    st.ic = 0;
+    if (++st.iph == 2) { st.iph = 0; ++st.il; }
+  }
+}
+// L2 prefetch of the `count` blocks that FOLLOW the issue cursor (lane i takes the i-th): called where the kernel is
+// about to spend a long stretch in projections / FFN with HBM idle, so that the ring refills of the next attention hit
+// L2 instead of waiting on DRAM.
+__device__ __forceinline__ void stream_prefetch(const DecStackParams& p, const Stream& st, int rank, int lane, int count) {
+  if (lane >= count) return;
+  int il = st.il, iph = st.iph, ic = st.ic;
+  for (int i = 0; i < lane && il < p.n_layers; ++i) {
+    if (++ic == (iph == 0 ? st.n_self : st.n_cross)) {
+      ic = 0;
+      if (++iph == 2) { iph = 0; ++il; }
     }
   }
+  if (il >= p.n_layers) return;
+  const DecStackLayer& L = p.L[il];
+  const bf16* src = iph == 0
+      ? L.self_kv + ((size_t)(st.b * CL + rank) * p.self_chunks + ic) * (HPC * DS_CHUNK_ELEMS)
+      : L.cross_kv + ((size_t)(st.b * CL + rank) * p.cross_chunks + ic) * (HPC * DS_CHUNK_ELEMS);
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(SLOT_BYTES) : "memory");
 }
 __device__ __forceinline__ void stream_wait(const Stream& st, int idx) {
   const uint32_t bar = st.bars + (idx % SLOTS) * 8, parity = (idx / SLOTS) & 1;
@@ -333,28 +355,25 @@ __device__ __forceinline__ void attend2(const DecStackParams& p, Smem& sm, Strea
   const int n_chunks = (n_keys + DS_CHUNK_KEYS - 1) / DS_CHUNK_KEYS;
   for (int ch = 0; ch < n_chunks; ++ch) {
     const int kmax = min(DS_CHUNK_KEYS, n_keys - ch * DS_CHUNK_KEYS);
-#pragma unroll
-    for (int hd = 0; hd < HPC; ++hd) stream_wait(st, st.consumed + hd);
+    const uint32_t base = st.ring + (st.consumed % SLOTS) * SLOT_BYTES;
+    stream_wait(st, st.consumed);
     DS_A(0);
-    if (patch_key >= 0 && (patch_key >> 5) == ch) {
+    const bool patched = patch_key >= 0 && (patch_key >> 5) == ch;
+    if (patched) {
       if (lane < 16) {
         const int u = lane & 3, isv = (lane >> 2) & 1, hd = lane >> 3, kr = patch_key & 31;
         const uint4 v = *reinterpret_cast<const uint4*>(isv ? &sm.Vn[warp][hd * DH + u * 8] : &sm.Kn[warp][hd * DH + u * 8]);
-        const uint32_t dst = st.ring + ((st.consumed + hd) % SLOTS) * SLOT_BYTES + isv * 2048 + kr * 64 +
-                             ((u ^ ((kr >> 1) & 3)) << 4);
+        const uint32_t dst = base + hd * (DS_CHUNK_ELEMS * 2) + isv * 2048 + kr * 64 + ((u ^ ((kr >> 1) & 3)) << 4);
         asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
       }
       __syncwarp();
     }
 #pragma unroll
-    for (int hd = 0; hd < HPC; ++hd)
-      attend_chunk(h[hd], st.ring + ((st.consumed + hd) % SLOTS) * SLOT_BYTES, kmax, lane);
-    __syncwarp();                                            // every lane is done reading the two slots
+    for (int hd = 0; hd < HPC; ++hd) attend_chunk(h[hd], base + hd * (DS_CHUNK_ELEMS * 2), kmax, lane);
+    __syncwarp();                                            // every lane is done reading the slot
     DS_A(1);
-    st.consumed += HPC;
-#pragma unroll
-    for (int hd = 0; hd < HPC; ++hd) stream_issue(p, st, rank, lane, policy);
-    __syncwarp();
+    ++st.consumed;
+    stream_issue(p, st, rank, lane, policy, patched);
     DS_A(2);
   }
   // lanes 0-3 hold the outputs: word (hd, nt) of quad lane c = dims hd*32 + 8 nt + 2c, +1, i.e. word index
@@ -414,18 +433,23 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
   pdl_launch_dependents();
   cluster_arrive_relaxed();                                  // "my shared memory exists" (waited on before the first push)
   if (tid < NWARP * SLOTS) ptx::mbar_init(&sm.bars[0][0] + tid, 1);
-  // stale shared memory may hold NaN bit patterns: rows of a chunk beyond the valid keys are multiplied by p = 0
-  for (int i = tid; i < (int)(sizeof(sm.ring) / 16); i += THREADS)
-    reinterpret_cast<uint4*>(&sm.ring[0][0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
+  // (no clearing of the ring: a slot is only ever read after a FULL 8 KB copy from the caches, whose rows beyond a
+  // sample's valid keys are finite — zero-initialised at allocation or a previous batch's values — and get p = 0)
   ptx::fence_barrier_init();
   __syncthreads();
   pdl_wait();                                                // ids, step counter and the self caches come from earlier kernels
 
+  if (p.stagger_cycles > 0) {
+    // all clusters run the same work and would move through HBM-bound (attention) and L2-bound (projection / FFN)
+    // phases in lock-step; a one-off start delay per cluster group spreads the phases over time
+    const long long until = clock64() + (long long)(blockIdx.y % p.stagger_groups) * p.stagger_cycles;
+    while (clock64() < until) { }
+  }
   const int t = *p.step;
   const bool row_ok = m0 + g < p.B;                          // this thread's GEMM output row is a real sample
   Stream st;
   st.issued = st.consumed = 0;
-  st.il = st.iph = st.ic = st.ih = 0;
+  st.il = st.iph = st.ic = 0;
   st.b = min(m0 + warp, p.B - 1);
   const int nv = max(1, __ldg(p.n_valid + st.b));
   st.n_self = t / DS_CHUNK_KEYS + 1;
@@ -434,7 +458,8 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
   st.bars = ptx::smem_u32(&sm.bars[warp][0]);
   const uint64_t policy = ptx::policy_evict_first();
 #pragma unroll 1
-  for (int i = 0; i < SLOTS; ++i) stream_issue(p, st, rank, lane, policy);
+  for (int i = 0; i < SLOTS; ++i) stream_issue(p, st, rank, lane, policy, false);
+  if (p.prefetch_blocks > 0) stream_prefetch(p, st, rank, lane, p.prefetch_blocks);
 
   // ---- DecoderEmbeddings: y = LN_eps(E_word[id] + E_pos[t]) (models/transformer_modules.py:113-129); warp w = row w ----
   {
@@ -499,9 +524,9 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
       *reinterpret_cast<uint32_t*>(&sm.Vn[g][scol]) = vv;
       if (row_ok) {
         // append to the cache for the steps to come (chunk t/32, row t%32, swizzled 16-byte units)
-        const int kr = t & 31, head = rank * HPC + (warp >> 2), unit = (warp & 3) ^ ((kr >> 1) & 3);
-        bf16* dst = L.self_kv + ((size_t)((m0 + g) * NH + head) * p.self_chunks + (t >> 5)) * DS_CHUNK_ELEMS + kr * 32 +
-                    unit * 8 + 2 * c;
+        const int kr = t & 31, unit = (warp & 3) ^ ((kr >> 1) & 3);
+        bf16* dst = L.self_kv + (((size_t)((m0 + g) * CL + rank) * p.self_chunks + (t >> 5)) * HPC + (warp >> 2)) * DS_CHUNK_ELEMS +
+                    kr * 32 + unit * 8 + 2 * c;
         *reinterpret_cast<uint32_t*>(dst) = kk;
         *reinterpret_cast<uint32_t*>(dst + 1024) = vv;
       }
@@ -573,6 +598,7 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
       load_w<2>(wa, wrow);
     }
     cluster_wait();                                          // #4
+    if (p.prefetch_blocks > 0) stream_prefetch(p, st, rank, lane, p.prefetch_blocks);
     DS_T(10);
     layernorm_row(sm.Y, sm.Abuf, L.ln3_g, L.ln3_b, 1e-5f, warp, lane);
     __syncthreads();
@@ -710,7 +736,7 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
 #endif
 }
 
-// rows of [K(256) | V(256)] -> [B][8][chunks][K 32x32 | V 32x32] with the 16-byte units of a key row XOR-swizzled by
+// rows of [K(256) | V(256)] -> [B][4 CTA ranks][chunks][2 heads][K 32x32 | V 32x32] with the 16-byte units of a key row XOR-swizzled by
 // ((key % 32) >> 1) & 3; dst_row (key compaction) maps a key to its rank among the sample's unpadded keys or -1.
 __global__ void kv_to_chunked_kernel(const bf16* __restrict__ kv, bf16* __restrict__ out, int B, int rows, int chunks,
                                      const int* __restrict__ dst_row) {
@@ -727,8 +753,8 @@ __global__ void kv_to_chunked_kernel(const bf16* __restrict__ kv, bf16* __restri
   }
   const int isv = u >= D / 8, e = (isv ? u - D / 8 : u) * 8, h = e / DH, unit = (e % DH) / 8, kr = r & 31;
   const uint4 val = *reinterpret_cast<const uint4*>(kv + br * (2 * D) + (size_t)u * 8);
-  bf16* dst = out + ((size_t)(b * NH + h) * chunks + (r >> 5)) * DS_CHUNK_ELEMS + isv * 1024 + kr * 32 +
-              ((unit ^ ((kr >> 1) & 3)) << 3);
+  bf16* dst = out + (((size_t)(b * CL + h / HPC) * chunks + (r >> 5)) * HPC + h % HPC) * DS_CHUNK_ELEMS + isv * 1024 +
+              kr * 32 + ((unit ^ ((kr >> 1) & 3)) << 3);
   *reinterpret_cast<uint4*>(dst) = val;
 }
 

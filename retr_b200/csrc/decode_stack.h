@@ -19,8 +19,8 @@ struct DecStackLayer {
   const bf16* w_co; const float* b_co;           // [d, d]
   const bf16* w_ff1; const float* b_ff1;         // [d_ff, d]
   const bf16* w_ff2; const float* b_ff2;         // [d, d_ff]
-  bf16* self_kv;                                 // [B][8][T/32][K 32x32 | V 32x32], rows swizzled
-  const bf16* cross_kv;                          // [B][8][cross_chunks][K 32x32 | V 32x32]
+  bf16* self_kv;                                 // [B][4][T/32][2 heads][K 32x32 | V 32x32], rows swizzled
+  const bf16* cross_kv;                          // [B][4][cross_chunks][2 heads][K 32x32 | V 32x32]
 };
 
 struct DecStackParams {
@@ -35,6 +35,8 @@ struct DecStackParams {
   const int* step;                               // device: position of the token being consumed
   const int* n_valid;                            // [B] unpadded cross keys per sample
   int B, self_chunks, cross_chunks, d_ff;
+  int stagger_cycles, stagger_groups;            // start delay of cluster group (blockIdx.y % groups), in SM cycles
+  int prefetch_blocks;                           // 8 KB blocks per warp prefetched into L2 ahead of the ring (0 = off)
 };
 
 bool decode_stack_supported(int d_model, int n_heads, int d_ff, int n_layers, int mlp_hidden, int max_pos);

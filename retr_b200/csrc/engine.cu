@@ -451,6 +451,12 @@ template <> void EngineT<bf16>::build_stack_params() {
   p.m2_out = m2_;
   p.step = step_; p.n_valid = cross_nvalid_;
   p.self_chunks = self_chunks_; p.cross_chunks = cross_chunks_; p.d_ff = desc.d_ff;
+  // measured at B = 256 (decode ms per 127 steps): no stagger 30.0; 2 groups x 8k cycles 29.7, 16k 28.3, 24k 28.8, 32k 30.1;
+  // 4 groups x 8k 28.6, 16k 29.6.  L2 prefetch ahead of the ring (RETR_STACK_PREFETCH blocks per warp): 0 -> 30.5, 4 -> 32.6,
+  // 8 -> 31.2, 12 -> 31.9, 16 -> 32.6 — not kept.
+  p.stagger_cycles = getenv("RETR_STACK_STAGGER") ? atoi(getenv("RETR_STACK_STAGGER")) : 16000;
+  p.stagger_groups = getenv("RETR_STACK_STAGGER_GROUPS") ? std::max(1, atoi(getenv("RETR_STACK_STAGGER_GROUPS"))) : 2;
+  p.prefetch_blocks = getenv("RETR_STACK_PREFETCH") ? std::min(32, std::max(0, atoi(getenv("RETR_STACK_PREFETCH")))) : 0;
 }
 
 // ---- backbone --------------------------------------------------------------------------------------
