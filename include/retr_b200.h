@@ -232,6 +232,27 @@ int retr_train_clip_adamw(retr_trainer* tr, float max_norm, float lr, float lr_b
                           void* stream);
 int64_t retr_train_kernel_launches(const retr_trainer* tr);
 
+/* ---- data-parallel training (the reference is single-device: main.py:16-24, seed offset main.py:19) ----
+ * The gradient arena (retr_train_set_arena) is cut into buckets in REVERSE-EXECUTION order — MLP head, decoder +
+ * embeddings, encoder + input/loc projections, backbone layer4, layer3, layer2 — each a contiguous range.
+ * retr_train_set_comm: hand the trainer an ncclComm_t (as void*; NULL switches it off).  From then on
+ *   retr_train_backward / retr_train_loss_and_grads all-reduce every bucket (ncclAvg = mean over the `world` ranks,
+ *   i.e. the gradient of the global batch: every rank averages over the same B*T positions) on a side stream as soon
+ *   as the backward pass has produced it, overlapped with the rest of the pass; the caller's stream waits for the last
+ *   bucket before the call's work is complete, so retr_train_clip_adamw (clip_grad_norm_ over the REDUCED gradients,
+ *   engine.py:81-83) needs nothing else.
+ * retr_allreduce_grads: the same buckets as one NCCL group on `stream`, for callers that drive the exchange
+ *   themselves (after retr_train_backward without retr_train_set_comm).
+ * retr_train_grad_buckets: lo_hi[2i], lo_hi[2i+1] = element range of bucket i in the arena; returns their number.
+ * retr_nccl_*: create the communicator without any other NCCL binding (rank 0 makes the 128-byte id, every rank
+ *   passes it to retr_nccl_comm_create with its device current).  libnccl.so.2 is loaded at run time. */
+int  retr_nccl_unique_id(void* out128);
+int  retr_nccl_comm_create(const void* id128, int32_t world, int32_t rank, void** comm_out);
+void retr_nccl_comm_destroy(void* comm);
+int  retr_train_set_comm(retr_trainer* tr, void* nccl_comm, int32_t world);
+int  retr_allreduce_grads(retr_trainer* tr, void* nccl_comm, void* stream);
+int  retr_train_grad_buckets(const retr_trainer* tr, int64_t* lo_hi, int32_t max_buckets);
+
 #ifdef __cplusplus
 }
 #endif

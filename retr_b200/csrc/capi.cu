@@ -4,6 +4,7 @@
 #include "small_gemm.h"
 #include "ffn_fused.h"
 #include "train.h"
+#include "dp.h"
 
 namespace retr {
 thread_local long long g_launches = 0;
@@ -341,6 +342,52 @@ int retr_train_clip_adamw(retr_trainer* tr, float max_norm, float lr, float lr_b
   tr->tr->clip_adamw(max_norm, lr, lr_backbone, beta1, beta2, eps, weight_decay, step, grad_sumsq_dev,
                      static_cast<cudaStream_t>(stream));
   API_END
+}
+
+int retr_nccl_unique_id(void* out128) {
+  API_BEGIN
+  RETR_CHECK(out128, "null argument");
+  nccl_unique_id id;
+  nccl_ok(nccl().GetUniqueId(&id), "ncclGetUniqueId");
+  memcpy(out128, id.internal, 128);
+  API_END
+}
+
+int retr_nccl_comm_create(const void* id128, int32_t world, int32_t rank, void** comm_out) {
+  API_BEGIN
+  RETR_CHECK(id128 && comm_out && world >= 1 && rank >= 0 && rank < world, "bad argument");
+  nccl_unique_id id;
+  memcpy(id.internal, id128, 128);
+  nccl_comm_t c = nullptr;
+  nccl_ok(nccl().CommInitRank(&c, world, id, rank), "ncclCommInitRank");
+  *comm_out = c;
+  API_END
+}
+
+void retr_nccl_comm_destroy(void* comm) {
+  try {
+    if (comm) nccl().CommDestroy(static_cast<nccl_comm_t>(comm));
+  } catch (...) {
+  }
+}
+
+int retr_train_set_comm(retr_trainer* tr, void* nccl_comm, int32_t world) {
+  API_BEGIN
+  RETR_CHECK(tr, "null trainer");
+  tr->tr->set_comm(nccl_comm, world);
+  API_END
+}
+
+int retr_allreduce_grads(retr_trainer* tr, void* nccl_comm, void* stream) {
+  API_BEGIN
+  RETR_CHECK(tr, "null trainer");
+  tr->tr->allreduce_grads(nccl_comm, static_cast<cudaStream_t>(stream));
+  API_END
+}
+
+int retr_train_grad_buckets(const retr_trainer* tr, int64_t* lo_hi, int32_t max_buckets) {
+  if (!tr) return -1;
+  return tr->tr->bucket_info(lo_hi, max_buckets);
 }
 
 int64_t retr_train_kernel_launches(const retr_trainer* tr) { return tr ? tr->tr->launches : -1; }

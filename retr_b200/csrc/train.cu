@@ -12,6 +12,7 @@
 // split-K.  Frozen parts (conv1, layer1 — models/backbone.py:58-60 — and all FrozenBatchNorm2d buffers) get no
 // gradient and nothing below them is back-propagated.
 #include "train.h"
+#include "dp.h"
 
 #include <algorithm>
 #include <map>
@@ -129,6 +130,36 @@ class TrainerT final : public TrainerBase {
   }
   ~TrainerT() override {
     for (void* p : owned_) cudaFree(p);
+    if (dp_stream_) cudaStreamDestroy(dp_stream_);
+    for (auto e : dp_ready_) cudaEventDestroy(e);
+    if (dp_done_) cudaEventDestroy(dp_done_);
+  }
+  void set_comm(void* nccl_comm, int world) override {
+    RETR_CHECK(finalized_, "set_comm before finalize");
+    RETR_CHECK(!nccl_comm || arena_g_, "data-parallel training needs the flat gradient arena (retr_train_set_arena)");
+    if (nccl_comm) nccl();                                 // load the library now, not in the middle of a step
+    comm_ = static_cast<nccl_comm_t>(nccl_comm); world_ = world;
+    if (comm_ && !dp_stream_) {
+      CUDA_OK(cudaStreamCreateWithFlags(&dp_stream_, cudaStreamNonBlocking));
+      for (size_t i = 0; i < buckets_.size(); ++i) {
+        cudaEvent_t e;
+        CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        dp_ready_.push_back(e);
+      }
+      CUDA_OK(cudaEventCreateWithFlags(&dp_done_, cudaEventDisableTiming));
+    }
+  }
+  void allreduce_grads(void* nccl_comm, cudaStream_t s) override {
+    RETR_CHECK(nccl_comm && arena_g_, "allreduce_grads needs a communicator and the flat gradient arena");
+    nccl_ok(nccl().GroupStart(), "ncclGroupStart");
+    for (const GradBucket& b : buckets_)
+      nccl_ok(nccl().AllReduce(arena_g_ + b.lo, arena_g_ + b.lo, (size_t)(b.hi - b.lo), NCCL_FLOAT32, NCCL_AVG,
+                               static_cast<nccl_comm_t>(nccl_comm), s), "ncclAllReduce");
+    nccl_ok(nccl().GroupEnd(), "ncclGroupEnd");
+  }
+  int bucket_info(int64_t* lo_hi, int max_buckets) const override {
+    for (int i = 0; i < (int)buckets_.size() && i < max_buckets; ++i) { lo_hi[2 * i] = buckets_[i].lo; lo_hi[2 * i + 1] = buckets_[i].hi; }
+    return (int)buckets_.size();
   }
   void bind(const std::string& name, float* param, float* grad, const int64_t* shape, int ndim) override {
     PBind b;
@@ -245,7 +276,88 @@ class TrainerT final : public TrainerBase {
   int cur_B_ = 0;
   float drop_p_ = 0.f;
   unsigned long long seed_ = 0;
+  // data parallel: gradient buckets in REVERSE-EXECUTION order (head, decoder + embeddings, encoder + token
+  // projections, layer4, layer3, layer2), each a contiguous range of the arena
+  std::vector<GradBucket> buckets_;
+  void build_buckets();
+  void bucket_ready(int k, cudaStream_t s);              // gradients of bucket k are final on stream s
+  void buckets_join(cudaStream_t s);                     // s waits for every bucket's all-reduce
+  nccl_comm_t comm_ = nullptr;
+  int world_ = 1;
+  cudaStream_t dp_stream_ = nullptr;
+  std::vector<cudaEvent_t> dp_ready_;
+  cudaEvent_t dp_done_ = nullptr;
 };
+
+static const char* const kFallbackBucket = "all";
+extern const char* kBucketNamesFwd[6];
+template <typename T>
+void TrainerT<T>::build_buckets() {
+  const char* const* kBucketNames = kBucketNamesFwd;
+  buckets_.clear();
+  if (!arena_g_) return;
+  auto bucket_of = [](const std::string& n) {
+    if (n.rfind("mlp.", 0) == 0) return 0;
+    if (n.rfind("transformer.decoder.", 0) == 0 || n.rfind("transformer.embeddings.", 0) == 0) return 1;
+    if (n.find("backbone") != std::string::npos) {
+      if (n.find("layer4") != std::string::npos) return 3;
+      if (n.find("layer3") != std::string::npos) return 4;
+      return 5;
+    }
+    return 2;
+  };
+  int64_t lo[6], hi[6], cnt[6];
+  for (int i = 0; i < 6; ++i) { lo[i] = arena_n_; hi[i] = 0; cnt[i] = 0; }
+  for (auto& kv : params_) {
+    if (!kv.second.g) continue;
+    const int64_t off = kv.second.g - arena_g_;
+    RETR_CHECK(off >= 0 && off + kv.second.numel <= arena_n_, "gradient of '" + kv.first + "' is outside the arena");
+    const int k = bucket_of(kv.first);
+    lo[k] = std::min(lo[k], off); hi[k] = std::max(hi[k], off + kv.second.numel); cnt[k] += kv.second.numel;
+  }
+  bool tiled = true;
+  int64_t total = 0;
+  for (int i = 0; i < 6; ++i) {
+    if (cnt[i] == 0) continue;
+    if (hi[i] - lo[i] != cnt[i]) tiled = false;            // a bucket's tensors must be contiguous in the arena
+    total += cnt[i];
+  }
+  if (!tiled || total != arena_n_) {                       // unexpected arena order: one bucket, after the backward pass
+    GradBucket b; b.name = kFallbackBucket; b.lo = 0; b.hi = arena_n_;
+    buckets_.push_back(b);
+    return;
+  }
+  for (int i = 0; i < 6; ++i)
+    if (cnt[i]) { GradBucket b; b.name = kBucketNames[i]; b.lo = lo[i]; b.hi = hi[i]; buckets_.push_back(b); }
+}
+
+const char* kBucketNamesFwd[6] = {"mlp head", "decoder + embeddings", "encoder + input/loc projections",
+                                  "backbone layer4", "backbone layer3", "backbone layer2"};
+static const char* const* kBucketNames = kBucketNamesFwd;
+
+template <typename T>
+void TrainerT<T>::bucket_ready(int k, cudaStream_t s) {
+  if (!comm_) return;
+  for (size_t i = 0; i < buckets_.size(); ++i) {
+    if (buckets_[i].name != kBucketNames[k]) continue;     // stages without trainable tensors have no bucket
+    CUDA_OK(cudaEventRecord(dp_ready_[i], s));
+    CUDA_OK(cudaStreamWaitEvent(dp_stream_, dp_ready_[i], 0));
+    nccl_ok(nccl().AllReduce(arena_g_ + buckets_[i].lo, arena_g_ + buckets_[i].lo, (size_t)(buckets_[i].hi - buckets_[i].lo),
+                             NCCL_FLOAT32, NCCL_AVG, comm_, dp_stream_), "ncclAllReduce");
+  }
+}
+
+template <typename T>
+void TrainerT<T>::buckets_join(cudaStream_t s) {
+  if (!comm_) return;
+  if (buckets_.size() == 1 && buckets_[0].name == kFallbackBucket) {   // unexpected arena order: one exchange, now
+    CUDA_OK(cudaEventRecord(dp_ready_[0], s));
+    CUDA_OK(cudaStreamWaitEvent(dp_stream_, dp_ready_[0], 0));
+    nccl_ok(nccl().AllReduce(arena_g_, arena_g_, (size_t)arena_n_, NCCL_FLOAT32, NCCL_AVG, comm_, dp_stream_), "ncclAllReduce");
+  }
+  CUDA_OK(cudaEventRecord(dp_done_, dp_stream_));
+  CUDA_OK(cudaStreamWaitEvent(s, dp_done_, 0));
+}
 
 // ---- construction ------------------------------------------------------------------------------------------
 template <typename T>
@@ -457,6 +569,7 @@ void TrainerT<T>::finalize() {
   ws_ = alloc<float>(ws_floats_);
   sumsq_ = alloc<float>(4);
   CUDA_OK(cudaDeviceSynchronize());
+  build_buckets();
   finalized_ = true;
 }
 
@@ -844,6 +957,7 @@ void TrainerT<T>::backward_impl(cudaStream_t s) {
   lin_bwd(mlp_[0], dqkv_, mlp_[0].out, hs_, d, Md, tmpf_, true, mlp_[0].gb, s);           // tmpf_ = d hs (fp32)
   layernorm_bwd(y_final_, dec_ng_, tmpf_, nullptr, dY_, 0, g_dec_ng_, g_dec_nb_, Md, d, 1e-5f, s);
   CUDA_OK(cudaMemsetAsync(dMem_, 0, Me * d * 4, s));
+  bucket_ready(0, s);                                      // the 16 M head gradients travel under the whole rest of the pass
 
   // ---- decoder layers ----
   for (int l = desc.dec_layers - 1; l >= 0; --l) {
@@ -888,6 +1002,9 @@ void TrainerT<T>::backward_impl(cudaStream_t s) {
   if (g_e_word_ && g_e_pos_)
     embed_ln_bwd(ids_, emb_pre_, emb_g_, dY_, g_e_word_, g_e_pos_, g_emb_g_, g_emb_b_, embtmp_, B, Tn, d, desc.embed_ln_eps,
                  drop(1), pad_id_, s);
+  // (decoder.norm's gradients were written before bucket 0 was recorded but belong to this bucket's range: fine,
+  // every bucket is recorded AFTER its last writer)
+  bucket_ready(1, s);
 
   // ---- encoder ----
   layernorm_bwd(x_final_, enc_ng_, dMem_, nullptr, dX_, 0, g_enc_ng_, g_enc_nb_, Me, d, 1e-5f, s);
@@ -917,6 +1034,7 @@ void TrainerT<T>::backward_impl(cudaStream_t s) {
   const int64_t cfeat = blocks_.back().c3.cout, Mt = NI * g2;
   T* dfeat = train_backbone_ ? bb_[0] : nullptr;
   lin_bwd(input_proj_, dtok_, d, feat_, cfeat, Mt, dfeat, false, input_proj_.gb, s);
+  bucket_ready(2, s);
 
   // ---- backbone layers 2-4 (torchvision Bottleneck, resnet.py:143-165) ----
   if (train_backbone_) {
@@ -941,8 +1059,15 @@ void TrainerT<T>::backward_impl(cudaStream_t s) {
       }
       conv_bwd(b.c1, t1, x_in, NI, b.Hin, b.Hin, dxn, idgrad, need_dx, s);
       std::swap(dy, dxn);
+      // the first block of a stage is the last one the reverse loop visits: the stage's gradients are final
+      int start = 0;
+      for (int st = 0; st < 4; ++st) {
+        if (bi == start && st >= 1) bucket_ready(6 - st, s);       // layer4 -> bucket 3, layer3 -> 4, layer2 -> 5
+        start += desc.blocks[st];
+      }
     }
   }
+  buckets_join(s);
   launches += g_launches - l0;
 }
 

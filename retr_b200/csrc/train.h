@@ -36,6 +36,13 @@ class TrainerBase {
   // lr_backbone (main.py:31-36).  `step` is the 1-based update count (bias correction).
   virtual void clip_adamw(float max_norm, float lr, float lr_backbone, float beta1, float beta2, float eps,
                           float weight_decay, int step, float* grad_norm_dev, cudaStream_t s) = 0;
+  // Data parallel.  set_comm: from now on every backward pass all-reduces (mean over `world` ranks) the
+  // gradient arena bucket by bucket, each bucket on a side stream as soon as the backward pass has finished it, and
+  // the caller's stream waits for the last one before backward returns control to it (comm == null switches it off).
+  // allreduce_grads: the same buckets, issued at once on `s` (for callers that drive the exchange themselves).
+  virtual void set_comm(void* nccl_comm, int world) = 0;
+  virtual void allreduce_grads(void* nccl_comm, cudaStream_t s) = 0;
+  virtual int bucket_info(int64_t* lo_hi, int max_buckets) const = 0;   // -> number of buckets; lo_hi[2*i], [2*i+1]
   long long launches = 0;
 };
 

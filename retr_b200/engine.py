@@ -68,9 +68,12 @@ def train_step_native(model, samples, caps, cap_masks, max_norm, lr, lr_backbone
     tr = model.trainer(inputs[0].shape[0])
     seed = int(torch.randint(0, 2 ** 62, (1,)).item())
     p = float(model.dropout_p) if model.training else 0.0
+    multi = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+    if multi and hasattr(tr, "enable_data_parallel"):
+        tr.enable_data_parallel()          # NCCL group: bucketed all-reduce inside the native backward pass, overlapped
     loss = tr.loss_and_grads(*inputs, caps[:, 1:], dropout_p=p, seed=seed)
-    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-        dist.all_reduce(tr.gflat)
+    if multi and not getattr(tr, "native_dp", False):
+        dist.all_reduce(tr.gflat)          # other backends (gloo in the CPU tests): one bucket after the pass
         tr.gflat.div_(dist.get_world_size())
     norm = tr.clip_adamw(max_norm, lr, lr_backbone, betas=betas, eps=eps, weight_decay=weight_decay)
     return loss, norm

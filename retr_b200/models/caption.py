@@ -41,6 +41,8 @@ class _NativeTrainForward(torch.autograd.Function):
     @staticmethod
     def forward(ctx, model, inputs, p_drop, seed, names, *params):
         trainer = model.trainer(inputs[0].shape[0])
+        if hasattr(trainer, "enable_data_parallel"):
+            trainer.enable_data_parallel()     # no-op without an NCCL process group of >= 2 ranks
         ctx.trainer, ctx.names = trainer, names               # names[i] is the state_dict key of params[i]
         return trainer.forward(*inputs, dropout_p=p_drop, seed=seed)
 
@@ -49,8 +51,8 @@ class _NativeTrainForward(torch.autograd.Function):
         trainer = ctx.trainer
         grads = trainer.backward(dlogits)
         if torch.distributed.is_available() and torch.distributed.is_initialized() \
-                and torch.distributed.get_world_size() > 1:
-            # data parallel: one all-reduce of the flat gradient buffer (NCCL over NVLink), mean over ranks
+                and torch.distributed.get_world_size() > 1 and not getattr(trainer, "native_dp", False):
+            # data parallel without the native NCCL path (e.g. gloo): one all-reduce of the flat gradient buffer
             torch.distributed.all_reduce(trainer.gflat)
             trainer.gflat.div_(torch.distributed.get_world_size())
         return (None, None, None, None, None) + tuple(grads[n] for n in ctx.names)

@@ -77,6 +77,12 @@ SIGNATURES = {
                                   [C.c_float, C.c_uint64, C.c_void_p, C.c_void_p]),
     "retr_train_clip_adamw": (C.c_int, [C.c_void_p] + [C.c_float] * 7 + [C.c_int32, C.c_void_p, C.c_void_p]),
     "retr_train_kernel_launches": (C.c_int64, [C.c_void_p]),
+    "retr_nccl_unique_id": (C.c_int, [C.c_void_p]),
+    "retr_nccl_comm_create": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
+    "retr_nccl_comm_destroy": (None, [C.c_void_p]),
+    "retr_train_set_comm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
+    "retr_allreduce_grads": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "retr_train_grad_buckets": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.c_int32]),
     "retr_op_attention": (C.c_int, [C.c_int32] + [C.c_void_p] * 4 + [C.c_int32] * 4 + [C.c_int64] * 4 +
                           [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
 }

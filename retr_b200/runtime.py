@@ -300,6 +300,44 @@ class Trainer:
         self._loss = torch.zeros(1, dtype=torch.float32, device=device)
         self._sumsq = torch.zeros(1, dtype=torch.float32, device=device)
 
+    # ---- data parallel ---------------------------------------------------------------------------------------
+    native_dp = False
+
+    def enable_data_parallel(self):
+        """Give the native trainer its own NCCL communicator over torch.distributed's ranks: from then on the backward
+        pass all-reduces (mean) the gradient buckets itself, overlapped with the rest of the pass.  No-op without an
+        initialised NCCL process group or with one rank."""
+        import torch.distributed as dist
+        if self.native_dp or not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() < 2 \
+                or dist.get_backend() != "nccl":
+            return self.native_dp
+        world, rank = dist.get_world_size(), dist.get_rank()
+        ident = torch.zeros(128, dtype=torch.uint8)
+        if rank == 0:
+            buf = (C.c_char * 128)()
+            native.check(self.lib.retr_nccl_unique_id(buf))
+            ident = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8).clone()
+        ident = ident.to(self.device)
+        dist.broadcast(ident, 0)
+        raw = bytes(ident.cpu().numpy().tobytes())
+        comm = C.c_void_p()
+        with torch.cuda.device(self.device):
+            native.check(self.lib.retr_nccl_comm_create(raw, world, rank, C.byref(comm)))
+            native.check(self.lib.retr_train_set_comm(self.handle, comm, world))
+        self._comm, self.native_dp = comm, True
+        return True
+
+    def grad_buckets(self):
+        buf = (C.c_int64 * 32)()
+        n = self.lib.retr_train_grad_buckets(self.handle, buf, 16)
+        return [(buf[2 * i], buf[2 * i + 1]) for i in range(max(n, 0))]
+
+    def allreduce_info(self):
+        b = self.grad_buckets()
+        return {"native_nccl": bool(self.native_dp), "overlapped_with_backward": bool(self.native_dp),
+                "buckets": len(b), "bucket_mb": [round((hi - lo) * 4 / 2 ** 20, 1) for lo, hi in b],
+                "order": "reverse execution: head, decoder+embeddings, encoder+projections, layer4, layer3, layer2"}
+
     @staticmethod
     def signature_of(model):
         """Changes when a bound pointer moved or a folded buffer (FrozenBatchNorm2d) was rewritten."""
@@ -308,6 +346,10 @@ class Trainer:
 
     def close(self):
         if getattr(self, "handle", None):
+            if getattr(self, "_comm", None):
+                self.lib.retr_train_set_comm(self.handle, None, 1)
+                self.lib.retr_nccl_comm_destroy(self._comm)
+                self._comm, self.native_dp = None, False
             self.lib.retr_train_destroy(self.handle)
             self.handle = None
 

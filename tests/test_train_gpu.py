@@ -263,3 +263,19 @@ if __name__ == "__main__":
     for n, na, err, cos in rows:
         flag = "  <<<" if err > (2e-3 if prec == "fp32" else 1e-1) else ""
         print(f"{n:70s} |g|={na:10.3e} err={err:9.2e} cos={cos:8.5f}{flag}")
+
+
+def test_native_nccl_data_parallel():
+    """the training step's one real collective.  Needs >= 2 GPUs (skipped on a 1-GPU box); launches
+    tests/dp_nccl_check.py under torchrun: bucketed + overlapped native all-reduce == one all-reduce after the pass."""
+    import os
+    import subprocess
+    import sys
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    here = os.path.dirname(os.path.abspath(__file__))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29611", os.path.join(here, "dp_nccl_check.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "DP_NCCL_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
