@@ -11,7 +11,8 @@ import math
 import torch
 import torch.distributed as dist
 
-from .eval_utils.decode import greedy, prune_cap_ids
+from .eval_utils.decode import greedy, greedy_stream, prune_cap_ids
+from .models.caption import _CaptionBase
 
 
 def shard_range(n_samples, rank, world):
@@ -28,11 +29,18 @@ def sharded_greedy(make_samples, n_samples, model, batch_size, max_len, device, 
     world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
     lo, hi = shard_range(n_samples, rank, world)
     local = []
-    for b0 in range(lo, hi, batch_size):
-        b1 = min(b0 + batch_size, hi)
-        ids = greedy(make_samples(b0, b1), model, max_len=max_len, device=device, bos_token=bos_token,
-                     eos_token=eos_token)
-        local += prune_cap_ids(ids.cpu().tolist(), clean=True, pad_token=pad_token, bos_token=bos_token,
+    spans = [(b0, min(b0 + batch_size, hi)) for b0 in range(lo, hi, batch_size)]
+    if isinstance(model, _CaptionBase) and torch.device(device).type == "cuda":
+        # native model: batches stream through one context, the next batch's images cross PCIe while this one decodes
+        if spans:
+            model.max_batch = max(model.max_batch, batch_size)
+        rows = greedy_stream((make_samples(b0, b1) for b0, b1 in spans), model, max_len=max_len, bos_token=bos_token,
+                             eos_token=eos_token)
+    else:
+        rows = (greedy(make_samples(b0, b1), model, max_len=max_len, device=device, bos_token=bos_token,
+                       eos_token=eos_token).cpu() for b0, b1 in spans)
+    for ids in rows:
+        local += prune_cap_ids(ids.tolist(), clean=True, pad_token=pad_token, bos_token=bos_token,
                                eos_token=eos_token)
     if not gather or world == 1:
         return local
