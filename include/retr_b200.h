@@ -174,6 +174,22 @@ int retr_op_decode_out_ln_proj(const void* att, const void* Wo, const float* bo,
 int retr_op_decode_cross_attention(const void* q, const void* kcache, const void* vcache, int32_t cache_rows, void* out,
                                    int32_t M, int32_t n_heads, int32_t d_model, const int32_t* n_keys, void* stream);
 
+/* ---- preprocessing: the step immediately before the hot path ------------------------
+ * replaces: RefCocoCaption.__getitem__'s image half in validation mode (data_utils/refcoco.py:105-188 with
+ * get_transforms('val') :14-46) and its helpers crop_image_to_bb, pad_img_to_max, pad_mask_to_max,
+ * compute_position_features (data_utils/utils.py:161-256): crop to the box, context = image with the box zeroed,
+ * pad to square (colour 0 / mask True), antialiased bilinear resize to out_size (PIL's fixed-point resampler for the
+ * image, torchvision's float resize + .to(bool) for the mask), /255, ImageNet normalisation.  Bit-identical outputs.
+ * pixels: packed uint8 RGB images (HWC), image b at byte offsets[b] with hw[2b] rows and hw[2b+1] columns;
+ * boxes: double [B,4] = (x, y, w, h) as annotated (unrounded; x, y >= 0, box not empty after clipping to the image).
+ * Outputs (device): t_img/g_img fp32 [B,3,out,out], t_mask/g_mask uint8 [B,out,out] (1 = padding / blanked target),
+ * loc fp32 [B,5] = [x1, y1, x2, y2, area] relative; g_img+g_mask and loc may be NULL.  All pointers are device
+ * pointers.  The padded square side must not exceed retr_preprocess_max_side(out_size) (6944 for 224). */
+int retr_preprocess(const uint8_t* pixels, const int64_t* offsets, const int32_t* hw, const double* boxes, int32_t batch,
+                    int32_t out_size, float* t_img, uint8_t* t_mask, float* g_img, uint8_t* g_mask, float* loc,
+                    void* stream);
+int retr_preprocess_max_side(int32_t out_size);
+
 /* ---- allocation-free operator ---------------------------------------------------------------------
  * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).

@@ -194,6 +194,14 @@ int retr_op_gemm(int32_t dtype, const retr_gemm_args* a, void* stream) {
   API_END
 }
 
+int retr_preprocess(const uint8_t* pixels, const int64_t* offsets, const int32_t* hw, const double* boxes, int32_t batch,
+                    int32_t out_size, float* t_img, uint8_t* t_mask, float* g_img, uint8_t* g_mask, float* loc, void* stream) {
+  API_BEGIN
+  preprocess(pixels, offsets, hw, boxes, batch, out_size, t_img, t_mask, g_img, g_mask, loc, static_cast<cudaStream_t>(stream));
+  API_END
+}
+int retr_preprocess_max_side(int32_t out_size) { return preprocess_max_side(out_size); }
+
 int retr_op_small_gemm_noalloc(const void* A, const void* W, const float* bias, float* C, int32_t M, int32_t N, int32_t K,
                                int32_t split_k, void* stream) {
   API_BEGIN

@@ -20,6 +20,11 @@ void stem_im2col(const float* img, T* out, int64_t nimg, int H, int W, int OH, i
 template <typename T>
 void maxpool_3x3s2(const T* in, T* out, int64_t nimg, int H, int W, int C, int OH, int OW, cudaStream_t s);
 
+// ---- preprocessing (preprocess.cu): raw RGB + box -> normalised 224x224 crops, masks, location features --------
+void preprocess(const uint8_t* pixels, const int64_t* offsets, const int32_t* hw, const double* bb, int batch, int out,
+                float* t_img, uint8_t* t_mask, float* g_img, uint8_t* g_mask, float* loc, cudaStream_t s);
+int preprocess_max_side(int out);          // largest padded square side the resampler's tap arrays cover
+
 // ---- token assembly (models/caption.py:119-147, models/ConcatTransformer.py:48-51) ------------
 // mask[b, off + p] = img_mask[b, floor(i*H/gh), floor(j*W/gw)]  (F.interpolate nearest, backbone.py:75)
 void subsample_mask(const uint8_t* img_mask, uint8_t* tok_mask, int B, int H, int W, int gh, int gw,

@@ -65,6 +65,8 @@ SIGNATURES = {
     "retr_op_decode_out_ln_proj": (C.c_int, [C.c_void_p] * 6 + [C.c_float] + [C.c_void_p] * 5 + [C.c_int32, C.c_void_p]),
     "retr_op_decode_cross_attention": (C.c_int, [C.c_void_p] * 3 + [C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
                                                  C.c_void_p, C.c_void_p]),
+    "retr_preprocess": (C.c_int, [C.c_void_p] * 4 + [C.c_int32, C.c_int32] + [C.c_void_p] * 6),
+    "retr_preprocess_max_side": (C.c_int, [C.c_int32]),
     "retr_op_small_gemm_noalloc": (C.c_int, [C.c_void_p] * 4 + [C.c_int32] * 4 + [C.c_void_p]),
     "retr_train_create": (C.c_int, [C.POINTER(ModelDesc), C.c_int32, C.POINTER(C.c_void_p)]),
     "retr_train_destroy": (None, [C.c_void_p]),
