@@ -141,6 +141,31 @@ def learned_variant():
     print("learned ->", path, os.path.getsize(path), "bytes")
 
 
+def basic_block_variant():
+    """backbone='ResNet18', dilation=False (models/backbone.py:86-93: BasicBlock, 512 channels, 7x7 = 49 tokens)."""
+    from retr_b200 import synthetic
+    RefConfig, ref_caption, RefNested, _ = ref_modules()
+    cfg = RefConfig()
+    cfg.use_global_features = cfg.use_location_features = True
+    cfg.backbone, cfg.dilation = "ResNet18", False
+    torch.manual_seed(42)
+    model, _ = ref_caption.build_model(cfg)
+    model.eval()
+    data = synthetic.make_batch(2, shard=0, train=True)
+    samples = (RefNested(data["t_img"], data["t_mask"]), RefNested(data["g_img"], data["g_mask"]), data["loc"])
+    with torch.no_grad():
+        logits = model(*samples, data["caps"][:, :-1], data["cap_masks"][:, :-1])
+    vidx = torch.arange(0, logits.shape[-1], 97)
+    top2 = logits.topk(2, dim=-1)
+    fx = {"kind": "CaptionGlobalLoc", "backbone": "ResNet18", "dilation": False, "batch": 2,
+          "fingerprint": fingerprint(model.state_dict()), "vocab_idx": vidx,
+          "logits_slice": logits[:, :12, :][:, :, vidx].clone(), "argmax": top2.indices[..., 0].clone(),
+          "margin": (top2.values[..., 0] - top2.values[..., 1]).clone(), "logits_absmax": float(logits.abs().max())}
+    path = os.path.join(OUT, "CaptionGlobalLoc_resnet18.pt")
+    torch.save(fx, path)
+    print("resnet18 ->", path, os.path.getsize(path), "bytes")
+
+
 class _StepLimited:
     """Wraps the reference model; after ``n`` calls raises StopIteration-like exit by making every
     row emit EOS (the reference loop then returns the caption as filled so far)."""
@@ -160,6 +185,9 @@ class _StepLimited:
 if __name__ == "__main__":
     if "--learned-only" in sys.argv:
         learned_variant()
+    elif "--resnet18-only" in sys.argv:
+        basic_block_variant()
     else:
         main()
         learned_variant()
+        basic_block_variant()

@@ -26,7 +26,7 @@ import torch.nn.functional as F
 
 SD = Dict[str, torch.Tensor]
 
-RESNET_BLOCKS = {"ResNet50": (3, 4, 6, 3), "ResNet101": (3, 4, 23, 3), "ResNet152": (3, 8, 36, 3)}
+RESNET_BLOCKS = {"ResNet18": (2, 2, 2, 2), "ResNet34": (3, 4, 6, 3), "ResNet50": (3, 4, 6, 3), "ResNet101": (3, 4, 23, 3), "ResNet152": (3, 8, 36, 3)}
 
 
 # --------------------------------------------------------------------------------------------
@@ -51,6 +51,15 @@ def bottleneck(x, sd: SD, p: str, stride: int, dilation: int):
     return F.relu(out + x)
 
 
+def basic_block(x, sd: SD, p: str, stride: int):
+    """torchvision BasicBlock.forward — torchvision/models/resnet.py:88-105 (ResNet-18/34; stride on the first 3x3)."""
+    out = F.relu(frozen_bn(F.conv2d(x, sd[p + ".conv1.weight"], stride=stride, padding=1), sd, p + ".bn1"))
+    out = frozen_bn(F.conv2d(out, sd[p + ".conv2.weight"], padding=1), sd, p + ".bn2")
+    if p + ".downsample.0.weight" in sd:
+        x = frozen_bn(F.conv2d(x, sd[p + ".downsample.0.weight"], stride=stride), sd, p + ".downsample.1")
+    return F.relu(out + x)
+
+
 def resnet_layer4(img, sd: SD, arch: str = "ResNet101", dilation: bool = True, p: str = "backbone.body"):
     """conv1/bn1/relu/maxpool + layer1..4 (torchvision/models/resnet.py:225-264 up to layer4, as kept
     by IntermediateLayerGetter, models/backbone.py:61-65); layer4's stride becomes dilation 2 with the
@@ -66,8 +75,11 @@ def resnet_layer4(img, sd: SD, arch: str = "ResNet101", dilation: bool = True, p
             dil *= stride
             stride = 1
         for bi in range(nblocks):
-            x = bottleneck(x, sd, f"{p}.layer{li + 1}.{bi}", stride if bi == 0 else 1,
-                           first_dil if bi == 0 else dil)
+            bp = f"{p}.layer{li + 1}.{bi}"
+            if bp + ".conv3.weight" in sd:
+                x = bottleneck(x, sd, bp, stride if bi == 0 else 1, first_dil if bi == 0 else dil)
+            else:
+                x = basic_block(x, sd, bp, stride if bi == 0 else 1)
     return x
 
 

@@ -69,6 +69,8 @@ template <typename T> struct Conv {
 template <typename T> struct Block {
   Conv<T> c1, c2, c3, ds;
   bool has_ds = false;
+  bool basic = false;       // torchvision BasicBlock (ResNet-18/34): 3x3 (stride) -> 3x3, no c3
+  int out_channels() const { return basic ? c2.cout : c3.cout; }
 };
 template <typename T> struct Linear {
   T* w = nullptr;           // [out, in]
@@ -264,9 +266,16 @@ void EngineT<T>::finalize() {
       const std::string p = bb + "layer" + std::to_string(st + 1) + "." + std::to_string(bi) + ".";
       const int s_ = bi == 0 ? stride : 1, dl = bi == 0 ? first_dil : dil;
       Block<T> b;
-      b.c1 = conv(p + "conv1.weight", p + "bn1", 1, 0, 1);
-      b.c2 = conv(p + "conv2.weight", p + "bn2", s_, dl, dl);
-      b.c3 = conv(p + "conv3.weight", p + "bn3", 1, 0, 1);
+      b.basic = raw_.count(p + "conv3.weight") == 0;
+      if (b.basic) {          // torchvision/models/resnet.py:59-105; dilation > 1 is refused there
+        RETR_CHECK(dl == 1, "BasicBlock backbones (ResNet-18/34) need dilation = False");
+        b.c1 = conv(p + "conv1.weight", p + "bn1", s_, 1, 1);
+        b.c2 = conv(p + "conv2.weight", p + "bn2", 1, 1, 1);
+      } else {
+        b.c1 = conv(p + "conv1.weight", p + "bn1", 1, 0, 1);
+        b.c2 = conv(p + "conv2.weight", p + "bn2", s_, dl, dl);
+        b.c3 = conv(p + "conv3.weight", p + "bn3", 1, 0, 1);
+      }
       b.has_ds = raw_.count(p + "downsample.0.weight") > 0;
       if (b.has_ds) b.ds = conv(p + "downsample.0.weight", p + "downsample.1", s_, 0, 1);
       blocks_.push_back(b);
@@ -350,7 +359,7 @@ void EngineT<T>::alloc_buffers() {
   const int64_t act = (int64_t)chunk_ * h1 * h1 * 64;              // largest activation of a chunk
   im2col_ = static_cast<T*>(dalloc(chunk_ * h1 * h1 * stem_.kpad * sizeof(T)));
   for (auto& a : act_) a = static_cast<T*>(dalloc(act * sizeof(T)));
-  const int64_t g2 = (int64_t)grid_hw * grid_hw, cfeat = blocks_.back().c3.cout;
+  const int64_t g2 = (int64_t)grid_hw * grid_hw, cfeat = blocks_.back().out_channels();
   feat_ = static_cast<T*>(dalloc(nimg * g2 * cfeat * sizeof(T)));
   const int64_t Me = B * S, Md = B * Tn, Mx = std::max(Me, Md);
   x_ = static_cast<float*>(dalloc(Me * d * 4));
@@ -503,16 +512,20 @@ void EngineT<T>::backbone(const float* img, int64_t n, T* feat, cudaStream_t s, 
   for (size_t bi = 0; bi < blocks_.size(); ++bi) {
     const Block<T>& b = blocks_[bi];
     int h1, w1, h2, w2, h3, w3;
+    T* out = (bi + 1 == blocks_.size()) ? feat : other;
     run_conv(b.c1, x, n, H, W, act_[2], nullptr, 1, &h1, &w1, s);
-    run_conv(b.c2, act_[2], n, h1, w1, act_[3], nullptr, 1, &h2, &w2, s);
     const T* identity = x;
     if (b.has_ds) {
       int hd, wd;
       run_conv(b.ds, x, n, H, W, act_[4], nullptr, 0, &hd, &wd, s);
       identity = act_[4];
     }
-    T* out = (bi + 1 == blocks_.size()) ? feat : other;
-    run_conv(b.c3, act_[3], n, h2, w2, out, identity, 2, &h3, &w3, s);     // relu(bn3(conv3) + identity)
+    if (b.basic) {
+      run_conv(b.c2, act_[2], n, h1, w1, out, identity, 2, &h3, &w3, s);      // relu(bn2(conv2) + identity)
+    } else {
+      run_conv(b.c2, act_[2], n, h1, w1, act_[3], nullptr, 1, &h2, &w2, s);
+      run_conv(b.c3, act_[3], n, h2, w2, out, identity, 2, &h3, &w3, s);      // relu(bn3(conv3) + identity)
+    }
     other = x; x = out;
     H = h3; W = w3;
   }
@@ -530,7 +543,7 @@ void EngineT<T>::encode(int B, const float* t_img, const uint8_t* t_mask, const 
   RETR_CHECK(desc.loc_in_dim == 0 || loc, "location features required");
   const long long l0 = g_launches;
   const int d = desc.d_model, g2 = grid_hw * grid_hw, Hi = desc.image_size;
-  const int64_t cfeat = blocks_.back().c3.cout, img_elems = 3LL * Hi * Hi;
+  const int64_t cfeat = blocks_.back().out_channels(), img_elems = 3LL * Hi * Hi;
   struct CapGuard { explicit CapGuard(int c) { gemm_set_cta_cap(c); } ~CapGuard() { gemm_set_cta_cap(0); } } cap_guard(encode_cta_cap);
   CUDA_OK(cudaEventRecord(ev_[0], s));
   // Per-launch ramp and tail cost ~18 us x 104 convs per pass, so both image sets go through the backbone in ONE pass
@@ -921,7 +934,7 @@ void EngineT<T>::decode_greedy(int bos, int eos, int max_len, int64_t* out_ids, 
 template <typename T>
 void EngineT<T>::read_state(const std::string& what, void* dst, int64_t bytes, cudaStream_t s) {
   RETR_CHECK(cur_B_ > 0, "nothing encoded yet");
-  const int64_t B = cur_B_, d = desc.d_model, g2 = (int64_t)grid_hw * grid_hw, cfeat = blocks_.back().c3.cout;
+  const int64_t B = cur_B_, d = desc.d_model, g2 = (int64_t)grid_hw * grid_hw, cfeat = blocks_.back().out_channels();
   auto conv_out = [&](const T* src, int64_t n) {
     RETR_CHECK(bytes >= n * 4, "destination too small for '" + what + "'");
     to_f32_kernel<T><<<(unsigned)cdiv(n, 256), 256, 0, s>>>(src, static_cast<float*>(dst), n);

@@ -17,6 +17,8 @@ from . import utils
 
 # name -> (block counts per stage, bottleneck?)
 RESNET_SPECS = {
+    "ResNet18": ((2, 2, 2, 2), False),
+    "ResNet34": ((3, 4, 6, 3), False),
     "ResNet50": ((3, 4, 6, 3), True),
     "ResNet101": ((3, 4, 23, 3), True),
     "ResNet152": ((3, 8, 36, 3), True),
@@ -66,12 +68,30 @@ class Bottleneck(nn.Module):
         self.downsample = downsample
 
 
+class BasicBlock(nn.Module):
+    """3x3 (carries the stride) -> 3x3 + identity/downsample, ReLU after the add (torchvision/models/resnet.py:59-105;
+    ResNet-18/34).  torchvision refuses dilation > 1 here, so these backbones need ``config.dilation = False``."""
+    expansion = 1
+
+    def __init__(self, inplanes, planes, stride, dilation, downsample):
+        super().__init__()
+        if dilation > 1:
+            raise NotImplementedError("Dilation > 1 not supported in BasicBlock")     # torchvision's own error
+        self.conv1 = _conv(inplanes, planes, 3, stride)
+        self.bn1 = FrozenBatchNorm2d(planes)
+        self.conv2 = _conv(planes, planes, 3)
+        self.bn2 = FrozenBatchNorm2d(planes)
+        self.downsample = downsample
+
+
 class ResNetBody(nn.Module):
     """conv1/bn1/maxpool + layer1..layer4; what IntermediateLayerGetter keeps of torchvision's
     ResNet when only layer4 is returned (reference models/backbone.py:61-65)."""
 
-    def __init__(self, blocks, dilate_last):
+    def __init__(self, blocks, dilate_last, bottleneck=True):
         super().__init__()
+        Block = Bottleneck if bottleneck else BasicBlock
+        ex = Block.expansion
         self.conv1 = nn.Conv2d(3, 64, 7, stride=2, padding=3, bias=False)
         self.bn1 = FrozenBatchNorm2d(64)
         inplanes, dilation = 64, 1
@@ -82,11 +102,11 @@ class ResNetBody(nn.Module):
                 dilation *= stride
                 stride = 1
             down = None
-            if stride != 1 or inplanes != planes * 4:
-                down = nn.Sequential(_conv(inplanes, planes * 4, 1, stride), FrozenBatchNorm2d(planes * 4))
-            stage = [Bottleneck(inplanes, planes, stride, prev_dilation, down)]
-            inplanes = planes * 4
-            stage += [Bottleneck(inplanes, planes, 1, dilation, None) for _ in range(1, n)]
+            if stride != 1 or inplanes != planes * ex:
+                down = nn.Sequential(_conv(inplanes, planes * ex, 1, stride), FrozenBatchNorm2d(planes * ex))
+            stage = [Block(inplanes, planes, stride, prev_dilation, down)]
+            inplanes = planes * ex
+            stage += [Block(inplanes, planes, 1, dilation, None) for _ in range(1, n)]
             setattr(self, f"layer{i + 1}", nn.Sequential(*stage))
         nn.Linear(inplanes, 1000)               # torchvision's classifier head: consumes RNG, then dropped
         for m in self.modules():
@@ -106,14 +126,14 @@ class Backbone(nn.Module):
         if return_interm_layers:
             raise NotImplementedError("only the layer4 feature map is on the hot path")
         if name not in RESNET_SPECS:
-            raise NotImplementedError(f"backbone {name!r}: Bottleneck ResNets only (ResNet50/101/152)")
+            raise NotImplementedError(f"backbone {name!r}: one of {sorted(RESNET_SPECS)}")
         if utils.is_main_process() and not getattr(Backbone, "_warned", False):
             # reference downloads ImageNet weights here (models/backbone.py:87-88); no network
             # on this box, so random init + load_state_dict is the only route.
             Backbone._warned = True
-        blocks, _ = RESNET_SPECS[name]
-        self.body = ResNetBody(blocks, dilation)
-        self.num_channels = 2048
+        blocks, bottleneck = RESNET_SPECS[name]
+        self.body = ResNetBody(blocks, dilation, bottleneck)
+        self.num_channels = 2048 if bottleneck else 512        # reference models/backbone.py:92
         self.arch = name
         self.dilation = bool(dilation)
         for pname, p in self.body.named_parameters():

@@ -65,6 +65,7 @@ class Engine:
         d = model_desc(model, device, precision, self.max_batch, image_size)
         self.desc = d
         self.T, self.V, self.d_model = d.max_pos, d.vocab, d.d_model
+        self.feat_channels = model.backbone.num_channels
         self.n_enc, self.n_dec = d.enc_layers, d.dec_layers
         handle = C.c_void_p()
         with torch.cuda.device(device):
@@ -226,7 +227,9 @@ class Engine:
         elif what in ("memory", "src"):
             out = torch.empty(B, S, d, dtype=torch.float32, device=self.device)
         else:
-            out = torch.empty(B, 14, 14, 2048, dtype=torch.float32, device=self.device)
+            g = int(round(((self.S - (self.desc.n_loc if self.desc.loc_in_dim == 1 else min(self.desc.loc_in_dim, 1)))
+                           / self.desc.n_images) ** 0.5))
+            out = torch.empty(B, g, g, self.feat_channels, dtype=torch.float32, device=self.device)
         with torch.cuda.device(self.device):
             native.check(self.lib.retr_read_state(self.handle, what.encode(), native.ptr(out),
                                                   out.numel() * out.element_size(), self._stream()))
@@ -256,6 +259,9 @@ class Trainer:
         d = model_desc(model, device, precision, self.max_batch, image_size)
         if not d.pre_norm:
             raise NotImplementedError("retr_b200 training implements pre_norm=True (configuration_template.py:51)")
+        if not RESNET_SPECS[model.backbone.arch][1]:
+            raise NotImplementedError("retr_b200 training implements the Bottleneck backbones (ResNet-50/101/152); "
+                                      "ResNet-18/34 run inference only")
         self.desc, self.T, self.V = d, d.max_pos, d.vocab
         sd = model.state_dict(keep_vars=True)
         self.names = [n for n, t in sd.items() if torch.is_floating_point(t)]

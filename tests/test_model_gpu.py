@@ -490,3 +490,40 @@ def test_decode_stack_kernel_consistent_with_teacher_forced(B, monkeypatch):
     first = (ids_old != ids).float().argmax(1)[(ids_old != ids).any(1)]
     print(f"  vs launch-chain path: {same * 100:.0f}% sequences identical; first divergences at {first.tolist()}")
     assert bool((ids_old[:, :4] == ids[:, :4]).all())
+
+
+@pytest.mark.parametrize("arch", ["ResNet18", "ResNet34"])
+def test_basic_block_backbones(arch):
+    """ResNet-18/34 (BasicBlock, dilation=False: 512 channels, 7x7 = 49 tokens per image; models/backbone.py:86-93):
+    fp32 logits vs the reference fixture (ResNet-18) and the oracle, greedy ids vs the oracle, the bf16 path within its
+    tolerance; the trainer refuses them loudly."""
+    kind = "CaptionGlobalLoc"
+    model, sd, cfg = gpu_model(kind, "fp32", calibrated=False, backbone=arch, dilation=False)
+    data, enc_in = synthetic_samples(kind, 2)
+    caps, cm = data["caps"].cuda(), data["cap_masks"].cuda()
+    with torch.no_grad():
+        logits = model(*samples_of(kind, enc_in), caps[:, :-1], cm[:, :-1]).cpu()
+        ref = O.forward(sd, cfg, *enc_in, data["caps"][:, :-1], data["cap_masks"][:, :-1])
+    assert model.engine(2).S == 49 + 5 + 49
+    assert (logits - ref).abs().max().item() <= 1e-4 * ref.abs().max().item()
+    if arch == "ResNet18":
+        fx = golden("CaptionGlobalLoc_resnet18")
+        got = logits[:, :12, :][:, :, fx["vocab_idx"]]
+        assert (got - fx["logits_slice"]).abs().max().item() <= 1e-4 * fx["logits_absmax"]
+    model, sd, cfg = gpu_model(kind, "fp32", calibrated=True, backbone=arch, dilation=False)
+    _, enc2 = synthetic_samples(kind, 3, shard=5, train=False)
+    with torch.no_grad():
+        ids = decode.greedy(samples_of(kind, enc2, "cpu"), model, max_len=128, device="cuda", bos_token=101,
+                            eos_token=102).cpu()
+        want, _ = O.greedy(sd, cfg, *enc2, max_len=128, bos_token=101, eos_token=102, literal=False)
+        ref = O.forward(sd, cfg, *enc_in, data["caps"][:, :-1], data["cap_masks"][:, :-1])
+    assert torch.equal(ids, want)
+    m16, _, _ = gpu_model(kind, "bf16", calibrated=True, backbone=arch, dilation=False)
+    with torch.no_grad():
+        l16 = m16(*samples_of(kind, enc_in), caps[:, :-1], cm[:, :-1]).cpu()
+        ids16 = decode.greedy(samples_of(kind, enc2, "cpu"), m16, max_len=128, device="cuda", bos_token=101, eos_token=102)
+    assert (l16 - ref).abs().max().item() <= BF16_LOGIT_TOL * ref.abs().max().item()
+    assert ids16.shape == (3, 128)
+    m16.train()
+    with pytest.raises(NotImplementedError):
+        m16(*samples_of(kind, enc_in), caps[:, :-1], cm[:, :-1])

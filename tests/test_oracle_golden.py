@@ -109,3 +109,29 @@ def test_learned_position_variant_init_and_oracle_forward():
     assert (got - fx["logits_slice"]).abs().max() <= 2e-5 * scale
     sure = fx["margin"] > 1e-4 * scale
     assert torch.equal(logits.argmax(-1)[sure], fx["argmax"][sure])
+
+
+def test_basic_block_backbone_init_and_oracle_forward():
+    """backbone='ResNet18', dilation=False (models/backbone.py:86-93): BasicBlock init replay
+    (bit-identical state_dict) and the oracle's forward against the fixture recorded from the unmodified reference."""
+    model, _, cfg = build_product_model("CaptionGlobalLoc", backbone="ResNet18", dilation=False)
+    sd = model.state_dict()
+    fx = golden("CaptionGlobalLoc_resnet18")
+    fp = fx["fingerprint"]
+    assert sorted(sd.keys()) == fp["keys"]
+    assert tuple(sd["input_proj.weight"].shape) == (256, 512, 1, 1)
+    for k, s in fp["sums"].items():
+        assert float(sd[k].double().sum()) == s, k
+    assert float(sum(sd[k].double().abs().sum() for k in sorted(sd.keys()))) == fp["abs_sum_total"]
+    data, enc_in = synthetic_samples("CaptionGlobalLoc", fx["batch"])
+    with torch.no_grad():
+        src, mask = O.encoder_inputs(sd, cfg, *enc_in)
+        logits = O.forward(sd, cfg, *enc_in, data["caps"][:, :-1], data["cap_masks"][:, :-1])
+    assert src.shape[1] == 49 + 5 + 49                      # 7x7 tokens per image without dilation
+    scale = fx["logits_absmax"]
+    got = logits[:, :12, :][:, :, fx["vocab_idx"]]
+    assert (got - fx["logits_slice"]).abs().max() <= 2e-5 * scale
+    sure = fx["margin"] > 1e-4 * scale
+    assert torch.equal(logits.argmax(-1)[sure], fx["argmax"][sure])
+    with pytest.raises(NotImplementedError):                # torchvision's BasicBlock refuses dilation
+        build_product_model("CaptionGlobalLoc", backbone="ResNet34", dilation=True)
