@@ -109,6 +109,16 @@ __global__ void gather_tok_kernel(const float* __restrict__ dx, T* __restrict__ 
     out[i] = from_f<T>(dx[((int64_t)b * S + (set ? off_g : 0) + j) * d + c]);
   }
 }
+// memory = x, memory + pos (pre_norm=False: no final encoder LayerNorm)
+template <typename T>
+__global__ void cast_pos_kernel(const float* __restrict__ x, T* __restrict__ y, T* __restrict__ y2,
+                                const float* __restrict__ pos, int period, int64_t n, int d) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float v = x[i];
+    y[i] = from_f<T>(v);
+    y2[i] = from_f<T>(v + pos[((i / d) % period) * d + i % d]);
+  }
+}
 inline unsigned ewb(int64_t n) { return (unsigned)std::min<int64_t>(cdiv(n, 256), 148 * 16); }
 
 template <typename T>
@@ -116,7 +126,6 @@ class TrainerT final : public TrainerBase {
  public:
   TrainerT(const retr_model_desc& d, int pad_token_id) : desc(d), pad_id_(pad_token_id) {
     RETR_CHECK(d.n_images == 1 || d.n_images == 2, "n_images must be 1 or 2");
-    RETR_CHECK(d.pre_norm, "the training path implements the pre_norm=True configuration (configuration_template.py:51)");
     CUDA_OK(cudaSetDevice(d.device));
     int side = d.image_size;
     side = (side + 2 * 3 - 7) / 2 + 1;
@@ -503,8 +512,10 @@ void TrainerT<T>::finalize() {
     e.att = alloc<T>(Me * d); e.n2 = alloc<T>(Me * d); e.h = alloc<T>(Me * ff);
     enc_.push_back(e);
   }
-  enc_ng_ = P("transformer.encoder.norm.weight").p; g_enc_ng_ = P("transformer.encoder.norm.weight").g;
-  enc_nb_ = P("transformer.encoder.norm.bias").p; g_enc_nb_ = P("transformer.encoder.norm.bias").g;
+  if (desc.pre_norm) {        // the final encoder LayerNorm exists only then (models/ConcatTransformer.py:24)
+    enc_ng_ = P("transformer.encoder.norm.weight").p; g_enc_ng_ = P("transformer.encoder.norm.weight").g;
+    enc_nb_ = P("transformer.encoder.norm.bias").p; g_enc_nb_ = P("transformer.encoder.norm.bias").g;
+  }
   for (int l = 0; l < desc.dec_layers; ++l) {
     const std::string p = "transformer.decoder.layers." + std::to_string(l) + ".";
     const std::string sa = p + "tgt_self_attn.sublayer.", ca = p + "tgt_src_cross_attn.sublayer.";
@@ -752,7 +763,12 @@ void TrainerT<T>::forward_impl(int B, const float* t_img, const uint8_t* t_mask,
     gemmT<T>(p, s);
     branch_out(e.ff2, e.h, Me, e.xb, x_next, drop(12 + 4 * l), s);
   }
-  layernorm_pos<T>(x_final_, enc_ng_, enc_nb_, memory_, memp_, pe_, S, Me, d, 1e-5f, s);
+  if (desc.pre_norm) {
+    layernorm_pos<T>(x_final_, enc_ng_, enc_nb_, memory_, memp_, pe_, S, Me, d, 1e-5f, s);
+  } else {                    // pre_norm=False: memory is the last layer's output as it is
+    cast_pos_kernel<T><<<ewb(Me * d), 256, 0, s>>>(x_final_, memory_, memp_, pe_, S, Me * d, d);
+    LAUNCH_OK();
+  }
 
   // ---- decoder (models/ConcatTransformer.py:63-70,197-257) ----
   embed_ln_train(ids_, e_word_, e_pos_, emb_g_, emb_b_, emb_pre_, dec_[0].ya, B, Tn, d, desc.embed_ln_eps, drop(1), s);
@@ -1007,7 +1023,8 @@ void TrainerT<T>::backward_impl(cudaStream_t s) {
   bucket_ready(1, s);
 
   // ---- encoder ----
-  layernorm_bwd(x_final_, enc_ng_, dMem_, nullptr, dX_, 0, g_enc_ng_, g_enc_nb_, Me, d, 1e-5f, s);
+  if (desc.pre_norm) layernorm_bwd(x_final_, enc_ng_, dMem_, nullptr, dX_, 0, g_enc_ng_, g_enc_nb_, Me, d, 1e-5f, s);
+  else CUDA_OK(cudaMemcpyAsync(dX_, dMem_, Me * d * 4, cudaMemcpyDeviceToDevice, s));
   for (int l = desc.enc_layers - 1; l >= 0; --l) {
     TEnc<T>& e = enc_[l];
     dropout_bwd_cast<T>(dX_, gb_, Me * d, drop(12 + 4 * l), s);

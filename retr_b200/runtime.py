@@ -257,8 +257,6 @@ class Trainer:
         self.lib = native.lib()
         self.device, self.precision, self.max_batch, self.image_size = device, precision, int(max_batch), image_size
         d = model_desc(model, device, precision, self.max_batch, image_size)
-        if not d.pre_norm:
-            raise NotImplementedError("retr_b200 training implements pre_norm=True (configuration_template.py:51)")
         if not RESNET_SPECS[model.backbone.arch][1]:
             raise NotImplementedError("retr_b200 training implements the Bottleneck backbones (ResNet-50/101/152); "
                                       "ResNet-18/34 run inference only")

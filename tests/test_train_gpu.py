@@ -26,8 +26,8 @@ pytestmark = pytest.mark.gpu
 KINDS = ["CaptionGlobalLoc", "Caption", "CaptionLoc"]
 
 
-def train_model(kind, precision, dropout=0.0):
-    model, _, cfg = build_product_model(kind)
+def train_model(kind, precision, dropout=0.0, **cfg_over):
+    model, _, cfg = build_product_model(kind, **cfg_over)
     model = copy.deepcopy(model)
     model.load_state_dict(synthetic.calibrate_frozen_bn(model.state_dict()))
     sd = {k: v.clone() for k, v in model.state_dict().items()}
@@ -86,6 +86,21 @@ def test_fp32_loss_and_grads_match_oracle(kind):
             assert err <= 2e-3, (n, na, err, cos)
     # frozen parts carry no gradient (models/backbone.py:58-60)
     assert all(p.grad is None for n, p in model.named_parameters() if not p.requires_grad)
+
+
+def test_fp32_grads_without_final_encoder_norm():
+    """pre_norm=False only drops the final encoder LayerNorm (models/ConcatTransformer.py:24)."""
+    kind = "CaptionGlobalLoc"
+    model, sd, cfg = train_model(kind, "fp32", pre_norm=False)
+    assert "transformer.encoder.norm.weight" not in sd
+    data, enc_in = synthetic_samples(kind, 2, shard=6)
+    ref_loss, ref = oracle_grads(model, sd, cfg, enc_in, data["caps"], data["cap_masks"])
+    loss, got = native_grads(model, enc_in, data["caps"], data["cap_masks"])
+    assert abs(loss - ref_loss) <= 2e-5 * abs(ref_loss), (loss, ref_loss)
+    gmax = max(r[1] for r in compare(ref, got))
+    for n, na, err, cos in compare(ref, got):
+        if na > 1e-6 * gmax:
+            assert err <= 2e-3, (n, na, err, cos)
 
 
 def test_bf16_grads_close_to_oracle():
