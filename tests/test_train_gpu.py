@@ -294,3 +294,36 @@ def test_native_nccl_data_parallel():
            "--master-port", "29611", os.path.join(here, "dp_nccl_check.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "DP_NCCL_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+def test_bf16_grads_at_bench_batch_equal_mean_of_chunks():
+    """The training bench runs B = 128 per GPU; parity against the oracle is checked at B = 2.  Samples are independent
+    and the loss is the mean over B*T positions, so the gradient of a 128-sample batch must equal the mean of the
+    gradients of its four 32-sample chunks (dropout 0): exercises the large-batch tiling / chunking of every kernel of
+    the backward pass.  Both sides are the bf16 path, so the tolerance is bf16 accumulation-order noise."""
+    kind = "CaptionGlobalLoc"
+    model, sd, cfg = train_model(kind, "bf16")
+    model.max_train_batch = 128
+    B, C = 128, 32
+    data = synthetic.make_batch(B, shard=40, train=True)
+    caps, masks = data["caps"].cuda(), data["cap_masks"].cuda()
+
+    def grads_of(lo, hi):
+        sub = {k: v[lo:hi] for k, v in data.items()}
+        samples = tuple(s.to("cuda") for s in synthetic.pack(sub))
+        t, g, loc = model._split_samples(samples)
+        inputs = model._train_inputs(t, g, loc, caps[lo:hi, :-1], masks[lo:hi, :-1])
+        tr = model.trainer(hi - lo)
+        loss = tr.loss_and_grads(*inputs, caps[lo:hi, 1:], dropout_p=0.0, seed=1)
+        torch.cuda.synchronize()
+        return float(loss), tr.gflat.clone()
+
+    loss_all, g_all = grads_of(0, B)
+    parts = [grads_of(i, i + C) for i in range(0, B, C)]
+    loss_mean = sum(p[0] for p in parts) / len(parts)
+    g_mean = torch.stack([p[1] for p in parts]).mean(0)
+    assert abs(loss_all - loss_mean) <= 2e-3 * abs(loss_mean), (loss_all, loss_mean)
+    rel = float((g_all - g_mean).norm() / g_mean.norm())
+    cos = float(torch.dot(g_all, g_mean) / (g_all.norm() * g_mean.norm()))
+    print(f"B=128 vs mean of 4x32: relative gradient difference {rel:.3e}, cosine {cos:.6f}")
+    assert rel <= 3e-2 and cos >= 0.999, (rel, cos)
