@@ -155,7 +155,12 @@ void attention(const AttnParams& p, cudaStream_t s) {
   const int dh = (int)(p.ldo / p.H);
   RETR_CHECK(dh == 32 || dh == 64, "head dim must be 32 or 64 (ldo = n_heads * head_dim)");
   if (p.out && std::is_same<T, bf16>::value && getenv("RETR_ATTN_SIMT") == nullptr) {
-    flash_attention_bf16(p, dh, s);                    // tensor-core path (attention_mma.cu)
+    // RETR_ATTENTION_TC=1: the tcgen05 / TMEM kernel (attention_tc.cu); default: the warp-level mma.sync flash kernel,
+    // which is faster at head dim 32 (measured)
+    const char* tce = getenv("RETR_ATTENTION_TC");
+    const bool tc = tce && atoi(tce) != 0;
+    if (tc && attention_tc_supported(p, dh)) attention_tc_bf16(p, s);
+    else flash_attention_bf16(p, dh, s);               // tensor-core path (attention_mma.cu)
   } else if (p.out) {
     if (dh == 32) attention_kernel<T, 32><<<grid, QT, 0, s>>>(p);
     else attention_kernel<T, 64><<<grid, QT, 0, s>>>(p);

@@ -56,6 +56,8 @@ struct AttnParams {
 };
 template <typename T> void attention(const AttnParams& p, cudaStream_t s);
 void flash_attention_bf16(const AttnParams& p, int dh, cudaStream_t s);   // attention_mma.cu
+bool attention_tc_supported(const AttnParams& p, int dh);                  // attention_tc.cu: tcgen05 / TMEM, head dim 32
+void attention_tc_bf16(const AttnParams& p, cudaStream_t s);
 
 // ---- greedy decode (decode_ops.cu) --------------------------------------------------------------
 // Single-query attention over head-major K/V caches ([B][H][cache_rows][dh] each), one CTA per (b, head).

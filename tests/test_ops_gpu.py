@@ -380,3 +380,34 @@ def test_decode_cross_attention_compacted_equals_masked():
     s = (qh @ K.double().transpose(-1, -2)).masked_fill(pad[:, None, None, :], float("-inf"))
     ref = (s.softmax(-1) @ V.double()).reshape(M, d).float()
     assert bool(((out.float() - ref).abs() <= ref.abs() * 2 ** -8 + 2e-3).all())
+
+
+@pytest.mark.parametrize("Lq,Lk,causal", [(397, 397, 0), (128, 128, 1), (130, 70, 0), (1, 397, 0)])
+def test_attention_tcgen05_kernel(Lq, Lk, causal, monkeypatch):
+    """attention_tc.cu (tcgen05.mma + TMEM, two heads per CTA as block-diagonal MMAs, head dim 32) behind
+    RETR_ATTENTION_TC=1, against the float64 reference and the default mma.sync flash kernel on the same operands."""
+    native, lib = _lib()
+    torch.manual_seed(Lq * 3 + Lk)
+    dev, B, H, d = "cuda", 3, 8, 256
+    q = torch.randn(B, Lq, 3 * d, device=dev).to(torch.bfloat16)       # q | k | v side by side, pitch 3d (encoder layout)
+    kv = torch.randn(B, Lk, 3 * d, device=dev).to(torch.bfloat16)
+    key_pad = torch.zeros(B, Lk, dtype=torch.uint8, device=dev)
+    key_pad[0, Lk // 2:] = 1
+    if Lk > 9:
+        key_pad[2, 5:9] = 1
+    if causal:
+        key_pad[:] = 0
+        key_pad[0, Lk - 10:] = 1
+    outs = []
+    for flag in ("1", "0"):
+        monkeypatch.setenv("RETR_ATTENTION_TC", flag)
+        out = torch.zeros(B, Lq, d, device=dev, dtype=torch.bfloat16)
+        native.check(lib.retr_op_attention(BF16, q.data_ptr(), kv[:, :, d:].data_ptr(), kv[:, :, 2 * d:].data_ptr(),
+                                           out.data_ptr(), B, Lq, Lk, H, 3 * d, 3 * d, 3 * d, d, key_pad.data_ptr(), causal,
+                                           None, native.stream_ptr()))
+        torch.cuda.synchronize()
+        outs.append(out.float())
+    ref, _ = ref_attention(q[:, :, :d], kv[:, :, d:2 * d], kv[:, :, 2 * d:], H, key_pad, causal)
+    valid = ~torch.isnan(ref)
+    assert (outs[0][valid] - ref[valid]).abs().max().item() < 2e-2
+    assert (outs[1][valid] - ref[valid]).abs().max().item() < 2e-2
