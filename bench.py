@@ -11,8 +11,8 @@ weak scaling), timing is CUDA events bracketed by barrier + synchronize, max ove
 
 Keys of the JSON line (see the round brief): value = device-resident throughput; e2e = the same
 through the host-buffer C-ABI call (H2D of the samples and D2H of the ids inside the timed region);
-roofline = the dominant kernel (tcgen05 implicit-GEMM over the backbone phase) + the decode phase against
-HBM + the combined two-phase figure; parity = strict / teacher-forced agreement of the benchmarked
+roofline = the dominant kernel (decode_stack_kernel, one launch per greedy step, against HBM); roofline_backbone = the
+tcgen05 implicit-GEMM over the backbone phase against the tensor peak; roofline_combined = the two-phase figure; parity = strict / teacher-forced agreement of the benchmarked
 precision against the fp32 mode on a sub-batch; train_step = the data-parallel training step
 (BASELINE.json configs[3]) at the same N, the path's one real collective; cpu_baseline = the
 reference's own greedy loop (oracle/_ref when present, else the oracle port) on the host cores for a
@@ -107,10 +107,10 @@ def measured_peaks():
     return 1400.0, 6650.0, "fallback"
 
 
-def backbone_traffic_bytes_per_image():
-    """DRAM read+write bytes per image of the backbone pass from the committed ncu table — only while the kernels
-    it was measured on are the kernels in the tree (the table records a hash of the GEMM + schedule sources)."""
-    p = os.path.join(ROOT, "profiles", "backbone_dram_traffic.json")
+def ncu_traffic_table(name, key):
+    """A DRAM read+write figure from a committed ncu table — only while the kernels it was measured on are the kernels
+    in the tree (the table records a hash of the kernel sources)."""
+    p = os.path.join(ROOT, "profiles", name)
     if not os.path.exists(p):
         return None, "no committed ncu table"
     t = json.load(open(p))
@@ -120,7 +120,11 @@ def backbone_traffic_bytes_per_image():
             h.update(fh.read())
     if h.hexdigest()[:16] != t.get("sources_sha16"):
         return None, f"stale: {t.get('from')} was measured on other kernel sources"
-    return float(t["dram_bytes_per_image"]), t.get("from")
+    return float(t[key]), t.get("from")
+
+
+def backbone_traffic_bytes_per_image():
+    return ncu_traffic_table("backbone_dram_traffic.json", "dram_bytes_per_image")
 
 
 # ---- the reference's CPU path --------------------------------------------------------------------------------
@@ -463,6 +467,7 @@ def main():
         n_img = 2 * B
         achieved = wl["backbone_gflop_img"] * n_img / (bb_ms / 1000.0) / 1000.0 if bb_ms > 0 else 0.0
         traffic_img, traffic_src = backbone_traffic_bytes_per_image() if args.workload == "default" else (None, "n/a")
+        dec_traffic, dec_traffic_src = ncu_traffic_table("decode_stack_dram_traffic.json", "dram_bytes_per_launch")
         decode_mb = wl["kv_mb"] + wl["weights_mb"] * (MAX_LEN - 1) / B
         dec_gbs = decode_mb * B / 1000.0 / (ph["decode"] / 1000.0) if ph["decode"] > 0 else 0.0
         ideal_ms = (wl["encode_gflop"] * B / (tf_peak * 1000.0) + decode_mb * B / (hbm_peak * 1000.0)) * 1000.0
@@ -486,16 +491,25 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks,
             "phases_ms_per_step": ph,
-            "roofline": {"bound": "tensor", "kernel": "gemm_tcgen05_kernel over the backbone phase (conv launches of "
-                         "2B images, incl. stem + maxpool)", "achieved": achieved, "peak": tf_peak,
-                         "unit": "TFLOP/s", "frac": achieved / tf_peak if tf_peak else None,
-                         "traffic": traffic_img * n_img if traffic_img and args.precision == "bf16" else None,
-                         "traffic_note": f"DRAM read+write bytes of the backbone phase per step, ncu: {traffic_src}",
-                         "peak_source": f"{which} bf16 sustained"},
-            "roofline_decode": {"bound": "hbm", "achieved": dec_gbs, "peak": hbm_peak, "unit": "GB/s",
-                                "frac": dec_gbs / hbm_peak,
-                                "bytes_note": f"algorithmic {decode_mb:.0f} MB/expression: all {127} steps x (cross K/V "
-                                              "of every key + self K/V) + decoder/head weights once per step per batch"},
+            # the dominant kernel by time: one decode_stack_kernel launch per greedy step (56 % of the step)
+            "roofline": {"bound": "hbm", "kernel": ("decode_stack_kernel: the whole decoder stack of one greedy step per "
+                         "launch; launch duration = decode phase / steps, i.e. including the vocabulary GEMM+argmax and "
+                         "greedy_update of the step (CUDA events on the launching stream around the captured loop)")
+                         if args.workload == "default" else "decode phase (d = 512: the launch-chain decode step)",
+                         "achieved": dec_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": dec_gbs / hbm_peak,
+                         "traffic": dec_traffic * B / 256.0 if dec_traffic and args.workload == "default" else None,
+                         "bytes_per_launch": decode_mb * 1e6 * B / (MAX_LEN - 1),
+                         "bytes_note": f"algorithmic {decode_mb:.0f} MB/expression over {MAX_LEN - 1} launches (SURVEY "
+                                       "§8d: cross K/V of EVERY key + self K/V + decoder/head weights once per step per "
+                                       "batch); measured DRAM traffic is lower because padded keys are dropped from "
+                                       f"the caches; traffic: {dec_traffic_src}",
+                         "peak_source": f"{which} HBM copy bandwidth"},
+            "roofline_backbone": {"bound": "tensor", "kernel": "gemm_tcgen05_kernel over the backbone phase (conv launches "
+                                  "of 2B images, incl. stem + maxpool)", "achieved": achieved, "peak": tf_peak,
+                                  "unit": "TFLOP/s", "frac": achieved / tf_peak if tf_peak else None,
+                                  "traffic": traffic_img * n_img if traffic_img and args.precision == "bf16" else None,
+                                  "traffic_note": f"DRAM read+write bytes of the backbone phase per step, ncu: {traffic_src}",
+                                  "peak_source": f"{which} bf16 sustained"},
             "roofline_combined": {"ideal_ms": ideal_ms, "measured_ms": ms / args.steps,
                                   "frac": ideal_ms / (ms / args.steps),
                                   "note": "SURVEY §8d: encode FLOPs / sustained bf16 peak + decode bytes / HBM peak, "
