@@ -527,3 +527,19 @@ def test_basic_block_backbones(arch):
     m16.train()
     with pytest.raises(NotImplementedError):
         m16(*samples_of(kind, enc_in), caps[:, :-1], cm[:, :-1])
+
+
+def test_decode_stack_more_clusters_than_fit_at_once():
+    """B = 300 needs 38 clusters of the one-kernel decode step, more than the 33 that are co-resident: the launch runs
+    in waves (and the last cluster is ragged).  Samples are independent, so the first and the last eight rows must
+    decode to exactly the ids they get as batches of their own."""
+    kind, B = "CaptionGlobalLoc", 300
+    model, sd, cfg = gpu_model(kind, "bf16", calibrated=True)
+    model.max_batch = B
+    _, enc_in = synthetic_samples(kind, B, shard=33, train=False)
+    with torch.no_grad():
+        ids = decode.greedy(samples_of(kind, enc_in), model, max_len=128, device="cuda", bos_token=101, eos_token=102)
+        for lo, hi in ((0, 8), (B - 8, B)):
+            sub = tuple(None if t is None else t[lo:hi] for t in enc_in)
+            alone = decode.greedy(samples_of(kind, sub), model, max_len=128, device="cuda", bos_token=101, eos_token=102)
+            assert torch.equal(ids[lo:hi], alone), (lo, hi)
