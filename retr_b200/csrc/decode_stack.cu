@@ -158,13 +158,26 @@ template <int NT> __device__ __forceinline__ void mma_w(const AFrag& a, const WF
     }
     acc[0][0] += alt[0]; acc[0][1] += alt[1];
   } else {
+    // two accumulators per tile (even / odd k blocks): 2 NT independent chains of 8 dependent HMMAs instead of NT of 16 —
+    // at M = 16 the GEMM phases are bound by the HMMA issue-to-result latency of those chains, not by throughput
+    float alt[NT][4];
 #pragma unroll
-    for (int kb = 0; kb < 8; ++kb) {
+    for (int j = 0; j < NT; ++j) alt[j][0] = alt[j][1] = alt[j][2] = alt[j][3] = 0.f;
 #pragma unroll
-      for (int j = 0; j < NT; ++j) mma16816(acc[j], a.x[kb].x, 0u, a.x[kb].y, 0u, f.w[j][kb].x, f.w[j][kb].y);
+    for (int kb = 0; kb < 8; kb += 2) {
 #pragma unroll
-      for (int j = 0; j < NT; ++j) mma16816(acc[j], a.x[kb].z, 0u, a.x[kb].w, 0u, f.w[j][kb].z, f.w[j][kb].w);
+      for (int j = 0; j < NT; ++j) {
+        mma16816(acc[j], a.x[kb].x, 0u, a.x[kb].y, 0u, f.w[j][kb].x, f.w[j][kb].y);
+        mma16816(alt[j], a.x[kb + 1].x, 0u, a.x[kb + 1].y, 0u, f.w[j][kb + 1].x, f.w[j][kb + 1].y);
+      }
+#pragma unroll
+      for (int j = 0; j < NT; ++j) {
+        mma16816(acc[j], a.x[kb].z, 0u, a.x[kb].w, 0u, f.w[j][kb].z, f.w[j][kb].w);
+        mma16816(alt[j], a.x[kb + 1].z, 0u, a.x[kb + 1].w, 0u, f.w[j][kb + 1].z, f.w[j][kb + 1].w);
+      }
     }
+#pragma unroll
+    for (int j = 0; j < NT; ++j) { acc[j][0] += alt[j][0]; acc[j][1] += alt[j][1]; }
   }
 }
 template <int NT> __device__ __forceinline__ void zero_acc(float (&acc)[NT][4]) {
