@@ -59,6 +59,8 @@ template <typename T> struct TConv {
 template <typename T> struct TBlock {
   TConv<T> c1, c2, c3, ds;
   bool has_ds = false, trainable = false;
+  bool basic = false;     // torchvision BasicBlock (ResNet-18/34): c1 = 3x3 (stride), c2 = 3x3, no c3
+  int out_channels() const { return basic ? c2.cout : c3.cout; }
   int Hin = 0, Hout = 0;
   T *o1 = nullptr, *o2 = nullptr, *idn = nullptr, *y = nullptr;     // kept activations (trainable blocks)
 };
@@ -440,9 +442,16 @@ void TrainerT<T>::finalize() {
       TBlock<T> b;
       // conv1 + layer1 frozen (models/backbone.py:58-60); a parameter with no bound grad is frozen too
       b.trainable = st >= 1 && P(p + "conv1.weight").g != nullptr;
-      b.c1 = conv(p + "conv1.weight", p + "bn1", 1, 0, 1, b.trainable);
-      b.c2 = conv(p + "conv2.weight", p + "bn2", s_, dl, dl, b.trainable);
-      b.c3 = conv(p + "conv3.weight", p + "bn3", 1, 0, 1, b.trainable);
+      b.basic = params_.count(p + "conv3.weight") == 0;
+      if (b.basic) {          // torchvision/models/resnet.py:59-105
+        RETR_CHECK(dl == 1, "BasicBlock backbones (ResNet-18/34) need dilation = False");
+        b.c1 = conv(p + "conv1.weight", p + "bn1", s_, 1, 1, b.trainable);
+        b.c2 = conv(p + "conv2.weight", p + "bn2", 1, 1, 1, b.trainable);
+      } else {
+        b.c1 = conv(p + "conv1.weight", p + "bn1", 1, 0, 1, b.trainable);
+        b.c2 = conv(p + "conv2.weight", p + "bn2", s_, dl, dl, b.trainable);
+        b.c3 = conv(p + "conv3.weight", p + "bn3", 1, 0, 1, b.trainable);
+      }
       b.has_ds = params_.count(p + "downsample.0.weight") > 0;
       if (b.has_ds) b.ds = conv(p + "downsample.0.weight", p + "downsample.1", s_, 0, 1, b.trainable);
       b.Hin = Hc;
@@ -451,22 +460,23 @@ void TrainerT<T>::finalize() {
       if (b.trainable) {
         if (!train_backbone_) first_trainable_ = (int)blocks_.size();
         train_backbone_ = true;
-        const int64_t Min = NI * b.Hin * b.Hin, Mout = NI * b.Hout * b.Hout;
-        b.o1 = alloc<T>(Min * b.c1.cout);
-        b.o2 = alloc<T>(Mout * b.c2.cout);
-        if (b.has_ds) b.idn = alloc<T>(Mout * b.c3.cout);
-        b.y = alloc<T>(Mout * b.c3.cout);
-        maxact = std::max({maxact, Min * b.c1.cout, Mout * b.c3.cout, Min * b.c1.cin});
-        max_col = std::max(max_col, rup(Mout, 16) * b.c2.kpad);
-        max_tA = std::max({max_tA, rup(Mout, 16) * b.c3.cout, rup(Min, 16) * b.c1.cout});
-        max_tB = std::max({max_tB, rup(Min, 16) * b.c1.cin, rup(Mout, 16) * b.c2.kpad, rup(Mout, 16) * b.c3.cin});
-        max_dwk = std::max(max_dwk, (int64_t)b.c2.cout * b.c2.kpad);
+        const int64_t Min = NI * b.Hin * b.Hin, Mout = NI * b.Hout * b.Hout, co = b.out_channels();
+        const int64_t M1 = b.basic ? Mout : Min;                     // rows of conv1's output
+        b.o1 = alloc<T>(M1 * b.c1.cout);
+        if (!b.basic) b.o2 = alloc<T>(Mout * b.c2.cout);
+        if (b.has_ds) b.idn = alloc<T>(Mout * co);
+        b.y = alloc<T>(Mout * co);
+        maxact = std::max({maxact, M1 * b.c1.cout, Mout * co, Min * b.c1.cin});
+        max_col = std::max(max_col, rup(Mout, 16) * (b.basic ? std::max(b.c1.kpad, b.c2.kpad) : b.c2.kpad));
+        max_tA = std::max({max_tA, rup(Mout, 16) * co, rup(M1, 16) * b.c1.cout});
+        max_tB = std::max({max_tB, rup(Min, 16) * b.c1.cin, rup(Mout, 16) * b.c2.kpad, rup(Mout, 16) * (b.basic ? b.c1.kpad : b.c3.cin)});
+        max_dwk = std::max({max_dwk, (int64_t)b.c2.cout * b.c2.kpad, b.basic ? (int64_t)b.c1.cout * b.c1.kpad : (int64_t)0});
       }
       blocks_.push_back(b);
     }
   }
   RETR_CHECK(Hc == grid_hw, "backbone output side mismatch");
-  const int64_t g2 = (int64_t)grid_hw * grid_hw, cfeat = blocks_.back().c3.cout;
+  const int64_t g2 = (int64_t)grid_hw * grid_hw, cfeat = blocks_.back().out_channels();
   // frozen-part buffers (ping-pong, nothing kept)
   const int64_t h1 = (desc.image_size + 6 - 7) / 2 + 1, hp = (h1 + 2 - 3) / 2 + 1;
   im2col_ = alloc<T>(NI * h1 * h1 * stem_.kpad);
@@ -603,7 +613,8 @@ void TrainerT<T>::refresh_all(cudaStream_t s) {
   if (!frozen_ready_) refresh(stem_, s);
   for (auto& b : blocks_) {
     if (!b.trainable && frozen_ready_) continue;       // frozen filters are repacked once
-    refresh(b.c1, s); refresh(b.c2, s); refresh(b.c3, s);
+    refresh(b.c1, s); refresh(b.c2, s);
+    if (!b.basic) refresh(b.c3, s);
     if (b.has_ds) refresh(b.ds, s);
   }
   frozen_ready_ = true;
@@ -720,13 +731,17 @@ void TrainerT<T>::forward_impl(int B, const float* t_img, const uint8_t* t_mask,
     T* y = b.trainable ? b.y : ((bi + 1 == blocks_.size()) ? feat_ : fz_[flip]);
     if (!b.trainable && train_backbone_ && (int)bi + 1 == first_trainable_) y = block_in_;
     run_conv(b.c1, x, NI, Hc, Hc, o1, nullptr, 1, &h1, s);
-    run_conv(b.c2, o1, NI, h1, h1, o2, nullptr, 1, &h2, s);
     const T* identity = x;
     if (b.has_ds) {
       run_conv(b.ds, x, NI, Hc, Hc, idn, nullptr, 0, &hd, s);
       identity = idn;
     }
-    run_conv(b.c3, o2, NI, h2, h2, y, identity, 2, &h3, s);
+    if (b.basic) {
+      run_conv(b.c2, o1, NI, h1, h1, y, identity, 2, &h3, s);
+    } else {
+      run_conv(b.c2, o1, NI, h1, h1, o2, nullptr, 1, &h2, s);
+      run_conv(b.c3, o2, NI, h2, h2, y, identity, 2, &h3, s);
+    }
     x = y;
     flip ^= 1;
     Hc = h3;
@@ -735,7 +750,7 @@ void TrainerT<T>::forward_impl(int B, const float* t_img, const uint8_t* t_mask,
   if (blocks_.back().trainable) feat_ = blocks_.back().y;
 
   // ---- tokens (models/caption.py:119-147) ----
-  const int64_t cfeat = blocks_.back().c3.cout;
+  const int64_t cfeat = blocks_.back().out_channels();
   const int off_loc = (int)g2, off_g = (int)g2 + n_loc_tok;
   float* x0 = enc_[0].xa;
   for (int set = 0; set < desc.n_images; ++set) {
@@ -1048,7 +1063,7 @@ void TrainerT<T>::backward_impl(cudaStream_t s) {
     loc_tokens_bwd(dX_, loc_, g_loc_w_, g_loc_b_, B, desc.n_loc, desc.loc_in_dim == 1, d, S, off_loc, s);
   gather_tok_kernel<T><<<ewb(NI * g2 * d), 256, 0, s>>>(dX_, dtok_, B, (int)g2, S, off_g, desc.n_images, d);
   LAUNCH_OK();
-  const int64_t cfeat = blocks_.back().c3.cout, Mt = NI * g2;
+  const int64_t cfeat = blocks_.back().out_channels(), Mt = NI * g2;
   T* dfeat = train_backbone_ ? bb_[0] : nullptr;
   lin_bwd(input_proj_, dtok_, d, feat_, cfeat, Mt, dfeat, false, input_proj_.gb, s);
   bucket_ready(2, s);
@@ -1063,18 +1078,24 @@ void TrainerT<T>::backward_impl(cudaStream_t s) {
       const T* x_in = bi == first_trainable_ ? block_in_ : blocks_[bi - 1].y;
       const int64_t Mo = NI * b.Hout * b.Hout, Mi = NI * b.Hin * b.Hin;
       T *g3s = bb_[2], *g3 = bb_[3], *t2 = bb_[4], *t1 = bb_[5], *gid = bb_[6];
-      relu_bn_bwd<T>(dy, b.y, b.c3.scale, g3s, g3, Mo, b.c3.cout, s);
-      if (!conv_bwd(b.c3, g3s, b.o2, NI, b.Hout, b.Hout, t2, nullptr, true, s, b.o2, b.c2.scale))
-        relu_bn_bwd<T>(t2, b.o2, b.c2.scale, t2, nullptr, Mo, b.c2.cout, s);
-      if (!conv_bwd(b.c2, t2, b.o1, NI, b.Hin, b.Hout, t1, nullptr, true, s, b.o1, b.c1.scale))
-        relu_bn_bwd<T>(t1, b.o1, b.c1.scale, t1, nullptr, Mi, b.c1.cout, s);
+      const TConv<T>& last = b.basic ? b.c2 : b.c3;
+      relu_bn_bwd<T>(dy, b.y, last.scale, g3s, g3, Mo, last.cout, s);
+      if (b.basic) {
+        if (!conv_bwd(b.c2, g3s, b.o1, NI, b.Hout, b.Hout, t1, nullptr, true, s, b.o1, b.c1.scale))
+          relu_bn_bwd<T>(t1, b.o1, b.c1.scale, t1, nullptr, Mo, b.c1.cout, s);
+      } else {
+        if (!conv_bwd(b.c3, g3s, b.o2, NI, b.Hout, b.Hout, t2, nullptr, true, s, b.o2, b.c2.scale))
+          relu_bn_bwd<T>(t2, b.o2, b.c2.scale, t2, nullptr, Mo, b.c2.cout, s);
+        if (!conv_bwd(b.c2, t2, b.o1, NI, b.Hin, b.Hout, t1, nullptr, true, s, b.o1, b.c1.scale))
+          relu_bn_bwd<T>(t1, b.o1, b.c1.scale, t1, nullptr, Mi, b.c1.cout, s);
+      }
       const T* idgrad = g3;
       if (b.has_ds) {
         relu_bn_bwd<T>(g3, nullptr, b.ds.scale, g3s, nullptr, Mo, b.ds.cout, s);
         conv_bwd(b.ds, g3s, x_in, NI, b.Hin, b.Hout, gid, nullptr, need_dx, s);
         idgrad = gid;
       }
-      conv_bwd(b.c1, t1, x_in, NI, b.Hin, b.Hin, dxn, idgrad, need_dx, s);
+      conv_bwd(b.c1, t1, x_in, NI, b.Hin, b.basic ? b.Hout : b.Hin, dxn, idgrad, need_dx, s);
       std::swap(dy, dxn);
       // the first block of a stage is the last one the reverse loop visits: the stage's gradients are final
       int start = 0;

@@ -257,9 +257,6 @@ class Trainer:
         self.lib = native.lib()
         self.device, self.precision, self.max_batch, self.image_size = device, precision, int(max_batch), image_size
         d = model_desc(model, device, precision, self.max_batch, image_size)
-        if not RESNET_SPECS[model.backbone.arch][1]:
-            raise NotImplementedError("retr_b200 training implements the Bottleneck backbones (ResNet-50/101/152); "
-                                      "ResNet-18/34 run inference only")
         self.desc, self.T, self.V = d, d.max_pos, d.vocab
         sd = model.state_dict(keep_vars=True)
         self.names = [n for n, t in sd.items() if torch.is_floating_point(t)]

@@ -496,7 +496,7 @@ def test_decode_stack_kernel_consistent_with_teacher_forced(B, monkeypatch):
 def test_basic_block_backbones(arch):
     """ResNet-18/34 (BasicBlock, dilation=False: 512 channels, 7x7 = 49 tokens per image; models/backbone.py:86-93):
     fp32 logits vs the reference fixture (ResNet-18) and the oracle, greedy ids vs the oracle, the bf16 path within its
-    tolerance; the trainer refuses them loudly."""
+    tolerance (training: tests/test_train_gpu.py::test_fp32_grads_basic_block_backbone)."""
     kind = "CaptionGlobalLoc"
     model, sd, cfg = gpu_model(kind, "fp32", calibrated=False, backbone=arch, dilation=False)
     data, enc_in = synthetic_samples(kind, 2)
@@ -524,9 +524,6 @@ def test_basic_block_backbones(arch):
         ids16 = decode.greedy(samples_of(kind, enc2, "cpu"), m16, max_len=128, device="cuda", bos_token=101, eos_token=102)
     assert (l16 - ref).abs().max().item() <= BF16_LOGIT_TOL * ref.abs().max().item()
     assert ids16.shape == (3, 128)
-    m16.train()
-    with pytest.raises(NotImplementedError):
-        m16(*samples_of(kind, enc_in), caps[:, :-1], cm[:, :-1])
 
 
 def test_decode_stack_more_clusters_than_fit_at_once():

@@ -103,6 +103,28 @@ def test_fp32_grads_without_final_encoder_norm():
             assert err <= 2e-3, (n, na, err, cos)
 
 
+def test_fp32_grads_basic_block_backbone():
+    """ResNet-18 (BasicBlock, dilation=False): layer2-4 gradients through 3x3 (stride 2) + 3x3 blocks vs oracle autograd."""
+    kind = "CaptionGlobalLoc"
+    model, sd, cfg = train_model(kind, "fp32", backbone="ResNet18", dilation=False)
+    data, enc_in = synthetic_samples(kind, 2, shard=7)
+    ref_loss, ref = oracle_grads(model, sd, cfg, enc_in, data["caps"], data["cap_masks"])
+    loss, got = native_grads(model, enc_in, data["caps"], data["cap_masks"])
+    assert abs(loss - ref_loss) <= 2e-5 * abs(ref_loss), (loss, ref_loss)
+    assert any("backbone.body.layer2" in n for n in got)
+    gmax = max(r[1] for r in compare(ref, got))
+    for n, na, err, cos in compare(ref, got):
+        if na > 1e-6 * gmax:
+            assert err <= 2e-3, (n, na, err, cos)
+    m16, _, _ = train_model(kind, "bf16", backbone="ResNet18", dilation=False)
+    loss16, got16 = native_grads(m16, enc_in, data["caps"], data["cap_masks"])
+    assert abs(loss16 - ref_loss) <= 2e-3 * abs(ref_loss)
+    rows = compare(ref, got16)
+    num = sum((r[1] * r[2]) ** 2 for r in rows) ** 0.5
+    den = sum(r[1] ** 2 for r in rows) ** 0.5
+    assert num / den <= 6e-2, num / den
+
+
 def test_bf16_grads_close_to_oracle():
     kind = "CaptionGlobalLoc"
     model, sd, cfg = train_model(kind, "bf16")
