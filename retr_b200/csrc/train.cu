@@ -13,6 +13,7 @@
 // gradient and nothing below them is back-propagated.
 #include "train.h"
 #include "dp.h"
+#include "dropout.cuh"
 
 #include <algorithm>
 #include <map>
@@ -120,6 +121,23 @@ __global__ void cast_pos_kernel(const float* __restrict__ x, T* __restrict__ y, 
     y[i] = from_f<T>(v);
     y2[i] = from_f<T>(v + pos[((i / d) % period) * d + i % d]);
   }
+}
+// learned positions in train mode (models/position_encoding.py:38-63): the LayerNormed table is repeated per sample and
+// dropped out per element; backward sums the (masked) gradients of every use over the batch
+__global__ void pos_expand_kernel(const float* __restrict__ pos_ln, float* __restrict__ posD, int64_t n, int64_t sd,
+                                  DropCfg dc) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    posD[i] = pos_ln[i % sd] * drop_scale(dc, (uint64_t)i);
+}
+__global__ void pos_reduce_kernel(const float* __restrict__ dPos, float* __restrict__ out, int B, int64_t sd, DropCfg dc) {
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < sd; j += (int64_t)gridDim.x * blockDim.x) {
+    float acc = 0.f;
+    for (int b = 0; b < B; ++b) acc += dPos[b * sd + j] * drop_scale(dc, (uint64_t)(b * sd + j));
+    out[j] = acc;
+  }
+}
+__global__ void axpy_kernel(float* __restrict__ y, const float* __restrict__ x, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) y[i] += x[i];
 }
 inline unsigned ewb(int64_t n) { return (unsigned)std::min<int64_t>(cdiv(n, 256), 148 * 16); }
 
@@ -257,6 +275,15 @@ class TrainerT final : public TrainerBase {
   std::vector<TEnc<T>> enc_;
   std::vector<TDec<T>> dec_;
   TLin<T> mlp_[3];
+  // learned position table ('v3' / 'learned'): LN(pos_embed.weight[:S]) -> per-sample dropout (train mode)
+  bool learned_ = false;
+  const float *pos_w_ = nullptr, *pos_g_ = nullptr, *pos_b_ = nullptr;
+  float *g_pos_w_ = nullptr, *g_pos_g_ = nullptr, *g_pos_b_ = nullptr;
+  float *pos_ln_ = nullptr, *posD_ = nullptr, *dPos_ = nullptr, *dposln_ = nullptr;
+  // the reference hard-codes this dropout to 0.1 (build_position_encoding); it follows the step's dropout switch here
+  DropCfg pos_drop() const { DropCfg dc; dc.p = drop_p_ > 0.f ? 0.1f : 0.f; dc.seed = seed_; dc.site = 2; return dc; }
+  const float* pos_ptr() const { return learned_ ? posD_ : pe_; }
+  int pos_period(int64_t Me) const { return learned_ ? (int)Me : S; }
   const float *pe_ = nullptr, *e_word_ = nullptr, *e_pos_ = nullptr, *emb_g_ = nullptr, *emb_b_ = nullptr;
   float *g_e_word_ = nullptr, *g_e_pos_ = nullptr, *g_emb_g_ = nullptr, *g_emb_b_ = nullptr;
   const float *enc_ng_ = nullptr, *enc_nb_ = nullptr, *dec_ng_ = nullptr, *dec_nb_ = nullptr;
@@ -491,11 +518,19 @@ void TrainerT<T>::finalize() {
     loc_w_ = P("loc_proj.weight").p; loc_b_ = P("loc_proj.bias").p;
     g_loc_w_ = P("loc_proj.weight").g; g_loc_b_ = P("loc_proj.bias").g;
   }
-  RETR_CHECK(params_.count("transformer.positional_encoding.pe") > 0,
-             "the training path implements the sine position table only (position_embedding 'v2'/'sine'); the learned "
-             "variant is served for inference");
-  pe_ = P("transformer.positional_encoding.pe").p;
-  RETR_CHECK(P("transformer.positional_encoding.pe").shape[0] >= S, "sequence longer than the sine table");
+  if (params_.count("transformer.positional_encoding.pe")) {
+    pe_ = P("transformer.positional_encoding.pe").p;
+  } else {
+    const std::string pk = "transformer.positional_encoding.";
+    learned_ = true;
+    RETR_CHECK(P(pk + "pos_embed.weight").shape[0] >= S, "sequence longer than the learned position table");
+    pos_w_ = P(pk + "pos_embed.weight").p; g_pos_w_ = P(pk + "pos_embed.weight").g;
+    pos_g_ = P(pk + "LayerNorm.weight").p; g_pos_g_ = P(pk + "LayerNorm.weight").g;
+    pos_b_ = P(pk + "LayerNorm.bias").p; g_pos_b_ = P(pk + "LayerNorm.bias").g;
+    pos_ln_ = alloc<float>((int64_t)S * d); dposln_ = alloc<float>((int64_t)S * d);
+    posD_ = alloc<float>(B * S * d); dPos_ = alloc<float>(B * S * d);
+  }
+  if (!learned_) RETR_CHECK(P("transformer.positional_encoding.pe").shape[0] >= S, "sequence longer than the sine table");
   const std::string em = "transformer.embeddings.";
   e_word_ = P(em + "word_embeddings.weight").p; g_e_word_ = P(em + "word_embeddings.weight").g;
   e_pos_ = P(em + "position_embeddings.weight").p; g_e_pos_ = P(em + "position_embeddings.weight").g;
@@ -763,11 +798,16 @@ void TrainerT<T>::forward_impl(int B, const float* t_img, const uint8_t* t_mask,
   if (desc.loc_in_dim)
     loc_tokens(loc_, loc_w_, loc_b_, x0, tok_mask_, B, desc.n_loc, desc.loc_in_dim == 1, d, S, off_loc, s);
 
+  if (learned_) {
+    layernorm<float>(pos_w_, pos_g_, pos_b_, pos_ln_, S, d, 1e-5f, s);
+    pos_expand_kernel<<<ewb(Me * d), 256, 0, s>>>(pos_ln_, posD_, Me * d, (int64_t)S * d, pos_drop());
+    LAUNCH_OK();
+  }
   // ---- encoder (models/ConcatTransformer.py:171-194, transformer_modules.py:22-46,77-97) ----
   for (int l = 0; l < desc.enc_layers; ++l) {
     TEnc<T>& e = enc_[l];
     float* x_next = l + 1 < desc.enc_layers ? enc_[l + 1].xa : x_final_;
-    layernorm_pos<T>(e.xa, e.g1, e.b1, e.n1, e.n1p, pe_, S, Me, d, 1e-5f, s);
+    layernorm_pos<T>(e.xa, e.g1, e.b1, e.n1, e.n1p, pos_ptr(), pos_period(Me), Me, d, 1e-5f, s);
     gemmT<T>(lp(e.qk, e.n1p, d, Me, e.qkv, 3 * d), s);
     gemmT<T>(lp(e.v, e.n1, d, Me, e.qkv + 2 * d, 3 * d), s);
     attn_fwd(e.qkv, 3 * d, e.qkv + d, e.qkv + 2 * d, 3 * d, e.att, e.P, e.lse, S, S, tok_mask_, 0, 10 + 4 * l, s);
@@ -779,9 +819,9 @@ void TrainerT<T>::forward_impl(int B, const float* t_img, const uint8_t* t_mask,
     branch_out(e.ff2, e.h, Me, e.xb, x_next, drop(12 + 4 * l), s);
   }
   if (desc.pre_norm) {
-    layernorm_pos<T>(x_final_, enc_ng_, enc_nb_, memory_, memp_, pe_, S, Me, d, 1e-5f, s);
+    layernorm_pos<T>(x_final_, enc_ng_, enc_nb_, memory_, memp_, pos_ptr(), pos_period(Me), Me, d, 1e-5f, s);
   } else {                    // pre_norm=False: memory is the last layer's output as it is
-    cast_pos_kernel<T><<<ewb(Me * d), 256, 0, s>>>(x_final_, memory_, memp_, pe_, S, Me * d, d);
+    cast_pos_kernel<T><<<ewb(Me * d), 256, 0, s>>>(x_final_, memory_, memp_, pos_ptr(), pos_period(Me), Me * d, d);
     LAUNCH_OK();
   }
 
@@ -980,6 +1020,7 @@ void TrainerT<T>::backward_impl(cudaStream_t s) {
       if (kv.second.g) CUDA_OK(cudaMemsetAsync(kv.second.g, 0, kv.second.numel * 4, s));
   }
 
+  if (learned_) CUDA_OK(cudaMemsetAsync(dPos_, 0, Me * d * 4, s));
   // ---- head ----
   lin_bwd(mlp_[2], dlg_, Vp, m2_, mlp_[1].out, Md, dh_, false, mlp_[2].gb, s);          // dh_ = d m2 [Md,512]
   relu_bwd<T>(dh_, m2_, Md * mlp_[1].out, s);
@@ -1016,6 +1057,11 @@ void TrainerT<T>::backward_impl(cudaStream_t s) {
       p.A = dckv_; p.lda = 2 * d; p.W = e.c_k.wtT; p.M = Me; p.N = d; p.K = e.c_k.out_pad; p.C = dMem_; p.ldc = d;
       p.out_fp32 = true; p.residual = dMem_; p.ldr = d; p.res_fp32 = true;
       gemmT<T>(p, s);
+      if (learned_) {                                       // k = memory + pos: the same term is the gradient of the positions
+        GemmParams q = p;
+        q.C = dPos_; q.residual = dPos_;
+        gemmT<T>(q, s);
+      }
       p.A = dckv_ + d; p.W = e.c_v.wtT; p.K = e.c_v.out_pad;
       gemmT<T>(p, s);
     }
@@ -1054,7 +1100,14 @@ void TrainerT<T>::backward_impl(cudaStream_t s) {
     if (e.gin_b) colsum<T>(dqkv_, 3 * d, e.gin_b, Me, 3 * d, 0, s);
     lin_bwd(e.qk, dqkv_, 3 * d, e.n1p, d, Me, tmpf_, true, nullptr, s);
     lin_bwd(e.v, dqkv_ + 2 * d, 3 * d, e.n1, d, Me, tmpf2_, true, nullptr, s);
+    if (learned_) { axpy_kernel<<<ewb(Me * d), 256, 0, s>>>(dPos_, tmpf_, Me * d); LAUNCH_OK(); }
     layernorm_bwd(e.xa, e.g1, tmpf_, tmpf2_, dX_, 1, e.gg1, e.gb1, Me, d, 1e-5f, s);
+  }
+  if (learned_ && g_pos_w_) {
+    // sum the masked gradients over the batch, then back through LayerNorm(pos_embed.weight[:S])
+    pos_reduce_kernel<<<ewb((int64_t)S * d), 256, 0, s>>>(dPos_, dposln_, B, (int64_t)S * d, pos_drop());
+    LAUNCH_OK();
+    layernorm_bwd(pos_w_, pos_g_, dposln_, nullptr, g_pos_w_, 0, g_pos_g_, g_pos_b_, S, d, 1e-5f, s);
   }
 
   // ---- tokens: location projection, input_proj ----

@@ -125,6 +125,38 @@ def test_fp32_grads_basic_block_backbone():
     assert num / den <= 6e-2, num / den
 
 
+def test_fp32_grads_learned_positions():
+    """position_embedding='learned' in train mode (models/position_encoding.py:38-63): LN(pos_embed[:S]) feeds every
+    encoder q/k input and the cross-attention keys; gradients of the table and its LayerNorm vs oracle autograd
+    (dropout 0; the reference's hard-coded 0.1 dropout of the table follows the step's dropout switch here)."""
+    kind = "CaptionGlobalLoc"
+    model, sd, cfg = train_model(kind, "fp32", position_embedding="learned")
+    data, enc_in = synthetic_samples(kind, 2, shard=8)
+    ref_loss, ref = oracle_grads(model, sd, cfg, enc_in, data["caps"], data["cap_masks"])
+    loss, got = native_grads(model, enc_in, data["caps"], data["cap_masks"])
+    assert abs(loss - ref_loss) <= 2e-5 * abs(ref_loss), (loss, ref_loss)
+    rows = compare(ref, got)
+    assert any(n == "transformer.positional_encoding.pos_embed.weight" and na > 0 for n, na, _, _ in rows)
+    gmax = max(r[1] for r in rows)
+    for n, na, err, cos in rows:
+        if na > 1e-6 * gmax:
+            assert err <= 2e-3, (n, na, err, cos)
+    assert float(got["transformer.positional_encoding.pos_embed.weight"][397:].abs().max()) == 0.0     # rows >= S unused
+    # with dropout on, the per-sample table dropout is a pure function of the seed: two steps, same seed, same gradients
+    model.dropout_p = 0.1
+    s = samples_of(enc_in)
+    t, g, loc = model._split_samples(s)
+    inputs = model._train_inputs(t, g, loc, data["caps"][:, :-1].cuda(), data["cap_masks"][:, :-1].cuda())
+    tr = model.trainer(2)
+    outs = []
+    for seed in (5, 5, 6):
+        tr.loss_and_grads(*inputs, data["caps"][:, 1:].cuda(), dropout_p=0.1, seed=seed)
+        torch.cuda.synchronize()
+        outs.append(tr.grads["transformer.positional_encoding.pos_embed.weight"].clone())
+    assert (outs[0] - outs[1]).abs().max().item() <= 1e-6 * outs[0].abs().max().item()
+    assert (outs[0] - outs[2]).abs().max().item() > 1e-3 * outs[0].abs().max().item()
+
+
 def test_bf16_grads_close_to_oracle():
     kind = "CaptionGlobalLoc"
     model, sd, cfg = train_model(kind, "bf16")
