@@ -22,7 +22,7 @@ namespace {
 constexpr int TQ = 128;                  // queries per CTA = TMEM lanes
 constexpr int TK = 64;                   // keys per head per chunk
 constexpr int TILE = 128 * 128;          // bytes of one 128-row x 128-byte tile
-constexpr int TC_SMEM = 7 * TILE + 1024; // Q, K x2, V x2, P (2 k-blocks) + alignment slack
+constexpr int TC_SMEM = 7 * TILE + 24 + 128 + 8;   // Q, K x2, V x2, P (2 k-blocks) + barriers: 2 CTAs per SM need <= 113 KB each
 
 // kind::f16 instruction descriptor: bf16 x bf16 -> fp32, A K-major, B MN-major (bit 16)
 __host__ __device__ constexpr uint32_t idesc_bf16_f32_bmn(int m, int n) {
@@ -74,12 +74,15 @@ __device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&r
 // when the running maximum has grown by more than 8 (log2 units), so P <= 256 and the usual per-chunk read-back of O
 // disappears — nothing waits for a P.V MMA except the P buffer's reuse one chunk later.
 __global__ void __launch_bounds__(256, 2) attention_tc_kernel(const AttnParams p) {
-  extern __shared__ uint8_t tc_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tc_raw) + 1023) & ~uintptr_t(1023));
+  // no static shared memory: the dynamic region then starts at the CTA's (1 KB aligned) shared-memory base, which the
+  // 128B-swizzled tiles need, without spending a kilobyte of slack that would cost the second CTA per SM
+  extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t Qs = ptx::smem_u32(smem), Ks0 = Qs + TILE, Vs0 = Ks0 + 2 * TILE, Ps = Vs0 + 2 * TILE;   // K, V x2; P: 2 k-blocks
-  __shared__ __align__(8) uint64_t bar_qk, bar_pv;
-  __shared__ uint32_t tmem_holder;
-  __shared__ uint32_t dead_w[2];
+  uint64_t& bar_qk = *reinterpret_cast<uint64_t*>(smem + 7 * TILE);
+  uint64_t& bar_pv = *reinterpret_cast<uint64_t*>(smem + 7 * TILE + 8);
+  uint32_t& tmem_holder = *reinterpret_cast<uint32_t*>(smem + 7 * TILE + 16);
+  uint32_t* dead_w = reinterpret_cast<uint32_t*>(smem + 7 * TILE + 24);      // one bit per key, 32 keys per word (<= 1024 keys)
+  if ((Qs & 1023u) != 0) __trap();
   const int b = blockIdx.z, hp = blockIdx.y, q0 = blockIdx.x * TQ, ha = 2 * hp;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int row = tid & 127, h = tid >> 7;                   // this thread's query row and head (0 = a, 1 = b)
@@ -99,6 +102,12 @@ __global__ void __launch_bounds__(256, 2) attention_tc_kernel(const AttnParams p
   fill_blockdiag(Ks0, kg, p.ldk, 0, k_end, ha, tid);
   fill_blockdiag(Vs0, vg, p.ldv, 0, k_end, ha, tid);
   asm volatile("cp.async.commit_group;" ::: "memory");
+  for (int w0 = warp; w0 * 32 < n_chunks * TK; w0 += 8) {    // padding / tail bits of every key, once
+    const int key = w0 * 32 + lane;
+    const bool dead = key >= k_end || (p.key_pad && p.key_pad[(int64_t)b * p.Lk + key]);
+    const unsigned w = __ballot_sync(0xffffffffu, dead);
+    if (lane == 0) dead_w[w0] = w;
+  }
   ptx::tc_fence_before_sync();
   __syncthreads();
   ptx::tc_fence_after_sync();
@@ -114,12 +123,6 @@ __global__ void __launch_bounds__(256, 2) attention_tc_kernel(const AttnParams p
   for (int c = 0; c < n_chunks; ++c) {
     const int k0 = c * TK;
     const uint32_t Ks = Ks0 + (c & 1) * TILE, Vs = Vs0 + (c & 1) * TILE;
-    if (tid < 64) {                                          // padding / tail bits of this chunk's 64 keys
-      const int key = k0 + tid;
-      const bool dead = key >= k_end || (p.key_pad && p.key_pad[(int64_t)b * p.Lk + key]);
-      const unsigned w = __ballot_sync(0xffffffffu, dead);
-      if (lane == 0) dead_w[warp] = w;
-    }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     ptx::fence_proxy_async_smem();
     ptx::tc_fence_before_sync();
@@ -141,7 +144,7 @@ __global__ void __launch_bounds__(256, 2) attention_tc_kernel(const AttnParams p
     ptx::tmem_ld_32x32(t_S, r0);
     ptx::tmem_ld_32x32(t_S + 32, r1);
     ptx::tmem_ld_wait();
-    const uint32_t d0 = dead_w[0], d1 = dead_w[1];
+    const uint32_t d0 = dead_w[2 * c], d1 = dead_w[2 * c + 1];
     float s[64], mx = -INFINITY;
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
@@ -240,7 +243,7 @@ __global__ void __launch_bounds__(256, 2) attention_tc_kernel(const AttnParams p
 }  // namespace
 
 bool attention_tc_supported(const AttnParams& p, int dh) {
-  return dh == 32 && p.H % 2 == 0 && p.out && p.ldq % 8 == 0 && p.ldk % 8 == 0 && p.ldv % 8 == 0 && p.ldo % 8 == 0;
+  return dh == 32 && p.H % 2 == 0 && p.out && p.Lk <= 1024 && p.ldq % 8 == 0 && p.ldk % 8 == 0 && p.ldv % 8 == 0 && p.ldo % 8 == 0;
 }
 
 void attention_tc_bf16(const AttnParams& p, cudaStream_t s) {
