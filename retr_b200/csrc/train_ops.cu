@@ -388,6 +388,83 @@ __global__ void layernorm_bwd_kernel(const float* __restrict__ x, const float* _
   }
 }
 
+// d % 128 == 0: one float4 per lane per 128 columns (four times fewer load / store instructions per row, and the
+// rows of a warp's loop are independent, so two rows are in flight per iteration)
+template <int NV>
+__global__ void __launch_bounds__(256)
+layernorm_bwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ dy1,
+                         const float* __restrict__ dy2, float* __restrict__ dx, int accumulate_dx,
+                         float* __restrict__ dgamma, float* __restrict__ dbeta, int64_t rows, int d, float eps) {
+  extern __shared__ float ln_red[];          // [2][d] block partial sums of dgamma / dbeta
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  for (int i = threadIdx.x; i < 2 * d; i += blockDim.x) ln_red[i] = 0.f;
+  __syncthreads();
+  float4 ga[NV], ag[NV], ab[NV];
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    ga[j] = __ldg(reinterpret_cast<const float4*>(gamma + j * 128 + lane * 4));
+    ag[j] = ab[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  const float inv_d = 1.f / d;
+  for (int64_t row = (int64_t)blockIdx.x * nwarp + warp; row < rows; row += (int64_t)gridDim.x * nwarp) {
+    float4 v[NV], g[NV], old[NV];
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int64_t o = row * d + j * 128 + lane * 4;
+      v[j] = *reinterpret_cast<const float4*>(x + o);
+      g[j] = *reinterpret_cast<const float4*>(dy1 + o);
+      if (dy2) {
+        const float4 t = *reinterpret_cast<const float4*>(dy2 + o);
+        g[j].x += t.x; g[j].y += t.y; g[j].z += t.z; g[j].w += t.w;
+      }
+      if (accumulate_dx) old[j] = *reinterpret_cast<const float4*>(dx + o);
+      s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
+    }
+    const float mean = warp_sum(s) * inv_d;
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      v[j].x -= mean; v[j].y -= mean; v[j].z -= mean; v[j].w -= mean;
+      q = fmaf(v[j].x, v[j].x, q); q = fmaf(v[j].y, v[j].y, q); q = fmaf(v[j].z, v[j].z, q); q = fmaf(v[j].w, v[j].w, q);
+    }
+    const float rstd = rsqrtf(warp_sum(q) * inv_d + eps);
+    float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      v[j].x *= rstd; v[j].y *= rstd; v[j].z *= rstd; v[j].w *= rstd;                 // x_hat
+      ag[j].x = fmaf(g[j].x, v[j].x, ag[j].x); ag[j].y = fmaf(g[j].y, v[j].y, ag[j].y);
+      ag[j].z = fmaf(g[j].z, v[j].z, ag[j].z); ag[j].w = fmaf(g[j].w, v[j].w, ag[j].w);
+      ab[j].x += g[j].x; ab[j].y += g[j].y; ab[j].z += g[j].z; ab[j].w += g[j].w;
+      g[j].x *= ga[j].x; g[j].y *= ga[j].y; g[j].z *= ga[j].z; g[j].w *= ga[j].w;
+      c1 += (g[j].x + g[j].y) + (g[j].z + g[j].w);
+      c2 = fmaf(g[j].x, v[j].x, c2); c2 = fmaf(g[j].y, v[j].y, c2); c2 = fmaf(g[j].z, v[j].z, c2); c2 = fmaf(g[j].w, v[j].w, c2);
+    }
+    c1 = warp_sum(c1) * inv_d;
+    c2 = warp_sum(c2) * inv_d;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      float4 r;
+      r.x = rstd * (g[j].x - c1 - v[j].x * c2); r.y = rstd * (g[j].y - c1 - v[j].y * c2);
+      r.z = rstd * (g[j].z - c1 - v[j].z * c2); r.w = rstd * (g[j].w - c1 - v[j].w * c2);
+      if (accumulate_dx) { r.x += old[j].x; r.y += old[j].y; r.z += old[j].z; r.w += old[j].w; }
+      *reinterpret_cast<float4*>(dx + row * d + j * 128 + lane * 4) = r;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    float* a = &ln_red[j * 128 + lane * 4];
+    atomicAdd(a, ag[j].x); atomicAdd(a + 1, ag[j].y); atomicAdd(a + 2, ag[j].z); atomicAdd(a + 3, ag[j].w);
+    float* bb = &ln_red[d + j * 128 + lane * 4];
+    atomicAdd(bb, ab[j].x); atomicAdd(bb + 1, ab[j].y); atomicAdd(bb + 2, ab[j].z); atomicAdd(bb + 3, ab[j].w);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < d; i += blockDim.x) {
+    if (dgamma) atomicAdd(dgamma + i, ln_red[i]);
+    if (dbeta) atomicAdd(dbeta + i, ln_red[d + i]);
+  }
+}
+
 // ---- attention with stored probabilities ---------------------------------------------------------------------
 constexpr int AT_WARPS = 8, AT_ROWS = 64;     // query rows per CTA
 
@@ -880,8 +957,17 @@ template void layernorm_pos<bf16>(const float*, const float*, const float*, bf16
 void layernorm_bwd(const float* x, const float* gamma, const float* dy1, const float* dy2, float* dx, int accumulate_dx,
                    float* dgamma, float* dbeta, int64_t rows, int d, float eps, cudaStream_t s) {
   RETR_CHECK(d % 32 == 0 && d <= 32 * LN_MAX_PER, "layernorm_bwd: d must be a multiple of 32, at most 1024");
-  const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(rows, 8), 148 * 4);
   const size_t sm = (size_t)2 * d * 4;
+  const bool aligned = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy1) | reinterpret_cast<uintptr_t>(dy2) |
+                         reinterpret_cast<uintptr_t>(dx)) & 15) == 0;
+  if (aligned && (d == 256 || d == 512) && getenv("RETR_LN_BWD_SCALAR") == nullptr) {
+    const unsigned vb = (unsigned)std::min<int64_t>(cdiv(rows, 8), 148 * 8);
+    if (d == 256) layernorm_bwd_vec_kernel<2><<<vb, 256, sm, s>>>(x, gamma, dy1, dy2, dx, accumulate_dx, dgamma, dbeta, rows, d, eps);
+    else layernorm_bwd_vec_kernel<4><<<vb, 256, sm, s>>>(x, gamma, dy1, dy2, dx, accumulate_dx, dgamma, dbeta, rows, d, eps);
+    LAUNCH_OK();
+    return;
+  }
+  const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(rows, 8), 148 * 4);
   if (d <= 256) layernorm_bwd_kernel<8><<<blocks, 256, sm, s>>>(x, gamma, dy1, dy2, dx, accumulate_dx, dgamma, dbeta, rows, d, eps);
   else if (d <= 512) layernorm_bwd_kernel<16><<<blocks, 256, sm, s>>>(x, gamma, dy1, dy2, dx, accumulate_dx, dgamma, dbeta, rows, d, eps);
   else layernorm_bwd_kernel<32><<<blocks, 256, sm, s>>>(x, gamma, dy1, dy2, dx, accumulate_dx, dgamma, dbeta, rows, d, eps);
