@@ -16,6 +16,8 @@ _PRECISION = {"fp32": native.FP32, "bf16": native.BF16}
 
 
 def _as(t, dtype, device):
+    if t.dtype == torch.bool and dtype == torch.uint8:
+        t = t.contiguous().view(torch.uint8)        # same bytes: no cast kernel for the padding masks
     return t.to(device=device, dtype=dtype).contiguous()
 
 
