@@ -102,25 +102,31 @@ __global__ void __launch_bounds__(256) stem_im2col_tiled_kernel(const float* __r
   __syncthreads();
   const int kchunks = kpad / 8;
   T* orow = out + ((int64_t)n * OH + oh) * OW * kpad;
-  for (int ch = tid; ch < OW * kchunks; ch += 256) {
-    const int ow = ch / kchunks, k0 = (ch - ow * kchunks) * 8;
-    float v[8];
+  // thread = (pixel lane, k chunk): the eight offsets of its chunk live in registers for the whole row (the first
+  // version looked them up in shared memory per element: 16 LDS per 16-byte chunk, shared-memory bound at 1.9 TB/s of
+  // output); consecutive threads still write consecutive 16-byte chunks
+  const int lanes = 256 / kchunks;                          // pixels in flight per pass (12 for kpad = 160)
+  if (tid < lanes * kchunks) {
+    const int kc = tid % kchunks, owl = tid / kchunks;
+    int off[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int off = lut[k0 + j];
-      v[j] = off >= 0 ? rows[off + ow * 2] : 0.f;
-    }
-    T* o = orow + (int64_t)ch * 8;
-    if (sizeof(T) == 2) {
-      uint4 t;
-      __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&t);
+    for (int j = 0; j < 8; ++j) off[j] = lut[kc * 8 + j];
+    for (int ow = owl; ow < OW; ow += lanes) {
+      float v[8];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
-      *reinterpret_cast<uint4*>(o) = t;
-    } else {
-      float* of = reinterpret_cast<float*>(o);
-      *reinterpret_cast<float4*>(of) = make_float4(v[0], v[1], v[2], v[3]);
-      *reinterpret_cast<float4*>(of + 4) = make_float4(v[4], v[5], v[6], v[7]);
+      for (int j = 0; j < 8; ++j) v[j] = off[j] >= 0 ? rows[off[j] + ow * 2] : 0.f;
+      T* o = orow + ((int64_t)ow * kchunks + kc) * 8;
+      if (sizeof(T) == 2) {
+        uint4 t;
+        __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&t);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+        *reinterpret_cast<uint4*>(o) = t;
+      } else {
+        float* of = reinterpret_cast<float*>(o);
+        *reinterpret_cast<float4*>(of) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(of + 4) = make_float4(v[4], v[5], v[6], v[7]);
+      }
     }
   }
 }
