@@ -173,6 +173,7 @@ class EngineT final : public EngineBase {
   cudaEvent_t gfork_ = nullptr;
   int cur_G_ = 1;                                    // row groups of the step being captured
   bool ffn_fused_ = false;                           // FFN sublayer of the decode step as one cluster kernel (ffn_fused.cu)
+  bf16* stem_wk_ = nullptr;                          // fused stem (stem_fused.cu): weights in its K order; null = three-launch stem
   // the whole decoder stack of a decode step as ONE cluster kernel (decode_stack.cu): its own chunked, swizzled caches
   bool stack_decode_ = false;
   int cross_chunks_ = 0, self_chunks_ = 0;
@@ -279,6 +280,13 @@ void EngineT<T>::finalize() {
       b.has_ds = raw_.count(p + "downsample.0.weight") > 0;
       if (b.has_ds) b.ds = conv(p + "downsample.0.weight", p + "downsample.1", s_, 0, 1);
       blocks_.push_back(b);
+    }
+  }
+  if constexpr (std::is_same<T, bf16>::value) {
+    const bool want = getenv("RETR_STEM_FUSED") && atoi(getenv("RETR_STEM_FUSED")) != 0;   // opt-in: measured equal
+    if (want && stem_fused_supported(desc.image_size, desc.image_size, stem_.cout, stem_.k, stem_.stride, stem_.pad)) {
+      stem_wk_ = static_cast<bf16*>(dalloc((size_t)stem_fused_weight_elems() * 2));
+      stem_fused_repack(raw(bb + "conv1.weight").dev, stem_wk_, 0);
     }
   }
   input_proj_ = linear("input_proj.weight", "input_proj.bias");
@@ -492,20 +500,31 @@ template <typename T>
 void EngineT<T>::backbone(const float* img, int64_t n, T* feat, cudaStream_t s, const float* img2, int64_t n2) {
   const int Hi = desc.image_size;
   int H = (Hi + 6 - 7) / 2 + 1, W = H;
-  stem_im2col<T>(img, im2col_, n, Hi, Hi, H, W, stem_.kpad, s);
-  if (img2) {          // a second image set rides in the same pass: every conv launch then covers n + n2 images
-    stem_im2col<T>(img2, im2col_ + n * H * W * stem_.kpad, n2, Hi, Hi, H, W, stem_.kpad, s);
-    n += n2;
+  const int PH = (H + 2 - 3) / 2 + 1;
+  bool fused_stem = false;
+  if constexpr (std::is_same<T, bf16>::value) {
+    if (stem_wk_) {        // conv + BN + ReLU + max-pool in one kernel: no im2col matrix, no full-resolution conv output
+      stem_fused(img, stem_wk_, stem_.scale, stem_.shift, act_[1], n, Hi, Hi, s);
+      if (img2) {
+        stem_fused(img2, stem_wk_, stem_.scale, stem_.shift, act_[1] + n * PH * PH * stem_.cout, n2, Hi, Hi, s);
+        n += n2;
+      }
+      fused_stem = true;
+    }
   }
-  {
+  if (!fused_stem) {
+    stem_im2col<T>(img, im2col_, n, Hi, Hi, H, W, stem_.kpad, s);
+    if (img2) {          // a second image set rides in the same pass: every conv launch then covers n + n2 images
+      stem_im2col<T>(img2, im2col_ + n * H * W * stem_.kpad, n2, Hi, Hi, H, W, stem_.kpad, s);
+      n += n2;
+    }
     GemmParams p;
     p.A = im2col_; p.W = stem_.w; p.C = act_[0];
     p.M = n * H * W; p.N = stem_.cout; p.K = stem_.kpad; p.lda = stem_.kpad; p.ldc = stem_.cout;
     p.scale = stem_.scale; p.bias = stem_.shift; p.relu = 1;
     gemm<T>(p, s);
+    maxpool_3x3s2<T>(act_[0], act_[1], n, H, W, stem_.cout, PH, PH, s);
   }
-  const int PH = (H + 2 - 3) / 2 + 1;
-  maxpool_3x3s2<T>(act_[0], act_[1], n, H, W, stem_.cout, PH, PH, s);
   H = W = PH;
   T* x = act_[1];
   T* other = act_[0];

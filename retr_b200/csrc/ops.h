@@ -16,6 +16,12 @@ void repack_filter(const float* oihw, T* out, int O, int I, int kh, int kw, int 
 // 7x7/2 pad 3 stem patches: NCHW fp32 image -> rows [(n,oh,ow)] x kpad, k = (r*7+s)*3+c
 template <typename T>
 void stem_im2col(const float* img, T* out, int64_t nimg, int H, int W, int OH, int OW, int kpad, cudaStream_t s);
+// the whole stem (7x7/2 conv + FrozenBN + ReLU + 3x3/2 max-pool) as one kernel, bf16 (stem_fused.cu)
+bool stem_fused_supported(int H, int W, int cout, int k, int stride, int pad);
+int stem_fused_weight_elems();
+void stem_fused_repack(const float* w_oihw, bf16* out, cudaStream_t s);
+void stem_fused(const float* img, const bf16* wk, const float* scale, const float* shift, bf16* out, int64_t nimg, int H,
+                int W, cudaStream_t s);
 // 3x3/2 pad 1 max pool, NHWC
 template <typename T>
 void maxpool_3x3s2(const T* in, T* out, int64_t nimg, int H, int W, int C, int OH, int OW, cudaStream_t s);

@@ -536,3 +536,24 @@ def test_decode_stack_more_clusters_than_fit_at_once():
             sub = tuple(None if t is None else t[lo:hi] for t in enc_in)
             alone = decode.greedy(samples_of(kind, sub), model, max_len=128, device="cuda", bos_token=101, eos_token=102)
             assert torch.equal(ids[lo:hi], alone), (lo, hi)
+
+
+def test_fused_stem_matches_three_launch_stem(monkeypatch):
+    """stem_fused.cu (7x7/2 conv + FrozenBN + ReLU + 3x3/2 max-pool in one kernel) against the im2col -> GEMM -> max-pool
+    path it replaces, through the whole bf16 backbone, and both against the oracle's fp32 feature map."""
+    kind = "CaptionGlobalLoc"
+    data, enc_in = synthetic_samples(kind, 3, shard=12)
+    feats = []
+    for flag in ("1", "0"):
+        monkeypatch.setenv("RETR_STEM_FUSED", flag)
+        model, sd, cfg = gpu_model(kind, "bf16", calibrated=True)
+        with torch.no_grad():
+            model(*samples_of(kind, enc_in), data["caps"][:, :-1].cuda(), data["cap_masks"][:, :-1].cuda())
+        feats.append(model.engine(3).read_state("feat_t").cpu())
+    with torch.no_grad():
+        ref = O.resnet_layer4(enc_in[0], sd, cfg.backbone, cfg.dilation).permute(0, 2, 3, 1)
+    scale = ref.abs().max().item()
+    for f in feats:
+        assert (f - ref).abs().max().item() <= 3e-2 * scale
+    assert (feats[0] - feats[1]).abs().max().item() <= 2e-2 * scale
+    assert not torch.equal(feats[0], feats[1])              # the two paths really are different kernels
