@@ -40,4 +40,5 @@ def main():
             print(f"{name:12s} {r['Kernel Name'][21:48]:28s} {us:8.1f} us {tf:7.1f} TF/s {gb:7.0f} GB/s(min traffic)")
     print("chunk total us", tot_t, "TFLOP/s", tot_f/tot_t/1e6)
     for k,(us,fl,n) in agg.items(): print(f"{k:12s} n={n:3d} {us:9.1f} us  {fl/us/1e6 if us else 0:7.1f} TF/s  share {us/tot_t:.3f}")
-main()
+if __name__ == "__main__":
+    main()

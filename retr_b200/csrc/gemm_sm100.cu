@@ -60,6 +60,7 @@ struct KArgs {
   int stages;            // smem ring depth (runtime: depends on the epilogue staging in use)
   int tma_epi;           // epilogue through smem staging + TMA store
   int res_tma;           // residual sub-tiles arrive by TMA (implies tma_epi)
+  int r_bufs;            // depth of the residual ring (<= R_BUFS): fewer buffers leave room for one more pipeline stage
   // split-K (weight-gradient GEMMs: tiny M x N, contraction over every token/pixel): tile t covers
   // k-blocks [sp*kb_per_split, ...) of output tile t / splits and writes an fp32 partial tile at row
   // offset sp*M of C (C = workspace [splits*M, N]); splitk_reduce() sums the partials.
@@ -68,7 +69,7 @@ struct KArgs {
 
 constexpr int MAX_STAGES = 8;
 constexpr int EPI_TILE_BYTES = BM * 128;     // 128 rows x 128 B (64 bf16 or 32 fp32 columns)
-constexpr int C_BUFS = 2, R_BUFS = 4;      // C staging: 2 buffers (1 in the gather variant: one more pipeline stage)
+constexpr int C_BUFS = 2, R_BUFS = 6;      // C staging: 2 buffers (1 in the gather variant: one more pipeline stage)
 constexpr int SMEM_LIMIT = 232448;           // 227 KB opt-in maximum per CTA
 constexpr int BARRIER_BYTES = 512;
 
@@ -77,12 +78,13 @@ template <int BN> struct Cfg {
   static constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
   static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
   static constexpr int SB_BYTES = 2 * BN * 4;
-  static int fixed_bytes(bool tma_epi, bool res_tma, bool gather) {
-    return 1024 + BARRIER_BYTES + SB_BYTES + (tma_epi ? (gather ? 1 : C_BUFS) * EPI_TILE_BYTES : 0) +
-           (res_tma ? R_BUFS * EPI_TILE_BYTES : 0);
+  // no alignment slack: the dynamic window of a kernel without static shared memory starts 1024-byte aligned (the
+  // kernel traps if it ever does not), and the slack cost the BN = 256 tiles their fourth pipeline stage
+  static int fixed_bytes(bool tma_epi, int r_bufs, bool gather) {
+    return BARRIER_BYTES + SB_BYTES + (tma_epi ? (gather ? 1 : C_BUFS) * EPI_TILE_BYTES : 0) + r_bufs * EPI_TILE_BYTES;
   }
-  static int stages_for(bool tma_epi, bool res_tma, bool gather) {
-    const int n = (SMEM_LIMIT - fixed_bytes(tma_epi, res_tma, gather)) / STAGE_BYTES;
+  static int stages_for(bool tma_epi, int r_bufs, bool gather) {
+    const int n = (SMEM_LIMIT - fixed_bytes(tma_epi, r_bufs, gather)) / STAGE_BYTES;
     return n > MAX_STAGES ? MAX_STAGES : n;
   }
 };
@@ -319,11 +321,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   constexpr bool TN_CONV = AMODE == 4;     // ... with B = im2col(NHWC input), loaded by TMA im2col, 64 pixels per k-block
   constexpr int EG = GATHER ? 1 : 2;
   const int STAGES = a.stages;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((ptx::smem_u32(smem_raw) & 1023u) != 0) __trap();                  // swizzled tiles need 1024-byte alignment
+  const int RB = a.r_bufs;
   uint8_t* cst = smem + STAGES * C::STAGE_BYTES;                         // C staging (TMA store source)
   uint8_t* rst = cst + (a.tma_epi ? (GATHER ? 1 : C_BUFS) * EPI_TILE_BYTES : 0);   // residual staging (TMA load dest)
-  float* sb = reinterpret_cast<float*>(rst + (a.res_tma ? R_BUFS * EPI_TILE_BYTES : 0));
+  float* sb = reinterpret_cast<float*>(rst + RB * EPI_TILE_BYTES);
   uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sb) + C::SB_BYTES);
   uint64_t* empty = full + MAX_STAGES;
   uint64_t* tfull = empty + MAX_STAGES;
@@ -470,7 +474,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           ptx::mbar_wait(&rempty[rb], rph ^ 1);
           ptx::mbar_arrive_expect_tx(&rfull[rb], EPI_TILE_BYTES);
           ptx::tma_load_2d(rst + rb * EPI_TILE_BYTES, &tmR, &rfull[rb], n0, m_blk * BM);
-          if (++rb == R_BUFS) { rb = 0; rph ^= 1; }
+          if (++rb == (uint32_t)RB) { rb = 0; rph ^= 1; }
         }
       }
     }
@@ -505,7 +509,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const int col = n0 - n_blk * BN;
           uint8_t* cbuf = cst + (EG == 2 ? grp : 0) * EPI_TILE_BYTES;       // one staging buffer per group
           const uint8_t* rbuf = nullptr;
-          const uint32_t rb = cit % R_BUFS, rph = (cit / R_BUFS) & 1;
+          const uint32_t rb = a.res_tma ? cit % RB : 0, rph = a.res_tma ? (cit / RB) & 1 : 0;
           if (a.res_tma) {
             ptx::mbar_wait(&rfull[rb], rph);
             rbuf = rst + rb * EPI_TILE_BYTES;
@@ -676,9 +680,11 @@ template <int BN, int AMODE>
 void launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const CUtensorMap& tmR,
             KArgs& ka, int grid, cudaStream_t stream, bool pdl) {
   constexpr bool GATHER = AMODE == 1;
-  ka.stages = Cfg<BN>::stages_for(ka.tma_epi, ka.res_tma, GATHER);
+  static const int want_rb = getenv("RETR_GEMM_RBUFS") ? std::min(R_BUFS, std::max(2, atoi(getenv("RETR_GEMM_RBUFS")) & ~1)) : 4;
+  ka.r_bufs = ka.res_tma ? want_rb : 0;
+  ka.stages = Cfg<BN>::stages_for(ka.tma_epi, ka.r_bufs, GATHER);
   RETR_CHECK(ka.stages >= (GATHER ? 3 : 2), "not enough shared memory for the pipeline");
-  const int smem = Cfg<BN>::fixed_bytes(ka.tma_epi, ka.res_tma, GATHER) + ka.stages * Cfg<BN>::STAGE_BYTES;
+  const int smem = Cfg<BN>::fixed_bytes(ka.tma_epi, ka.r_bufs, GATHER) + ka.stages * Cfg<BN>::STAGE_BYTES;
   if (pdl) {
     launch_pdl(gemm_tcgen05_kernel<BN, AMODE>, dim3((unsigned)grid), dim3(384), (size_t)smem, stream, tmA, tmB, tmC, tmR, ka);
   } else {
@@ -768,6 +774,11 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
     splits = std::max(splits, 1);
   } else {
     while (bn > bn_min && (bn / 2 >= p.N || cdiv(p.M, BM) * cdiv(p.N, bn) < sms)) bn /= 2;
+    // a residual GEMM whose whole width is one 256-column tile (the encoder's out-projection / FF2) runs faster as two
+    // 128-column tiles: 4 pipeline stages instead of 2 next to the residual ring (encoder 5.90 -> 5.72 ms); the wide
+    // conv3 GEMMs of the backbone do not gain (14.84 vs 14.97 ms)
+    static const int bn_res = getenv("RETR_GEMM_BN_RES") ? atoi(getenv("RETR_GEMM_BN_RES")) : 0;
+    if (p.residual && !gather && !tn && (bn_res > 0 || p.N <= 256)) bn = std::max(bn_min, std::min(bn, bn_res > 0 ? bn_res : 128));
   }
   ka.kb_per_split = (int)cdiv(ka.num_kb, splits);
   splits = (int)cdiv(ka.num_kb, ka.kb_per_split);          // no empty split
