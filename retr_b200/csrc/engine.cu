@@ -158,6 +158,7 @@ class EngineT final : public EngineBase {
   int *step_ = nullptr, *done_ = nullptr;
   int* done_host_ = nullptr;                         // pinned [2]: done, step
   unsigned long long* argmax_keys_ = nullptr;
+  unsigned int* vocab_ticket_ = nullptr;             // CTA ticket counter of vocab_argmax_kernel (zero between launches)
   std::map<std::tuple<int, int, int>, cudaGraphExec_t> graphs_;
   cudaStream_t capture_stream_ = nullptr;
   long long step_kernels_ = 0;
@@ -398,6 +399,8 @@ void EngineT<T>::alloc_buffers() {
   done_ = step_ + 1;
   argmax_keys_ = static_cast<unsigned long long*>(dalloc(Md * 8));
   CUDA_OK(cudaMemset(argmax_keys_, 0, Md * 8));
+  vocab_ticket_ = static_cast<unsigned int*>(dalloc(256));
+  CUDA_OK(cudaMemset(vocab_ticket_, 0, 256));
   CUDA_OK(cudaMallocHost(&done_host_, 16));
   if (const char* e = getenv("RETR_CROSS_PREFETCH")) cross_prefetch_ = atoi(e);
   if (const char* e = getenv("RETR_DECODE_GROUPS")) groups_ = std::min(16, std::max(1, atoi(e)));
@@ -834,6 +837,17 @@ void EngineT<T>::decode_step_fused(int B, int eos, int max_len, cudaStream_t s) 
       DecStackParams p = stack_params_;
       p.B = B; p.max_len = max_len;
       decode_stack(p, s);
+      const bool own_head = !(getenv("RETR_VOCAB_ARGMAX") && atoi(getenv("RETR_VOCAB_ARGMAX")) == 0);
+      if (own_head && vocab_argmax_supported(B, mlp_[2].out, mlp_[2].in)) {
+        // TWO launches per step: the vocabulary slice kernel also does the token bookkeeping in its last CTA
+        VocabArgmaxParams vp;
+        vp.A = m2_; vp.lda = mlp_[2].in; vp.W = mlp_[2].w; vp.bias = mlp_[2].b;
+        vp.M = B; vp.N = mlp_[2].out; vp.K = mlp_[2].in;
+        vp.keys = argmax_keys_; vp.caption = caption_; vp.max_len = max_len; vp.eos = eos;
+        vp.step = step_; vp.done = done_; vp.finished = finished_; vp.ticket = vocab_ticket_;
+        vocab_argmax(vp, s);
+        return;
+      }
       GemmParams gp = lin(mlp_[2], m2_, B, nullptr);
       gp.argmax_out = argmax_keys_;
       gemm<T>(gp, s);                                                  // logits never reach HBM

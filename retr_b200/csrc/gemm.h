@@ -54,6 +54,26 @@ struct GemmParams {
   int64_t ldb = 0;
 };
 
+// Vocabulary head of one greedy step (gemm_sm100.cu: vocab_argmax_kernel): keys[m] = max over n of
+// pack_argmax(A[m,:] . W[n,:] + bias[n], n); the logits are never written.  With `ticket` set (a zeroed device word) the
+// last CTA also does greedy_update's token bookkeeping (models/caption.py:161-174 + eval_utils/decode.py:70-79).
+struct VocabArgmaxParams {
+  const void* A = nullptr;      // bf16 [M, K], row pitch lda
+  const void* W = nullptr;      // bf16 [N, K]
+  const float* bias = nullptr;
+  int64_t M = 0, lda = 0;
+  int N = 0, K = 0;
+  unsigned long long* keys = nullptr;
+  int64_t* caption = nullptr;
+  int max_len = 0, eos = 0;
+  int* step = nullptr;
+  int* done = nullptr;
+  uint8_t* finished = nullptr;
+  unsigned int* ticket = nullptr;
+};
+bool vocab_argmax_supported(int64_t M, int N, int K);
+void vocab_argmax(const VocabArgmaxParams& p, cudaStream_t stream);
+
 void gemm_fp32(const GemmParams& p, cudaStream_t stream);   // gemm_simt.cu  (A, W fp32)
 void gemm_bf16(const GemmParams& p, cudaStream_t stream);   // gemm_sm100.cu (A, W bf16, tcgen05)
 int  sm_count();

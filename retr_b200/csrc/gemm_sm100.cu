@@ -693,6 +693,179 @@ void launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& t
   }
 }
 
+
+// ---- vocabulary head of a greedy step: argmax_n( A[M,K] . W[N,K]^T + bias ) with the token bookkeeping fused ----
+// The general kernel above runs this shape (M = 256, N = 30522, K = 512) as 240 tiles of 128 x 256 over 148 CTAs: two
+// rounds, and every tile re-reads its 128 KB of A next to 256 KB of W, 92 MB through L2 per step (19 us inside the
+// decode graph).  Here ONE CTA owns a 208-column slice of the vocabulary (147 CTAs for 30522 words: one round) and
+// multiplies it with BOTH 128-row halves of A from the same shared-memory stage (two accumulators = all 512 TMEM
+// columns), so W crosses L2 -> SM exactly once per step.  The last CTA to finish (ticket counter) does the work of
+// greedy_update_kernel, which removes that launch from the step as well.
+constexpr int VA_BN = 208;
+constexpr int VA_B_BYTES = VA_BN * BK * 2;                       // 26 KB, a multiple of 1024
+constexpr int VA_STAGE_BYTES = 2 * A_TILE_BYTES + VA_B_BYTES;
+constexpr int VA_STAGES = 3;
+constexpr int VA_THREADS = 320;                                  // producer, MMA, 8 epilogue warps
+constexpr int VA_SB = (VA_BN + 31) / 32 * 32;                     // bias slice, padded to whole 32-column chunks
+constexpr int VA_SMEM = VA_STAGES * VA_STAGE_BYTES + 128 + VA_SB * 4;
+
+struct VocabArgs {
+  int M, N, num_kb;
+  const float* bias;
+  unsigned long long* keys;
+  int64_t* caption;
+  int max_len, eos;
+  int* step;
+  int* done;
+  uint8_t* finished;
+  unsigned int* ticket;
+};
+
+__global__ void __launch_bounds__(VA_THREADS, 1)
+vocab_argmax_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const VocabArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + VA_STAGES * VA_STAGE_BYTES);
+  uint64_t* empty = full + VA_STAGES;
+  uint64_t* tfull = empty + VA_STAGES;
+  uint64_t* tempty = tfull + 1;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tempty + 1);
+  int* flags = reinterpret_cast<int*>(tmem_holder + 1);          // [0] this is the last CTA, [1] some row unfinished
+  float* sbias = reinterpret_cast<float*>(smem + VA_STAGES * VA_STAGE_BYTES + 128);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * VA_BN;
+  const int m_pairs = (a.M + 2 * BM - 1) / (2 * BM);
+
+  if (threadIdx.x == 0) {
+    if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
+    ptx::prefetch_tmap(&tmA);
+    ptx::prefetch_tmap(&tmB);
+    for (int s = 0; s < VA_STAGES; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], 1); }
+    ptx::mbar_init(tfull, 1);
+    ptx::mbar_init(tempty, VA_THREADS - 64);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_holder, 512);
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  ptx::tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_holder;
+  pdl_launch_dependents();
+  pdl_wait();                                   // A is the previous kernel's output; done / step / keys likewise
+  const bool skip = a.done != nullptr && *a.done != 0;          // the same for every thread of the grid
+
+  if (!skip) {
+    if (warp == 0) {
+      if (lane == 0) {
+        uint32_t s = 0, ph = 0;
+        for (int mp = 0; mp < m_pairs; ++mp) {
+          const bool two = mp * 2 * BM + BM < a.M;
+          for (int kb = 0; kb < a.num_kb; ++kb) {
+            ptx::mbar_wait(&empty[s], ph ^ 1);
+            uint8_t* As = smem + s * VA_STAGE_BYTES;
+            ptx::mbar_arrive_expect_tx(&full[s], VA_B_BYTES + (two ? 2 : 1) * A_TILE_BYTES);
+            ptx::tma_load_2d(As, &tmA, &full[s], kb * BK, mp * 2 * BM);
+            if (two) ptx::tma_load_2d(As + A_TILE_BYTES, &tmA, &full[s], kb * BK, mp * 2 * BM + BM);
+            ptx::tma_load_2d(As + 2 * A_TILE_BYTES, &tmB, &full[s], kb * BK, n0);
+            if (++s == VA_STAGES) { s = 0; ph ^= 1; }
+          }
+        }
+      }
+    } else if (warp == 1) {
+      if (lane == 0) {
+        constexpr uint32_t idesc = ptx::idesc_bf16_f32(BM, VA_BN);
+        uint32_t s = 0, ph = 0;
+        for (int mp = 0; mp < m_pairs; ++mp) {
+          const bool two = mp * 2 * BM + BM < a.M;
+          ptx::mbar_wait(tempty, (mp & 1) ^ 1);
+          ptx::tc_fence_after_sync();
+          for (int kb = 0; kb < a.num_kb; ++kb) {
+            ptx::mbar_wait(&full[s], ph);
+            ptx::tc_fence_after_sync();
+            const uint32_t a_addr = ptx::smem_u32(smem + s * VA_STAGE_BYTES);
+            const uint32_t b_addr = a_addr + 2 * A_TILE_BYTES;
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t bd = ptx::smem_desc_sw128(b_addr + k * 32);
+              ptx::mma_bf16_ss(tmem_base, ptx::smem_desc_sw128(a_addr + k * 32), bd, idesc, (kb | k) != 0);
+              if (two)
+                ptx::mma_bf16_ss(tmem_base + 256, ptx::smem_desc_sw128(a_addr + A_TILE_BYTES + k * 32), bd, idesc,
+                                 (kb | k) != 0);
+            }
+            ptx::mma_commit(&empty[s]);
+            if (++s == VA_STAGES) { s = 0; ph ^= 1; }
+          }
+          ptx::mma_commit(tfull);
+        }
+      }
+    } else {
+      const int e = threadIdx.x - 64;                 // 0..255
+      const int h = e >> 7;                           // accumulator = 128-row half of the pair
+      const int q = warp & 3;                         // TMEM lane quarter this warp may read
+      const int row = q * 32 + lane;
+      for (int i = e; i < VA_SB; i += VA_THREADS - 64)
+        sbias[i] = (a.bias && i < VA_BN && n0 + i < a.N) ? __ldg(a.bias + n0 + i) : 0.f;
+      ptx::named_bar_sync(1, VA_THREADS - 64);
+      for (int mp = 0; mp < m_pairs; ++mp) {
+        ptx::mbar_wait(tfull, mp & 1);
+        ptx::tc_fence_after_sync();
+        const int m = mp * 2 * BM + h * BM + row;
+        if (mp * 2 * BM + h * BM < a.M) {             // warp-uniform: this accumulator was written
+          float best_v = -INFINITY;
+          uint32_t best_i = 0;
+#pragma unroll 1
+          for (int c = 0; c < (VA_BN + 31) / 32; ++c) {
+            uint32_t r[32];
+            ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + h * 256 + c * 32, r);
+            ptx::tmem_ld_wait();
+            const int nv = min(32, min(VA_BN - c * 32, a.N - n0 - c * 32));
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float v = __uint_as_float(r[j]) + sbias[c * 32 + j];
+              if (j < nv && v > best_v) { best_v = v; best_i = (uint32_t)(n0 + c * 32 + j); }
+            }
+          }
+          if (m < a.M && best_v > -INFINITY) atomicMax(a.keys + m, pack_argmax(best_v, best_i));
+        }
+        ptx::tc_fence_before_sync();
+        ptx::mbar_arrive(tempty);
+      }
+    }
+  }
+  __threadfence();
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem_base, 512);
+  if (skip || a.ticket == nullptr) return;
+
+  // ---- token bookkeeping by the last CTA (eval_utils/decode.py:70-79, as greedy_update_kernel) ----
+  if (threadIdx.x == 0) {
+    const unsigned int t = atomicAdd(a.ticket, 1u);
+    flags[0] = t == gridDim.x - 1;
+    flags[1] = 0;
+  }
+  __syncthreads();
+  if (!flags[0]) return;
+  __threadfence();
+  const int i = *a.step;
+  for (int b = threadIdx.x; b < a.M; b += VA_THREADS) {
+    const int tok = (int)unpack_argmax_index(__ldcg(a.keys + b));
+    const uint8_t fin = a.finished[b] | (uint8_t)(tok == a.eos);
+    a.finished[b] = fin;
+    if (!fin) flags[1] = 1;
+  }
+  __syncthreads();
+  const bool all_done = flags[1] == 0;
+  for (int b = threadIdx.x; b < a.M; b += VA_THREADS) {
+    if (!all_done) a.caption[(int64_t)b * a.max_len + i + 1] = (int64_t)unpack_argmax_index(__ldcg(a.keys + b));
+    a.keys[b] = 0ull;
+  }
+  if (threadIdx.x == 0) {
+    *a.step = i + 1;
+    if (all_done || i + 1 >= a.max_len - 1) *a.done = 1;
+    *a.ticket = 0u;
+  }
+}
+
 }  // namespace
 
 template <int BN> static void prepare_bn() {
@@ -708,6 +881,27 @@ void gemm_bf16_prepare() {
   prepare_bn<32>(); prepare_bn<64>(); prepare_bn<128>(); prepare_bn<256>();
   get_encode_fn();
   get_encode_im2col_fn();
+}
+
+bool vocab_argmax_supported(int64_t M, int N, int K) { return M > 0 && N > 0 && K > 0 && K % BK == 0; }
+
+void vocab_argmax(const VocabArgmaxParams& p, cudaStream_t stream) {
+  static bool prepared = false;
+  if (!prepared) {
+    get_encode_fn();
+    CUDA_OK(cudaFuncSetAttribute(vocab_argmax_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, VA_SMEM));
+    prepared = true;
+  }
+  RETR_CHECK(vocab_argmax_supported(p.M, p.N, p.K), "vocab_argmax: K must be a positive multiple of 64");
+  RETR_CHECK(!p.ticket || (p.caption && p.step && p.done && p.finished), "vocab_argmax: fused bookkeeping operands");
+  VocabArgs a{};
+  a.M = (int)p.M; a.N = p.N; a.num_kb = p.K / BK;
+  a.bias = p.bias; a.keys = p.keys;
+  a.caption = p.caption; a.max_len = p.max_len; a.eos = p.eos;
+  a.step = p.step; a.done = p.done; a.finished = p.finished; a.ticket = p.ticket;
+  const CUtensorMap tmA = make_tmap_2d(p.A, p.M, p.K, p.lda, BM);
+  const CUtensorMap tmB = make_tmap_2d(p.W, p.N, p.K, p.K, VA_BN);
+  launch_pdl(vocab_argmax_kernel, dim3((unsigned)cdiv(p.N, VA_BN)), dim3(VA_THREADS), (size_t)VA_SMEM, stream, tmA, tmB, a);
 }
 
 int sm_count() {

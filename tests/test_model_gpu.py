@@ -538,6 +538,32 @@ def test_decode_stack_more_clusters_than_fit_at_once():
             assert torch.equal(ids[lo:hi], alone), (lo, hi)
 
 
+@pytest.mark.parametrize("B", [19, 300])
+def test_vocab_slice_kernel_matches_gemm_and_update(B, monkeypatch):
+    """vocab_argmax_kernel (gemm_sm100.cu: one CTA per 208-word slice, both 128-row halves of the batch against the same
+    weight stage, greedy_update's bookkeeping in the last CTA) against the general tcgen05 GEMM with the argmax
+    epilogue + greedy_update_kernel it replaces in the decode step: identical ids, also when an eos token ends
+    sequences early (eval_utils/decode.py:70-79).  B = 300 needs two row pairs per CTA and a ragged second pair."""
+    kind = "CaptionGlobalLoc"
+    _, enc_in = synthetic_samples(kind, B, shard=35, train=False)
+    s = samples_of(kind, enc_in)
+    out = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("RETR_VOCAB_ARGMAX", flag)
+        model, sd, cfg = gpu_model(kind, "bf16", calibrated=True)
+        model.max_batch = B
+        with torch.no_grad():
+            ids = decode.greedy(s, model, max_len=128, device="cuda", bos_token=101, eos_token=102)
+            eos = int(ids[:, 1:].flatten().mode().values)          # a token the model does emit: sequences finish
+            ids_eos = decode.greedy(s, model, max_len=128, device="cuda", bos_token=101, eos_token=eos)
+        out[flag] = (ids.cpu(), eos, ids_eos.cpu())
+    assert torch.equal(out["1"][0], out["0"][0])
+    assert out["1"][1] == out["0"][1]
+    assert torch.equal(out["1"][2], out["0"][2])
+    assert not torch.equal(out["1"][2], out["1"][0])        # the eos run did stop early (decode.py:74-76 writes no
+                                                            # tokens at the step where every row has finished)
+
+
 def test_fused_stem_matches_three_launch_stem(monkeypatch):
     """stem_fused.cu (7x7/2 conv + FrozenBN + ReLU + 3x3/2 max-pool in one kernel) against the im2col -> GEMM -> max-pool
     path it replaces, through the whole bf16 backbone, and both against the oracle's fp32 feature map."""
