@@ -10,7 +10,7 @@ def main():
     path, nimg = sys.argv[1], int(sys.argv[2])
     peaks = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "MEASURED_PEAKS.json")))
     tf_peak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1367.0)))
-    bw_peak = float(peaks.get("hbm_gbps_sustained", peaks.get("hbm_gbps", 6538.0)))
+    bw_peak = float(peaks.get("hbm_gbs", 6538.0))
     rows = []
     for l in (gzip.open(path, "rt") if path.endswith(".gz") else open(path)):
         if l.startswith("#") or l.startswith("id,"):
