@@ -55,10 +55,15 @@ __global__ void __launch_bounds__(128) flash_attention_kernel(const AttnParams p
   __shared__ uint8_t Ms[2][FK];
   const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * FQ;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const bf16* qg = static_cast<const bf16*>(p.q) + (int64_t)b * p.Lq * p.ldq + h * DH;
-  const bf16* kg = static_cast<const bf16*>(p.k) + (int64_t)b * p.Lk * p.ldk + h * DH;
-  const bf16* vg = static_cast<const bf16*>(p.v) + (int64_t)b * p.Lk * p.ldv + h * DH;
-  const int k_end = CAUSAL ? min(p.Lk, q0 + FQ) : p.Lk;
+  // packed sequences: this sample's rows start at seq_off[b] and there are seq_len[b] of them
+  const int Lq = p.seq_len ? __ldg(p.seq_len + b) : p.Lq, Lk = p.seq_len ? Lq : p.Lk;
+  if (q0 >= Lq) return;
+  const int64_t q_row0 = p.seq_off ? (int64_t)__ldg(p.seq_off + b) : (int64_t)b * p.Lq;
+  const int64_t k_row0 = p.seq_off ? q_row0 : (int64_t)b * p.Lk;
+  const bf16* qg = static_cast<const bf16*>(p.q) + q_row0 * p.ldq + h * DH;
+  const bf16* kg = static_cast<const bf16*>(p.k) + k_row0 * p.ldk + h * DH;
+  const bf16* vg = static_cast<const bf16*>(p.v) + k_row0 * p.ldv + h * DH;
+  const int k_end = CAUSAL ? min(Lk, q0 + FQ) : Lk;
   const int n_tiles = (k_end + FK - 1) / FK;
 
   auto load_kv = [&](int t, int buf) {
@@ -72,13 +77,13 @@ __global__ void __launch_bounds__(128) flash_attention_kernel(const AttnParams p
     }
     if (tid < FK) {
       const int j = k0 + tid;
-      Ms[buf][tid] = (j >= k_end) || (p.key_pad && p.key_pad[(int64_t)b * p.Lk + j]);
+      Ms[buf][tid] = (j >= k_end) || (p.key_pad && p.key_pad[(int64_t)b * Lk + j]);
     }
   };
   // Q tile + first K/V tile
   for (int idx = tid; idx < FQ * CPR; idx += 128) {
     const int r = idx / CPR, c = idx % CPR;
-    const bool ok = q0 + r < p.Lq;
+    const bool ok = q0 + r < Lq;
     cp16((uint32_t)__cvta_generic_to_shared(&Qs[r * LDS + c * 8]), qg + (int64_t)(ok ? q0 + r : 0) * p.ldq + c * 8, ok);
   }
   load_kv(0, 0);
@@ -185,13 +190,13 @@ __global__ void __launch_bounds__(128) flash_attention_kernel(const AttnParams p
   l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
   l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
   const float i0 = 1.f / l0, i1 = 1.f / l1;
-  bf16* og = static_cast<bf16*>(p.out) + (int64_t)b * p.Lq * p.ldo + h * DH;
+  bf16* og = static_cast<bf16*>(p.out) + q_row0 * p.ldo + h * DH;
 #pragma unroll
   for (int nt = 0; nt < NT; ++nt) {
     const int col = nt * 8 + c4 * 2;
-    if (qrow0 < p.Lq)
+    if (qrow0 < Lq)
       *reinterpret_cast<__nv_bfloat162*>(og + (int64_t)qrow0 * p.ldo + col) = __floats2bfloat162_rn(o[nt][0] * i0, o[nt][1] * i0);
-    if (qrow0 + 8 < p.Lq)
+    if (qrow0 + 8 < Lq)
       *reinterpret_cast<__nv_bfloat162*>(og + (int64_t)(qrow0 + 8) * p.ldo + col) = __floats2bfloat162_rn(o[nt][2] * i1, o[nt][3] * i1);
   }
 }

@@ -242,6 +242,69 @@ __global__ void key_compaction_kernel(const uint8_t* __restrict__ pad, int B, in
   if (lane == 0) n_valid[b] = base;
 }
 
+// ---- packed encoder (engine.cu: encode): only the unpadded tokens of every sample go through the encoder layers ----
+// exclusive prefix sum of n_valid over the batch: off[b] = first packed row of sample b, off[B] = total rows
+__global__ void seq_offsets_kernel(const int* __restrict__ n_valid, int B, int* __restrict__ off) {
+  __shared__ int part[32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  int carry = 0;
+  for (int b0 = 0; b0 < B; b0 += (int)blockDim.x) {
+    const int b = b0 + tid;
+    const int v = b < B ? n_valid[b] : 0;
+    int x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) part[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+      int w = lane < (int)(blockDim.x >> 5) ? part[lane] : 0;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += y; }
+      part[lane] = w;
+    }
+    __syncthreads();
+    const int before = carry + (warp ? part[warp - 1] : 0) + x - v;
+    if (b < B) off[b] = before;
+    carry += part[(blockDim.x >> 5) - 1];
+    __syncthreads();
+  }
+  if (tid == 0) off[B] = carry;
+}
+
+// x [B*S, d] fp32 -> xp [off[B], d]: row off[b] + dst_row[b,s] = row (b, s) for every unpadded token; row_pos = s
+__global__ void pack_rows_kernel(const float* __restrict__ x, float* __restrict__ xp, const int* __restrict__ dst_row,
+                                 const int* __restrict__ off, int* __restrict__ row_pos, int64_t rows, int S, int d) {
+  const int64_t br = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (br >= rows) return;
+  const int r = dst_row[br];
+  if (r < 0) return;
+  const int b = (int)(br / S);
+  const int64_t to = (int64_t)off[b] + r;
+  const float4* src = reinterpret_cast<const float4*>(x + br * d);
+  float4* dst = reinterpret_cast<float4*>(xp + to * d);
+  for (int i = lane; i < d / 4; i += 32) dst[i] = src[i];
+  if (lane == 0) row_pos[to] = (int)(br - (int64_t)b * S);
+}
+
+// packed rows -> [B*S, d] (padded rows zero): what the full-sequence consumers of the encoder memory read
+template <typename T>
+__global__ void unpack_rows_kernel(const T* __restrict__ xp, T* __restrict__ x, const int* __restrict__ dst_row,
+                                   const int* __restrict__ off, int64_t rows, int S, int d) {
+  constexpr int VN = 16 / sizeof(T);
+  const int64_t br = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (br >= rows) return;
+  const int r = dst_row[br];
+  uint4* dst = reinterpret_cast<uint4*>(x + br * d);
+  if (r < 0) {
+    for (int i = lane; i < d / VN; i += 32) dst[i] = make_uint4(0u, 0u, 0u, 0u);
+    return;
+  }
+  const uint4* src = reinterpret_cast<const uint4*>(xp + ((int64_t)off[br / S] + r) * d);
+  for (int i = lane; i < d / VN; i += 32) dst[i] = src[i];
+}
+
 template <typename T>
 __global__ void kv_to_head_major_kernel(const T* __restrict__ kv, T* __restrict__ kh, T* __restrict__ vh, int B,
                                         int rows, int H, int dh, const int* __restrict__ dst_row) {
@@ -349,6 +412,28 @@ void kv_to_head_major(const T* kv, T* kh, T* vh, int B, int rows, int H, int dh,
 }
 template void kv_to_head_major<float>(const float*, float*, float*, int, int, int, int, cudaStream_t, const int*);
 template void kv_to_head_major<bf16>(const bf16*, bf16*, bf16*, int, int, int, int, cudaStream_t, const int*);
+
+void seq_offsets(const int* n_valid, int B, int* off, cudaStream_t s) {
+  seq_offsets_kernel<<<1, 256, 0, s>>>(n_valid, B, off);
+  LAUNCH_OK();
+}
+void pack_rows(const float* x, float* xp, const int* dst_row, const int* off, int* row_pos, int B, int S, int d,
+               cudaStream_t s) {
+  RETR_CHECK(d % 4 == 0, "pack_rows: d % 4");
+  const int64_t rows = (int64_t)B * S;
+  CUDA_OK(cudaMemsetAsync(row_pos, 0, rows * 4, s));             // rows past the packed total index position 0
+  pack_rows_kernel<<<(unsigned)cdiv(rows, 8), 256, 0, s>>>(x, xp, dst_row, off, row_pos, rows, S, d);
+  LAUNCH_OK();
+}
+template <typename T>
+void unpack_rows(const T* xp, T* x, const int* dst_row, const int* off, int B, int S, int d, cudaStream_t s) {
+  RETR_CHECK(d % (16 / (int)sizeof(T)) == 0, "unpack_rows: 16-byte rows");
+  const int64_t rows = (int64_t)B * S;
+  unpack_rows_kernel<T><<<(unsigned)cdiv(rows, 8), 256, 0, s>>>(xp, x, dst_row, off, rows, S, d);
+  LAUNCH_OK();
+}
+template void unpack_rows<float>(const float*, float*, const int*, const int*, int, int, int, cudaStream_t);
+template void unpack_rows<bf16>(const bf16*, bf16*, const int*, const int*, int, int, int, cudaStream_t);
 
 void greedy_update(unsigned long long* argmax_keys, int64_t* caption, int max_len, int B, int eos, int* step,
                    int* done, uint8_t* finished, cudaStream_t s, bool allow_pdl) {

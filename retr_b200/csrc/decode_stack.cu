@@ -751,8 +751,9 @@ decode_stack_kernel(const __grid_constant__ DecStackParams p) {
 
 // rows of [K(256) | V(256)] -> [B][4 CTA ranks][chunks][2 heads][K 32x32 | V 32x32] with the 16-byte units of a key row XOR-swizzled by
 // ((key % 32) >> 1) & 3; dst_row (key compaction) maps a key to its rank among the sample's unpadded keys or -1.
+// With src_off (packed encoder) the source rows are packed too: key r of sample b is row src_off[b] + r of kv.
 __global__ void kv_to_chunked_kernel(const bf16* __restrict__ kv, bf16* __restrict__ out, int B, int rows, int chunks,
-                                     const int* __restrict__ dst_row) {
+                                     const int* __restrict__ dst_row, const int* __restrict__ src_off) {
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;       // one 16-byte unit each
   const int upr = 2 * D / 8;                                                // units per source row
   if (idx >= (int64_t)B * rows * upr) return;
@@ -765,7 +766,8 @@ __global__ void kv_to_chunked_kernel(const bf16* __restrict__ kv, bf16* __restri
     if (r < 0) return;
   }
   const int isv = u >= D / 8, e = (isv ? u - D / 8 : u) * 8, h = e / DH, unit = (e % DH) / 8, kr = r & 31;
-  const uint4 val = *reinterpret_cast<const uint4*>(kv + br * (2 * D) + (size_t)u * 8);
+  const int64_t sr = src_off ? (int64_t)src_off[b] + r : br;
+  const uint4 val = *reinterpret_cast<const uint4*>(kv + sr * (2 * D) + (size_t)u * 8);
   bf16* dst = out + (((size_t)(b * CL + h / HPC) * chunks + (r >> 5)) * HPC + h % HPC) * DS_CHUNK_ELEMS + isv * 1024 +
               kr * 32 + ((unit ^ ((kr >> 1) & 3)) << 3);
   *reinterpret_cast<uint4*>(dst) = val;
@@ -829,9 +831,11 @@ void decode_stack(const DecStackParams& p, cudaStream_t s) {
   ++g_launches;
 }
 
-void kv_to_chunked(const bf16* kv, bf16* out, int B, int rows, int chunks, const int* dst_row, cudaStream_t s) {
+void kv_to_chunked(const bf16* kv, bf16* out, int B, int rows, int chunks, const int* dst_row, cudaStream_t s,
+                   const int* src_off) {
+  RETR_CHECK(!src_off || dst_row, "kv_to_chunked: packed source rows need the compaction map");
   const int64_t n = (int64_t)B * rows * (2 * D / 8);
-  kv_to_chunked_kernel<<<(unsigned)cdiv(n, 256), 256, 0, s>>>(kv, out, B, rows, chunks, dst_row);
+  kv_to_chunked_kernel<<<(unsigned)cdiv(n, 256), 256, 0, s>>>(kv, out, B, rows, chunks, dst_row, src_off);
   LAUNCH_OK();
 }
 

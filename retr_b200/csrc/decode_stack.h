@@ -47,6 +47,8 @@ void decode_stack(const DecStackParams& p, cudaStream_t s);
 void repack_frag(const bf16* W, bf16* out, int N, int K, cudaStream_t s);
 
 // encoder-side cache build: rows of [K(d) | V(d)] (d = 256, 8 heads) -> chunked, swizzled, compacted cross cache
-void kv_to_chunked(const bf16* kv, bf16* out, int B, int rows, int chunks, const int* dst_row, cudaStream_t s);
+// src_off: the source rows are packed as well (row src_off[b] + rank), see engine.cu: encode
+void kv_to_chunked(const bf16* kv, bf16* out, int B, int rows, int chunks, const int* dst_row, cudaStream_t s,
+                   const int* src_off = nullptr);
 
 }  // namespace retr

@@ -177,6 +177,11 @@ class EngineT final : public EngineBase {
   bf16* stem_wk_ = nullptr;                          // fused stem (stem_fused.cu): weights in its K order; null = three-launch stem
   // the whole decoder stack of a decode step as ONE cluster kernel (decode_stack.cu): its own chunked, swizzled caches
   bool stack_decode_ = false;
+  // packed encoder (encode): only the unpadded tokens run through the encoder layers and the cross K/V projections
+  bool packed_encoder_ = false, enc_packed_ = false;    // enabled / memory_ and ckv_ currently hold packed rows
+  float* xp_ = nullptr;                                // packed residual stream [<= B*S, d]
+  int *seq_off_ = nullptr, *row_pos_ = nullptr;        // [B + 1] first packed row per sample (+ total); [B*S] position of a row
+  void materialize_unpacked(cudaStream_t s);
   int cross_chunks_ = 0, self_chunks_ = 0;
   std::vector<bf16*> ckv2_, skv2_;
   DecStackParams stack_params_;
@@ -393,6 +398,8 @@ void EngineT<T>::alloc_buffers() {
   tok_mask_ = static_cast<uint8_t*>(dalloc(Me));
   cross_dst_ = static_cast<int*>(dalloc(Me * 4));
   cross_nvalid_ = static_cast<int*>(dalloc((size_t)B * 4));
+  seq_off_ = static_cast<int*>(dalloc((size_t)(B + 1) * 4));
+  row_pos_ = static_cast<int*>(dalloc(Me * 4));
   finished_ = static_cast<uint8_t*>(dalloc(B));
   caption_ = static_cast<int64_t*>(dalloc(Md * 8));
   step_ = static_cast<int*>(dalloc(16));
@@ -424,6 +431,11 @@ void EngineT<T>::alloc_buffers() {
   stack_decode_ = fast_decode_ && stack_decode_wanted() &&
                   decode_stack_supported((int)d, desc.n_heads, (int)ff, desc.dec_layers, mlp_[0].out, (int)Tn) &&
                   mlp_[1].out == mlp_[0].out && mlp_[2].in == mlp_[1].out;
+  packed_encoder_ = stack_decode_ && !(getenv("RETR_ENCODER_PACKED") && atoi(getenv("RETR_ENCODER_PACKED")) == 0);
+  if (packed_encoder_) {
+    xp_ = static_cast<float*>(dalloc(Me * d * 4));
+    CUDA_OK(cudaMemset(xp_, 0, Me * d * 4));
+  }
   if (stack_decode_) {
     cross_chunks_ = (int)cdiv(S, DS_CHUNK_KEYS);
     self_chunks_ = (int)Tn / DS_CHUNK_KEYS;
@@ -594,52 +606,89 @@ void EngineT<T>::encode(int B, const float* t_img, const uint8_t* t_mask, const 
     loc_tokens(loc, loc_w_, loc_b_, x_, tok_mask_, B, desc.n_loc, desc.loc_in_dim == 1, d, S, off_loc, s);
   const int64_t Me = (int64_t)B * S;
   CUDA_OK(cudaMemcpyAsync(src_copy_, x_, Me * d * 4, cudaMemcpyDeviceToDevice, s));
+  key_compaction(tok_mask_, B, S, cross_dst_, cross_nvalid_, s);
+  // Packed encoder: a padded token is never a key (src_key_padding_mask in every encoder layer, memory_key_padding_mask
+  // in every decoder layer: models/ConcatTransformer.py:171-194, 220-257) and every other operation is row-wise, so
+  // the rows of padded tokens influence nothing that is returned.  The unpadded rows of all samples are gathered into
+  // one dense [sum n_valid, d] matrix (~72 % of B*S on the benchmark's masks); its height exists on the device only, so
+  // the GEMMs are sized for B*S rows and stop after ceil(*m_dyn / 128) row blocks, the positional row bias is looked
+  // up through row_pos_, and the self-attention runs on variable-length sequences without any key mask.
+  const bool packed = packed_encoder_ && !att_enc_capture;
+  float* xs = x_;
+  const int* m_dyn = nullptr;
+  const int* ridx = nullptr;
+  if (packed) {
+    seq_offsets(cross_nvalid_, B, seq_off_, s);
+    pack_rows(x_, xp_, cross_dst_, seq_off_, row_pos_, B, S, d, s);
+    xs = xp_; m_dyn = seq_off_ + B; ridx = row_pos_;
+  }
   // encoder (models/ConcatTransformer.py:171-194)
   for (int l = 0; l < desc.enc_layers; ++l) {
     const EncLayer<T>& e = enc_[l];
-    layernorm<T>(x_, e.ln1_g, e.ln1_b, n_, Me, d, 1e-5f, s);
+    layernorm<T>(xs, e.ln1_g, e.ln1_b, n_, Me, d, 1e-5f, s, m_dyn);
     GemmParams p = lin(e.qkv, n_, Me, qkv_);
-    p.rowbias = e.rb_qkv; p.rowbias_period = S;
+    p.rowbias = e.rb_qkv; p.rowbias_period = S; p.rowbias_idx = ridx; p.m_dyn = m_dyn;
     gemm<T>(p, s);
     AttnParams a{};
     a.q = qkv_; a.k = qkv_ + d; a.v = qkv_ + 2 * d; a.out = att_;
     a.B = B; a.Lq = S; a.Lk = S; a.H = desc.n_heads;
     a.ldq = a.ldk = a.ldv = 3 * d; a.ldo = d; a.key_pad = tok_mask_; a.causal = 0;
     a.probs = att_enc_capture ? att_enc_capture + (int64_t)l * B * S * S : nullptr;
+    if (packed) { a.key_pad = nullptr; a.seq_off = seq_off_; a.seq_len = cross_nvalid_; }
     attention<T>(a, s);
-    p = lin(e.out, att_, Me, x_);
-    p.out_fp32 = true; p.residual = x_; p.ldr = d; p.res_fp32 = true;
+    p = lin(e.out, att_, Me, xs);
+    p.out_fp32 = true; p.residual = xs; p.ldr = d; p.res_fp32 = true; p.m_dyn = m_dyn;
     gemm<T>(p, s);
-    layernorm<T>(x_, e.ln2_g, e.ln2_b, n_, Me, d, 1e-5f, s);
+    layernorm<T>(xs, e.ln2_g, e.ln2_b, n_, Me, d, 1e-5f, s, m_dyn);
     p = lin(e.ff1, n_, Me, h_);
-    p.relu = 1;
+    p.relu = 1; p.m_dyn = m_dyn;
     gemm<T>(p, s);
-    p = lin(e.ff2, h_, Me, x_);
-    p.out_fp32 = true; p.residual = x_; p.ldr = d; p.res_fp32 = true;
+    p = lin(e.ff2, h_, Me, xs);
+    p.out_fp32 = true; p.residual = xs; p.ldr = d; p.res_fp32 = true; p.m_dyn = m_dyn;
     gemm<T>(p, s);
   }
   if (desc.pre_norm) {
-    layernorm<T>(x_, enc_norm_g_, enc_norm_b_, memory_, Me, d, 1e-5f, s);
+    layernorm<T>(xs, enc_norm_g_, enc_norm_b_, memory_, Me, d, 1e-5f, s, m_dyn);
   } else {
-    from_f32_kernel<T><<<(unsigned)cdiv(Me * d, 256), 256, 0, s>>>(x_, memory_, Me * d);
+    from_f32_kernel<T><<<(unsigned)cdiv(Me * d, 256), 256, 0, s>>>(xs, memory_, Me * d);
     LAUNCH_OK();
   }
   // cross-attention K/V of every decoder layer, once per sample (k = memory+pos, v = memory)
   for (int l = 0; l < desc.dec_layers; ++l) {
     GemmParams p = lin(dec_[l].c_kv, memory_, Me, ckv_[l]);
-    p.rowbias = dec_[l].rb_c_kv; p.rowbias_period = S;
+    p.rowbias = dec_[l].rb_c_kv; p.rowbias_period = S; p.rowbias_idx = ridx; p.m_dyn = m_dyn;
     gemm<T>(p, s);
-    if (l == 0) key_compaction(tok_mask_, B, S, cross_dst_, cross_nvalid_, s);
     if constexpr (std::is_same<T, bf16>::value) {
-      if (stack_decode_) { kv_to_chunked(ckv_[l], ckv2_[l], B, S, cross_chunks_, cross_dst_, s); continue; }
+      if (stack_decode_) {
+        kv_to_chunked(ckv_[l], ckv2_[l], B, S, cross_chunks_, cross_dst_, s, packed ? seq_off_ : nullptr);
+        continue;
+      }
     }
     kv_to_head_major<T>(ckv_[l], ck_[l], cv_[l], B, S, desc.n_heads, d / desc.n_heads, s, cross_dst_);
   }
+  enc_packed_ = packed;
   CUDA_OK(cudaEventRecord(ev_[2], s));
   cur_B_ = B;
   launches += g_launches - l0;
 }
 
+
+// The full-sequence consumers (teacher-forced decoder, read_state) read memory_ and ckv_ as [B*S] rows: after a packed
+// encode the memory is scattered back (padded rows zero: they are masked keys) and the cross K/V projections re-run.
+template <typename T>
+void EngineT<T>::materialize_unpacked(cudaStream_t s) {
+  if (!enc_packed_) return;
+  const int B = cur_B_, d = desc.d_model;
+  const int64_t Me = (int64_t)B * S;
+  unpack_rows<T>(memory_, n_, cross_dst_, seq_off_, B, S, d, s);
+  CUDA_OK(cudaMemcpyAsync(memory_, n_, Me * d * sizeof(T), cudaMemcpyDeviceToDevice, s));
+  for (int l = 0; l < desc.dec_layers; ++l) {
+    GemmParams p = lin(dec_[l].c_kv, memory_, Me, ckv_[l]);
+    p.rowbias = dec_[l].rb_c_kv; p.rowbias_period = S;
+    gemm<T>(p, s);
+  }
+  enc_packed_ = false;
+}
 
 // ---- teacher-forced decoder + head (models/ConcatTransformer.py:63-74, models/caption.py:153) ------------
 template <typename T>
@@ -647,6 +696,7 @@ void EngineT<T>::teacher_forced(const int64_t* ids, const uint8_t* id_mask, floa
                                 float* att_cross, cudaStream_t s) {
   RETR_CHECK(cur_B_ > 0, "retr_encode must run before the decoder");
   const long long l0 = g_launches;
+  materialize_unpacked(s);
   const int B = cur_B_, d = desc.d_model, Tn = desc.max_pos;
   const int64_t Md = (int64_t)B * Tn;
   embed_ln(ids, Tn, e_word_, e_pos_, emb_g_, emb_b_, y_, B, Tn, 0, nullptr, d, desc.embed_ln_eps, s);
@@ -973,7 +1023,7 @@ void EngineT<T>::read_state(const std::string& what, void* dst, int64_t bytes, c
     to_f32_kernel<T><<<(unsigned)cdiv(n, 256), 256, 0, s>>>(src, static_cast<float*>(dst), n);
     LAUNCH_OK();
   };
-  if (what == "memory") conv_out(memory_, B * S * d);
+  if (what == "memory") { materialize_unpacked(s); conv_out(memory_, B * S * d); }
   else if (what == "feat_t") conv_out(feat_, B * g2 * cfeat);
   else if (what == "feat_g") { RETR_CHECK(desc.n_images == 2, "no context images"); conv_out(feat_ + B * g2 * cfeat, B * g2 * cfeat); }
   else if (what == "src") {

@@ -37,6 +37,12 @@ struct GemmParams {
   int c_group = 0, c_group_stride = 0;
   // If set, every row uses rowbias[*rowbias_dyn] (decode: the device-side step counter).
   const int* rowbias_dyn = nullptr;
+  // If set, row m uses rowbias[rowbias_idx[m]] (packed encoder: the token's position in its sequence).
+  const int* rowbias_idx = nullptr;
+  // If set, only the first *m_dyn rows (<= M) are computed: M sizes the tensor maps and the grid, the persistent loop
+  // stops at ceil(*m_dyn / 128) row blocks (packed encoder: the number of unpadded tokens is known on the device only).
+  // bf16 / tcgen05 only.
+  const int* m_dyn = nullptr;
   // Weight-gradient shape (small M x N, very long K): split the contraction over split_k CTAs per output
   // tile (0 = choose from the SM count), fp32 partial tiles in split_ws ([split_k*M, N] floats), summed into C
   // (C += sum when accumulate).  Requires a plain fp32 C with ldc == N and no epilogue operands.

@@ -57,6 +57,8 @@ struct KArgs {
   int kh, kw, stride, pad, dil, H, W, Cin, OH, OW, cblocks;
   int c_group, c_group_stride;
   const int* rowbias_dyn;
+  const int* rowbias_idx;
+  const int* m_dyn;
   int stages;            // smem ring depth (runtime: depends on the epilogue staging in use)
   int tma_epi;           // epilogue through smem staging + TMA store
   int res_tma;           // residual sub-tiles arrive by TMA (implies tma_epi)
@@ -338,7 +340,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int total_tiles = a.m_tiles * a.n_tiles * a.splits;
   const int EC = a.out_fp32 ? 32 : 64;                 // columns per staged sub-tile (128 B rows)
 
   if (warp == 0 && lane == 0) {
@@ -371,6 +372,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   // global memory waits for the previous grid here (operands may be its output — activations, refreshed weights).
   pdl_launch_dependents();
   pdl_wait();
+  // row blocks to compute: all of them, or (packed encoder) as many as the device-side row count says
+  const int m_tiles_run = a.m_dyn ? min(a.m_tiles, (__ldg(a.m_dyn) + BM - 1) / BM) : a.m_tiles;
+  const int total_tiles = m_tiles_run * a.n_tiles * a.splits;
 
   if (warp == 0) {
     if (lane == 0) {
@@ -491,7 +495,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const int m_blk = tc.m_blk, n_blk = tc.n_blk;
       const uint32_t as = tcount & 1, aph = (tcount >> 1) & 1;
       const int64_t m = (int64_t)m_blk * BM + row;
-      const int64_t rb_row = a.rowbias_dyn ? (int64_t)__ldg(a.rowbias_dyn) : (m % a.rowbias_period);
+      const int64_t rb_row = a.rowbias_dyn   ? (int64_t)__ldg(a.rowbias_dyn)
+                             : a.rowbias_idx ? (m < a.M ? (int64_t)__ldg(a.rowbias_idx + m) : 0)
+                                             : (m % a.rowbias_period);
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
       if (a.tma_epi) {
         // per-tile column parameters -> smem (all epilogue threads)
@@ -937,6 +943,8 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
   ka.residual = p.residual; ka.ldr = p.ldr; ka.res_fp32 = p.res_fp32; ka.relu = p.relu;
   ka.argmax_out = p.argmax_out;
   ka.c_group = p.c_group; ka.c_group_stride = p.c_group_stride; ka.rowbias_dyn = p.rowbias_dyn;
+  ka.rowbias_idx = p.rowbias_idx; ka.m_dyn = p.m_dyn;
+  RETR_CHECK(!p.m_dyn || p.split_k == 1, "m_dyn: no split-K");
   const int64_t cbytes = p.out_fp32 ? 4 : 2, rbytes = p.res_fp32 ? 4 : 2;
   ka.vecC = p.C && (reinterpret_cast<uintptr_t>(p.C) % 16 == 0) && (p.ldc * cbytes) % 16 == 0;
   ka.vecR = p.residual && (reinterpret_cast<uintptr_t>(p.residual) % 16 == 0) && (p.ldr * rbytes) % 16 == 0;

@@ -219,9 +219,11 @@ __device__ __forceinline__ void ln_row(float (&v)[MAXPER], int per, int lane, co
 // One warp per row, float4 loads (lane holds columns j*128 + lane*4 .. +3), d % 128 == 0.
 template <typename T, int D>
 __global__ void layernorm_vec_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
-                                     const float* __restrict__ beta, T* __restrict__ y, int64_t rows, float eps) {
+                                     const float* __restrict__ beta, T* __restrict__ y, int64_t rows, float eps,
+                                     const int* __restrict__ rows_dyn) {
   constexpr int NV = D / 128;
   const int lane = threadIdx.x & 31;
+  if (rows_dyn) rows = min(rows, (int64_t)__ldg(rows_dyn));      // packed encoder: device-side row count
   float4 g[NV], be[NV];
 #pragma unroll
   for (int j = 0; j < NV; ++j) {
@@ -361,20 +363,22 @@ void loc_tokens(const float* loc, const float* w, const float* bias, float* x, u
 
 template <typename T>
 void layernorm(const float* x, const float* gamma, const float* beta, T* y, int64_t rows, int d, float eps,
-               cudaStream_t s) {
+               cudaStream_t s, const int* rows_dyn) {
   RETR_CHECK(d % 32 == 0 && d <= 1024, "LayerNorm width must be a multiple of 32, <= 1024");
   if (d == 256 || d == 512) {
     const unsigned grid = (unsigned)std::min<int64_t>(cdiv(rows, 8), 148 * 8);     // grid-stride, 8 warps per CTA
-    if (d == 256) layernorm_vec_kernel<T, 256><<<grid, 256, 0, s>>>(x, gamma, beta, y, rows, eps);
-    else layernorm_vec_kernel<T, 512><<<grid, 256, 0, s>>>(x, gamma, beta, y, rows, eps);
+    if (d == 256) layernorm_vec_kernel<T, 256><<<grid, 256, 0, s>>>(x, gamma, beta, y, rows, eps, rows_dyn);
+    else layernorm_vec_kernel<T, 512><<<grid, 256, 0, s>>>(x, gamma, beta, y, rows, eps, rows_dyn);
     LAUNCH_OK();
     return;
   }
   layernorm_kernel<T><<<blocks_for(rows, 8), 256, 0, s>>>(x, gamma, beta, y, rows, d, eps);
   LAUNCH_OK();
 }
-template void layernorm<float>(const float*, const float*, const float*, float*, int64_t, int, float, cudaStream_t);
-template void layernorm<bf16>(const float*, const float*, const float*, bf16*, int64_t, int, float, cudaStream_t);
+template void layernorm<float>(const float*, const float*, const float*, float*, int64_t, int, float, cudaStream_t,
+                               const int*);
+template void layernorm<bf16>(const float*, const float*, const float*, bf16*, int64_t, int, float, cudaStream_t,
+                              const int*);
 
 void embed_ln(const int64_t* ids, int64_t ld_ids, const float* e_word, const float* e_pos, const float* gamma,
               const float* beta, float* y, int B, int rows_per, int t0, const int* t0_dyn, int d, float eps,

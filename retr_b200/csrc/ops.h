@@ -41,10 +41,10 @@ void loc_tokens(const float* loc, const float* w, const float* bias, float* x, u
                 int n_loc, int per_scalar, int d, int S, int off, cudaStream_t s);
 
 // ---- transformer pieces -------------------------------------------------------------------------
-// y[r,:] = LN(x[r,:]) ; x fp32, y fp32|bf16
+// y[r,:] = LN(x[r,:]) ; x fp32, y fp32|bf16; rows_dyn (d = 256 / 512 only): stop at min(rows, *rows_dyn) rows
 template <typename T>
 void layernorm(const float* x, const float* gamma, const float* beta, T* y, int64_t rows, int d, float eps,
-               cudaStream_t s);
+               cudaStream_t s, const int* rows_dyn = nullptr);
 // y[b*rows_per+j, :] = LN_eps(E_word[ids[b*ld_ids + t0 + j]] + E_pos[t0 + j]); t0 = t0_dyn ? *t0_dyn : t0
 // (DecoderEmbeddings, models/transformer_modules.py:113-129)
 void embed_ln(const int64_t* ids, int64_t ld_ids, const float* e_word, const float* e_pos, const float* gamma,
@@ -59,6 +59,10 @@ struct AttnParams {
   const uint8_t* key_pad;                   // [B,Lk] non-zero = masked, or null
   int causal;
   float* probs;                             // optional [B,Lq,Lk] head-averaged probabilities
+  // packed (variable-length) self-attention, flash_attention_bf16 only: sample b owns rows seq_off[b] .. +seq_len[b] of
+  // q/k/v/out (no padded keys inside a sequence); Lq = Lk = the longest possible sequence (sizes the grid)
+  const int* seq_off;
+  const int* seq_len;
 };
 template <typename T> void attention(const AttnParams& p, cudaStream_t s);
 void flash_attention_bf16(const AttnParams& p, int dh, cudaStream_t s);   // attention_mma.cu
@@ -80,6 +84,13 @@ template <typename T>
 void kv_to_head_major(const T* kv, T* kh, T* vh, int B, int rows, int H, int dh, cudaStream_t s,
                       const int* dst_row = nullptr);
 // dst_row[b*S + j] = rank of key j among sample b's unpadded keys (-1 if padded); n_valid[b] = their number
+// packed encoder: exclusive offsets of the unpadded-token counts (off[B] = total), gather of the unpadded rows (row_pos =
+// position of each packed row inside its sequence, 0 past the total), scatter back to [B*S, d] with zero padding
+void seq_offsets(const int* n_valid, int B, int* off, cudaStream_t s);
+void pack_rows(const float* x, float* xp, const int* dst_row, const int* off, int* row_pos, int B, int S, int d,
+               cudaStream_t s);
+template <typename T>
+void unpack_rows(const T* xp, T* x, const int* dst_row, const int* off, int B, int S, int d, cudaStream_t s);
 void key_compaction(const uint8_t* pad, int B, int S, int* dst_row, int* n_valid, cudaStream_t s);
 // After the vocab GEMM+argmax of step i=*step: the bookkeeping of eval_utils/decode.py:70-79.
 void greedy_update(unsigned long long* argmax_keys, int64_t* caption, int max_len, int B, int eos, int* step,

@@ -564,6 +564,39 @@ def test_vocab_slice_kernel_matches_gemm_and_update(B, monkeypatch):
                                                             # tokens at the step where every row has finished)
 
 
+def test_packed_encoder_matches_padded_encoder(monkeypatch):
+    """The bf16 engine runs the encoder layers and the cross K/V projections on the UNPADDED tokens only (engine.cu:
+    encode, packed branch: rows gathered per sample, variable-length self-attention, GEMMs that stop at the device-side
+    row count).  Padded tokens are masked keys everywhere (models/ConcatTransformer.py:171-194, 220-257), so nothing
+    returned may change: memory at the unpadded positions, teacher-forced logits and greedy ids against the padded
+    encoder (RETR_ENCODER_PACKED=0) — the two differ only in the summation order of the attention's key tiles."""
+    kind, B = "CaptionGlobalLoc", 5
+    data, enc_in = synthetic_samples(kind, B, shard=37)
+    s = samples_of(kind, enc_in)
+    res = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("RETR_ENCODER_PACKED", flag)
+        model, sd, cfg = gpu_model(kind, "bf16", calibrated=True)
+        model.max_batch = B
+        with torch.no_grad():
+            logits = model(*s, data["caps"][:, :-1].cuda(), data["cap_masks"][:, :-1].cuda()).float().cpu()
+            eng = model.engine(B)
+            mem = eng.read_state("memory").cpu()
+            mask = eng.read_state("mask").cpu().bool()
+            ids = decode.greedy(s, model, max_len=128, device="cuda", bos_token=101, eos_token=102).cpu()
+        res[flag] = (logits, mem, mask, ids)
+    (l1, m1, k1, i1), (l0, m0, k0, i0) = res["1"], res["0"]
+    assert torch.equal(k1, k0) and bool(k1.any()) and not bool(k1.all(1).any())
+    valid = ~k1
+    assert (m1[valid] - m0[valid]).abs().max().item() <= 2e-2 * m0[valid].abs().max().item()
+    assert bool((m1[k1] == 0).all())                       # packed mode: padded rows come back as zeros
+    assert not torch.equal(m1[valid], m0[valid])           # the two encoders really are different schedules
+    assert (l1 - l0).abs().max().item() <= 1e-2 * l0.abs().max().item()
+    assert torch.equal(i1[:, :4], i0[:, :4])
+    print(f"packed vs padded encoder: {(i1 == i0).all(1).float().mean().item() * 100:.0f}% of sequences identical, "
+          f"memory diff {(m1[valid] - m0[valid]).abs().max().item() / m0[valid].abs().max().item():.2e}")
+
+
 def test_fused_stem_matches_three_launch_stem(monkeypatch):
     """stem_fused.cu (7x7/2 conv + FrozenBN + ReLU + 3x3/2 max-pool in one kernel) against the im2col -> GEMM -> max-pool
     path it replaces, through the whole bf16 backbone, and both against the oracle's fp32 feature map."""
