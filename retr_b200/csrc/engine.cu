@@ -289,7 +289,7 @@ void EngineT<T>::finalize() {
     }
   }
   if constexpr (std::is_same<T, bf16>::value) {
-    const bool want = getenv("RETR_STEM_FUSED") && atoi(getenv("RETR_STEM_FUSED")) != 0;   // opt-in: measured equal
+    const bool want = !(getenv("RETR_STEM_FUSED") && atoi(getenv("RETR_STEM_FUSED")) == 0);   // RETR_STEM_FUSED=0: im2col + GEMM + max-pool
     if (want && stem_fused_supported(desc.image_size, desc.image_size, stem_.cout, stem_.k, stem_.stride, stem_.pad)) {
       stem_wk_ = static_cast<bf16*>(dalloc((size_t)stem_fused_weight_elems() * 2));
       stem_fused_repack(raw(bb + "conv1.weight").dev, stem_wk_, 0);

@@ -11,6 +11,8 @@
 // 32-bit shared load per register: K is ordered (channel, row, tap) with the 7 taps padded to 8, so a register pair is
 // two adjacent input columns; weights as ldmatrix B fragments), applies scale/shift + ReLU, and max-pools from a
 // shared-memory tile.  Nothing but the image is read and nothing but the pooled activation is written.
+#include <algorithm>
+
 #include "ops.h"
 
 namespace retr {
@@ -45,41 +47,67 @@ __device__ __forceinline__ void sf_mma(float (&c)[4], const uint32_t (&a)[4], ui
 }
 
 // wk: [64][SF_K] bf16, k = (c * 7 + r) * 8 + s (s = 7 and group 21: zero)
+// Persistent: a CTA keeps the weights in shared memory and walks tiles blockIdx.x, + gridDim.x, ...; the NEXT tile's input
+// patch is loaded into registers before the current tile's MMAs start and written to shared memory after them (the
+// one-tile-per-CTA version spent 45 % of its time waiting for the patch loads: profiles/r2_ncu_full_stem_fused.txt).
+constexpr int SF_FILL = 3 * SF_IN * (SF_PW / 2);            // bf16 pairs of a patch
+constexpr int SF_FILL_IT = (SF_FILL + 255) / 256;           // 11 per thread
+
 __global__ void __launch_bounds__(256, 2)
 stem_fused_kernel(const float* __restrict__ img, const bf16* __restrict__ wk, const float* __restrict__ scale,
-                  const float* __restrict__ shift, bf16* __restrict__ out, int H, int W, int CH, int CW, int PH, int PW) {
+                  const float* __restrict__ shift, bf16* __restrict__ out, int H, int W, int CH, int CW, int PH, int PW,
+                  int total_tiles) {
   extern __shared__ __align__(16) uint8_t sf_raw[];
   SfSmem& sm = *reinterpret_cast<SfSmem*>(sf_raw);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, c4 = lane & 3;
-  const int tiles_x = PW / SF_PT;
-  const int ty = blockIdx.x / tiles_x, tx = blockIdx.x - ty * tiles_x, n = blockIdx.y;
-  const int p0y = ty * SF_PT, p0x = tx * SF_PT;            // first pooled pixel of the tile
-  const int c0y = 2 * p0y - 1, c0x = 2 * p0x - 1;          // first conv pixel (max-pool 3x3/2 pad 1)
-  const int i0y = 2 * c0y - 3, i0x = 2 * c0x - 3;          // first input pixel (conv 7x7/2 pad 3)
-  const float* base = img + (int64_t)n * 3 * H * W;
-  // weights + BN (independent of the previous kernel) and the input patch
+  const int tiles_x = PW / SF_PT, tiles_img = tiles_x * (PH / SF_PT);
+  // weights + BN: once per CTA
   for (int idx = tid; idx < 64 * (SF_K / 8); idx += 256) {
     const int r = idx / (SF_K / 8), ch = idx - r * (SF_K / 8);
     *reinterpret_cast<uint4*>(&sm.w[r][ch * 8]) = __ldg(reinterpret_cast<const uint4*>(wk + (int64_t)r * SF_K + ch * 8));
   }
   if (tid < 64) { sm.scale[tid] = __ldg(scale + tid); sm.shift[tid] = __ldg(shift + tid); }
-  for (int idx = tid; idx < 3 * SF_IN * (SF_PW / 2); idx += 256) {
-    const int cr = idx / (SF_PW / 2), q = idx - cr * (SF_PW / 2);
-    const int c = cr / SF_IN, r = cr - c * SF_IN, iy = i0y + r, ix = i0x + 2 * q;
-    float v0 = 0.f, v1 = 0.f;
-    if (iy >= 0 && iy < H) {
-      const float* rowp = base + ((int64_t)c * H + iy) * W;
-      if (ix >= 0 && ix < W) v0 = __ldg(rowp + ix);
-      if (ix + 1 >= 0 && ix + 1 < W) v1 = __ldg(rowp + ix + 1);
+  float pv[SF_FILL_IT][2];
+  auto load_patch = [&](int tile) {
+    const int n = tile / tiles_img, t = tile - n * tiles_img, ty = t / tiles_x, tx = t - ty * tiles_x;
+    const int i0y = 2 * (2 * ty * SF_PT - 1) - 3, i0x = 2 * (2 * tx * SF_PT - 1) - 3;
+    const float* base = img + (int64_t)n * 3 * H * W;
+#pragma unroll
+    for (int it = 0; it < SF_FILL_IT; ++it) {
+      const int idx = tid + it * 256;
+      const int cr = idx / (SF_PW / 2), q = idx - cr * (SF_PW / 2);
+      const int c = cr / SF_IN, r = cr - c * SF_IN, iy = i0y + r, ix = i0x + 2 * q;
+      float v0 = 0.f, v1 = 0.f;
+      if (idx < SF_FILL && iy >= 0 && iy < H) {
+        const float* rowp = base + ((int64_t)c * H + iy) * W;
+        if (ix >= 0 && ix < W) v0 = __ldg(rowp + ix);
+        if (ix + 1 >= 0 && ix + 1 < W) v1 = __ldg(rowp + ix + 1);
+      }
+      pv[it][0] = v0; pv[it][1] = v1;
     }
-    *reinterpret_cast<__nv_bfloat162*>(&sm.patch[c][r][2 * q]) = __floats2bfloat162_rn(v0, v1);
-  }
+  };
+  auto store_patch = [&]() {
+#pragma unroll
+    for (int it = 0; it < SF_FILL_IT; ++it) {
+      const int idx = tid + it * 256;
+      if (idx < SF_FILL)
+        *reinterpret_cast<__nv_bfloat162*>(&sm.patch[0][0][0] + 2 * idx) = __floats2bfloat162_rn(pv[it][0], pv[it][1]);
+    }
+  };
+  if ((int)blockIdx.x < total_tiles) { load_patch(blockIdx.x); store_patch(); }
   __syncthreads();
 
-  // implicit GEMM: M = 289 conv pixels (19 m-tiles over 8 warps), N = 64, K = 176; one m-tile at a time (32 accumulator
-  // registers: two CTAs per SM, so that one CTA's fill / epilogue / pooling hides under the other's MMAs)
   const uint32_t w_base = (uint32_t)__cvta_generic_to_shared(&sm.w[(lane >> 4) * 8 + (lane & 7)][((lane >> 3) & 1) * 8]);
   const bf16* patch0 = &sm.patch[0][0][0];
+#pragma unroll 1
+  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+  const int n = tile / tiles_img, t_in = tile - n * tiles_img, ty = t_in / tiles_x, tx = t_in - ty * tiles_x;
+  const int p0y = ty * SF_PT, p0x = tx * SF_PT;            // first pooled pixel of the tile
+  const int c0y = 2 * p0y - 1, c0x = 2 * p0x - 1;          // first conv pixel (max-pool 3x3/2 pad 1)
+  const bool has_next = tile + (int)gridDim.x < total_tiles;
+  if (has_next) load_patch(tile + gridDim.x);              // in flight under this tile's MMAs
+  // implicit GEMM: M = 289 conv pixels (19 m-tiles over 8 warps), N = 64, K = 176; one m-tile at a time (32 accumulator
+  // registers: two CTAs per SM, so that one CTA's fill / epilogue / pooling hides under the other's MMAs)
 #pragma unroll 1
   for (int mt = warp; mt < SF_MT; mt += 8) {
     float acc[8][4];
@@ -127,7 +155,8 @@ stem_fused_kernel(const float* __restrict__ img, const bf16* __restrict__ wk, co
       }
     }
   }
-  __syncthreads();
+  __syncthreads();                                         // conv tile complete, every read of the patch done
+  if (has_next) store_patch();
   // 3x3/2 max-pool: pooled (py, px) covers conv tile rows 2py .. 2py+2; one 8-channel chunk per thread item
   for (int idx = tid; idx < SF_PT * SF_PT * 8; idx += 256) {
     const int chunk = idx & 7, pp = idx >> 3, py = pp / SF_PT, px = pp - py * SF_PT;
@@ -152,6 +181,8 @@ stem_fused_kernel(const float* __restrict__ img, const bf16* __restrict__ wk, co
     oh[0] = m[0]; oh[1] = m[1]; oh[2] = m[2]; oh[3] = m[3];
     *reinterpret_cast<uint4*>(out + (((int64_t)n * PH + p0y + py) * PW + p0x + px) * 64 + chunk * 8) = o;
   }
+  __syncthreads();                                         // conv tile free again, next patch visible
+  }
 }
 
 // OIHW fp32 [64,3,7,7] -> [64][SF_K] bf16 in the kernel's K order
@@ -165,6 +196,16 @@ __global__ void stem_repack_kernel(const float* __restrict__ w, bf16* __restrict
     v = w[((o * 3 + c) * 7 + r) * 7 + s];
   }
   out[idx] = __float2bfloat16_rn(v);
+}
+
+int sm_count_cached() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    CUDA_OK(cudaGetDevice(&dev));
+    CUDA_OK(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+  }
+  return n;
 }
 
 }  // namespace
@@ -188,9 +229,10 @@ void stem_fused(const float* img, const bf16* wk, const float* scale, const floa
     configured = true;
   }
   const int CH = (H + 6 - 7) / 2 + 1, CW = (W + 6 - 7) / 2 + 1, PH = (CH + 2 - 3) / 2 + 1, PW = (CW + 2 - 3) / 2 + 1;
-  RETR_CHECK(nimg <= 65535, "stem_fused: too many images per launch");
-  stem_fused_kernel<<<dim3((unsigned)((PH / SF_PT) * (PW / SF_PT)), (unsigned)nimg), 256, sizeof(SfSmem), s>>>(
-      img, wk, scale, shift, out, H, W, CH, CW, PH, PW);
+  const int64_t total = nimg * (PH / SF_PT) * (PW / SF_PT);
+  RETR_CHECK(total < (1ll << 31), "stem_fused: too many tiles per launch");
+  const int grid = (int)std::min<int64_t>(total, 2ll * sm_count_cached());
+  stem_fused_kernel<<<grid, 256, sizeof(SfSmem), s>>>(img, wk, scale, shift, out, H, W, CH, CW, PH, PW, (int)total);
   LAUNCH_OK();
 }
 
