@@ -5,7 +5,7 @@ import csv, hashlib, json, os, sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 path = sys.argv[1]
-n_launch = int(sys.argv[2]) if len(sys.argv) > 2 else 108
+n_launch = int(sys.argv[2]) if len(sys.argv) > 2 else 105      # fused stem + 104 convolutions
 images = int(sys.argv[3]) if len(sys.argv) > 3 else 512
 rows = list(csv.DictReader(l for l in open(path) if not l.startswith("==")))
 per = {}
@@ -18,7 +18,7 @@ ids = sorted(per)[:n_launch]
 rd = sum(per[i]["dram__bytes_read.sum"] for i in ids)
 wr = sum(per[i]["dram__bytes_write.sum"] for i in ids)
 ns = sum(per[i]["gpu__time_duration.sum"] for i in ids)
-sources = ["retr_b200/csrc/gemm_sm100.cu"]
+sources = ["retr_b200/csrc/gemm_sm100.cu", "retr_b200/csrc/stem_fused.cu"]
 h = hashlib.sha256()
 for f in sources:
     h.update(open(os.path.join(ROOT, f), "rb").read())

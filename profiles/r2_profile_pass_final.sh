@@ -10,8 +10,11 @@ ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"decode_stack
 ncu --set full --clock-control none --import-source on -k regex:vocab_argmax_kernel -s 60 -c 1 -o gpurun_out/r2f_full_vocab_argmax -f $B > gpurun_out/ncu3.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:gemm_tcgen05 -s 28 -c 3 -o gpurun_out/r2f_full_layer3_convs -f $B > gpurun_out/ncu4.log 2>&1
 # (3) DRAM traffic of the backbone phase (bench.py roofline_backbone.traffic)
-ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:"gemm_tcgen05|stem_im2col|maxpool" -c 110 --csv --log-file gpurun_out/r2f_backbone_dram.csv $B > gpurun_out/ncu5.log 2>&1
-for r in r2f_full_vocab_argmax r2f_full_layer3_convs; do
+ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:"gemm_tcgen05|stem_im2col|stem_fused|maxpool" -c 110 --csv --log-file gpurun_out/r2f_backbone_dram.csv $B > gpurun_out/ncu5.log 2>&1
+# (4) decode stack kernel at a mid-sequence step (bench.py roofline.traffic) and the persistent fused stem
+ncu --set full --clock-control none --import-source on -k regex:decode_stack_kernel -s 60 -c 1 -o gpurun_out/r2f_full_decode_stack -f $B > gpurun_out/ncu6.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:stem_fused_kernel -s 1 -c 1 -o gpurun_out/r2f_full_stem_fused_v3 -f $B > gpurun_out/ncu7.log 2>&1
+for r in r2f_full_vocab_argmax r2f_full_layer3_convs r2f_full_decode_stack r2f_full_stem_fused_v3; do
   ncu -i gpurun_out/$r.ncu-rep --page raw --csv > gpurun_out/$r.raw.csv 2>/dev/null
 done
 ls -la gpurun_out | tail -12

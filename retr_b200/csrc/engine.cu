@@ -81,6 +81,7 @@ template <typename T> struct EncLayer {
   float *ln1_g, *ln1_b, *ln2_g, *ln2_b;
   Linear<T> qkv, out, ff1, ff2;
   float* rb_qkv;            // [S, 3d]: pos.Wqk^T + b_qk | b_v
+  float* b_v_tail;          // [3d]: 0 | b_v (with GemmParams::rowbias_cols = 2d the V columns skip the table)
 };
 template <typename T> struct DecLayer {
   float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *ln3_g, *ln3_b;
@@ -88,6 +89,7 @@ template <typename T> struct DecLayer {
   float* rb_s_qkv;          // [T, 3d]: E_pos.Wqk^T + b_qk | b_v
   float* rb_c_q;            // [T, d] : E_pos.Wq^T + b_q
   float* rb_c_kv;           // [S, 2d]: pos.Wk^T + b_k | b_v
+  float* b_cv_tail;         // [2d]: 0 | b_v
 };
 
 template <typename T>
@@ -116,6 +118,7 @@ class EngineT final : public EngineBase {
   Conv<T> conv(const std::string& wname, const std::string& bn, int stride, int pad, int dil);
   float* pos_bias_table(const float* pos, int rows, const RawWeight& w, const RawWeight& b, int row0, int n_proj,
                         int n_total);
+  float* bias_tail(const RawWeight& b, int row0, int n_proj, int n_total);   // [n_total]: 0 | b[row0+n_proj ...]
   void run_conv(const Conv<T>& c, const T* in, int64_t n, int H, int W, T* out, const T* residual, int relu,
                 int* OH, int* OW, cudaStream_t s);
   void backbone(const float* img, int64_t n, T* feat, cudaStream_t s, const float* img2 = nullptr, int64_t n2 = 0);
@@ -178,7 +181,7 @@ class EngineT final : public EngineBase {
   // the whole decoder stack of a decode step as ONE cluster kernel (decode_stack.cu): its own chunked, swizzled caches
   bool stack_decode_ = false;
   // packed encoder (encode): only the unpadded tokens run through the encoder layers and the cross K/V projections
-  bool packed_encoder_ = false, enc_packed_ = false;    // enabled / memory_ and ckv_ currently hold packed rows
+  bool packed_encoder_ = false, enc_packed_ = false, src_in_x_ = false;    // enabled / memory_ and ckv_ currently hold packed rows
   float* xp_ = nullptr;                                // packed residual stream [<= B*S, d]
   int *seq_off_ = nullptr, *row_pos_ = nullptr;        // [B + 1] first packed row per sample (+ total); [B*S] position of a row
   void materialize_unpacked(cudaStream_t s);
@@ -258,6 +261,14 @@ float* EngineT<T>::pos_bias_table(const float* pos, int rows, const RawWeight& w
 }
 
 template <typename T>
+float* EngineT<T>::bias_tail(const RawWeight& b, int row0, int n_proj, int n_total) {
+  float* t = static_cast<float*>(dalloc((size_t)n_total * 4));
+  CUDA_OK(cudaMemset(t, 0, (size_t)n_total * 4));
+  CUDA_OK(cudaMemcpy(t + n_proj, b.dev + row0 + n_proj, (size_t)(n_total - n_proj) * 4, cudaMemcpyDeviceToDevice));
+  return t;
+}
+
+template <typename T>
 void EngineT<T>::finalize() {
   RETR_CHECK(!finalized_, "finalize called twice");
   const int d = desc.d_model;
@@ -330,6 +341,7 @@ void EngineT<T>::finalize() {
     e.ff2 = linear(p + "ff.sublayer.2.weight", p + "ff.sublayer.2.bias");
     e.rb_qkv = pos_bias_table(pe, S, raw(p + "self_attn.sublayer.in_proj_weight"),
                               raw(p + "self_attn.sublayer.in_proj_bias"), 0, 2 * d, 3 * d);
+    e.b_v_tail = bias_tail(raw(p + "self_attn.sublayer.in_proj_bias"), 0, 2 * d, 3 * d);
     enc_.push_back(e);
   }
   if (desc.pre_norm) { enc_norm_g_ = raw("transformer.encoder.norm.weight").dev; enc_norm_b_ = raw("transformer.encoder.norm.bias").dev; }
@@ -350,6 +362,7 @@ void EngineT<T>::finalize() {
     e.rb_s_qkv = pos_bias_table(e_pos_, Tn, raw(sa + "in_proj_weight"), raw(sa + "in_proj_bias"), 0, 2 * d, 3 * d);
     e.rb_c_q = pos_bias_table(e_pos_, Tn, raw(ca + "in_proj_weight"), raw(ca + "in_proj_bias"), 0, d, d);
     e.rb_c_kv = pos_bias_table(pe, S, raw(ca + "in_proj_weight"), raw(ca + "in_proj_bias"), d, d, 2 * d);
+    e.b_cv_tail = bias_tail(raw(ca + "in_proj_bias"), d, d, 2 * d);
     dec_.push_back(e);
   }
   dec_norm_g_ = raw("transformer.decoder.norm.weight").dev; dec_norm_b_ = raw("transformer.decoder.norm.bias").dev;
@@ -605,7 +618,6 @@ void EngineT<T>::encode(int B, const float* t_img, const uint8_t* t_mask, const 
   if (desc.loc_in_dim)
     loc_tokens(loc, loc_w_, loc_b_, x_, tok_mask_, B, desc.n_loc, desc.loc_in_dim == 1, d, S, off_loc, s);
   const int64_t Me = (int64_t)B * S;
-  CUDA_OK(cudaMemcpyAsync(src_copy_, x_, Me * d * 4, cudaMemcpyDeviceToDevice, s));
   key_compaction(tok_mask_, B, S, cross_dst_, cross_nvalid_, s);
   // Packed encoder: a padded token is never a key (src_key_padding_mask in every encoder layer, memory_key_padding_mask
   // in every decoder layer: models/ConcatTransformer.py:171-194, 220-257) and every other operation is row-wise, so
@@ -614,6 +626,9 @@ void EngineT<T>::encode(int B, const float* t_img, const uint8_t* t_mask, const 
   // the GEMMs are sized for B*S rows and stop after ceil(*m_dyn / 128) row blocks, the positional row bias is looked
   // up through row_pos_, and the self-attention runs on variable-length sequences without any key mask.
   const bool packed = packed_encoder_ && !att_enc_capture;
+  // the encoder input for read_state("src"): the packed encoder leaves x_ untouched, the padded one works in place
+  src_in_x_ = packed;
+  if (!packed) CUDA_OK(cudaMemcpyAsync(src_copy_, x_, Me * d * 4, cudaMemcpyDeviceToDevice, s));
   float* xs = x_;
   const int* m_dyn = nullptr;
   const int* ridx = nullptr;
@@ -628,6 +643,7 @@ void EngineT<T>::encode(int B, const float* t_img, const uint8_t* t_mask, const 
     layernorm<T>(xs, e.ln1_g, e.ln1_b, n_, Me, d, 1e-5f, s, m_dyn);
     GemmParams p = lin(e.qkv, n_, Me, qkv_);
     p.rowbias = e.rb_qkv; p.rowbias_period = S; p.rowbias_idx = ridx; p.m_dyn = m_dyn;
+    if (packed) { p.rowbias_cols = 2 * d; p.bias = e.b_v_tail; }      // the V third takes its bias from a vector
     gemm<T>(p, s);
     AttnParams a{};
     a.q = qkv_; a.k = qkv_ + d; a.v = qkv_ + 2 * d; a.out = att_;
@@ -657,6 +673,7 @@ void EngineT<T>::encode(int B, const float* t_img, const uint8_t* t_mask, const 
   for (int l = 0; l < desc.dec_layers; ++l) {
     GemmParams p = lin(dec_[l].c_kv, memory_, Me, ckv_[l]);
     p.rowbias = dec_[l].rb_c_kv; p.rowbias_period = S; p.rowbias_idx = ridx; p.m_dyn = m_dyn;
+    if (packed) { p.rowbias_cols = d; p.bias = dec_[l].b_cv_tail; }
     gemm<T>(p, s);
     if constexpr (std::is_same<T, bf16>::value) {
       if (stack_decode_) {
@@ -1028,7 +1045,7 @@ void EngineT<T>::read_state(const std::string& what, void* dst, int64_t bytes, c
   else if (what == "feat_g") { RETR_CHECK(desc.n_images == 2, "no context images"); conv_out(feat_ + B * g2 * cfeat, B * g2 * cfeat); }
   else if (what == "src") {
     RETR_CHECK(bytes >= B * S * d * 4, "destination too small for 'src'");
-    CUDA_OK(cudaMemcpyAsync(dst, src_copy_, B * S * d * 4, cudaMemcpyDeviceToDevice, s));
+    CUDA_OK(cudaMemcpyAsync(dst, src_in_x_ ? x_ : src_copy_, B * S * d * 4, cudaMemcpyDeviceToDevice, s));
   } else if (what == "mask") {
     RETR_CHECK(bytes >= B * S, "destination too small for 'mask'");
     CUDA_OK(cudaMemcpyAsync(dst, tok_mask_, B * S, cudaMemcpyDeviceToDevice, s));

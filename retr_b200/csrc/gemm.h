@@ -37,6 +37,9 @@ struct GemmParams {
   int c_group = 0, c_group_stride = 0;
   // If set, every row uses rowbias[*rowbias_dyn] (decode: the device-side step counter).
   const int* rowbias_dyn = nullptr;
+  // > 0: only columns [0, rowbias_cols) carry a per-row bias (a multiple of 32); the columns after it take `bias` alone.
+  // Saves the epilogue's gather of table entries that are the same for every row (the V third of a q|k|v projection).
+  int rowbias_cols = 0;
   // If set, row m uses rowbias[rowbias_idx[m]] (packed encoder: the token's position in its sequence).
   const int* rowbias_idx = nullptr;
   // If set, only the first *m_dyn rows (<= M) are computed: M sizes the tensor maps and the grid, the persistent loop

@@ -59,6 +59,7 @@ struct KArgs {
   const int* rowbias_dyn;
   const int* rowbias_idx;
   const int* m_dyn;
+  int rowbias_cols;
   int stages;            // smem ring depth (runtime: depends on the epilogue staging in use)
   int tma_epi;           // epilogue through smem staging + TMA store
   int res_tma;           // residual sub-tiles arrive by TMA (implies tma_epi)
@@ -118,7 +119,7 @@ __device__ __forceinline__ void epilogue_chunk(const KArgs& a, uint32_t (&r)[32]
 #pragma unroll
     for (int j = 0; j < 32; ++j) if (j < nv) v[j] += __ldg(a.bias + n0 + j);
   }
-  if (a.rowbias) {
+  if (a.rowbias && n0 < a.rowbias_cols) {
     const float* rb = a.rowbias + rb_row * a.N + n0;
     if (a.vecRB && nv == 32) {
 #pragma unroll
@@ -230,7 +231,7 @@ __device__ __forceinline__ void epilogue_chunk_staged(const KArgs& a, uint32_t (
       v[4 * j] += t.x; v[4 * j + 1] += t.y; v[4 * j + 2] += t.z; v[4 * j + 3] += t.w;
     }
   }
-  if (a.rowbias) {
+  if (a.rowbias && n0 < a.rowbias_cols) {
     const float* rb = a.rowbias + rb_row * a.N + n0;
     if (a.vecRB && n0 + 32 <= a.N) {
 #pragma unroll
@@ -944,6 +945,8 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
   ka.argmax_out = p.argmax_out;
   ka.c_group = p.c_group; ka.c_group_stride = p.c_group_stride; ka.rowbias_dyn = p.rowbias_dyn;
   ka.rowbias_idx = p.rowbias_idx; ka.m_dyn = p.m_dyn;
+  RETR_CHECK(p.rowbias_cols % 32 == 0 && p.rowbias_cols <= p.N, "rowbias_cols: a multiple of 32, at most N");
+  ka.rowbias_cols = p.rowbias_cols > 0 ? p.rowbias_cols : p.N;
   RETR_CHECK(!p.m_dyn || p.split_k == 1, "m_dyn: no split-K");
   const int64_t cbytes = p.out_fp32 ? 4 : 2, rbytes = p.res_fp32 ? 4 : 2;
   ka.vecC = p.C && (reinterpret_cast<uintptr_t>(p.C) % 16 == 0) && (p.ldc * cbytes) % 16 == 0;
