@@ -60,6 +60,8 @@ struct KArgs {
   const int* rowbias_idx;
   const int* m_dyn;
   int rowbias_cols;
+  int epi_mode;          // bf16 staged epilogue: 0 general, 1-3 the specialised forms (epilogue_chunk_lean)
+  int warp_store;        // staged epilogue: every warp stores its own 32 rows (no CTA-level barriers in the epilogue)
   int stages;            // smem ring depth (runtime: depends on the epilogue staging in use)
   int tma_epi;           // epilogue through smem staging + TMA store
   int res_tma;           // residual sub-tiles arrive by TMA (implies tma_epi)
@@ -204,6 +206,63 @@ __device__ __forceinline__ void epilogue_chunk(const KArgs& a, uint32_t (&r)[32]
         for (int j = 0; j < 32; ++j) if (j < nv) cp[j] = __float2bfloat16_rn(v[j]);
       }
     }
+  }
+}
+
+// Specialised forms of epilogue_chunk_staged<bf16> for the epilogues the hot path is made of; the general function
+// carries every feature behind run-time branches (~650 instructions per chunk in the binary), and the epilogue is the
+// pacing side of every GEMM with K <= 512: FF1 118 -> 96 us with the lean form.
+//   MODE 1: bias, ReLU floor `lo` (0 or -inf)                      linears of the encoder / head
+//   MODE 2: scale, bias, ReLU floor                                 conv1 / conv2 / downsample (FrozenBN folded)
+//   MODE 3: scale, bias, + bf16 residual sub-tile, ReLU after       conv3 of a bottleneck
+//   MODE 4: bias + per-row bias `rowb` (null past rowbias_cols)     q|k|v and k|v projections (positions)
+template <int MODE>
+__device__ __forceinline__ void epilogue_chunk_lean(const uint32_t (&r)[32], const float* __restrict__ scale,
+                                                    const float* __restrict__ bias, float lo, int row, int chunk16,
+                                                    const uint8_t* rsm, uint8_t* csm, const float* __restrict__ rowb = nullptr) {
+  const uint32_t swz = (uint32_t)(row & 7);
+  uint8_t* crow = csm + row * 128;
+  const uint8_t* rrow = rsm + row * 128;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[8 * c + j]);
+    const float4 b0 = *reinterpret_cast<const float4*>(bias + 8 * c), b1 = *reinterpret_cast<const float4*>(bias + 8 * c + 4);
+    if (MODE >= 2) {
+      const float4 s0 = *reinterpret_cast<const float4*>(scale + 8 * c), s1 = *reinterpret_cast<const float4*>(scale + 8 * c + 4);
+      // multiply, THEN add, each rounded: what the general epilogues compute (their scale and bias steps sit behind
+      // separate branches and are never contracted), so a row's result does not depend on which epilogue its launch
+      // shape selects (batch invariance: test_generate_host_matches_device_path)
+      const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+      const float bi[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = __fadd_rn(__fmul_rn(v[j], sc[j]), bi[j]);
+    } else {
+      v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w; v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+    }
+    if (MODE == 4 && rowb) {
+      const float4 r0 = __ldg(reinterpret_cast<const float4*>(rowb + 8 * c)), r1 = __ldg(reinterpret_cast<const float4*>(rowb + 8 * c + 4));
+      v[0] += r0.x; v[1] += r0.y; v[2] += r0.z; v[3] += r0.w; v[4] += r1.x; v[5] += r1.y; v[6] += r1.z; v[7] += r1.w;
+    }
+    const uint32_t off = ((uint32_t)(chunk16 + c) ^ swz) << 4;
+    if (MODE == 3) {
+      const uint4 t = *reinterpret_cast<const uint4*>(rrow + off);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&t);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float2 f = __bfloat1622float2(h[q]);
+        v[2 * q] = fmaxf(v[2 * q] + f.x, 0.f); v[2 * q + 1] = fmaxf(v[2 * q + 1] + f.y, 0.f);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], lo);
+    }
+    uint4 o;
+    __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) oh[q] = __floats2bfloat162_rn(v[2 * q], v[2 * q + 1]);
+    *reinterpret_cast<uint4*>(crow + off) = o;
   }
 }
 
@@ -500,7 +559,89 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                              : a.rowbias_idx ? (m < a.M ? (int64_t)__ldg(a.rowbias_idx + m) : 0)
                                              : (m % a.rowbias_period);
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
-      if (a.tma_epi) {
+      if (a.tma_epi && a.warp_store) {
+        // Warp-autonomous staged epilogue.  The accumulator leaves TMEM at 64 B/cycle (a 128 x 256 fp32 tile: 2048
+        // cycles, as long as its MMAs with K = 256), so the epilogue is the pacing side of every GEMM with K <= 512 and
+        // anything that idles the TMEM port costs directly: here a warp owns rows 32q .. 32q+31 of its group's
+        // sub-tiles end to end — tcgen05.ld, scale/bias straight from global (L1 broadcast), swizzled staging slice,
+        // its own 32-row TMA store — with no barrier wider than the warp.
+        ptx::mbar_wait(&tfull[as], aph);
+        ptx::tc_fence_after_sync();
+        const int n_end = min(a.N, (n_blk + 1) * BN);
+        uint8_t* cbuf = cst + (EG == 2 ? grp : 0) * EPI_TILE_BYTES;
+        // sub-tile prologue / epilogue shared by both output types
+        auto sub_begin = [&](uint32_t rb, uint32_t rph) -> const uint8_t* {
+          const uint8_t* rbuf = nullptr;
+          if (a.res_tma) {
+            ptx::mbar_wait(&rfull[rb], rph);
+            rbuf = rst + rb * EPI_TILE_BYTES;
+          }
+          if (lane == 0) ptx::bulk_wait_read<0>();              // this warp's previous store has read its slice
+          __syncwarp();
+          return rbuf;
+        };
+        auto sub_end = [&](uint32_t rb, int n0) {
+          if (a.res_tma) ptx::mbar_arrive(&rempty[rb]);
+          ptx::fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            ptx::tma_store_2d(&tmC, cbuf + q * 32 * 128, n0, m_blk * BM + q * 32);
+            ptx::bulk_commit();
+          }
+        };
+        if (a.out_fp32) {
+          for (int n0 = n_blk * BN; n0 < n_end; n0 += EC, ++cit) {
+            if (EG == 2 && (int)(cit & 1) != grp) continue;      // the other group's sub-tile
+            const uint32_t rb = a.res_tma ? cit % RB : 0, rph = a.res_tma ? (cit / RB) & 1 : 0;
+            const uint8_t* rbuf = sub_begin(rb, rph);
+            uint32_t r[32];
+            ptx::tmem_ld_32x32(t_row + (n0 - n_blk * BN), r);
+            ptx::tmem_ld_wait();
+            epilogue_chunk_staged<float>(a, r, a.scale ? a.scale + n0 : nullptr, a.bias ? a.bias + n0 : nullptr, rb_row, n0,
+                                         row, 0, rbuf, cbuf);
+            sub_end(rb, n0);
+          }
+        } else {
+          // bf16: a sub-tile is two 32-column halves.  The TMEM loads run one half AHEAD of the arithmetic (ping-pong
+          // register sets, also across the sub-tiles of the tile), so the port has a request from this warp queued
+          // while the warp converts, stages and stores — without it all eight warps load, then all eight compute.
+          const int first = n_blk * BN + (EG == 2 ? grp : 0) * EC, step = EG * EC;
+          const float lo = a.relu == 1 ? 0.f : -INFINITY;
+          auto chunk_bf16 = [&](uint32_t (&rr)[32], int nc, int chunk16, const uint8_t* rbuf) {
+            switch (a.epi_mode) {                                 // warp-uniform
+              case 1: epilogue_chunk_lean<1>(rr, nullptr, a.bias + nc, lo, row, chunk16, rbuf, cbuf); break;
+              case 2: epilogue_chunk_lean<2>(rr, a.scale + nc, a.bias + nc, lo, row, chunk16, rbuf, cbuf); break;
+              case 3: epilogue_chunk_lean<3>(rr, a.scale + nc, a.bias + nc, lo, row, chunk16, rbuf, cbuf); break;
+              case 4:
+                epilogue_chunk_lean<4>(rr, nullptr, a.bias + nc, lo, row, chunk16, rbuf, cbuf,
+                                       nc < a.rowbias_cols ? a.rowbias + rb_row * a.N + nc : nullptr);
+                break;
+              default:
+                epilogue_chunk_staged<bf16>(a, rr, a.scale ? a.scale + nc : nullptr, a.bias ? a.bias + nc : nullptr, rb_row,
+                                            nc, row, chunk16, rbuf, cbuf);
+            }
+          };
+          uint32_t ra[32], rc[32];
+          if (first < n_end) ptx::tmem_ld_32x32(t_row + (first - n_blk * BN), ra);
+          for (int n0 = first; n0 < n_end; n0 += step) {
+            const uint32_t sub = cit + (uint32_t)((n0 - n_blk * BN) / EC);
+            const uint32_t rb = a.res_tma ? sub % RB : 0, rph = a.res_tma ? (sub / RB) & 1 : 0;
+            const int col = n0 - n_blk * BN;
+            ptx::tmem_ld_wait();
+            ptx::tmem_ld_32x32(t_row + col + 32, rc);
+            const uint8_t* rbuf = sub_begin(rb, rph);
+            chunk_bf16(ra, n0, 0, rbuf);
+            ptx::tmem_ld_wait();
+            if (n0 + step < n_end) ptx::tmem_ld_32x32(t_row + col + step, ra);
+            chunk_bf16(rc, n0 + 32, 4, rbuf);
+            sub_end(rb, n0);
+          }
+          cit += (uint32_t)((n_end - n_blk * BN + EC - 1) / EC);
+          ptx::tmem_ld_wait();
+        }
+        ptx::tc_fence_before_sync();
+        ptx::mbar_arrive(&tempty[as]);
+      } else if (a.tma_epi) {
         // per-tile column parameters -> smem (all epilogue threads)
         ptx::named_bar_sync(2, 128 * EG);
         for (int i = tid_all; i < BN; i += 128 * EG) {
@@ -567,7 +708,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           atomicMax(a.argmax_out + m, pack_argmax(best_v, best_i));
       }
     }
-    if (a.tma_epi && tid_e == 0) ptx::bulk_wait_read<0>();   // smem must outlive the last store's read
+    if (a.tma_epi && (a.warp_store ? lane == 0 : tid_e == 0)) ptx::bulk_wait_read<0>();   // smem must outlive the last store's read
   } else if (GATHER && warp >= 8) {
     // ===== im2col gather producer: one thread per tile row =====
     const int row = threadIdx.x - 256;
@@ -1013,7 +1154,20 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
                     : im2col ? make_tmap_im2col(p.A, n_img, p.conv)
                     : gather ? tmB
                              : make_tmap_2d(p.A, p.M, p.K, p.lda, BM);
-  CUtensorMap tmC = ka.tma_epi ? make_tmap_2d(p.C, p.M, p.N, p.ldc, BM, p.out_fp32) : tmB;
+  static const bool warp_store_on = !(getenv("RETR_GEMM_WARP_STORE") && atoi(getenv("RETR_GEMM_WARP_STORE")) == 0);
+  ka.warp_store = ka.tma_epi && warp_store_on && p.N % 64 == 0;
+  ka.epi_mode = 0;
+  static const bool lean_on = !(getenv("RETR_GEMM_LEAN_EPILOGUE") && atoi(getenv("RETR_GEMM_LEAN_EPILOGUE")) == 0);
+  if (lean_on && ka.warp_store && !p.out_fp32 && p.bias && p.rowbias && ka.vecRB && !p.scale && !p.residual && p.relu <= 1 &&
+      reinterpret_cast<uintptr_t>(p.bias) % 16 == 0)
+    ka.epi_mode = 4;
+  if (lean_on && ka.warp_store && !p.out_fp32 && p.bias && !p.rowbias && p.relu <= 2 &&
+      reinterpret_cast<uintptr_t>(p.bias) % 16 == 0 && (!p.scale || reinterpret_cast<uintptr_t>(p.scale) % 16 == 0)) {
+    if (!p.scale && !p.residual && p.relu <= 1) ka.epi_mode = 1;
+    else if (p.scale && !p.residual && p.relu <= 1) ka.epi_mode = 2;
+    else if (p.scale && ka.res_tma && !ka.res_fp32 && p.relu == 2) ka.epi_mode = 3;
+  }
+  CUtensorMap tmC = ka.tma_epi ? make_tmap_2d(p.C, p.M, p.N, p.ldc, ka.warp_store ? 32 : BM, p.out_fp32) : tmB;
   CUtensorMap tmR = ka.res_tma ? make_tmap_2d(ka.residual, p.M, p.N, ka.ldr, BM, ka.res_fp32 != 0) : tmB;
   // a capped grid shares the GPU with another context: an early-launched dependent grid would park its CTAs on
   // exactly the SMs the cap leaves free, so programmatic dependent launch is off then
