@@ -773,6 +773,30 @@ __global__ void kv_to_chunked_kernel(const bf16* __restrict__ kv, bf16* __restri
   *reinterpret_cast<uint4*>(dst) = val;
 }
 
+// All decoder layers at once from the batched projections: k_all / v_all are [rows, L*256] (layer l in columns
+// l*256 ..), rows packed per sample (src_off); out[l] as kv_to_chunked writes it.
+struct ChunkedOut { bf16* p[DS_MAX_LAYERS]; };
+__global__ void kv_all_to_chunked_kernel(const bf16* __restrict__ k_all, const bf16* __restrict__ v_all, ChunkedOut out,
+                                         int B, int rows, int chunks, int n_layers, const int* __restrict__ dst_row,
+                                         const int* __restrict__ src_off) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;       // one 16-byte unit each
+  const int upl = 2 * D / 8;                                                // units per (row, layer): K then V
+  if (idx >= (int64_t)B * rows * n_layers * upl) return;
+  const int u = (int)(idx % upl);
+  const int64_t t = idx / upl;
+  const int l = (int)(t % n_layers);
+  const int64_t br = t / n_layers;
+  const int b = (int)(br / rows);
+  const int r = dst_row[br];
+  if (r < 0) return;
+  const int isv = u >= D / 8, e = (isv ? u - D / 8 : u) * 8, h = e / DH, unit = (e % DH) / 8, kr = r & 31;
+  const int64_t sr = (int64_t)src_off[b] + r;
+  const uint4 val = *reinterpret_cast<const uint4*>((isv ? v_all : k_all) + sr * ((int64_t)n_layers * D) + l * D + e);
+  bf16* dst = out.p[l] + (((size_t)(b * CL + h / HPC) * chunks + (r >> 5)) * HPC + h % HPC) * DS_CHUNK_ELEMS + isv * 1024 +
+              kr * 32 + ((unit ^ ((kr >> 1) & 3)) << 3);
+  *reinterpret_cast<uint4*>(dst) = val;
+}
+
 // row-major W[N][K] -> fragment order (see load_w); one thread per 16-byte piece
 __global__ void repack_frag_kernel(const bf16* __restrict__ W, bf16* __restrict__ out, int N, int K) {
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -836,6 +860,16 @@ void kv_to_chunked(const bf16* kv, bf16* out, int B, int rows, int chunks, const
   RETR_CHECK(!src_off || dst_row, "kv_to_chunked: packed source rows need the compaction map");
   const int64_t n = (int64_t)B * rows * (2 * D / 8);
   kv_to_chunked_kernel<<<(unsigned)cdiv(n, 256), 256, 0, s>>>(kv, out, B, rows, chunks, dst_row, src_off);
+  LAUNCH_OK();
+}
+
+void kv_all_to_chunked(const bf16* k_all, const bf16* v_all, bf16* const* out, int n_layers, int B, int rows, int chunks,
+                       const int* dst_row, const int* src_off, cudaStream_t s) {
+  RETR_CHECK(n_layers <= DS_MAX_LAYERS && dst_row && src_off, "kv_all_to_chunked: layers / maps");
+  ChunkedOut o{};
+  for (int l = 0; l < n_layers; ++l) o.p[l] = out[l];
+  const int64_t n = (int64_t)B * rows * n_layers * (2 * D / 8);
+  kv_all_to_chunked_kernel<<<(unsigned)cdiv(n, 256), 256, 0, s>>>(k_all, v_all, o, B, rows, chunks, n_layers, dst_row, src_off);
   LAUNCH_OK();
 }
 

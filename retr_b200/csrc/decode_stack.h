@@ -51,4 +51,8 @@ void repack_frag(const bf16* W, bf16* out, int N, int K, cudaStream_t s);
 void kv_to_chunked(const bf16* kv, bf16* out, int B, int rows, int chunks, const int* dst_row, cudaStream_t s,
                    const int* src_off = nullptr);
 
+// every decoder layer's cache in one launch from the batched K / V projections ([rows, n_layers*256] each, packed rows)
+void kv_all_to_chunked(const bf16* k_all, const bf16* v_all, bf16* const* out, int n_layers, int B, int rows, int chunks,
+                       const int* dst_row, const int* src_off, cudaStream_t s);
+
 }  // namespace retr

@@ -82,6 +82,7 @@ template <typename T> struct EncLayer {
   Linear<T> qkv, out, ff1, ff2;
   float* rb_qkv;            // [S, 3d]: pos.Wqk^T + b_qk | b_v
   float* b_v_tail;          // [3d]: 0 | b_v (with GemmParams::rowbias_cols = 2d the V columns skip the table)
+  float* b_in;              // [3d] in_proj_bias (q | k | v): the packed encoder adds the positions before the projection
 };
 template <typename T> struct DecLayer {
   float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *ln3_g, *ln3_b;
@@ -90,6 +91,7 @@ template <typename T> struct DecLayer {
   float* rb_c_q;            // [T, d] : E_pos.Wq^T + b_q
   float* rb_c_kv;           // [S, 2d]: pos.Wk^T + b_k | b_v
   float* b_cv_tail;         // [2d]: 0 | b_v
+  float* b_ca;              // [3d] cross-attention in_proj_bias (q | k | v)
 };
 
 template <typename T>
@@ -183,6 +185,10 @@ class EngineT final : public EngineBase {
   // packed encoder (encode): only the unpadded tokens run through the encoder layers and the cross K/V projections
   bool packed_encoder_ = false, enc_packed_ = false, src_in_x_ = false;    // enabled / memory_ and ckv_ currently hold packed rows
   float* xp_ = nullptr;                                // packed residual stream [<= B*S, d]
+  const float* pos_table_ = nullptr;                   // [S, d] fp32 positions of the concatenated sequence
+  T *n2_ = nullptr, *mempos_ = nullptr;                // LN(x) + pos, memory + pos (packed encoder)
+  T *wk_all_ = nullptr, *wv_all_ = nullptr, *kall_ = nullptr, *vall_ = nullptr;   // cross K / V of ALL decoder layers:
+  float *bk_all_ = nullptr, *bv_all_ = nullptr;        // weights [L*d, d], biases [L*d], projections [<= B*S, L*d]
   int *seq_off_ = nullptr, *row_pos_ = nullptr;        // [B + 1] first packed row per sample (+ total); [B*S] position of a row
   void materialize_unpacked(cudaStream_t s);
   int cross_chunks_ = 0, self_chunks_ = 0;
@@ -325,6 +331,7 @@ void EngineT<T>::finalize() {
     layernorm<float>(pw.dev, raw(pk + "LayerNorm.weight").dev, raw(pk + "LayerNorm.bias").dev, t, S, d, 1e-5f, 0);
     pe = t;
   }
+  pos_table_ = pe;
   e_word_ = raw("transformer.embeddings.word_embeddings.weight").dev;
   e_pos_ = raw("transformer.embeddings.position_embeddings.weight").dev;
   emb_g_ = raw("transformer.embeddings.LayerNorm.weight").dev;
@@ -342,6 +349,7 @@ void EngineT<T>::finalize() {
     e.rb_qkv = pos_bias_table(pe, S, raw(p + "self_attn.sublayer.in_proj_weight"),
                               raw(p + "self_attn.sublayer.in_proj_bias"), 0, 2 * d, 3 * d);
     e.b_v_tail = bias_tail(raw(p + "self_attn.sublayer.in_proj_bias"), 0, 2 * d, 3 * d);
+    e.b_in = raw(p + "self_attn.sublayer.in_proj_bias").dev;
     enc_.push_back(e);
   }
   if (desc.pre_norm) { enc_norm_g_ = raw("transformer.encoder.norm.weight").dev; enc_norm_b_ = raw("transformer.encoder.norm.bias").dev; }
@@ -363,6 +371,7 @@ void EngineT<T>::finalize() {
     e.rb_c_q = pos_bias_table(e_pos_, Tn, raw(ca + "in_proj_weight"), raw(ca + "in_proj_bias"), 0, d, d);
     e.rb_c_kv = pos_bias_table(pe, S, raw(ca + "in_proj_weight"), raw(ca + "in_proj_bias"), d, d, 2 * d);
     e.b_cv_tail = bias_tail(raw(ca + "in_proj_bias"), d, d, 2 * d);
+    e.b_ca = raw(ca + "in_proj_bias").dev;
     dec_.push_back(e);
   }
   dec_norm_g_ = raw("transformer.decoder.norm.weight").dev; dec_norm_b_ = raw("transformer.decoder.norm.bias").dev;
@@ -448,6 +457,24 @@ void EngineT<T>::alloc_buffers() {
   if (packed_encoder_) {
     xp_ = static_cast<float*>(dalloc(Me * d * 4));
     CUDA_OK(cudaMemset(xp_, 0, Me * d * 4));
+    // positions are added to the projections' INPUT (a second LayerNorm output) instead of through a per-row bias
+    // table in the GEMM epilogue, and the cross K / V projections of all decoder layers become two GEMMs
+    const int L = desc.dec_layers;
+    n2_ = static_cast<T*>(dalloc(Me * d * sizeof(T)));
+    mempos_ = static_cast<T*>(dalloc(Me * d * sizeof(T)));
+    kall_ = static_cast<T*>(dalloc(Me * L * d * sizeof(T)));
+    vall_ = static_cast<T*>(dalloc(Me * L * d * sizeof(T)));
+    wk_all_ = static_cast<T*>(dalloc((size_t)L * d * d * sizeof(T)));
+    wv_all_ = static_cast<T*>(dalloc((size_t)L * d * d * sizeof(T)));
+    bk_all_ = static_cast<float*>(dalloc((size_t)L * d * 4));
+    bv_all_ = static_cast<float*>(dalloc((size_t)L * d * 4));
+    for (int l = 0; l < L; ++l) {
+      const size_t wb = (size_t)d * d * sizeof(T);
+      CUDA_OK(cudaMemcpy(wk_all_ + (size_t)l * d * d, dec_[l].c_kv.w, wb, cudaMemcpyDeviceToDevice));
+      CUDA_OK(cudaMemcpy(wv_all_ + (size_t)l * d * d, dec_[l].c_kv.w + (size_t)d * d, wb, cudaMemcpyDeviceToDevice));
+      CUDA_OK(cudaMemcpy(bk_all_ + (size_t)l * d, dec_[l].b_ca + d, (size_t)d * 4, cudaMemcpyDeviceToDevice));
+      CUDA_OK(cudaMemcpy(bv_all_ + (size_t)l * d, dec_[l].b_ca + 2 * d, (size_t)d * 4, cudaMemcpyDeviceToDevice));
+    }
   }
   if (stack_decode_) {
     cross_chunks_ = (int)cdiv(S, DS_CHUNK_KEYS);
@@ -640,11 +667,22 @@ void EngineT<T>::encode(int B, const float* t_img, const uint8_t* t_mask, const 
   // encoder (models/ConcatTransformer.py:171-194)
   for (int l = 0; l < desc.enc_layers; ++l) {
     const EncLayer<T>& e = enc_[l];
-    layernorm<T>(xs, e.ln1_g, e.ln1_b, n_, Me, d, 1e-5f, s, m_dyn);
-    GemmParams p = lin(e.qkv, n_, Me, qkv_);
-    p.rowbias = e.rb_qkv; p.rowbias_period = S; p.rowbias_idx = ridx; p.m_dyn = m_dyn;
-    if (packed) { p.rowbias_cols = 2 * d; p.bias = e.b_v_tail; }      // the V third takes its bias from a vector
-    gemm<T>(p, s);
+    GemmParams p;
+    if (packed) {
+      // q = k = (LN(x) + pos) W^T, v = LN(x) W^T (transformer_modules.py:33-36): the LayerNorm writes both inputs
+      layernorm<T>(xs, e.ln1_g, e.ln1_b, n_, Me, d, 1e-5f, s, m_dyn, n2_, pos_table_, row_pos_);
+      p = lin(e.qkv, n2_, Me, qkv_);
+      p.N = 2 * d; p.ldc = 3 * d; p.bias = e.b_in; p.m_dyn = m_dyn;
+      gemm<T>(p, s);
+      p = lin(e.qkv, n_, Me, qkv_ + 2 * d);
+      p.W = e.qkv.w + (int64_t)2 * d * d; p.N = d; p.ldc = 3 * d; p.bias = e.b_in + 2 * d; p.m_dyn = m_dyn;
+      gemm<T>(p, s);
+    } else {
+      layernorm<T>(xs, e.ln1_g, e.ln1_b, n_, Me, d, 1e-5f, s, m_dyn);
+      p = lin(e.qkv, n_, Me, qkv_);
+      p.rowbias = e.rb_qkv; p.rowbias_period = S;
+      gemm<T>(p, s);
+    }
     AttnParams a{};
     a.q = qkv_; a.k = qkv_ + d; a.v = qkv_ + 2 * d; a.out = att_;
     a.B = B; a.Lq = S; a.Lk = S; a.H = desc.n_heads;
@@ -663,14 +701,30 @@ void EngineT<T>::encode(int B, const float* t_img, const uint8_t* t_mask, const 
     p.out_fp32 = true; p.residual = xs; p.ldr = d; p.res_fp32 = true; p.m_dyn = m_dyn;
     gemm<T>(p, s);
   }
-  if (desc.pre_norm) {
+  const bool kv_batched = packed && desc.pre_norm;
+  if (kv_batched) {
+    layernorm<T>(xs, enc_norm_g_, enc_norm_b_, memory_, Me, d, 1e-5f, s, m_dyn, mempos_, pos_table_, row_pos_);
+  } else if (desc.pre_norm) {
     layernorm<T>(xs, enc_norm_g_, enc_norm_b_, memory_, Me, d, 1e-5f, s, m_dyn);
   } else {
     from_f32_kernel<T><<<(unsigned)cdiv(Me * d, 256), 256, 0, s>>>(xs, memory_, Me * d);
     LAUNCH_OK();
   }
   // cross-attention K/V of every decoder layer, once per sample (k = memory+pos, v = memory)
-  for (int l = 0; l < desc.dec_layers; ++l) {
+  if constexpr (std::is_same<T, bf16>::value) {
+    if (kv_batched) {
+      // all layers at once: K = (memory + pos) . [Wk_0 .. Wk_L]^T, V = memory . [Wv_0 .. Wv_L]^T, then every layer's cache
+      const int L = desc.dec_layers;
+      GemmParams p;
+      p.A = mempos_; p.W = wk_all_; p.C = kall_; p.M = Me; p.N = L * d; p.K = d; p.lda = d; p.ldc = L * d; p.bias = bk_all_;
+      p.m_dyn = m_dyn;
+      gemm<T>(p, s);
+      p.A = memory_; p.W = wv_all_; p.C = vall_; p.bias = bv_all_;
+      gemm<T>(p, s);
+      kv_all_to_chunked(kall_, vall_, ckv2_.data(), L, B, S, cross_chunks_, cross_dst_, seq_off_, s);
+    }
+  }
+  for (int l = 0; l < desc.dec_layers && !kv_batched; ++l) {
     GemmParams p = lin(dec_[l].c_kv, memory_, Me, ckv_[l]);
     p.rowbias = dec_[l].rb_c_kv; p.rowbias_period = S; p.rowbias_idx = ridx; p.m_dyn = m_dyn;
     if (packed) { p.rowbias_cols = d; p.bias = dec_[l].b_cv_tail; }

@@ -220,7 +220,8 @@ __device__ __forceinline__ void ln_row(float (&v)[MAXPER], int per, int lane, co
 template <typename T, int D>
 __global__ void layernorm_vec_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                                      const float* __restrict__ beta, T* __restrict__ y, int64_t rows, float eps,
-                                     const int* __restrict__ rows_dyn) {
+                                     const int* __restrict__ rows_dyn, T* __restrict__ y2,
+                                     const float* __restrict__ pos, const int* __restrict__ pos_idx) {
   constexpr int NV = D / 128;
   const int lane = threadIdx.x & 31;
   if (rows_dyn) rows = min(rows, (int64_t)__ldg(rows_dyn));      // packed encoder: device-side row count
@@ -259,6 +260,19 @@ __global__ void layernorm_vec_kernel(const float* __restrict__ x, const float* _
         pk.x = *reinterpret_cast<uint32_t*>(&lo);
         pk.y = *reinterpret_cast<uint32_t*>(&hi);
         *reinterpret_cast<uint2*>(dst) = pk;
+      }
+      if (y2) {                                  // second output: LN(x) + pos[pos_idx[row]] (with_pos_embed for q / k)
+        const float4 pp = __ldg(reinterpret_cast<const float4*>(pos + (int64_t)__ldg(pos_idx + row) * D + j * 128 + lane * 4));
+        T* dst2 = y2 + row * D + j * 128 + lane * 4;
+        if (sizeof(T) == 4) {
+          *reinterpret_cast<float4*>(dst2) = make_float4(o0 + pp.x, o1 + pp.y, o2 + pp.z, o3 + pp.w);
+        } else {
+          __nv_bfloat162 lo = __floats2bfloat162_rn(o0 + pp.x, o1 + pp.y), hi = __floats2bfloat162_rn(o2 + pp.z, o3 + pp.w);
+          uint2 pk;
+          pk.x = *reinterpret_cast<uint32_t*>(&lo);
+          pk.y = *reinterpret_cast<uint32_t*>(&hi);
+          *reinterpret_cast<uint2*>(dst2) = pk;
+        }
       }
     }
   }
@@ -363,12 +377,13 @@ void loc_tokens(const float* loc, const float* w, const float* bias, float* x, u
 
 template <typename T>
 void layernorm(const float* x, const float* gamma, const float* beta, T* y, int64_t rows, int d, float eps,
-               cudaStream_t s, const int* rows_dyn) {
+               cudaStream_t s, const int* rows_dyn, T* y2, const float* pos, const int* pos_idx) {
   RETR_CHECK(d % 32 == 0 && d <= 1024, "LayerNorm width must be a multiple of 32, <= 1024");
+  RETR_CHECK(!y2 || ((d == 256 || d == 512) && pos && pos_idx), "LayerNorm: the position-added output needs d = 256 / 512");
   if (d == 256 || d == 512) {
     const unsigned grid = (unsigned)std::min<int64_t>(cdiv(rows, 8), 148 * 8);     // grid-stride, 8 warps per CTA
-    if (d == 256) layernorm_vec_kernel<T, 256><<<grid, 256, 0, s>>>(x, gamma, beta, y, rows, eps, rows_dyn);
-    else layernorm_vec_kernel<T, 512><<<grid, 256, 0, s>>>(x, gamma, beta, y, rows, eps, rows_dyn);
+    if (d == 256) layernorm_vec_kernel<T, 256><<<grid, 256, 0, s>>>(x, gamma, beta, y, rows, eps, rows_dyn, y2, pos, pos_idx);
+    else layernorm_vec_kernel<T, 512><<<grid, 256, 0, s>>>(x, gamma, beta, y, rows, eps, rows_dyn, y2, pos, pos_idx);
     LAUNCH_OK();
     return;
   }
@@ -376,9 +391,9 @@ void layernorm(const float* x, const float* gamma, const float* beta, T* y, int6
   LAUNCH_OK();
 }
 template void layernorm<float>(const float*, const float*, const float*, float*, int64_t, int, float, cudaStream_t,
-                               const int*);
+                               const int*, float*, const float*, const int*);
 template void layernorm<bf16>(const float*, const float*, const float*, bf16*, int64_t, int, float, cudaStream_t,
-                              const int*);
+                              const int*, bf16*, const float*, const int*);
 
 void embed_ln(const int64_t* ids, int64_t ld_ids, const float* e_word, const float* e_pos, const float* gamma,
               const float* beta, float* y, int B, int rows_per, int t0, const int* t0_dyn, int d, float eps,

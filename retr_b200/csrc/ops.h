@@ -44,7 +44,8 @@ void loc_tokens(const float* loc, const float* w, const float* bias, float* x, u
 // y[r,:] = LN(x[r,:]) ; x fp32, y fp32|bf16; rows_dyn (d = 256 / 512 only): stop at min(rows, *rows_dyn) rows
 template <typename T>
 void layernorm(const float* x, const float* gamma, const float* beta, T* y, int64_t rows, int d, float eps,
-               cudaStream_t s, const int* rows_dyn = nullptr);
+               cudaStream_t s, const int* rows_dyn = nullptr, T* y2 = nullptr, const float* pos = nullptr,
+               const int* pos_idx = nullptr);   // y2[r,:] = LN(x[r,:]) + pos[pos_idx[r],:] (d = 256 / 512)
 // y[b*rows_per+j, :] = LN_eps(E_word[ids[b*ld_ids + t0 + j]] + E_pos[t0 + j]); t0 = t0_dyn ? *t0_dyn : t0
 // (DecoderEmbeddings, models/transformer_modules.py:113-129)
 void embed_ln(const int64_t* ids, int64_t ld_ids, const float* e_word, const float* e_pos, const float* gamma,
