@@ -20,7 +20,11 @@ def main():
     first = next(i for i, r in enumerate(rows) if r[0].startswith(("stem_im2col", "stem_fused")))
     seq = [r for r in rows[first:] if r[0].startswith(("stem_im2col", "stem_fused", "gemm_tcgen05", "maxpool"))]
     n_im2col = sum(1 for r in seq[:3] if r[0].startswith("stem_im2col"))
-    seq = [("stem_im2col x%d" % n_im2col, sum(r[1] for r in seq[:n_im2col]))] + seq[n_im2col:]
+    n_fused = sum(1 for r in seq[:3] if r[0].startswith("stem_fused"))
+    if n_fused:      # fused stem (conv + BN + ReLU + max-pool in one kernel, one launch per image set): one table row
+        seq = [("-", 0.0), ("stem_fused x%d" % n_fused, sum(r[1] for r in seq[:n_fused])), ("-", 0.0)] + seq[n_fused:]
+    else:
+        seq = [("stem_im2col x%d" % n_im2col, sum(r[1] for r in seq[:n_im2col]))] + seq[n_im2col:]
     tot = floor = 0.0
     print("%-12s %-28s %9s %9s %8s %9s %6s" % ("conv", "kernel", "us", "TFLOP/s", "GB/s", "floor us", "ratio"))
     for (name, shape), (kern, ns) in zip(convs(), seq):
