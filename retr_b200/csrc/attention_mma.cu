@@ -131,9 +131,18 @@ __global__ void __launch_bounds__(128) flash_attention_kernel(const AttnParams p
     // per-score test is then a bit of a register (the kernel is issue-bound: one LDS.U8 + ISETP per score was 15 % of
     // its instructions), and a tile without padding or causal cut skips the masking altogether.
     const int kbase = t * FK;
-    const unsigned dead_lo = __ballot_sync(0xffffffffu, Ms[buf][lane] != 0) >> (c4 * 2);
-    const unsigned dead_hi = __ballot_sync(0xffffffffu, Ms[buf][32 + lane] != 0) >> (c4 * 2);
+    const unsigned ball_lo = __ballot_sync(0xffffffffu, Ms[buf][lane] != 0);
+    const unsigned ball_hi = __ballot_sync(0xffffffffu, Ms[buf][32 + lane] != 0);
+    const unsigned dead_lo = ball_lo >> (c4 * 2), dead_hi = ball_hi >> (c4 * 2);
     float mx0 = -INFINITY, mx1 = -INFINITY;
+    if (!CAUSAL && (ball_lo | ball_hi) == 0u) {
+      // no masked key in this tile (every full tile of a packed sequence): running maxima only
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        mx0 = fmaxf(mx0, fmaxf(s[nt][0], s[nt][1]));
+        mx1 = fmaxf(mx1, fmaxf(s[nt][2], s[nt][3]));
+      }
+    } else
 #pragma unroll
     for (int nt = 0; nt < 8; ++nt) {
 #pragma unroll
