@@ -44,7 +44,7 @@ __device__ __forceinline__ float fast_exp2(float x) {
 }
 
 template <int DH, bool CAUSAL>
-__global__ void __launch_bounds__(128) flash_attention_kernel(const AttnParams p) {
+__global__ void __launch_bounds__(128, 6) flash_attention_kernel(const AttnParams p) {
   constexpr int LDS = DH + 8;                       // padded row (elements): conflict-free ldmatrix
   constexpr int KS = DH / 16;                       // k-steps of Q.K^T
   constexpr int NT = DH / 8;                        // n-tiles of the output
