@@ -480,6 +480,9 @@ def main():
                        "batch_per_gpu": B, "decode_steps_executed": int(steps_run[-1]), "sharding": "samples",
                        "l2": f"inputs ({h2d / 1e6:.0f} MB/step) exceed L2; no flush",
                        "cross_kv": "padded keys dropped when the cross K/V caches are built (exact: exp(-inf) = 0)",
+                       "encoder": "encoder layers run on the unpadded tokens only (padded tokens are masked keys in every "
+                                  "layer, so no returned value depends on their rows); FLOP / byte counts of the rooflines "
+                                  "stay the reference's (all tokens)",
                        "weights": "seed-42 build_model init + seeded FrozenBN calibration"},
             "e2e": {"value": e2e, "unit": "expr/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps,
