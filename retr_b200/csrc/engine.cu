@@ -1013,6 +1013,7 @@ void EngineT<T>::decode_greedy(int bos, int eos, int max_len, int64_t* out_ids, 
   CUDA_OK(cudaMemsetAsync(trace_dev, 0, 64, s));
 #endif
   greedy_init(caption_, max_len, B, bos, step_, done_, finished_, argmax_keys_, s);
+  CUDA_OK(cudaMemsetAsync(vocab_ticket_, 0, 4, s));     // a decode that was cut short must not leave a partial ticket count
   const bool use_graph = getenv("RETR_NO_GRAPH") == nullptr;
   cudaGraphExec_t exec = nullptr;
   long long per_step = 0;
