@@ -5,11 +5,13 @@
 //   warp 1      MMA issuer        one thread issues tcgen05.mma (M=128, N=BN, K=16) x4 per k-block
 //   warp 2      TMEM allocator    2 accumulator stages x BN columns
 //   warp 3      residual producer TMA loads of the residual sub-tiles (4-deep ring) ahead of the epilogue
-//   warps 4-7   epilogue          tcgen05.ld -> scale/bias/rowbias/ReLU/residual -> swizzled smem staging
-//                                 -> TMA store (128 rows x 128 B sub-tiles, double buffered); a direct
-//                                 register->global path remains for argmax-only / remapped / unaligned C
-//   warps 8-11  A gather          (convolution only) cp.async im2col rows with zero fill, written
-//                                 in the same swizzled layout TMA would produce
+//   warps 4-11  epilogue          two groups of four warps on alternate 128-byte column sub-tiles: tcgen05.ld (one
+//                                 32-column half ahead of the arithmetic) -> scale/bias/rowbias/ReLU/residual
+//                                 (specialised forms for the hot-path combinations) -> swizzled smem staging ->
+//                                 one 32-row TMA store PER WARP, no CTA-level barrier; a direct register->global
+//                                 path remains for argmax-only / remapped / unaligned C
+//   warps 8-11  A gather          (AMODE 1 fallback only, instead of the second epilogue group) cp.async im2col
+//                                 rows with zero fill, written in the same swizzled layout TMA would produce
 // Pipelines: smem full/empty ring (TMA|gather -> MMA), TMEM full/empty pair (MMA -> epilogue) so the
 // epilogue of tile i overlaps the main loop of tile i+1.
 //
