@@ -218,6 +218,7 @@ __device__ __forceinline__ void epilogue_chunk(const KArgs& a, uint32_t (&r)[32]
 //   MODE 2: scale, bias, ReLU floor                                 conv1 / conv2 / downsample (FrozenBN folded)
 //   MODE 3: scale, bias, + bf16 residual sub-tile, ReLU after       conv3 of a bottleneck
 //   MODE 4: bias + per-row bias `rowb` (null past rowbias_cols)     q|k|v and k|v projections (positions)
+//   MODE 5: scale, kept where the bf16 `residual` tile is > 0       input-gradient GEMMs with the ReLU backward fused
 template <int MODE>
 __device__ __forceinline__ void epilogue_chunk_lean(const uint32_t (&r)[32], const float* __restrict__ scale,
                                                     const float* __restrict__ bias, float lo, int row, int chunk16,
@@ -230,8 +231,15 @@ __device__ __forceinline__ void epilogue_chunk_lean(const uint32_t (&r)[32], con
     float v[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[8 * c + j]);
-    const float4 b0 = *reinterpret_cast<const float4*>(bias + 8 * c), b1 = *reinterpret_cast<const float4*>(bias + 8 * c + 4);
-    if (MODE >= 2) {
+    float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
+    if (MODE != 5) {
+      b0 = *reinterpret_cast<const float4*>(bias + 8 * c);
+      b1 = *reinterpret_cast<const float4*>(bias + 8 * c + 4);
+    }
+    if (MODE == 5) {
+      const float4 s0 = *reinterpret_cast<const float4*>(scale + 8 * c), s1 = *reinterpret_cast<const float4*>(scale + 8 * c + 4);
+      v[0] *= s0.x; v[1] *= s0.y; v[2] *= s0.z; v[3] *= s0.w; v[4] *= s1.x; v[5] *= s1.y; v[6] *= s1.z; v[7] *= s1.w;
+    } else if (MODE >= 2 && MODE != 4) {
       const float4 s0 = *reinterpret_cast<const float4*>(scale + 8 * c), s1 = *reinterpret_cast<const float4*>(scale + 8 * c + 4);
       // multiply, THEN add, each rounded: what the general epilogues compute (their scale and bias steps sit behind
       // separate branches and are never contracted), so a row's result does not depend on which epilogue its launch
@@ -248,7 +256,16 @@ __device__ __forceinline__ void epilogue_chunk_lean(const uint32_t (&r)[32], con
       v[0] += r0.x; v[1] += r0.y; v[2] += r0.z; v[3] += r0.w; v[4] += r1.x; v[5] += r1.y; v[6] += r1.z; v[7] += r1.w;
     }
     const uint32_t off = ((uint32_t)(chunk16 + c) ^ swz) << 4;
-    if (MODE == 3) {
+    if (MODE == 5) {
+      const uint4 t = *reinterpret_cast<const uint4*>(rrow + off);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&t);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float2 f = __bfloat1622float2(h[q]);
+        if (!(f.x > 0.f)) v[2 * q] = 0.f;
+        if (!(f.y > 0.f)) v[2 * q + 1] = 0.f;
+      }
+    } else if (MODE == 3) {
       const uint4 t = *reinterpret_cast<const uint4*>(rrow + off);
       const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&t);
 #pragma unroll
@@ -614,6 +631,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               case 1: epilogue_chunk_lean<1>(rr, nullptr, a.bias + nc, lo, row, chunk16, rbuf, cbuf); break;
               case 2: epilogue_chunk_lean<2>(rr, a.scale + nc, a.bias + nc, lo, row, chunk16, rbuf, cbuf); break;
               case 3: epilogue_chunk_lean<3>(rr, a.scale + nc, a.bias + nc, lo, row, chunk16, rbuf, cbuf); break;
+              case 5: epilogue_chunk_lean<5>(rr, a.scale + nc, nullptr, lo, row, chunk16, rbuf, cbuf); break;
               case 4:
                 epilogue_chunk_lean<4>(rr, nullptr, a.bias + nc, lo, row, chunk16, rbuf, cbuf,
                                        nc < a.rowbias_cols ? a.rowbias + rb_row * a.N + nc : nullptr);
@@ -1163,6 +1181,9 @@ void gemm_bf16(const GemmParams& p, cudaStream_t stream) {
   if (lean_on && ka.warp_store && !p.out_fp32 && p.bias && p.rowbias && ka.vecRB && !p.scale && !p.residual && p.relu <= 1 &&
       reinterpret_cast<uintptr_t>(p.bias) % 16 == 0)
     ka.epi_mode = 4;
+  if (lean_on && ka.warp_store && !p.out_fp32 && !p.bias && !p.rowbias && p.scale && p.relu == 3 && ka.res_tma && !ka.res_fp32 &&
+      reinterpret_cast<uintptr_t>(p.scale) % 16 == 0)
+    ka.epi_mode = 5;
   if (lean_on && ka.warp_store && !p.out_fp32 && p.bias && !p.rowbias && p.relu <= 2 &&
       reinterpret_cast<uintptr_t>(p.bias) % 16 == 0 && (!p.scale || reinterpret_cast<uintptr_t>(p.scale) % 16 == 0)) {
     if (!p.scale && !p.residual && p.relu <= 1) ka.epi_mode = 1;
