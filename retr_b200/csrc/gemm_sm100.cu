@@ -62,6 +62,7 @@ struct KArgs {
   const int* rowbias_idx;
   const int* m_dyn;
   int rowbias_cols;
+  int c_dbl;             // warp-store epilogue: two staging buffers per group (short main loops: the epilogue paces the tile)
   int epi_mode;          // bf16 staged epilogue: 0 general, 1-3 the specialised forms (epilogue_chunk_lean)
   int warp_store;        // staged epilogue: every warp stores its own 32 rows (no CTA-level barriers in the epilogue)
   int stages;            // smem ring depth (runtime: depends on the epilogue staging in use)
@@ -87,11 +88,12 @@ template <int BN> struct Cfg {
   static constexpr int SB_BYTES = 2 * BN * 4;
   // no alignment slack: the dynamic window of a kernel without static shared memory starts 1024-byte aligned (the
   // kernel traps if it ever does not), and the slack cost the BN = 256 tiles their fourth pipeline stage
-  static int fixed_bytes(bool tma_epi, int r_bufs, bool gather) {
-    return BARRIER_BYTES + SB_BYTES + (tma_epi ? (gather ? 1 : C_BUFS) * EPI_TILE_BYTES : 0) + r_bufs * EPI_TILE_BYTES;
+  static int fixed_bytes(bool tma_epi, int r_bufs, bool gather, int c_dbl = 0) {
+    return BARRIER_BYTES + SB_BYTES + (tma_epi ? (gather ? 1 : C_BUFS * (1 + c_dbl)) * EPI_TILE_BYTES : 0) +
+           r_bufs * EPI_TILE_BYTES;
   }
-  static int stages_for(bool tma_epi, int r_bufs, bool gather) {
-    const int n = (SMEM_LIMIT - fixed_bytes(tma_epi, r_bufs, gather)) / STAGE_BYTES;
+  static int stages_for(bool tma_epi, int r_bufs, bool gather, int c_dbl = 0) {
+    const int n = (SMEM_LIMIT - fixed_bytes(tma_epi, r_bufs, gather, c_dbl)) / STAGE_BYTES;
     return n > MAX_STAGES ? MAX_STAGES : n;
   }
 };
@@ -407,7 +409,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if ((ptx::smem_u32(smem_raw) & 1023u) != 0) __trap();                  // swizzled tiles need 1024-byte alignment
   const int RB = a.r_bufs;
   uint8_t* cst = smem + STAGES * C::STAGE_BYTES;                         // C staging (TMA store source)
-  uint8_t* rst = cst + (a.tma_epi ? (GATHER ? 1 : C_BUFS) * EPI_TILE_BYTES : 0);   // residual staging (TMA load dest)
+  uint8_t* rst = cst + (a.tma_epi ? (GATHER ? 1 : C_BUFS * (1 + a.c_dbl)) * EPI_TILE_BYTES : 0);   // residual staging (TMA load dest)
   float* sb = reinterpret_cast<float*>(rst + RB * EPI_TILE_BYTES);
   uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sb) + C::SB_BYTES);
   uint64_t* empty = full + MAX_STAGES;
@@ -568,7 +570,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int row = q * 32 + lane;                   // row inside the tile == TMEM lane
     const int tid_e = (threadIdx.x - 128) & 127;     // thread inside its group
     const int tid_all = threadIdx.x - 128;
-    uint32_t tcount = 0, cit = 0;
+    uint32_t tcount = 0, cit = 0, subcnt = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
       const TileCoord tc = tile_coord(a, tile);
       const int m_blk = tc.m_blk, n_blk = tc.n_blk;
@@ -587,7 +589,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         ptx::mbar_wait(&tfull[as], aph);
         ptx::tc_fence_after_sync();
         const int n_end = min(a.N, (n_blk + 1) * BN);
-        uint8_t* cbuf = cst + (EG == 2 ? grp : 0) * EPI_TILE_BYTES;
+        // staging: one buffer per group, or two used alternately (c_dbl) so that a warp does not wait for the TMA
+        // engine to have read its previous sub-tile before it converts the next one
+        uint8_t* const cgrp = cst + (EG == 2 ? grp : 0) * (1 + a.c_dbl) * EPI_TILE_BYTES;
+        uint8_t* cbuf = cgrp;
         // sub-tile prologue / epilogue shared by both output types
         auto sub_begin = [&](uint32_t rb, uint32_t rph) -> const uint8_t* {
           const uint8_t* rbuf = nullptr;
@@ -595,7 +600,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             ptx::mbar_wait(&rfull[rb], rph);
             rbuf = rst + rb * EPI_TILE_BYTES;
           }
-          if (lane == 0) ptx::bulk_wait_read<0>();              // this warp's previous store has read its slice
+          if (a.c_dbl) {
+            cbuf = cgrp + (subcnt & 1u) * EPI_TILE_BYTES;
+            ++subcnt;
+            if (lane == 0) ptx::bulk_wait_read<1>();            // the store before the previous one has read this buffer
+          } else {
+            if (lane == 0) ptx::bulk_wait_read<0>();            // this warp's previous store has read its slice
+          }
           __syncwarp();
           return rbuf;
         };
@@ -850,9 +861,13 @@ void launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& t
   constexpr bool GATHER = AMODE == 1;
   static const int want_rb = getenv("RETR_GEMM_RBUFS") ? std::min(R_BUFS, std::max(2, atoi(getenv("RETR_GEMM_RBUFS")) & ~1)) : 4;
   ka.r_bufs = ka.res_tma ? want_rb : 0;
-  ka.stages = Cfg<BN>::stages_for(ka.tma_epi, ka.r_bufs, GATHER);
+  // short main loops (K <= 256) are paced by the epilogue: a second staging buffer per group is worth a pipeline stage
+  static const int cdbl_kb = getenv("RETR_GEMM_CDBL_KB") ? atoi(getenv("RETR_GEMM_CDBL_KB")) : 4;
+  ka.c_dbl = ka.warp_store && !GATHER && ka.num_kb <= cdbl_kb && AMODE < 3 &&
+             Cfg<BN>::stages_for(ka.tma_epi, ka.r_bufs, GATHER, 1) >= 2;
+  ka.stages = Cfg<BN>::stages_for(ka.tma_epi, ka.r_bufs, GATHER, ka.c_dbl);
   RETR_CHECK(ka.stages >= (GATHER ? 3 : 2), "not enough shared memory for the pipeline");
-  const int smem = Cfg<BN>::fixed_bytes(ka.tma_epi, ka.r_bufs, GATHER) + ka.stages * Cfg<BN>::STAGE_BYTES;
+  const int smem = Cfg<BN>::fixed_bytes(ka.tma_epi, ka.r_bufs, GATHER, ka.c_dbl) + ka.stages * Cfg<BN>::STAGE_BYTES;
   if (pdl) {
     launch_pdl(gemm_tcgen05_kernel<BN, AMODE>, dim3((unsigned)grid), dim3(384), (size_t)smem, stream, tmA, tmB, tmC, tmR, ka);
   } else {
